@@ -1,0 +1,168 @@
+/*
+ * ssf.h -- C ABI of the B200-native screen-fitting hot path (libssf_b200.so).
+ *
+ * The reference (ska-sdp-screen-fitting @ 213c471) is pure Python; there is no FFI in it.
+ * These entry points are what a binding for the hot path h5parm solutions -> a-term cube
+ * replaces, function by function.  Each declaration cites the
+ * reference code it stands in for.  Conventions:
+ *
+ *   - every function returns 0 on success, a negative SSF_E* code on failure;
+ *     ssf_last_error() returns a thread-local message for the last failure
+ *   - no exceptions, no torch types: plain pointers + sizes
+ *   - pointers are DEVICE pointers unless the parameter name ends in _host
+ *   - the caller owns every buffer; nothing is allocated behind the caller's back except
+ *     by the *_host convenience entry points (which allocate, copy, run, copy back, free)
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *     all device entry points are asynchronous on it and re-entrant per (device, stream)
+ *
+ * Layouts (row-major, last index fastest):
+ *   column  = one (time, freq, antenna) cell, flattened in that order (the h5parm `val`
+ *             layout [time, freq, ant, dir] makes each column a contiguous ndir vector)
+ *   slab    = float32 [ncol, 4, ny, nx]  -- the FITS cube layout [t, f, a, 4, y, x] of
+ *             processing_utils.py:190-194 restricted to a run of columns;
+ *             planes = (Re XX, Im XX, Re YY, Im YY), screen.py:319-324
+ *   voxel   = one (pixel, column) cell = 4 float32 = 16 bytes
+ */
+#ifndef SSF_H
+#define SSF_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SSF_OK 0
+#define SSF_EINVAL (-1)   /* bad argument (null pointer, size out of range) */
+#define SSF_ECUDA (-2)    /* CUDA runtime error (message in ssf_last_error) */
+#define SSF_ENOCONV (-3)  /* eigen-solver did not converge */
+#define SSF_ENOTSUP (-4)  /* shape not supported by this kernel variant */
+
+#define SSF_MAX_DIR 112   /* max directions (pierce points) per system (2 n^2 doubles of smem) */
+
+int ssf_version(void);
+const char *ssf_last_error(void);
+/* Number of kernel launches issued through this library by the calling process so far. */
+uint64_t ssf_launch_count(void);
+
+/* ------------------------------------------------------------------------------------
+ * KL setup.  Replaces _calculate_svd (stationscreen.py:390-430) for a BATCH of direction
+ * subsets ("flag patterns"): for pattern p with unflagged set S_p (mask bit d of
+ * masks[p*2 + d/64]) over the pierce points pp[ndir,2]:
+ *     C   = -((|pi-pj|^2 / r0^2)^(beta/2)) / 2           on S_p
+ *     U   = left singular vectors of C, singular values descending (|eigenvalues|)
+ *     pinvC = pinv(C) with absolute cutoff `pinv_cut`    (scipy 1.7.3 rcond semantics)
+ * Output matrices are [npat, ndir, ndir] float64, compacted to the top-left n_p x n_p
+ * block (n_p = popcount(mask)), rows/cols in increasing direction order.  sv = [npat, ndir]
+ * singular values.  One CTA per pattern, cyclic Jacobi in shared memory.
+ */
+int ssf_kl_decompose(const double *pp, int ndir, const uint64_t *masks, int npat,
+                     double r0, double beta, double pinv_cut,
+                     double *C, double *pinvC, double *U, double *sv, void *stream);
+
+/* ------------------------------------------------------------------------------------
+ * KL fit, one pass over all systems.  Replaces _fit_screen (stationscreen.py:433-594) and
+ * the per-time body of _process_station (:681-779) for phase screens.
+ *
+ *   phase   [nsys, ndir] f64   referenced phases (rad)
+ *   weights [nsys, ndir] f32   >0 = used
+ *   pat     [nsys] i32         index of each system's flag pattern in the decompose output
+ *   order   [nsys] f64 in/out  current screen order (the reference stores it as float)
+ *   station_order [nsys] f64   per-system lower bound (= order of the station, :656)
+ *   mode 0: iteration 0       -> one fit at min(order, n_unfl-1)         (:681-722)
+ *   mode 1: iteration > 0     -> order-adjust state machine, first order iteration skips
+ *                                the fit (reference quirk, :694-705), <= 3 refits (:692-779)
+ *   white, resid [nsys, ndir] f64 in/out (mode 1 reads the residual of the previous pass)
+ * Systems with no unflagged direction are left untouched (:683-684).
+ */
+int ssf_kl_fit_pass(const double *phase, const float *weights, const int32_t *pat,
+                    const double *pp, int ndir, int64_t nsys,
+                    const double *C, const double *pinvC, const double *U,
+                    double r0, double beta, double pinv_cut, int mode,
+                    double *order, const double *station_order,
+                    double *white, double *resid, void *stream);
+
+/* Replaces _flag_outliers (stationscreen.py:303-350) + normalize_phase / nancircstd
+ * (processing_utils.py:73-132): per system, sigma = circular std of the unflagged
+ * residuals over directions; weights of |resid| > nsigma*sigma are set to 0 in place.
+ * Also emits each system's new 128-bit flag mask (masks_out [nsys, 2]).  */
+int ssf_kl_flag_outliers(const double *resid, float *weights, int ndir, int64_t nsys,
+                         double nsigma, uint64_t *masks_out, void *stream);
+
+/* ------------------------------------------------------------------------------------
+ * KL evaluation.  Replaces KLScreen.make_matrix + calculate_kl_screen
+ * (kl_screen.py:192-380, 411-449) for all columns of a slab at once.
+ *
+ * ssf_kl_basis: per-pixel interpolation basis (once per run)
+ *     Bt[d, pix] = sum_e K(pix, e) * pinvC[e, d],  K(pix,e) = -((|g_pix - p_e|^2/r0^2)^(beta/2))/2
+ *   with the separable grid g_pix = (x_coord[i], y_coord[j]), pix = j*nx + i
+ *   (kl_screen.py:255-259, 444-448).  FP64 math, stored float32 direction-major
+ *   [ndir, ny*nx] (pixel fastest: coalesced for SIMT, MN-major operand for tcgen05).
+ * ssf_kl_coeffs: per-column coefficients  G[col, d] = sum_e C[d, e] * white[col, e]
+ *   (FP64 math, stored float32 [ncol, ldg], zero padded); then
+ *       Phi[pix, col] = Bt[:,pix] . G[col,:]  ==  K(pix,:) . white[col,:]   (kl_screen.py:449)
+ *   because white = pinvC * fit lies in the range of pinvC*C.
+ * ssf_kl_eval: slab[col, 0|2, pix] = cos Phi, slab[col, 1|3, pix] = sin Phi
+ *   (kl_screen.py:368-373), NaN -> (1, 0) (screen.py:364-378) fused into the store.
+ */
+int ssf_kl_basis(const double *x_coord, const double *y_coord, int nx, int ny,
+                 const double *pp, int ndir, const double *pinvC,
+                 double r0, double beta, float *Bt, void *stream);
+int ssf_kl_coeffs(const double *white, int64_t ncol, int ndir, const double *C,
+                  float *G, int ldg, void *stream);
+/* variant: 0 = FP32 SIMT, 1 = tcgen05 (3xTF32 split, FP32 accumulate in TMEM), -1 = auto */
+int ssf_kl_eval(const float *Bt, const float *G, int ndir, int ldg, int64_t npix,
+                int64_t ncol, float *slab, int variant, void *stream);
+
+/* ------------------------------------------------------------------------------------
+ * Voronoi.  ssf_voronoi_assign: float64 nearest patch per integer pixel, lowest index
+ * wins ties; tmpl[j*nx+i] = patch index + 1 (the values of data_rasertize_template,
+ * voronoi_screen.py:329-350).  ssf_voronoi_lut: cos/sin of the referenced phases in FP64,
+ * rounded once to float32: lut[col, d, 2] (voronoi_screen.py:203-214 + the float32 store
+ * of screen.py:343).  ssf_voronoi_fill: slab[col, p, pix] = lut[col, tmpl[pix]-1, p&1]
+ * (VoronoiScreen.make_matrix, voronoi_screen.py:169-216), NaN fix fused.
+ */
+int ssf_voronoi_assign(const double *px, const double *py, int ndir, int nx, int ny,
+                       int32_t *tmpl, void *stream);
+int ssf_voronoi_lut(const double *phase, const double *amp, int64_t ncol, int ndir,
+                    float *lut, void *stream);
+int ssf_voronoi_fill(const int32_t *tmpl, const float *lut, int ndir, int64_t npix,
+                     int64_t ncol, float *slab, int fix_nan, void *stream);
+
+/* Smoothed Voronoi through linearity: slab[col, p, pix] = sum_d S[d, pix] * lut[col, d, p&1]
+ * where S[d, :] is the Gaussian-smoothed indicator image of cell d (built with
+ * ssf_voronoi_indicators + ssf_gauss_smooth).  Same result as fill -> gaussian_filter
+ * (screen.py:353-362) up to float32 rounding of the intermediate. */
+int ssf_voronoi_indicators(const int32_t *tmpl, int ndir, int64_t npix, float *ind,
+                           void *stream);
+int ssf_voronoi_contract(const float *S, const float *lut, int ndir, int64_t npix,
+                         int64_t ncol, float *slab, int variant, void *stream);
+
+/* ------------------------------------------------------------------------------------
+ * Separable Gaussian smoothing, in place, of nimg images [ny, nx] float32: y pass then x
+ * pass, scipy 'reflect' boundary, radius int(4*sigma+0.5), weights exp(-x^2/(2 sigma^2))
+ * normalised, float32 storage between the passes (ndimage.gaussian_filter with
+ * sigma=(0,s,s), screen.py:358-362).  `scratch` holds nimg*ny*nx floats. */
+int ssf_gauss_smooth(float *images, int64_t nimg, int ny, int nx, double sigma,
+                     float *scratch, void *stream);
+
+/* NaN -> 1.0 (planes 0, 2) / 0.0 (planes 1, 3), screen.py:364-378, on a slab. */
+int ssf_nan_fix(float *slab, int64_t ncol, int64_t npix, void *stream);
+
+/* ------------------------------------------------------------------------------------
+ * Host convenience entry points (what a ctypes/cffi binding of the reference would call):
+ * HOST buffers in, HOST slab out; allocation, H2D, kernels, D2H inside.
+ */
+int ssf_voronoi_cube_host(const int32_t *tmpl_host, const double *phase_host, int ndir,
+                          int ny, int nx, int64_t ncol, double smooth_pix,
+                          float *slab_host);
+int ssf_kl_cube_host(const double *x_host, const double *y_host, int nx, int ny,
+                     const double *pp_host, int ndir, const double *white_host,
+                     int64_t ncol, double r0, double beta, double pinv_cut,
+                     float *slab_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SSF_H */

@@ -1,0 +1,140 @@
+// KL evaluation support: the per-pixel interpolation basis (FP64, once per run), the
+// per-column coefficients (FP64 GEMV per column), and the ssf_kl_eval / ssf_voronoi_contract
+// dispatch between the SIMT and tcgen05 contraction kernels.
+#include "common.cuh"
+
+namespace ssf {
+int kl_eval_simt(const float *, const float *, int, int, int64_t, int64_t, float *, cudaStream_t);
+int voronoi_contract_simt(const float *, const float *, int, int64_t, int64_t, float *, cudaStream_t);
+int contract_tc(bool kl, const float *, const float *, int, int, int64_t, int64_t, float *, cudaStream_t);
+bool contract_tc_supported(bool kl, int ndir, int64_t npix, int64_t ncol, const void *bt, const void *slab);
+}  // namespace ssf
+
+namespace {
+
+// One thread per pixel.  K(pix, e) in FP64 for all e, then the ndir x ndir product with
+// pinvC (shared memory).  Bt is written pixel-fastest -> coalesced.
+__global__ void __launch_bounds__(128)
+basis_kernel(const double *__restrict__ xc, const double *__restrict__ yc, int nx, int ny,
+             const double *__restrict__ pp, int ndir, const double *__restrict__ pinvC, double r0sq,
+             double half_beta, float *__restrict__ Bt) {
+  SSF_DYN_SMEM(double, sm);
+  double *s_pinv = sm;                 // [ndir][ndir]
+  double *s_pp = sm + ndir * ndir;     // [ndir][2]
+  for (int i = threadIdx.x; i < ndir * ndir; i += blockDim.x) s_pinv[i] = pinvC[i];
+  for (int i = threadIdx.x; i < ndir * 2; i += blockDim.x) s_pp[i] = pp[i];
+  __syncthreads();
+  const int64_t npix = (int64_t)nx * ny;
+  const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= npix) return;
+  const double x = xc[p % nx], y = yc[p / nx];
+  double k[SSF_MAX_DIR];
+  for (int e = 0; e < ndir; ++e) {
+    // kl_screen.py:446-448: sum of squares over (x, y, 0), then -((d2/r0^2)^(beta/2))/2
+    double dx = s_pp[2 * e] - x, dy = s_pp[2 * e + 1] - y;
+    double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+    double q = d2 / r0sq;
+    k[e] = q > 0.0 ? -0.5 * pow(q, half_beta) : 0.0;
+  }
+  for (int d = 0; d < ndir; ++d) {
+    double acc = 0.0;
+    for (int e = 0; e < ndir; ++e) acc = fma(k[e], s_pinv[e * ndir + d], acc);
+    Bt[(int64_t)d * npix + p] = (float)acc;
+  }
+}
+
+// G[col, d] = sum_e C[d, e] * white[col, e]; block = 128 threads, each block handles a run
+// of columns; thread t handles (col_local, d) pairs.  C (symmetric) lives in shared memory.
+__global__ void __launch_bounds__(128)
+coeffs_kernel(const double *__restrict__ white, int64_t ncol, int ndir, const double *__restrict__ C,
+              float *__restrict__ G, int ldg, int cols_per_block) {
+  SSF_DYN_SMEM(double, sm);
+  double *s_c = sm;                    // [ndir][ndir]
+  double *s_w = sm + ndir * ndir;      // [cols_per_block][ndir]
+  for (int i = threadIdx.x; i < ndir * ndir; i += blockDim.x) s_c[i] = C[i];
+  for (int64_t c0 = (int64_t)blockIdx.x * cols_per_block; c0 < ncol;
+       c0 += (int64_t)gridDim.x * cols_per_block) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < cols_per_block * ndir; i += blockDim.x) {
+      int64_t col = c0 + i / ndir;
+      s_w[i] = col < ncol ? white[col * ndir + (i % ndir)] : 0.0;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < cols_per_block * ldg; i += blockDim.x) {
+      int cl = i / ldg, d = i - cl * ldg;
+      int64_t col = c0 + cl;
+      if (col >= ncol) continue;
+      double acc = 0.0;
+      if (d < ndir) {
+        const double *w = s_w + cl * ndir;
+        // C is symmetric: read column d as row d (stride-1 in e would bank-conflict across d)
+        for (int e = 0; e < ndir; ++e) acc = fma(s_c[e * ndir + d], w[e], acc);
+      }
+      G[col * ldg + d] = (float)acc;
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" int ssf_kl_basis(const double *x_coord, const double *y_coord, int nx, int ny,
+                            const double *pp, int ndir, const double *pinvC, double r0, double beta,
+                            float *Bt, void *stream) {
+  SSF_REQUIRE(x_coord && y_coord && pp && pinvC && Bt, "ssf_kl_basis: null pointer");
+  SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR, "ssf_kl_basis: ndir=%d out of range [1,%d]", ndir, SSF_MAX_DIR);
+  SSF_REQUIRE(nx >= 1 && ny >= 1, "ssf_kl_basis: empty image");
+  size_t smem = sizeof(double) * ((size_t)ndir * ndir + 2 * ndir);
+  if (smem > 48 * 1024)
+    SSF_CUDA(cudaFuncSetAttribute(basis_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int64_t npix = (int64_t)nx * ny;
+  SSF_LAUNCH(basis_kernel, ssf::div_up(npix, 128), 128, smem, (cudaStream_t)stream,
+             x_coord, y_coord, nx, ny, pp, ndir, pinvC, r0 * r0, beta / 2.0, Bt);
+  SSF_LAUNCHED();
+  return SSF_OK;
+}
+
+extern "C" int ssf_kl_coeffs(const double *white, int64_t ncol, int ndir, const double *C, float *G,
+                             int ldg, void *stream) {
+  SSF_REQUIRE(white && C && G, "ssf_kl_coeffs: null pointer");
+  SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR && ldg >= ndir, "ssf_kl_coeffs: bad ndir/ldg");
+  if (ncol <= 0) return SSF_OK;
+  const int cpb = 16;
+  size_t smem = sizeof(double) * ((size_t)ndir * ndir + (size_t)cpb * ndir);
+  if (smem > 48 * 1024)
+    SSF_CUDA(cudaFuncSetAttribute(coeffs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int64_t blocks = (ncol + cpb - 1) / cpb;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  SSF_LAUNCH(coeffs_kernel, (int)blocks, 128, smem, (cudaStream_t)stream, white, ncol, ndir, C, G, ldg, cpb);
+  SSF_LAUNCHED();
+  return SSF_OK;
+}
+
+extern "C" int ssf_kl_eval(const float *Bt, const float *G, int ndir, int ldg, int64_t npix,
+                           int64_t ncol, float *slab, int variant, void *stream) {
+  SSF_REQUIRE(Bt && G && slab, "ssf_kl_eval: null pointer");
+  SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR && ldg >= ndir && npix >= 1, "ssf_kl_eval: bad sizes");
+  if (ncol <= 0) return SSF_OK;
+  bool tc_ok = ssf::contract_tc_supported(true, ndir, npix, ncol, Bt, slab) && (ldg % 4 == 0);
+  if (variant == 1 && !tc_ok) {
+    ssf::set_error("ssf_kl_eval: tcgen05 variant needs npix %% 128 == 0, 16 B aligned buffers, ldg %% 4 == 0");
+    return SSF_ENOTSUP;
+  }
+  if (variant == 1 || (variant < 0 && tc_ok))
+    return ssf::contract_tc(true, Bt, G, ndir, ldg, npix, ncol, slab, (cudaStream_t)stream);
+  return ssf::kl_eval_simt(Bt, G, ndir, ldg, npix, ncol, slab, (cudaStream_t)stream);
+}
+
+extern "C" int ssf_voronoi_contract(const float *S, const float *lut, int ndir, int64_t npix,
+                                    int64_t ncol, float *slab, int variant, void *stream) {
+  SSF_REQUIRE(S && lut && slab, "ssf_voronoi_contract: null pointer");
+  SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR && npix >= 1, "ssf_voronoi_contract: bad sizes");
+  if (ncol <= 0) return SSF_OK;
+  bool tc_ok = ssf::contract_tc_supported(false, ndir, npix, ncol, S, slab);
+  if (variant == 1 && !tc_ok) {
+    ssf::set_error("ssf_voronoi_contract: tcgen05 variant needs npix %% 128 == 0 and 16 B aligned buffers");
+    return SSF_ENOTSUP;
+  }
+  if (variant == 1 || (variant < 0 && tc_ok))
+    return ssf::contract_tc(false, S, lut, ndir, ndir, npix, ncol, slab, (cudaStream_t)stream);
+  return ssf::voronoi_contract_simt(S, lut, ndir, npix, ncol, slab, (cudaStream_t)stream);
+}

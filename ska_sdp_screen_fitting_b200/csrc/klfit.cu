@@ -1,0 +1,455 @@
+// Batched Karhunen-Loeve phase-screen fit.  One CTA per system (one (time, freq, station)
+// cell = one ndir-vector of phases + weights), FP64 throughout, everything in shared memory
+// except the pattern matrices (C_S, pinv C_S, U_S), which are shared by all systems with the
+// same flag pattern and are read through L1/L2.
+//
+// Replaces _fit_screen (stationscreen.py:433-594), the per-time body of _process_station
+// (:681-779), _circ_chi2 (:353-387) and _flag_outliers (:303-350).
+#include "common.cuh"
+
+namespace {
+
+constexpr int FT = 128;  // threads per CTA (>= SSF_MAX_DIR)
+constexpr double TWO_PI = 6.283185307179586476925286766559;
+constexpr double PI = 3.141592653589793238462643383279;
+
+struct Pattern {
+  const double *C, *P, *U;  // [n][n] blocks with row stride ld
+  const double *Pfull;      // pinv of the full pattern (pattern 0)
+  int ld;
+};
+
+struct Smem {
+  double *ph, *w;                   // [nall] phases, weights
+  double *rc, *rs, *wc;             // [n] compact cos, sin, weight
+  double *zc, *zs;                  // [k]
+  double *yc, *ys, *gc, *gs_;       // [n]
+  double *fit, *wh, *fall;          // [n], [n], [nall]
+  double *A;                        // [k][k] (non-uniform weights only)
+  int *idx;                         // [n] compact -> direction
+};
+
+__device__ Smem carve(double *base, int nall) {
+  Smem s;
+  double *p = base;
+  s.ph = p; p += nall;
+  s.w = p; p += nall;
+  s.rc = p; p += nall;
+  s.rs = p; p += nall;
+  s.wc = p; p += nall;
+  s.zc = p; p += nall;
+  s.zs = p; p += nall;
+  s.yc = p; p += nall;
+  s.ys = p; p += nall;
+  s.gc = p; p += nall;
+  s.gs_ = p; p += nall;
+  s.fit = p; p += nall;
+  s.wh = p; p += nall;
+  s.fall = p; p += nall;
+  s.idx = reinterpret_cast<int *>(p); p += (nall + 1) / 2;
+  s.A = p;
+  return s;
+}
+
+__host__ __device__ inline size_t smem_doubles(int nall) {
+  return (size_t)14 * nall + (nall + 1) / 2 + (size_t)nall * nall;
+}
+
+// One screen fit at `order` (stationscreen.py:501-590, phase type).  Whole CTA participates.
+// On return s.wh/s.fall hold the results: white_out/resid_out are written to global.
+// Returns false (for all threads) if the weights need the general pinv (some weight in
+// (0, cut]) -- not supported by the Cholesky path.
+__device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restrict__ pp, int nall,
+                         int n, int k, double r0sq, double half_beta, double cut,
+                         double *__restrict__ white_out, double *__restrict__ resid_out) {
+  __shared__ int sh_uniform, sh_ok;
+  const int tid = threadIdx.x;
+  const int ld = pt.ld;
+  if (tid < n) {
+    double phi = s.ph[s.idx[tid]];
+    double sn, cs;
+    sincos(phi, &sn, &cs);
+    s.rc[tid] = cs;
+    s.rs[tid] = sn;
+    s.wc[tid] = s.w[s.idx[tid]];
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int uni = 1;
+    double wmin = s.wc[0];
+    for (int i = 1; i < n; ++i) {
+      uni &= (s.wc[i] == s.wc[0]);
+      wmin = fmin(wmin, s.wc[i]);
+    }
+    sh_uniform = uni;
+    sh_ok = uni ? 1 : (wmin > cut);
+  }
+  // rr1 = U_k^T W r   (:513-516, :522-525)
+  if (tid < k) {
+    double ac = 0.0, as = 0.0;
+    for (int i = 0; i < n; ++i) {
+      double u = pt.U[i * ld + tid] * s.wc[i];
+      ac = fma(u, s.rc[i], ac);
+      as = fma(u, s.rs[i], as);
+    }
+    s.zc[tid] = ac;
+    s.zs[tid] = as;
+  }
+  __syncthreads();
+  if (!sh_ok) return false;
+  if (sh_uniform) {
+    // A = w0 U_k^T U_k = w0 I  ->  pinv(A) = I / w0 when w0 > cut, else 0   (:501-504)
+    if (tid < k) {
+      double w0 = s.wc[0];
+      double inv = w0 > cut ? 1.0 / w0 : 0.0;
+      s.zc[tid] *= inv;
+      s.zs[tid] *= inv;
+    }
+  } else {
+    // A = U_k^T W U_k is SPD with eigenvalues in [min w, max w] (Rayleigh quotient, U_k
+    // orthonormal); min w > cut so pinv(A, cut) = inv(A): Cholesky solve.
+    for (int e = tid; e < k * k; e += FT) {
+      int a = e / k, b = e - a * k;
+      if (b > a) continue;
+      double acc = 0.0;
+      for (int i = 0; i < n; ++i) acc = fma(pt.U[i * ld + a] * s.wc[i], pt.U[i * ld + b], acc);
+      s.A[a * k + b] = acc;
+      s.A[b * k + a] = acc;
+    }
+    __syncthreads();
+    for (int j = 0; j < k; ++j) {  // right-looking Cholesky, lower triangle
+      if (tid == 0) s.A[j * k + j] = sqrt(s.A[j * k + j]);
+      __syncthreads();
+      double d = s.A[j * k + j];
+      for (int i = j + 1 + tid; i < k; i += FT) s.A[i * k + j] /= d;
+      __syncthreads();
+      for (int e = tid; e < (k - j - 1) * (k - j - 1); e += FT) {
+        int a = j + 1 + e / (k - j - 1), b = j + 1 + e % (k - j - 1);
+        if (b <= a) s.A[a * k + b] -= s.A[a * k + j] * s.A[b * k + j];
+      }
+      __syncthreads();
+    }
+    if (tid < 2) {  // two right-hand sides, forward then backward substitution
+      double *z = tid == 0 ? s.zc : s.zs;
+      for (int i = 0; i < k; ++i) {
+        double v = z[i];
+        for (int j = 0; j < i; ++j) v -= s.A[i * k + j] * z[j];
+        z[i] = v / s.A[i * k + i];
+      }
+      for (int i = k - 1; i >= 0; --i) {
+        double v = z[i];
+        for (int j = i + 1; j < k; ++j) v -= s.A[j * k + i] * z[j];
+        z[i] = v / s.A[i * k + i];
+      }
+    }
+  }
+  __syncthreads();
+  // y = U_k z
+  if (tid < n) {
+    double ac = 0.0, as = 0.0;
+    for (int j = 0; j < k; ++j) {
+      double u = pt.U[tid * ld + j];
+      ac = fma(u, s.zc[j], ac);
+      as = fma(u, s.zs[j], as);
+    }
+    s.yc[tid] = ac;
+    s.ys[tid] = as;
+  }
+  __syncthreads();
+  // g = pinvC y   (:517-519, :526-528); pinvC symmetric -> column reads are coalesced
+  if (tid < n) {
+    double ac = 0.0, as = 0.0;
+    for (int e = 0; e < n; ++e) {
+      double p = pt.P[e * ld + tid];
+      ac = fma(p, s.yc[e], ac);
+      as = fma(p, s.ys[e], as);
+    }
+    s.gc[tid] = ac;
+    s.gs_[tid] = as;
+  }
+  __syncthreads();
+  // screen_fit = atan2(C g_imag, C g_real)   (:531-533)
+  if (tid < n) {
+    double ac = 0.0, as = 0.0;
+    for (int e = 0; e < n; ++e) {
+      double c = pt.C[e * ld + tid];
+      ac = fma(c, s.gc[e], ac);
+      as = fma(c, s.gs_[e], as);
+    }
+    s.fit[tid] = atan2(as, ac);
+  }
+  __syncthreads();
+  // white = pinvC fit   (:534)
+  if (tid < n) {
+    double a = 0.0;
+    for (int e = 0; e < n; ++e) a = fma(pt.P[e * ld + tid], s.fit[e], a);
+    s.wh[tid] = a;
+  }
+  __syncthreads();
+  if (n == nall) {
+    // resid = phase - C white   (:590)
+    if (tid < n) {
+      double a = 0.0;
+      for (int e = 0; e < n; ++e) a = fma(pt.C[e * ld + tid], s.wh[e], a);
+      white_out[tid] = s.wh[tid];
+      resid_out[tid] = s.ph[tid] - a;
+    }
+  } else {
+    // flagged directions are predicted from the unflagged screen   (:565-574)
+    if (tid < nall) s.fall[tid] = 0.0;
+    __syncthreads();
+    if (tid < n) s.fall[s.idx[tid]] = s.fit[tid];
+    __syncthreads();
+    if (tid < nall && !(s.w[tid] > 0.0)) {
+      double a = 0.0;
+      for (int i = 0; i < n; ++i) {
+        int e = s.idx[i];
+        double dx = pp[2 * e] - pp[2 * tid], dy = pp[2 * e + 1] - pp[2 * tid + 1];
+        double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+        double q = d2 / r0sq;
+        double c = q > 0.0 ? -0.5 * pow(q, half_beta) : 0.0;
+        a = fma(c, s.wh[i], a);
+      }
+      s.fall[tid] = a;
+    }
+    __syncthreads();
+    if (tid < nall) {
+      double a = 0.0;
+      for (int e = 0; e < nall; ++e) a = fma(pt.Pfull[e * ld + tid], s.fall[e], a);
+      white_out[tid] = a;
+      resid_out[tid] = s.ph[tid] - s.fall[tid];
+    }
+  }
+  __syncthreads();
+  return true;
+}
+
+__global__ void __launch_bounds__(FT)
+fit_pass_kernel(const double *__restrict__ phase, const float *__restrict__ weights,
+                const int32_t *__restrict__ pat, const double *__restrict__ pp, int nall, int64_t nsys,
+                const double *__restrict__ C, const double *__restrict__ P, const double *__restrict__ U,
+                double r0sq, double half_beta, double cut, int mode, double *__restrict__ order,
+                const double *__restrict__ station_order, double *__restrict__ white,
+                double *__restrict__ resid, int32_t *__restrict__ status) {
+  SSF_DYN_SMEM(double, sm);
+  __shared__ int sh_n, sh_k, sh_go;
+  __shared__ double sh_t1[FT], sh_t2[FT];
+  const int tid = threadIdx.x;
+  Smem s = carve(sm, nall);
+
+  for (int64_t sys = blockIdx.x; sys < nsys; sys += gridDim.x) {
+    __syncthreads();
+    if (tid < nall) {
+      s.ph[tid] = phase[sys * nall + tid];
+      s.w[tid] = (double)weights[sys * nall + tid];
+    }
+    __syncthreads();
+    if (tid == 0) {
+      int n = 0;
+      for (int d = 0; d < nall; ++d)
+        if (s.w[d] > 0.0) s.idx[n++] = d;
+      sh_n = n;
+    }
+    __syncthreads();
+    const int n = sh_n;
+    if (n == 0) continue;  // :683-684
+    Pattern pt;
+    const size_t off = (size_t)pat[sys] * nall * nall;
+    pt.C = C + off;
+    pt.P = P + off;
+    pt.U = U + off;
+    pt.Pfull = P;
+    pt.ld = nall;
+    double *w_out = white + sys * nall;
+    double *r_out = resid + sys * nall;
+
+    double ord = order[sys];
+    if (ord > (double)(n - 1)) ord = (double)(n - 1);  // :685-686
+    const double st_order = station_order[sys];
+
+    if (mode == 0) {
+      bool ok = fit_once(s, pt, pp, nall, n, (int)ord, r0sq, half_beta, cut, w_out, r_out);
+      if (!ok && tid == 0) atomicExch(status, 1);
+      if (tid == 0) order[sys] = ord;
+      continue;
+    }
+
+    // mode 1: order-adjust loop (:692-779).  The reference's flagged weights alias its
+    // "previous" weights, so the first order iteration never refits (:694-705).
+    bool hit_upper = false, hit_lower = false, hit_upper2 = false, hit_lower2 = false;
+    double sign = 1.0, prev_redchi2 = 0.0;
+    for (int oi = 0; oi < 4; ++oi) {
+      if (oi > 0) {
+        bool ok = fit_once(s, pt, pp, nall, n, (int)ord, r0sq, half_beta, cut, w_out, r_out);
+        if (!ok && tid == 0) atomicExch(status, 1);
+      }
+      if (hit_lower2 || hit_upper2) break;
+      // redchi2 = circ_chi2(resid, w) / (n_unfl - order)   (:729-731, :353-387)
+      __syncthreads();
+      if (tid < nall) {
+        double r = r_out[tid];
+        double sn, cs;
+        sincos(r, &sn, &cs);
+        sh_t1[tid] = s.w[tid] * sn * sn;
+        sh_t2[tid] = s.w[tid] * cs * cs;
+      }
+      __syncthreads();
+      if (tid == 0) {
+        double a1 = 0.0, a2 = 0.0, sw = 0.0;
+        for (int i = 0; i < n; ++i) {
+          int d = s.idx[i];
+          a1 += sh_t1[d];
+          a2 += sh_t2[d];
+          sw += s.w[d];
+        }
+        double chi2 = (1.0 - hypot(a1 / sw, a2 / sw)) * sw;
+        double redchi2 = chi2 / ((double)n - ord);
+        if (oi > 0) {
+          if (redchi2 > 1.0 && prev_redchi2 < redchi2) sign = -sign;
+          if (redchi2 < 1.0 && prev_redchi2 > redchi2) sign = -sign;
+        }
+        prev_redchi2 = redchi2;
+        double factor = pow((double)n - ord, 0.2);
+        double target = ord - sign * factor * (1.0 - redchi2);   // :753-756
+        target = fmax(st_order, target);                          // :757
+        double t_int = fmin(rint(target), (double)(n - 1));       // :758-760 (round half even)
+        if (t_int <= 0.0) t_int = fmin(st_order, (double)(n - 1));
+        int go = 1;
+        if (t_int == ord) {
+          go = 0;                                                 // :763-766
+        } else {
+          if (t_int == (double)(n - 1)) {
+            if (hit_upper) hit_upper2 = true;
+            hit_upper = true;
+          }
+          if (t_int == st_order) {
+            if (hit_lower) hit_lower2 = true;
+            hit_lower = true;
+          }
+          ord = t_int;
+        }
+        sh_go = go;
+        sh_k = (int)ord;
+        sh_t1[0] = ord;
+        sh_t2[0] = (hit_upper2 || hit_lower2) ? 1.0 : 0.0;
+      }
+      __syncthreads();
+      const int go = sh_go;
+      ord = sh_t1[0];
+      const bool hit2 = sh_t2[0] != 0.0;
+      __syncthreads();
+      hit_upper2 = hit2;  // only their OR is used by the other threads
+      hit_lower2 = false;
+      if (tid == 0) {
+        // keep thread 0's private copies coherent with what it computed
+        hit_upper2 = hit2;
+      }
+      if (!go) break;
+    }
+    if (tid == 0) order[sys] = ord;
+  }
+}
+
+// _flag_outliers (stationscreen.py:303-350) per system; one warp per system.
+__global__ void __launch_bounds__(128)
+flag_kernel(const double *__restrict__ resid, float *__restrict__ weights, int nall, int64_t nsys,
+            double nsigma, uint64_t *__restrict__ masks) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t sys = warp; sys < nsys; sys += nwarps) {
+    const double *r = resid + sys * nall;
+    float *w = weights + sys * nall;
+    double ssum = 0.0, csum = 0.0;
+    int cnt = 0;
+    double rn[(SSF_MAX_DIR + 31) / 32];
+#pragma unroll
+    for (int j = 0; j < (SSF_MAX_DIR + 31) / 32; ++j) {
+      int d = lane + 32 * j;
+      rn[j] = 0.0;
+      if (d < nall) {
+        // normalize_phase (processing_utils.py:73-98)
+        double v = fmod(r[d], TWO_PI);
+        if (v < -PI) v += TWO_PI;
+        if (v > PI) v -= TWO_PI;
+        rn[j] = v;
+        if (w[d] != 0.0f && v == v) {  // nanmean over the non-flagged, non-NaN entries
+          double sn, cs;
+          sincos(v, &sn, &cs);
+          ssum += sn;
+          csum += cs;
+          ++cnt;
+        }
+      }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      ssum += __shfl_xor_sync(0xffffffffu, ssum, o);
+      csum += __shfl_xor_sync(0xffffffffu, csum, o);
+      cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    }
+    // nancircstd (processing_utils.py:124-132); cnt == 0 -> NaN -> nothing is flagged
+    double rv = hypot(ssum / (double)cnt, csum / (double)cnt);
+    double sd = sqrt(-2.0 * log(rv));
+    uint64_t m0 = 0, m1 = 0;
+#pragma unroll
+    for (int j = 0; j < (SSF_MAX_DIR + 31) / 32; ++j) {
+      int d = lane + 32 * j;
+      if (d < nall) {
+        float wd = w[d];
+        if (fabs(rn[j]) > nsigma * sd) {
+          wd = 0.0f;
+          w[d] = 0.0f;
+        }
+        if (wd > 0.0f) {
+          if (d < 64) m0 |= 1ull << d;
+          else m1 |= 1ull << (d - 64);
+        }
+      }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      m0 |= __shfl_xor_sync(0xffffffffu, m0, o);
+      m1 |= __shfl_xor_sync(0xffffffffu, m1, o);
+    }
+    if (lane == 0) {
+      masks[2 * sys] = m0;
+      masks[2 * sys + 1] = m1;
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" int ssf_kl_fit_pass(const double *phase, const float *weights, const int32_t *pat,
+                               const double *pp, int ndir, int64_t nsys, const double *C,
+                               const double *pinvC, const double *U, double r0, double beta,
+                               double pinv_cut, int mode, double *order, const double *station_order,
+                               double *white, double *resid, int32_t *status, void *stream) {
+  SSF_REQUIRE(phase && weights && pat && pp && C && pinvC && U && order && station_order && white &&
+                  resid && status,
+              "ssf_kl_fit_pass: null pointer");
+  SSF_REQUIRE(ndir >= 2 && ndir <= SSF_MAX_DIR, "ssf_kl_fit_pass: ndir=%d out of range [2,%d]", ndir, SSF_MAX_DIR);
+  SSF_REQUIRE(mode == 0 || mode == 1, "ssf_kl_fit_pass: mode must be 0 or 1");
+  if (nsys <= 0) return SSF_OK;
+  size_t smem = sizeof(double) * smem_doubles(ndir);
+  if (smem > 48 * 1024)
+    SSF_CUDA(cudaFuncSetAttribute(fit_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int64_t blocks = nsys < 148 * 16 ? nsys : 148 * 16;
+  SSF_LAUNCH(fit_pass_kernel, (int)blocks, FT, smem, (cudaStream_t)stream, phase, weights, pat, pp, ndir,
+             nsys, C, pinvC, U, r0 * r0, beta / 2.0, pinv_cut, mode, order, station_order, white, resid,
+             status);
+  SSF_LAUNCHED();
+  return SSF_OK;
+}
+
+extern "C" int ssf_kl_flag_outliers(const double *resid, float *weights, int ndir, int64_t nsys,
+                                    double nsigma, uint64_t *masks_out, void *stream) {
+  SSF_REQUIRE(resid && weights && masks_out, "ssf_kl_flag_outliers: null pointer");
+  SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR, "ssf_kl_flag_outliers: ndir out of range");
+  if (nsys <= 0) return SSF_OK;
+  int64_t blocks = (nsys + 3) / 4;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  SSF_LAUNCH(flag_kernel, (int)blocks, 128, 0, (cudaStream_t)stream, resid, weights, ndir, nsys, nsigma,
+             masks_out);
+  SSF_LAUNCHED();
+  return SSF_OK;
+}

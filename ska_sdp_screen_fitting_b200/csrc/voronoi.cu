@@ -1,0 +1,173 @@
+// Voronoi (tessellated) screen kernels: nearest-patch template, cos/sin LUT, cube fill,
+// indicator images, NaN fix.  All are HBM-bound streaming kernels: 16 B written per voxel.
+#include "common.cuh"
+
+namespace {
+
+// ------------------------------------------------------------------------------------
+// Template: one thread per pixel, patch sites staged in shared memory, float64 distance
+// compare, strict '<' so the lowest patch index wins ties (bit-exact against the float64
+// CPU definition oracle.port.screens.nearest_patch_template).
+__global__ void assign_kernel(const double *__restrict__ px, const double *__restrict__ py,
+                              int ndir, int nx, int ny, int32_t *__restrict__ tmpl) {
+  __shared__ double sx[SSF_MAX_DIR * 8], sy[SSF_MAX_DIR * 8];
+  for (int d = threadIdx.x; d < ndir; d += blockDim.x) {
+    sx[d] = px[d];
+    sy[d] = py[d];
+  }
+  __syncthreads();
+  int64_t npix = (int64_t)nx * ny;
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < npix;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    double x = (double)(p % nx), y = (double)(p / nx);
+    double best = INFINITY;
+    int arg = 0;
+    for (int d = 0; d < ndir; ++d) {
+      // same association as numpy: (x-px)^2 + (y-py)^2, no FMA contraction
+      double dx = x - sx[d], dy = y - sy[d];
+      double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+      if (d2 < best) {
+        best = d2;
+        arg = d;
+      }
+    }
+    tmpl[p] = arg + 1;
+  }
+}
+
+// LUT: lut[col, d, 0] = (float)(amp*cos(phi)), lut[col, d, 1] = (float)(amp*sin(phi)),
+// evaluated in FP64 so the single rounding to float32 matches numpy's.
+__global__ void lut_kernel(const double *__restrict__ phase, const double *__restrict__ amp,
+                           int64_t n, float2 *__restrict__ lut) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    double s, c;
+    sincos(phase[i], &s, &c);
+    double a = amp ? amp[i] : 1.0;
+    lut[i] = make_float2((float)(a * c), (float)(a * s));
+  }
+}
+
+// Fill: work item = (column, run of 4*VEC consecutive pixels).  The template is tiny and
+// L2/L1 resident; the LUT row of a column is 8*ndir bytes and L1 resident; the only HBM
+// stream is the 4-plane store.  float4 stores when the plane size allows 16 B alignment.
+template <bool VEC4>
+__global__ void fill_kernel(const int32_t *__restrict__ tmpl, const float2 *__restrict__ lut,
+                            int ndir, int64_t npix, int64_t ncol, float *__restrict__ slab,
+                            int fix_nan) {
+  const int64_t per_col = VEC4 ? npix / 4 : npix;
+  const int64_t total = per_col * ncol;
+  for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < total;
+       w += (int64_t)gridDim.x * blockDim.x) {
+    int64_t col = w / per_col;
+    int64_t q = w - col * per_col;
+    const float2 *row = lut + col * ndir;
+    float *out = slab + col * 4 * npix;
+    if (VEC4) {
+      int4 t = __ldg(reinterpret_cast<const int4 *>(tmpl) + q);
+      float2 a = __ldg(row + (t.x - 1)), b = __ldg(row + (t.y - 1));
+      float2 c = __ldg(row + (t.z - 1)), d = __ldg(row + (t.w - 1));
+      float4 re = make_float4(a.x, b.x, c.x, d.x), im = make_float4(a.y, b.y, c.y, d.y);
+      if (fix_nan) {
+        re = make_float4(ssf::fix_re(re.x), ssf::fix_re(re.y), ssf::fix_re(re.z), ssf::fix_re(re.w));
+        im = make_float4(ssf::fix_im(im.x), ssf::fix_im(im.y), ssf::fix_im(im.z), ssf::fix_im(im.w));
+      }
+      float4 *o = reinterpret_cast<float4 *>(out) + q;
+      const int64_t ps = npix / 4;
+      __stcs(o, re);
+      __stcs(o + ps, im);
+      __stcs(o + 2 * ps, re);
+      __stcs(o + 3 * ps, im);
+    } else {
+      float2 a = __ldg(row + (__ldg(tmpl + q) - 1));
+      float re = fix_nan ? ssf::fix_re(a.x) : a.x, im = fix_nan ? ssf::fix_im(a.y) : a.y;
+      out[q] = re;
+      out[npix + q] = im;
+      out[2 * npix + q] = re;
+      out[3 * npix + q] = im;
+    }
+  }
+}
+
+__global__ void indicator_kernel(const int32_t *__restrict__ tmpl, int ndir, int64_t npix,
+                                 float *__restrict__ ind) {
+  // ind[d, pix] = (tmpl[pix] == d + 1)
+  int64_t total = npix * ndir;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t d = i / npix, p = i - d * npix;
+    ind[i] = (tmpl[p] == (int32_t)d + 1) ? 1.0f : 0.0f;
+  }
+}
+
+__global__ void nan_fix_kernel(float *__restrict__ slab, int64_t ncol, int64_t npix) {
+  int64_t total = ncol * 4 * npix;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    float v = slab[i];
+    if (v != v) slab[i] = ((i / npix) & 1) ? 0.0f : 1.0f;
+  }
+}
+
+int grid_for(int64_t work, int threads, int ctas_per_sm) {
+  int64_t blocks = (work + threads - 1) / threads;
+  int64_t cap = (int64_t)148 * ctas_per_sm;
+  return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
+}
+
+}  // namespace
+
+extern "C" int ssf_voronoi_assign(const double *px, const double *py, int ndir, int nx, int ny,
+                                  int32_t *tmpl, void *stream) {
+  SSF_REQUIRE(px && py && tmpl, "ssf_voronoi_assign: null pointer");
+  SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR * 8, "ssf_voronoi_assign: ndir=%d out of range", ndir);
+  SSF_REQUIRE(nx >= 1 && ny >= 1, "ssf_voronoi_assign: empty image");
+  int64_t npix = (int64_t)nx * ny;
+  SSF_LAUNCH(assign_kernel, grid_for(npix, 256, 8), 256, 0, (cudaStream_t)stream, px, py, ndir, nx, ny, tmpl);
+  SSF_LAUNCHED();
+  return SSF_OK;
+}
+
+extern "C" int ssf_voronoi_lut(const double *phase, const double *amp, int64_t ncol, int ndir,
+                               float *lut, void *stream) {
+  SSF_REQUIRE(phase && lut, "ssf_voronoi_lut: null pointer");
+  SSF_REQUIRE(ncol >= 0 && ndir >= 1, "ssf_voronoi_lut: bad sizes");
+  if (ncol == 0) return SSF_OK;
+  int64_t n = ncol * ndir;
+  SSF_LAUNCH(lut_kernel, grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream, phase, amp, n, (float2 *)lut);
+  SSF_LAUNCHED();
+  return SSF_OK;
+}
+
+extern "C" int ssf_voronoi_fill(const int32_t *tmpl, const float *lut, int ndir, int64_t npix,
+                                int64_t ncol, float *slab, int fix_nan, void *stream) {
+  SSF_REQUIRE(tmpl && lut && slab, "ssf_voronoi_fill: null pointer");
+  SSF_REQUIRE(ndir >= 1 && npix >= 1 && ncol >= 0, "ssf_voronoi_fill: bad sizes");
+  if (ncol == 0) return SSF_OK;
+  bool vec = (npix % 4 == 0) && ((uintptr_t)slab % 16 == 0) && ((uintptr_t)tmpl % 16 == 0);
+  if (vec) {
+    SSF_LAUNCH(fill_kernel<true>, grid_for(npix / 4 * ncol, 256, 8), 256, 0, (cudaStream_t)stream,
+               tmpl, (const float2 *)lut, ndir, npix, ncol, slab, fix_nan);
+  } else {
+    SSF_LAUNCH(fill_kernel<false>, grid_for(npix * ncol, 256, 8), 256, 0, (cudaStream_t)stream,
+               tmpl, (const float2 *)lut, ndir, npix, ncol, slab, fix_nan);
+  }
+  SSF_LAUNCHED();
+  return SSF_OK;
+}
+
+extern "C" int ssf_voronoi_indicators(const int32_t *tmpl, int ndir, int64_t npix, float *ind,
+                                      void *stream) {
+  SSF_REQUIRE(tmpl && ind, "ssf_voronoi_indicators: null pointer");
+  SSF_LAUNCH(indicator_kernel, grid_for(npix * ndir, 256, 8), 256, 0, (cudaStream_t)stream, tmpl, ndir, npix, ind);
+  SSF_LAUNCHED();
+  return SSF_OK;
+}
+
+extern "C" int ssf_nan_fix(float *slab, int64_t ncol, int64_t npix, void *stream) {
+  SSF_REQUIRE(slab, "ssf_nan_fix: null pointer");
+  if (ncol == 0) return SSF_OK;
+  SSF_LAUNCH(nan_fix_kernel, grid_for(ncol * 4 * npix, 256, 8), 256, 0, (cudaStream_t)stream, slab, ncol, npix);
+  SSF_LAUNCHED();
+  return SSF_OK;
+}
