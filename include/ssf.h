@@ -75,13 +75,16 @@ int ssf_kl_decompose(const double *pp, int ndir, const uint64_t *masks, int npat
  *                                the fit (reference quirk, :694-705), <= 3 refits (:692-779)
  *   white, resid [nsys, ndir] f64 in/out (mode 1 reads the residual of the previous pass)
  * Systems with no unflagged direction are left untouched (:683-684).
+ *   status  [1] i32 in/out     set to 1 if any system had a weight in (0, pinv_cut] (the
+ *                              Cholesky normal-equation path does not cover it); the
+ *                              caller zero-initialises it and checks it after the pass.
  */
 int ssf_kl_fit_pass(const double *phase, const float *weights, const int32_t *pat,
                     const double *pp, int ndir, int64_t nsys,
                     const double *C, const double *pinvC, const double *U,
                     double r0, double beta, double pinv_cut, int mode,
                     double *order, const double *station_order,
-                    double *white, double *resid, void *stream);
+                    double *white, double *resid, int32_t *status, void *stream);
 
 /* Replaces _flag_outliers (stationscreen.py:303-350) + normalize_phase / nancircstd
  * (processing_utils.py:73-132): per system, sigma = circular std of the unflagged
