@@ -1,0 +1,111 @@
+"""
+ctypes binding of ``libssf_b200.so`` (include/ssf.h).
+
+There is NO CPU fallback: if the library is missing the import of any compute entry
+point raises ``SsfLibraryError``.  ``check()`` turns negative status codes into
+``SsfError`` carrying ``ssf_last_error()``.
+"""
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_double, c_int, c_int32, c_int64, c_uint64, c_void_p
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG, "libssf_b200.so")
+# When set (tests only), load this library instead: tests/emu builds the same kernel sources
+# with g++ against a CUDA emulator so kernel logic can be checked in a GPU-less container.
+_OVERRIDE_ENV = "SSF_B200_LIBRARY"
+
+
+class SsfLibraryError(RuntimeError):
+    """libssf_b200.so is missing or cannot be loaded."""
+
+
+class SsfError(RuntimeError):
+    """A C-ABI call returned a negative status."""
+
+    def __init__(self, fn, code, message):
+        super().__init__(f"{fn} failed with status {code}: {message}")
+        self.code = code
+
+
+# name -> (restype, [argtypes]); mirrors include/ssf.h declaration by declaration
+_P = c_void_p
+SIGNATURES = {
+    "ssf_version": (c_int, []),
+    "ssf_last_error": (c_char_p, []),
+    "ssf_launch_count": (c_uint64, []),
+    "ssf_kl_decompose": (c_int, [_P, c_int, _P, c_int, c_double, c_double, c_double,
+                                 _P, _P, _P, _P, _P]),
+    "ssf_kl_fit_pass": (c_int, [_P, _P, _P, _P, c_int, c_int64, _P, _P, _P, c_double, c_double,
+                                c_double, c_int, _P, _P, _P, _P, _P, _P]),
+    "ssf_kl_flag_outliers": (c_int, [_P, _P, c_int, c_int64, c_double, _P, _P]),
+    "ssf_kl_basis": (c_int, [_P, _P, c_int, c_int, _P, c_int, _P, c_double, c_double, _P, _P]),
+    "ssf_kl_coeffs": (c_int, [_P, c_int64, c_int, _P, _P, c_int, _P]),
+    "ssf_kl_eval": (c_int, [_P, _P, c_int, c_int, c_int64, c_int64, _P, c_int, _P]),
+    "ssf_voronoi_assign": (c_int, [_P, _P, c_int, c_int, c_int, _P, _P]),
+    "ssf_voronoi_lut": (c_int, [_P, _P, c_int64, c_int, _P, _P]),
+    "ssf_voronoi_fill": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, c_int, _P]),
+    "ssf_voronoi_indicators": (c_int, [_P, c_int, c_int64, _P, _P]),
+    "ssf_voronoi_contract": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, c_int, _P]),
+    "ssf_gauss_smooth": (c_int, [_P, c_int64, c_int, c_int, c_double, _P, _P]),
+    "ssf_nan_fix": (c_int, [_P, c_int64, c_int64, _P]),
+    "ssf_voronoi_cube_host": (c_int, [_P, _P, c_int, c_int, c_int, c_int64, c_double, _P]),
+    "ssf_kl_cube_host": (c_int, [_P, _P, c_int, c_int, _P, c_int, _P, c_int64, c_double, c_double,
+                                 c_double, _P]),
+}
+
+_lib = None
+
+
+def library_path():
+    return os.environ.get(_OVERRIDE_ENV) or LIB_PATH
+
+
+def load():
+    """Loads the shared library once and declares every signature."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = library_path()
+    if not os.path.exists(path):
+        raise SsfLibraryError(
+            f"{path} not found: build it with `python -m ska_sdp_screen_fitting_b200._build` "
+            "(there is no CPU fallback)")
+    if path == LIB_PATH:
+        # libcudart.so.12 is resolved through the copy torch has already mapped
+        import torch  # noqa: F401  pylint: disable=import-outside-toplevel,unused-import
+    try:
+        lib = ctypes.CDLL(path, mode=ctypes.RTLD_GLOBAL)
+    except OSError as exc:
+        raise SsfLibraryError(f"cannot load {path}: {exc}") from exc
+    for name, (res, args) in SIGNATURES.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError as exc:
+            raise SsfLibraryError(f"{path} does not export {name}") from exc
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def unload_for_tests():
+    global _lib
+    _lib = None
+
+
+def last_error():
+    return (load().ssf_last_error() or b"").decode("utf8", "replace")
+
+
+def launch_count():
+    return int(load().ssf_launch_count())
+
+
+def call(name, *args):
+    """Calls ``name`` and raises SsfError on a negative status."""
+    fn = getattr(load(), name)
+    rc = fn(*args)
+    if rc != 0:
+        raise SsfError(name, rc, last_error())
+    return rc

@@ -1,0 +1,221 @@
+"""
+Device-side orchestration of the hot path: torch tensors supply device memory and the
+current CUDA stream; every computation is a call into ``libssf_b200.so`` (include/ssf.h).
+
+torch is plumbing only (allocation, views, ``unique`` over flag masks); nothing here
+computes a screen in Python or falls back to the CPU.
+"""
+import math
+
+import numpy as np
+import torch
+
+from . import _lib
+
+R_0 = 100.0            # stationscreen.py:1046
+BETA = 5.0 / 3.0       # stationscreen.py:862
+PINV_CUT = 1e-3        # stationscreen.py:427, :504 (absolute cutoff, scipy 1.7.3 semantics)
+MAX_DIR = 112          # SSF_MAX_DIR
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+class Engine:
+    """Thin, stateless-per-call wrapper; ``device`` is a CUDA device (or "cpu" only when the
+    test emulator library is loaded through SSF_B200_LIBRARY)."""
+
+    def __init__(self, device=None):
+        _lib.load()
+        emulated = _lib.library_path() != _lib.LIB_PATH
+        if device is None:
+            device = "cpu" if emulated else "cuda"
+        self.device = torch.device(device)
+        if not emulated and self.device.type != "cuda":
+            raise _lib.SsfLibraryError("libssf_b200.so needs a CUDA device; there is no CPU path")
+        if self.device.type == "cuda" and self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+
+    # ------------------------------------------------------------------ helpers
+    def stream(self):
+        if self.device.type == "cuda":
+            return torch.cuda.current_stream(self.device).cuda_stream
+        return None
+
+    def tensor(self, array, dtype):
+        t = torch.as_tensor(np.ascontiguousarray(array), dtype=dtype)
+        return t.to(self.device).contiguous()
+
+    def empty(self, shape, dtype):
+        return torch.empty(shape, dtype=dtype, device=self.device)
+
+    def zeros(self, shape, dtype):
+        return torch.zeros(shape, dtype=dtype, device=self.device)
+
+    def _check(self, t, dtype, name):
+        if t.dtype != dtype or not t.is_contiguous() or t.device != self.device:
+            raise ValueError(f"{name}: need contiguous {dtype} tensor on {self.device}, got "
+                             f"{t.dtype} contiguous={t.is_contiguous()} on {t.device}")
+
+    # ------------------------------------------------------------------ KL setup
+    @staticmethod
+    def full_mask(ndir):
+        m = (1 << ndir) - 1
+        lo, hi = m & (2**64 - 1), m >> 64
+        # torch has no uint64 arithmetic: masks travel as int64 bit patterns
+        return [lo - 2**64 if lo >= 2**63 else lo, hi - 2**64 if hi >= 2**63 else hi]
+
+    def kl_decompose(self, pp, masks, r0=R_0, beta=BETA, cut=PINV_CUT):
+        """ssf_kl_decompose: pp [ndir, 2] f64, masks [npat, 2] int64 bit patterns.
+        Returns C, pinvC, U [npat, ndir, ndir] and sv [npat, ndir]."""
+        self._check(pp, torch.float64, "pp")
+        self._check(masks, torch.int64, "masks")
+        ndir, npat = pp.shape[0], masks.shape[0]
+        c = self.empty((npat, ndir, ndir), torch.float64)
+        p = self.empty((npat, ndir, ndir), torch.float64)
+        u = self.empty((npat, ndir, ndir), torch.float64)
+        sv = self.empty((npat, ndir), torch.float64)
+        _lib.call("ssf_kl_decompose", _ptr(pp), ndir, _ptr(masks), npat, r0, beta, cut,
+                  _ptr(c), _ptr(p), _ptr(u), _ptr(sv), self.stream())
+        return c, p, u, sv
+
+    def kl_flag_outliers(self, resid, weights, nsigma):
+        """ssf_kl_flag_outliers in place on ``weights``; returns the [nsys, 2] masks.
+        ``nsigma = inf`` flags nothing and just reports the masks of the weights."""
+        nsys, ndir = resid.shape
+        self._check(resid, torch.float64, "resid")
+        self._check(weights, torch.float32, "weights")
+        masks = self.empty((nsys, 2), torch.int64)
+        _lib.call("ssf_kl_flag_outliers", _ptr(resid), _ptr(weights), ndir, nsys, float(nsigma),
+                  _ptr(masks), self.stream())
+        return masks
+
+    def kl_fit_pass(self, phase, weights, pat, pp, mats, mode, order, station_order, white, resid,
+                    r0=R_0, beta=BETA, cut=PINV_CUT):
+        nsys, ndir = phase.shape
+        c, p, u = mats
+        for t, dt, nm in ((phase, torch.float64, "phase"), (weights, torch.float32, "weights"),
+                          (pat, torch.int32, "pat"), (order, torch.float64, "order"),
+                          (station_order, torch.float64, "station_order"),
+                          (white, torch.float64, "white"), (resid, torch.float64, "resid")):
+            self._check(t, dt, nm)
+        status = self.zeros((1,), torch.int32)
+        _lib.call("ssf_kl_fit_pass", _ptr(phase), _ptr(weights), _ptr(pat), _ptr(pp), ndir, nsys,
+                  _ptr(c), _ptr(p), _ptr(u), r0, beta, cut, mode, _ptr(order), _ptr(station_order),
+                  _ptr(white), _ptr(resid), _ptr(status), self.stream())
+        if int(status.item()) != 0:
+            raise _lib.SsfError("ssf_kl_fit_pass", _lib_status_weights(), "a system has a weight in "
+                                "(0, pinv_cut]: outside the normal-equation path of this kernel")
+
+    def kl_fit(self, phase, weights, station_order, pp, niter=2, nsigma=5.0, adjust_order=True,
+               r0=R_0, beta=BETA, cut=PINV_CUT, pattern_budget_bytes=4 << 30):
+        """The iteration structure of _process_station (stationscreen.py:658-779) for a batch
+        of independent systems.  phase [nsys, ndir] f64 (already referenced), weights
+        [nsys, ndir] f32 (modified in place by the flagging), station_order [nsys] f64.
+        Returns (white, resid, order) with shapes [nsys, ndir], [nsys, ndir], [nsys]."""
+        nsys, ndir = phase.shape
+        white = self.zeros((nsys, ndir), torch.float64)
+        resid = self.zeros((nsys, ndir), torch.float64)
+        order = station_order.clone()
+        full = torch.tensor([self.full_mask(ndir)], dtype=torch.int64, device=self.device)
+        per_pattern = 3 * ndir * ndir * 8 + ndir * 8
+        chunk = max(1024, pattern_budget_bytes // per_pattern)
+        for s0 in range(0, nsys, chunk):
+            s1 = min(nsys, s0 + chunk)
+            ph, w = phase[s0:s1], weights[s0:s1]
+            wh, rs, od, so = white[s0:s1], resid[s0:s1], order[s0:s1], station_order[s0:s1]
+            for it in range(niter):
+                masks = self.kl_flag_outliers(rs, w, nsigma if it > 0 else math.inf)
+                uniq, inv = torch.unique(masks, dim=0, return_inverse=True)
+                patterns = torch.cat([full, uniq]).contiguous()
+                pat = (inv + 1).to(torch.int32).contiguous()
+                c, p, u, sv = self.kl_decompose(pp, patterns, r0, beta, cut)
+                if bool(torch.isnan(sv).any()):
+                    raise _lib.SsfError("ssf_kl_decompose", -3, "Jacobi eigen-solver did not converge")
+                mode = 1 if (it > 0 and adjust_order) else 0
+                self.kl_fit_pass(ph, w, pat, pp, (c, p, u), mode, od, so, wh, rs, r0, beta, cut)
+        return white, resid, order
+
+    # ------------------------------------------------------------------ KL evaluation
+    def kl_basis(self, x_coord, y_coord, pp, pinv_c, r0=R_0, beta=BETA):
+        nx, ny, ndir = x_coord.numel(), y_coord.numel(), pp.shape[0]
+        bt = self.empty((ndir, ny * nx), torch.float32)
+        _lib.call("ssf_kl_basis", _ptr(x_coord), _ptr(y_coord), nx, ny, _ptr(pp), ndir,
+                  _ptr(pinv_c), r0, beta, _ptr(bt), self.stream())
+        return bt
+
+    def kl_coeffs(self, white, c, out=None):
+        ncol, ndir = white.shape
+        self._check(white, torch.float64, "white")
+        ldg = (ndir + 3) // 4 * 4
+        g = out if out is not None else self.empty((ncol, ldg), torch.float32)
+        _lib.call("ssf_kl_coeffs", _ptr(white), ncol, ndir, _ptr(c), _ptr(g), ldg, self.stream())
+        return g
+
+    def kl_eval(self, bt, g, ndir, slab, variant=-1):
+        ncol, ldg = g.shape
+        npix = bt.shape[1]
+        self._check(slab, torch.float32, "slab")
+        if slab.numel() != ncol * 4 * npix:
+            raise ValueError("slab has the wrong size")
+        _lib.call("ssf_kl_eval", _ptr(bt), _ptr(g), ndir, ldg, npix, ncol, _ptr(slab), variant,
+                  self.stream())
+        return slab
+
+    # ------------------------------------------------------------------ Voronoi
+    def voronoi_assign(self, px, py, nx, ny):
+        tmpl = self.empty((ny, nx), torch.int32)
+        _lib.call("ssf_voronoi_assign", _ptr(px), _ptr(py), px.numel(), nx, ny, _ptr(tmpl),
+                  self.stream())
+        return tmpl
+
+    def voronoi_lut(self, phase, amp=None, out=None):
+        ncol, ndir = phase.shape
+        self._check(phase, torch.float64, "phase")
+        lut = out if out is not None else self.empty((ncol, ndir, 2), torch.float32)
+        _lib.call("ssf_voronoi_lut", _ptr(phase), _ptr(amp), ncol, ndir, _ptr(lut), self.stream())
+        return lut
+
+    def voronoi_fill(self, tmpl, lut, slab, fix_nan=True):
+        ncol, ndir, _ = lut.shape
+        npix = tmpl.numel()
+        self._check(tmpl, torch.int32, "tmpl")
+        self._check(slab, torch.float32, "slab")
+        if slab.numel() != ncol * 4 * npix:
+            raise ValueError("slab has the wrong size")
+        _lib.call("ssf_voronoi_fill", _ptr(tmpl), _ptr(lut), ndir, npix, ncol, _ptr(slab),
+                  1 if fix_nan else 0, self.stream())
+        return slab
+
+    def voronoi_indicators(self, tmpl, ndir):
+        npix = tmpl.numel()
+        ind = self.empty((ndir,) + tuple(tmpl.shape), torch.float32)
+        _lib.call("ssf_voronoi_indicators", _ptr(tmpl), ndir, npix, _ptr(ind), self.stream())
+        return ind
+
+    def voronoi_contract(self, smoothed_ind, lut, slab, variant=-1):
+        ncol, ndir, _ = lut.shape
+        npix = smoothed_ind.numel() // ndir
+        _lib.call("ssf_voronoi_contract", _ptr(smoothed_ind), _ptr(lut), ndir, npix, ncol,
+                  _ptr(slab), variant, self.stream())
+        return slab
+
+    def gauss_smooth(self, images, sigma, scratch=None):
+        """In place on images [..., ny, nx] float32."""
+        self._check(images, torch.float32, "images")
+        ny, nx = images.shape[-2:]
+        nimg = images.numel() // (ny * nx)
+        if scratch is None:
+            scratch = torch.empty_like(images)
+        _lib.call("ssf_gauss_smooth", _ptr(images), nimg, ny, nx, float(sigma), _ptr(scratch),
+                  self.stream())
+        return images
+
+    def nan_fix(self, slab, ncol, npix):
+        _lib.call("ssf_nan_fix", _ptr(slab), ncol, npix, self.stream())
+        return slab
+
+
+def _lib_status_weights():
+    return -4

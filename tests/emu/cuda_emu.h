@@ -86,10 +86,10 @@ static inline double __dadd_rn(double a, double b) { volatile double r = a + b; 
 static inline double __dmul_rn(double a, double b) { volatile double r = a * b; return r; }
 static inline float __fmul_rn(float a, float b) { volatile float r = a * b; return r; }
 static inline float __fadd_rn(float a, float b) { volatile float r = a + b; return r; }
-static inline void sincos(double x, double *s, double *c) { *s = sin(x); *c = cos(x); }
-static inline void sincosf(float x, float *s, float *c) { *s = sinf(x); *c = cosf(x); }
 static inline float __int_as_float(int i) { float f; memcpy(&f, &i, 4); return f; }
 static inline int __float_as_int(float f) { int i; memcpy(&i, &f, 4); return i; }
+template <typename T> static inline T atomicExch(T *p, T v) { T o = *p; *p = v; return o; }
+template <typename T> static inline T atomicAdd(T *p, T v) { T o = *p; *p = o + v; return o; }
 static inline int __popcll(unsigned long long v) { return __builtin_popcountll(v); }
 
 // ---- the slice of the runtime API the library uses ---------------------------------------
