@@ -153,6 +153,11 @@ int ssf_gauss_smooth(float *images, int64_t nimg, int ny, int nx, double sigma,
 /* NaN -> 1.0 (planes 0, 2) / 0.0 (planes 1, 3), screen.py:364-378, on a slab. */
 int ssf_nan_fix(float *slab, int64_t ncol, int64_t npix, void *stream);
 
+/* In-place byte swap of `count` 32-bit words: float32 little-endian -> the big-endian
+ * storage order of a BITPIX -32 FITS cube (astropy does this inside hdu.writeto,
+ * screen.py:381-382).  `data` must be 16-byte aligned. */
+int ssf_bswap32(void *data, int64_t count, void *stream);
+
 /* ------------------------------------------------------------------------------------
  * Host convenience entry points (what a ctypes/cffi binding of the reference would call):
  * HOST buffers in, HOST slab out; allocation, H2D, kernels, D2H inside.

@@ -49,6 +49,7 @@ SIGNATURES = {
     "ssf_voronoi_contract": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, c_int, _P]),
     "ssf_gauss_smooth": (c_int, [_P, c_int64, c_int, c_int, c_double, _P, _P]),
     "ssf_nan_fix": (c_int, [_P, c_int64, c_int64, _P]),
+    "ssf_bswap32": (c_int, [_P, c_int64, _P]),
     "ssf_voronoi_cube_host": (c_int, [_P, _P, c_int, c_int, c_int, c_int64, c_double, _P]),
     "ssf_kl_cube_host": (c_int, [_P, _P, c_int, c_int, _P, c_int, _P, c_int64, c_double, c_double,
                                  c_double, _P]),

@@ -109,6 +109,25 @@ __global__ void nan_fix_kernel(float *__restrict__ slab, int64_t ncol, int64_t n
   }
 }
 
+// float32 little-endian -> big-endian in place (FITS BITPIX -32 storage order), 16 B per thread.
+__global__ void bswap32_kernel(uint32_t *__restrict__ data, int64_t n) {
+  const int64_t n4 = n / 4;
+  uint4 *v = reinterpret_cast<uint4 *>(data);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    uint4 a = v[i];
+    a.x = __byte_perm(a.x, 0, 0x0123);
+    a.y = __byte_perm(a.y, 0, 0x0123);
+    a.z = __byte_perm(a.z, 0, 0x0123);
+    a.w = __byte_perm(a.w, 0, 0x0123);
+    v[i] = a;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    int64_t i = n4 * 4 + threadIdx.x;
+    data[i] = __byte_perm(data[i], 0, 0x0123);
+  }
+}
+
 int grid_for(int64_t work, int threads, int ctas_per_sm) {
   int64_t blocks = (work + threads - 1) / threads;
   int64_t cap = (int64_t)148 * ctas_per_sm;
@@ -168,6 +187,16 @@ extern "C" int ssf_nan_fix(float *slab, int64_t ncol, int64_t npix, void *stream
   SSF_REQUIRE(slab, "ssf_nan_fix: null pointer");
   if (ncol == 0) return SSF_OK;
   SSF_LAUNCH(nan_fix_kernel, grid_for(ncol * 4 * npix, 256, 8), 256, 0, (cudaStream_t)stream, slab, ncol, npix);
+  SSF_LAUNCHED();
+  return SSF_OK;
+}
+
+extern "C" int ssf_bswap32(void *data, int64_t count, void *stream) {
+  SSF_REQUIRE(data, "ssf_bswap32: null pointer");
+  SSF_REQUIRE(((uintptr_t)data % 16) == 0, "ssf_bswap32: buffer must be 16-byte aligned");
+  if (count <= 0) return SSF_OK;
+  SSF_LAUNCH(bswap32_kernel, grid_for(count / 4 + 1, 256, 8), 256, 0, (cudaStream_t)stream,
+             (uint32_t *)data, count);
   SSF_LAUNCHED();
   return SSF_OK;
 }

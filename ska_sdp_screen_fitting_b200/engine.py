@@ -127,6 +127,10 @@ class Engine:
             wh, rs, od, so = white[s0:s1], resid[s0:s1], order[s0:s1], station_order[s0:s1]
             for it in range(niter):
                 masks = self.kl_flag_outliers(rs, w, nsigma if it > 0 else math.inf)
+                if it > 0 and not adjust_order:
+                    # the flagged weights alias the "previous" weights in the reference, so
+                    # without order adjustment nothing is refitted (stationscreen.py:694-701)
+                    continue
                 uniq, inv = torch.unique(masks, dim=0, return_inverse=True)
                 patterns = torch.cat([full, uniq]).contiguous()
                 pat = (inv + 1).to(torch.int32).contiguous()
@@ -215,6 +219,12 @@ class Engine:
     def nan_fix(self, slab, ncol, npix):
         _lib.call("ssf_nan_fix", _ptr(slab), ncol, npix, self.stream())
         return slab
+
+
+    def bswap32(self, t):
+        """In place: float32 little-endian -> big-endian (FITS storage order)."""
+        _lib.call("ssf_bswap32", _ptr(t), t.numel(), self.stream())
+        return t
 
 
 def _lib_status_weights():

@@ -1,0 +1,188 @@
+"""
+Minimal FITS primary-HDU writer / reader for the a-term cube (no astropy / cfitsio here).
+
+Layout written: one primary HDU, BITPIX -32, big-endian float32, numpy shape
+``[time, freq, ant, 4, y, x]`` (processing_utils.py:190-194, 202), header cards in the order
+``make_template_image`` creates them (processing_utils.py:204-289).
+
+The writer streams: ``CubeWriter`` creates the file with its full header, and time slabs are
+written at their byte offset as they come off the GPU, so a cube never has to exist in host
+memory and every byte is written once (the reference writes the cube twice,
+screen.py:331-334 then :381-382).
+"""
+import os
+
+import numpy as np
+
+BLOCK = 2880
+
+
+def _fmt_float(value):
+    """astropy.io.fits.card._format_float: 16 significant digits, always a decimal point."""
+    text = f"{float(value):.16G}"
+    if "." not in text and "E" not in text:
+        text += ".0"
+    elif "E" in text:
+        mant, exp = text.split("E")
+        sign = "-" if exp[0] == "-" else ""
+        exp = exp.lstrip("+-").lstrip("0")
+        if "." not in mant:
+            mant += ".0"
+        text = f"{mant}E{sign}{int(exp or 0):02d}"
+    return text[:20]
+
+
+def _card(key, value, comment=""):
+    if isinstance(value, (bool, np.bool_)):
+        val = f"{'T' if value else 'F':>20}"
+    elif isinstance(value, (int, np.integer)):
+        val = f"{int(value):>20d}"
+    elif isinstance(value, (float, np.floating)):
+        val = f"{_fmt_float(value):>20}"
+    elif isinstance(value, str):
+        val = "'" + f"{value.replace(chr(39), chr(39) * 2):<8}" + "'"
+        val = f"{val:<20}"
+    else:
+        raise TypeError(f"unsupported FITS value {value!r}")
+    text = f"{key:<8}= {val}"
+    if comment:
+        text += f" / {comment}"
+    if len(text) > 80:
+        text = text[:80]
+    return f"{text:<80}"
+
+
+def header_bytes(cards):
+    text = "".join(_card(*c) for c in cards) + f"{'END':<80}"
+    pad = (-len(text)) % BLOCK
+    return (text + " " * pad).encode("ascii")
+
+
+def aterm_cards(shape, rad, dec, cellsize_deg, freqs, times):
+    """Header of a "gain" a-term cube (processing_utils.py:202-289).  ``shape`` is the numpy
+    shape [nt, nf, na, 4, ny, nx]."""
+    nt, nf, _, _, ny, nx = shape
+    freqs = np.asarray(freqs, np.float64)
+    times = np.asarray(times, np.float64)
+    cards = [("SIMPLE", True, "conforms to FITS standard"),
+             ("BITPIX", -32, "array data type"),
+             ("NAXIS", 6, "number of array dimensions")]
+    cards += [(f"NAXIS{i + 1}", int(n)) for i, n in enumerate(reversed(shape))]
+    cards.append(("EXTEND", True))
+
+    def axis(i, crval, cdelt, crpix, cunit, ctype):
+        return [(f"CRVAL{i}", crval), (f"CDELT{i}", cdelt), (f"CRPIX{i}", crpix),
+                (f"CUNIT{i}", cunit), (f"CTYPE{i}", ctype)]
+
+    cards += axis(1, float(rad), -float(cellsize_deg), nx / 2.0, "deg", "RA---SIN")
+    cards += axis(2, float(dec), float(cellsize_deg), ny / 2.0, "deg", "DEC--SIN")
+    cards += axis(3, 0.0, 1.0, 1.0, "", "MATRIX")
+    cards += axis(4, 0.0, 1.0, 1.0, "", "ANTENNA")
+    del_freq = float(np.min(freqs[1:] - freqs[:-1])) if nf > 1 else 1e8       # :249-253
+    cards.append(("RESTFRQ", float(freqs[0])))
+    cards += axis(5, float(freqs[0]), del_freq, 1.0, "Hz", "FREQ")
+    if nt > 1:                                                                 # :263-276
+        deltas = times[1:] - times[:-1]
+        del_time = float(np.min(deltas[:-1])) if nt > 2 else float(deltas[0])
+    else:
+        del_time = 1.0
+    cards += axis(6, float(times[0]), del_time, 1.0, "s", "TIME")
+    cards += [("EQUINOX", 2000.0), ("TELESCOP", "LOFAR")]
+    return cards
+
+
+class CubeWriter:
+    """Creates ``path`` with its header and accepts time slabs in any order."""
+
+    def __init__(self, path, shape, cards, create=True):
+        """``create=False`` opens a file another process (rank 0) has already laid out."""
+        self.path = path
+        self.shape = tuple(int(s) for s in shape)
+        self._head = header_bytes(cards)
+        self._row_bytes = int(np.prod(self.shape[1:])) * 4
+        data_bytes = self.shape[0] * self._row_bytes
+        self._total = len(self._head) + data_bytes + (-data_bytes) % BLOCK
+        if create:
+            self._fd = os.open(path, os.O_WRONLY | os.O_CREAT | os.O_TRUNC, 0o644)
+            os.pwrite(self._fd, self._head, 0)
+            os.ftruncate(self._fd, self._total)      # zero padding to a whole block
+        else:
+            self._fd = os.open(path, os.O_WRONLY)
+
+    def write_times(self, t0, slab, already_big_endian=False):
+        """slab: array whose leading axis is time, starting at time index ``t0``."""
+        arr = np.ascontiguousarray(slab)
+        if arr.dtype.itemsize != 4:
+            raise TypeError("slab must be a 4-byte type")
+        if not already_big_endian:
+            arr = arr.astype(">f4", copy=False)
+        nbytes = arr.nbytes
+        if nbytes % self._row_bytes or t0 * self._row_bytes + nbytes > self.shape[0] * self._row_bytes:
+            raise ValueError("slab does not fit the cube")
+        view = memoryview(arr).cast("B")
+        off = len(self._head) + t0 * self._row_bytes
+        done = 0
+        while done < nbytes:                         # pwrite caps at ~2 GiB per call
+            done += os.pwrite(self._fd, view[done:done + (1 << 30)], off + done)
+
+    def close(self):
+        if self._fd is not None:
+            os.close(self._fd)
+            self._fd = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+
+def write_image(path, data, cards):
+    """Small convenience: whole array in one go (used for the Voronoi template image)."""
+    data = np.asarray(data, np.float32)
+    with CubeWriter(path, data.shape, cards) as wr:
+        wr.write_times(0, data)
+
+
+def read(path, memmap=True):
+    """Returns (header dict in card order, data array native-endian view or memmap)."""
+    header = {}
+    with open(path, "rb") as fh:
+        pos = 0
+        done = False
+        while not done:
+            block = fh.read(BLOCK)
+            if len(block) < BLOCK:
+                raise ValueError("truncated FITS header")
+            pos += BLOCK
+            for i in range(0, BLOCK, 80):
+                card = block[i:i + 80].decode("ascii")
+                key = card[:8].strip()
+                if key == "END":
+                    done = True
+                    break
+                if card[8:10] != "= ":
+                    continue
+                raw = card[10:].split(" / ")[0].strip() if not card[10:].lstrip().startswith("'") \
+                    else card[10:]
+                if raw.lstrip().startswith("'"):
+                    body = raw.lstrip()[1:]
+                    end = body.find("'")
+                    while end + 1 < len(body) and body[end + 1] == "'":
+                        end = body.find("'", end + 2)
+                    header[key] = body[:end].replace("''", "'").rstrip()
+                elif raw in ("T", "F"):
+                    header[key] = raw == "T"
+                else:
+                    try:
+                        header[key] = int(raw)
+                    except ValueError:
+                        header[key] = float(raw)
+    naxis = header["NAXIS"]
+    shape = tuple(header[f"NAXIS{i}"] for i in range(naxis, 0, -1))
+    dtype = {-32: ">f4", -64: ">f8", 32: ">i4", 16: ">i2"}[header["BITPIX"]]
+    if memmap:
+        data = np.memmap(path, dtype=dtype, mode="r", offset=pos, shape=shape)
+    else:
+        data = np.fromfile(path, dtype=dtype, offset=pos, count=int(np.prod(shape))).reshape(shape)
+    return header, data

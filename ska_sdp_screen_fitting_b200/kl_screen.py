@@ -1,0 +1,144 @@
+"""
+Karhunen-Loeve screens -- drop-in for the reference's ``kl_screen.py:22-449`` with
+
+* ``fit()``: the ``stationscreen.run`` operation (stationscreen.py:858-1161) as a batched
+  FP64 GPU fit over all (time, freq, station) systems at once (``Engine.kl_fit``), and
+* ``make_matrix()`` / ``write()``: ``calculate_kl_screen`` (kl_screen.py:411-449) as a
+  pixel-basis contraction with a fused cos/sin epilogue (``ssf_kl_eval``).
+
+Unlike the reference, the fit results stay in memory: nothing is appended to the input
+h5parm (the reference's ``remove_soltabs`` never succeeds, so a second run would read a stale
+table -- SURVEY.md section 5).
+"""
+import numpy as np
+import torch
+
+from . import wcs
+from .engine import BETA, PINV_CUT, R_0
+from .screen import Screen
+
+
+def reference_station(weights, max_ind=10):
+    """processing_utils.py:538-574 on weights [time, freq, ant, dir(, pol)]: the first of
+    the ``max_ind`` leading antennas with the largest weight sum."""
+    n_ant = weights.shape[2]
+    if max_ind is None or max_ind > n_ant:
+        max_ind = n_ant
+    axes = tuple(i for i in range(weights.ndim) if i != 2)
+    sums = np.sum(weights, axis=axes, dtype=float)[:max_ind]
+    return int(np.nonzero(sums == sums.max())[0][0])
+
+
+def station_orders(station_positions, ref_ant, order, min_order=5):
+    """Per-station screen order from the distance to the reference station
+    (stationscreen.py:999-1033, scale_order=True, scale_dist=None).  Positions are the
+    float32 rows of the antenna table and the reference does this arithmetic in float32."""
+    pos = np.asarray(station_positions, np.float32)
+    if ref_ant == -1:
+        return [order] * len(pos)
+    diff = pos[ref_ant][None, :] - pos
+    dist = [np.sqrt(d[0] ** 2 + d[1] ** 2 + d[2] ** 2) for d in diff]
+    scale = max(dist)
+    return [max(min_order, min(order, int(np.float32(order) * np.sqrt(d / scale)))) for d in dist]
+
+
+class KLScreen(Screen):
+    """Class for KL (Karhunen-Lo`eve) screens (reference: kl_screen.py:22-59)."""
+
+    def __init__(self, name, h5parm_filename, skymodel_filename, rad, dec, width_ra, width_dec,
+                 solset_name="sol000", phase_soltab_name="phase000", amplitude_soltab_name=None):
+        super().__init__(name, h5parm_filename, skymodel_filename, rad, dec, width_ra, width_dec,
+                         solset_name=solset_name, phase_soltab_name=phase_soltab_name,
+                         amplitude_soltab_name=amplitude_soltab_name)
+        self.height = 0.0
+        self.beta_val = BETA
+        self.r_0 = R_0
+        self.piercepoints = None
+        self.mid_ra = None
+        self.mid_dec = None
+        self.screen_order = None          # [t, f, a] final orders (reference: resid soltab weights)
+        self.residuals = None             # [t, f, a, d]
+        self.weights_out = None           # [t, f, a, d] weights after outlier flagging
+        self.eval_variant = -1            # ssf_kl_eval variant (-1 auto, 0 SIMT, 1 tcgen05)
+        self._basis = None
+        self._basis_key = None
+        self._c_full = None
+        self._pinv_full = None
+
+    # ------------------------------------------------------------------ fit
+    def fit(self):
+        """kl_screen.py:61-155 + stationscreen.run (phase type)."""
+        if not self.phase_only:
+            raise NotImplementedError("amplitude ('gain') soltabs are not supported by this engine yet")
+        sol = self._load_solutions(self.input_phase_soltab_name)
+        if sol.val.ndim != 4:
+            raise NotImplementedError("phase soltabs with a pol axis are not supported yet")
+        eng = self.engine
+        n_t, n_f, n_a, n_d = sol.val.shape
+        if n_d > 112:
+            raise ValueError(f"{n_d} directions exceed the engine limit of 112")
+        ref_ind = reference_station(sol.weight, 10)                       # kl_screen.py:93
+        screen_order = min(20, n_d - 1)                                   # kl_screen.py:101
+        st_order = station_orders(sol.station_positions, ref_ind, screen_order)
+
+        # pierce points: TAN-projected float32 source table (stationscreen.py:99-108)
+        src = np.asarray(sol.source_positions, np.float32)
+        ra_deg, dec_deg = np.rad2deg(src[:, 0]), np.rad2deg(src[:, 1])
+        px, py, self.mid_ra, self.mid_dec = wcs.refined_screen_xy(ra_deg, dec_deg)
+        self.piercepoints = np.column_stack([px, py, np.zeros(n_d)])
+        pp = eng.tensor(self.piercepoints[:, :2], torch.float64)
+
+        val = eng.tensor(sol.val, torch.float64)
+        weight = eng.tensor(sol.weight, torch.float32)
+        if ref_ind != -1:                                                 # stationscreen.py:994-997
+            val = val - val[:, :, ref_ind:ref_ind + 1, :]
+        # stations skipped by _process_single_freq (stationscreen.py:818-825)
+        skip = torch.isnan(val).all(dim=3).all(dim=0) | (weight == 0).all(dim=3).all(dim=0)  # [f, a]
+        skip[:, ref_ind] = True
+        work_w = torch.where(skip[None, :, :, None], torch.zeros_like(weight), weight).contiguous()
+        so = torch.tensor(st_order, dtype=torch.float64, device=eng.device)
+        so = so[None, None, :].expand(n_t, n_f, n_a).reshape(-1).contiguous()
+        white, resid, order = eng.kl_fit(val.reshape(-1, n_d).contiguous(), work_w.view(-1, n_d),
+                                         so, pp, niter=2, nsigma=5.0, adjust_order=True,
+                                         r0=self.r_0, beta=self.beta_val, cut=PINV_CUT)
+        order = order.view(n_t, n_f, n_a)
+        order = torch.where(skip[None], torch.zeros_like(order), order)
+        self._dev_vals = white.view(n_t, n_f, n_a, n_d)
+        self.vals_ph = self._dev_vals.cpu().numpy()
+        self.residuals = resid.view(n_t, n_f, n_a, n_d).cpu().numpy()
+        self.screen_order = order.cpu().numpy()
+        self.weights_out = torch.where(skip[None, :, :, None], weight, work_w).cpu().numpy()
+        full = torch.tensor([eng.full_mask(n_d)], dtype=torch.int64, device=eng.device)
+        c, pinv, _, _ = eng.kl_decompose(pp, full, self.r_0, self.beta_val, PINV_CUT)
+        self._c_full, self._pinv_full = c[0].contiguous(), pinv[0].contiguous()
+        self._pp_dev = pp
+        self.times_ph = sol.time
+        self.freqs_ph = sol.freq
+        self.source_names = sol.dir
+        self.source_dict = sol.source_dict
+        self.source_positions = sol.source_positions
+        self.station_names = sol.ant
+        self.station_dict = sol.station_dict
+        self.station_positions = sol.station_positions
+
+    # ------------------------------------------------------------------ evaluation
+    def _prepare(self, cellsize_deg, out_dir):
+        key = (float(cellsize_deg), float(self.width_ra), float(self.rad), float(self.dec))
+        if self._basis is not None and self._basis_key == key:
+            return
+        eng = self.engine
+        x_coord, y_coord = wcs.kl_grid(self.rad, self.dec, self.width_ra, cellsize_deg,
+                                       self.mid_ra, self.mid_dec)
+        self._basis = eng.kl_basis(eng.tensor(x_coord, torch.float64), eng.tensor(y_coord, torch.float64),
+                                   self._pp_dev, self._pinv_full, self.r_0, self.beta_val)
+        self._basis_key = key
+
+    def _fill_columns(self, cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan):
+        # smooth_pix is forced to 0 for KL screens by make_aterm_image (make_aterm_images.py:101-103);
+        # NaN -> (1, 0) is fused into the store of ssf_kl_eval either way.
+        self._prepare(cellsize_deg, out_dir)
+        eng = self.engine
+        coeffs = eng.kl_coeffs(cols, self._c_full)
+        eng.kl_eval(self._basis, coeffs, cols.shape[1], slab, self.eval_variant)
+        if smooth_pix and smooth_pix > 0:
+            eng.gauss_smooth(slab, smooth_pix)

@@ -1,0 +1,129 @@
+"""
+Voronoi-tessellated screens -- drop-in for the reference's ``voronoi_screen.py:24-351``.
+
+``fit()`` re-references the phases on the device; the cube is produced per time slab by
+``ssf_voronoi_lut`` (FP64 cos/sin of each solution, rounded once to float32) and
+``ssf_voronoi_fill`` (template lookup, four coalesced plane stores per pixel), followed --
+when smoothing is requested -- by the separable Gaussian of ``ssf_gauss_smooth`` and the
+NaN fix, or by the algebraically equivalent contraction against pre-smoothed cell indicator
+images (``smooth_mode = "linear"``).
+"""
+import os
+
+import numpy as np
+import torch
+
+from . import fits, skymodel, template, wcs
+from .kl_screen import reference_station
+from .screen import Screen
+
+
+class VoronoiScreen(Screen):
+    """Class for Voronoi screens (reference: voronoi_screen.py:24-55)."""
+
+    def __init__(self, name, h5parm_filename, skymodel_filename, rad, dec, width_ra, width_dec,
+                 solset_name="sol000", phase_soltab_name="phase000", amplitude_soltab_name=None):
+        super().__init__(name, h5parm_filename, skymodel_filename, rad, dec, width_ra, width_dec,
+                         solset_name=solset_name, phase_soltab_name=phase_soltab_name,
+                         amplitude_soltab_name=amplitude_soltab_name)
+        self.data_rasertize_template = None
+        self.polygons = None
+        self.template_mode = "reference"      # "reference" (host pipeline) | "nearest" (CUDA kernel)
+        self.smooth_mode = "direct"           # "direct" (fill -> gaussian) | "linear" (contraction)
+        self.patch_radec = None               # optional [ndir, 2] deg override of the sky model
+        self._tmpl_dev = None
+        self._tmpl_key = None
+        self._ind_dev = None
+        self._ind_key = None
+
+    def fit(self):
+        """voronoi_screen.py:57-102: no fitting, the phases are referenced to one station."""
+        if not self.phase_only:
+            raise NotImplementedError("amplitude ('gain') soltabs are not supported by this engine yet")
+        sol = self._load_solutions(self.input_phase_soltab_name)
+        if sol.val.ndim != 4:
+            raise NotImplementedError("phase soltabs with a pol axis are not supported yet")
+        eng = self.engine
+        ref_ind = reference_station(sol.weight, 10)
+        val = eng.tensor(sol.val, torch.float64)
+        self._dev_vals = (val - val[:, :, ref_ind:ref_ind + 1, :]).contiguous()
+        self.vals_ph = self._dev_vals.cpu().numpy()
+        self.times_ph = sol.time
+        self.freqs_ph = sol.freq
+        self.vals_amp = np.ones_like(self.vals_ph)
+        self.times_amp = self.times_ph
+        self.freqs_amp = self.freqs_ph
+        self.source_names = sol.dir
+        self.source_dict = sol.source_dict
+        self.source_positions = sol.source_positions
+        self.station_names = sol.ant
+        self.station_dict = sol.station_dict
+        self.station_positions = sol.station_positions
+
+    # ------------------------------------------------------------------ template
+    def _patch_radec(self):
+        if self.patch_radec is not None:
+            arr = np.asarray(self.patch_radec, np.float64)
+            return arr[:, 0], arr[:, 1]
+        positions = skymodel.patch_positions(self.input_skymodel_filename)   # voronoi_screen.py:241-249
+        radec = np.array([positions[name.strip("[]")] for name in self.source_names])
+        return radec[:, 0], radec[:, 1]
+
+    def make_rasertize_template(self, cellsize_deg, out_dir):
+        """voronoi_screen.py:218-351.  Also writes ``{name}_template.fits`` (a one-time-slot
+        zero cube, :229-232) when ``out_dir`` is given, because the reference leaves it behind
+        and its test asserts it exists."""
+        eng = self.engine
+        n_y, n_x = self.image_shape(cellsize_deg)
+        ra_deg, dec_deg = self._patch_radec()
+        if out_dir is not None:
+            shape = (1, len(self.freqs_ph), len(self.station_names), 4, n_y, n_x)
+            cards = fits.aterm_cards(shape, self.rad, self.dec, cellsize_deg, self.freqs_ph,
+                                     np.asarray(self.times_ph)[0:1])
+            fits.CubeWriter(os.path.join(out_dir, f"{self.name}_template.fits"), shape, cards).close()
+        if self.template_mode == "reference":
+            tmpl, _, _ = template.reference_template(ra_deg, dec_deg, self.rad, self.dec,
+                                                     self.width_ra, cellsize_deg)
+            self._tmpl_dev = eng.tensor(tmpl, torch.int32)
+        elif self.template_mode == "nearest":
+            px, py = wcs.patch_pixels(ra_deg, dec_deg, self.rad, self.dec, n_x, cellsize_deg)
+            self._tmpl_dev = eng.voronoi_assign(eng.tensor(px, torch.float64),
+                                                eng.tensor(py, torch.float64), n_x, n_y)
+            tmpl = self._tmpl_dev.cpu().numpy()
+        else:
+            raise ValueError(f"unknown template_mode {self.template_mode!r}")
+        self.data_rasertize_template = tmpl.astype(np.float64)
+        self._ind_dev = None
+
+    def _prepare(self, cellsize_deg, out_dir):
+        key = (float(cellsize_deg), float(self.width_ra), float(self.rad), float(self.dec),
+               self.template_mode)
+        if self._tmpl_dev is None or self._tmpl_key != key:
+            self.make_rasertize_template(cellsize_deg, out_dir)
+            self._tmpl_key = key
+
+    def _smoothed_indicators(self, smooth_pix):
+        key = (self._tmpl_key, float(smooth_pix))
+        if self._ind_dev is None or self._ind_key != key:
+            eng = self.engine
+            ind = eng.voronoi_indicators(self._tmpl_dev, len(self.source_names))
+            self._ind_dev = eng.gauss_smooth(ind, smooth_pix)
+            self._ind_key = key
+        return self._ind_dev
+
+    # ------------------------------------------------------------------ fill
+    def _fill_columns(self, cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan):
+        self._prepare(cellsize_deg, out_dir)
+        eng = self.engine
+        lut = eng.voronoi_lut(cols)
+        npix = self._tmpl_dev.numel()
+        smooth = bool(smooth_pix) and smooth_pix > 0
+        if smooth and self.smooth_mode == "linear":
+            eng.voronoi_contract(self._smoothed_indicators(smooth_pix), lut, slab)
+        elif smooth:
+            eng.voronoi_fill(self._tmpl_dev, lut, slab, fix_nan=False)
+            eng.gauss_smooth(slab, smooth_pix)
+            if fix_nan:
+                eng.nan_fix(slab, cols.shape[0], npix)
+        else:
+            eng.voronoi_fill(self._tmpl_dev, lut, slab, fix_nan=fix_nan)
