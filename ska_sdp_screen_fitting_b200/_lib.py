@@ -7,7 +7,7 @@ point raises ``SsfLibraryError``.  ``check()`` turns negative status codes into
 """
 import ctypes
 import os
-from ctypes import POINTER, c_char_p, c_double, c_int, c_int32, c_int64, c_uint64, c_void_p
+from ctypes import c_char_p, c_double, c_int, c_int64, c_uint64, c_void_p
 
 PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(PKG, "libssf_b200.so")
@@ -55,19 +55,18 @@ SIGNATURES = {
                                  c_double, _P]),
 }
 
-_lib = None
+_loaded = {}
 
 
 def library_path():
     return os.environ.get(_OVERRIDE_ENV) or LIB_PATH
 
 
-def load():
-    """Loads the shared library once and declares every signature."""
-    global _lib
-    if _lib is not None:
-        return _lib
-    path = library_path()
+def load(path=None):
+    """Loads a shared library once per path and declares every signature."""
+    path = path or library_path()
+    if path in _loaded:
+        return _loaded[path]
     if not os.path.exists(path):
         raise SsfLibraryError(
             f"{path} not found: build it with `python -m ska_sdp_screen_fitting_b200._build` "
@@ -76,7 +75,7 @@ def load():
         # libcudart.so.12 is resolved through the copy torch has already mapped
         import torch  # noqa: F401  pylint: disable=import-outside-toplevel,unused-import
     try:
-        lib = ctypes.CDLL(path, mode=ctypes.RTLD_GLOBAL)
+        lib = ctypes.CDLL(path)
     except OSError as exc:
         raise SsfLibraryError(f"cannot load {path}: {exc}") from exc
     for name, (res, args) in SIGNATURES.items():
@@ -86,27 +85,22 @@ def load():
             raise SsfLibraryError(f"{path} does not export {name}") from exc
         fn.restype = res
         fn.argtypes = args
-    _lib = lib
+    _loaded[path] = lib
     return lib
 
 
-def unload_for_tests():
-    global _lib
-    _lib = None
+def last_error(lib=None):
+    return ((lib or load()).ssf_last_error() or b"").decode("utf8", "replace")
 
 
-def last_error():
-    return (load().ssf_last_error() or b"").decode("utf8", "replace")
+def launch_count(lib=None):
+    return int((lib or load()).ssf_launch_count())
 
 
-def launch_count():
-    return int(load().ssf_launch_count())
-
-
-def call(name, *args):
+def call(name, *args, lib=None):
     """Calls ``name`` and raises SsfError on a negative status."""
-    fn = getattr(load(), name)
-    rc = fn(*args)
+    lib = lib or load()
+    rc = getattr(lib, name)(*args)
     if rc != 0:
-        raise SsfError(name, rc, last_error())
+        raise SsfError(name, rc, last_error(lib))
     return rc

@@ -26,9 +26,12 @@ class Engine:
     """Thin, stateless-per-call wrapper; ``device`` is a CUDA device (or "cpu" only when the
     test emulator library is loaded through SSF_B200_LIBRARY)."""
 
-    def __init__(self, device=None):
-        _lib.load()
-        emulated = _lib.library_path() != _lib.LIB_PATH
+    def __init__(self, device=None, library=None):
+        path = library or _lib.library_path()
+        self._lib = _lib.load(path)
+        self._fit_status = None
+        self.timers = None
+        emulated = path != _lib.LIB_PATH
         if device is None:
             device = "cpu" if emulated else "cuda"
         self.device = torch.device(device)
@@ -38,14 +41,42 @@ class Engine:
             self.device = torch.device("cuda", torch.cuda.current_device())
 
     # ------------------------------------------------------------------ helpers
+    def _call(self, name, *args):
+        return _lib.call(name, *args, lib=self._lib)
+
+    def _timed_call(self, key, name, *args):
+        """Like _call, bracketed by CUDA events on the launching stream when ``self.timers`` is a
+        dict (bench.py: per-kernel durations measured live inside the timed region)."""
+        if self.timers is None or self.device.type != "cuda":
+            return self._call(name, *args)
+        start = torch.cuda.Event(enable_timing=True)
+        stop = torch.cuda.Event(enable_timing=True)
+        start.record()
+        rc = self._call(name, *args)
+        stop.record()
+        self.timers.setdefault(key, []).append((start, stop))
+        return rc
+
+    def timer_summary(self):
+        """{key: (launch groups, mean ms)} -- call after a synchronize."""
+        out = {}
+        for key, pairs in (self.timers or {}).items():
+            ms = [a.elapsed_time(b) for a, b in pairs]
+            out[key] = (len(ms), sum(ms) / max(len(ms), 1))
+        return out
+
+    def launch_count(self):
+        return _lib.launch_count(self._lib)
+
     def stream(self):
         if self.device.type == "cuda":
             return torch.cuda.current_stream(self.device).cuda_stream
         return None
 
     def tensor(self, array, dtype):
-        t = torch.as_tensor(np.ascontiguousarray(array), dtype=dtype)
-        return t.to(self.device).contiguous()
+        # always a fresh buffer: in-place kernels must never alias the caller's host array
+        t = torch.as_tensor(np.ascontiguousarray(array))
+        return t.to(device=self.device, dtype=dtype, copy=True).contiguous()
 
     def empty(self, shape, dtype):
         return torch.empty(shape, dtype=dtype, device=self.device)
@@ -76,7 +107,7 @@ class Engine:
         p = self.empty((npat, ndir, ndir), torch.float64)
         u = self.empty((npat, ndir, ndir), torch.float64)
         sv = self.empty((npat, ndir), torch.float64)
-        _lib.call("ssf_kl_decompose", _ptr(pp), ndir, _ptr(masks), npat, r0, beta, cut,
+        self._call("ssf_kl_decompose", _ptr(pp), ndir, _ptr(masks), npat, r0, beta, cut,
                   _ptr(c), _ptr(p), _ptr(u), _ptr(sv), self.stream())
         return c, p, u, sv
 
@@ -87,12 +118,12 @@ class Engine:
         self._check(resid, torch.float64, "resid")
         self._check(weights, torch.float32, "weights")
         masks = self.empty((nsys, 2), torch.int64)
-        _lib.call("ssf_kl_flag_outliers", _ptr(resid), _ptr(weights), ndir, nsys, float(nsigma),
+        self._call("ssf_kl_flag_outliers", _ptr(resid), _ptr(weights), ndir, nsys, float(nsigma),
                   _ptr(masks), self.stream())
         return masks
 
     def kl_fit_pass(self, phase, weights, pat, pp, mats, mode, order, station_order, white, resid,
-                    r0=R_0, beta=BETA, cut=PINV_CUT):
+                    r0=R_0, beta=BETA, cut=PINV_CUT, status=None):
         nsys, ndir = phase.shape
         c, p, u = mats
         for t, dt, nm in ((phase, torch.float64, "phase"), (weights, torch.float32, "weights"),
@@ -100,20 +131,21 @@ class Engine:
                           (station_order, torch.float64, "station_order"),
                           (white, torch.float64, "white"), (resid, torch.float64, "resid")):
             self._check(t, dt, nm)
-        status = self.zeros((1,), torch.int32)
-        _lib.call("ssf_kl_fit_pass", _ptr(phase), _ptr(weights), _ptr(pat), _ptr(pp), ndir, nsys,
-                  _ptr(c), _ptr(p), _ptr(u), r0, beta, cut, mode, _ptr(order), _ptr(station_order),
-                  _ptr(white), _ptr(resid), _ptr(status), self.stream())
-        if int(status.item()) != 0:
-            raise _lib.SsfError("ssf_kl_fit_pass", _lib_status_weights(), "a system has a weight in "
-                                "(0, pinv_cut]: outside the normal-equation path of this kernel")
+        if status is None:
+            status = self.zeros((1,), torch.int32)
+        self._call("ssf_kl_fit_pass", _ptr(phase), _ptr(weights), _ptr(pat), _ptr(pp), ndir, nsys,
+                   _ptr(c), _ptr(p), _ptr(u), r0, beta, cut, mode, _ptr(order), _ptr(station_order),
+                   _ptr(white), _ptr(resid), _ptr(status), self.stream())
+        return status
 
     def kl_fit(self, phase, weights, station_order, pp, niter=2, nsigma=5.0, adjust_order=True,
-               r0=R_0, beta=BETA, cut=PINV_CUT, pattern_budget_bytes=4 << 30):
+               r0=R_0, beta=BETA, cut=PINV_CUT, pattern_budget_bytes=4 << 30, check=True):
         """The iteration structure of _process_station (stationscreen.py:658-779) for a batch
         of independent systems.  phase [nsys, ndir] f64 (already referenced), weights
         [nsys, ndir] f32 (modified in place by the flagging), station_order [nsys] f64.
-        Returns (white, resid, order) with shapes [nsys, ndir], [nsys, ndir], [nsys]."""
+        Returns (white, resid, order) with shapes [nsys, ndir], [nsys, ndir], [nsys].
+        ``check=False`` defers the convergence / weight-range checks: the caller must call
+        ``check_fit_status()`` later (avoids a host sync per slab in streaming loops)."""
         nsys, ndir = phase.shape
         white = self.zeros((nsys, ndir), torch.float64)
         resid = self.zeros((nsys, ndir), torch.float64)
@@ -121,6 +153,8 @@ class Engine:
         full = torch.tensor([self.full_mask(ndir)], dtype=torch.int64, device=self.device)
         per_pattern = 3 * ndir * ndir * 8 + ndir * 8
         chunk = max(1024, pattern_budget_bytes // per_pattern)
+        if self._fit_status is None:
+            self._fit_status = self.zeros((2,), torch.int32)     # [weights out of range, no convergence]
         for s0 in range(0, nsys, chunk):
             s1 = min(nsys, s0 + chunk)
             ph, w = phase[s0:s1], weights[s0:s1]
@@ -135,17 +169,30 @@ class Engine:
                 patterns = torch.cat([full, uniq]).contiguous()
                 pat = (inv + 1).to(torch.int32).contiguous()
                 c, p, u, sv = self.kl_decompose(pp, patterns, r0, beta, cut)
-                if bool(torch.isnan(sv).any()):
-                    raise _lib.SsfError("ssf_kl_decompose", -3, "Jacobi eigen-solver did not converge")
+                self._fit_status[1:2] += torch.isnan(sv).any().to(torch.int32)
                 mode = 1 if (it > 0 and adjust_order) else 0
-                self.kl_fit_pass(ph, w, pat, pp, (c, p, u), mode, od, so, wh, rs, r0, beta, cut)
+                self.kl_fit_pass(ph, w, pat, pp, (c, p, u), mode, od, so, wh, rs, r0, beta, cut,
+                                 status=self._fit_status[0:1])
+        if check:
+            self.check_fit_status()
         return white, resid, order
+
+    def check_fit_status(self):
+        if self._fit_status is None:
+            return
+        bad_w, no_conv = (int(v) for v in self._fit_status.tolist())
+        self._fit_status.zero_()
+        if no_conv:
+            raise _lib.SsfError("ssf_kl_decompose", -3, "Jacobi eigen-solver did not converge")
+        if bad_w:
+            raise _lib.SsfError("ssf_kl_fit_pass", -4, "a system has a weight in (0, pinv_cut]: "
+                                "outside the normal-equation path of this kernel")
 
     # ------------------------------------------------------------------ KL evaluation
     def kl_basis(self, x_coord, y_coord, pp, pinv_c, r0=R_0, beta=BETA):
         nx, ny, ndir = x_coord.numel(), y_coord.numel(), pp.shape[0]
         bt = self.empty((ndir, ny * nx), torch.float32)
-        _lib.call("ssf_kl_basis", _ptr(x_coord), _ptr(y_coord), nx, ny, _ptr(pp), ndir,
+        self._call("ssf_kl_basis", _ptr(x_coord), _ptr(y_coord), nx, ny, _ptr(pp), ndir,
                   _ptr(pinv_c), r0, beta, _ptr(bt), self.stream())
         return bt
 
@@ -154,7 +201,7 @@ class Engine:
         self._check(white, torch.float64, "white")
         ldg = (ndir + 3) // 4 * 4
         g = out if out is not None else self.empty((ncol, ldg), torch.float32)
-        _lib.call("ssf_kl_coeffs", _ptr(white), ncol, ndir, _ptr(c), _ptr(g), ldg, self.stream())
+        self._call("ssf_kl_coeffs", _ptr(white), ncol, ndir, _ptr(c), _ptr(g), ldg, self.stream())
         return g
 
     def kl_eval(self, bt, g, ndir, slab, variant=-1):
@@ -163,14 +210,14 @@ class Engine:
         self._check(slab, torch.float32, "slab")
         if slab.numel() != ncol * 4 * npix:
             raise ValueError("slab has the wrong size")
-        _lib.call("ssf_kl_eval", _ptr(bt), _ptr(g), ndir, ldg, npix, ncol, _ptr(slab), variant,
+        self._timed_call("kl_eval", "ssf_kl_eval", _ptr(bt), _ptr(g), ndir, ldg, npix, ncol, _ptr(slab), variant,
                   self.stream())
         return slab
 
     # ------------------------------------------------------------------ Voronoi
     def voronoi_assign(self, px, py, nx, ny):
         tmpl = self.empty((ny, nx), torch.int32)
-        _lib.call("ssf_voronoi_assign", _ptr(px), _ptr(py), px.numel(), nx, ny, _ptr(tmpl),
+        self._call("ssf_voronoi_assign", _ptr(px), _ptr(py), px.numel(), nx, ny, _ptr(tmpl),
                   self.stream())
         return tmpl
 
@@ -178,7 +225,7 @@ class Engine:
         ncol, ndir = phase.shape
         self._check(phase, torch.float64, "phase")
         lut = out if out is not None else self.empty((ncol, ndir, 2), torch.float32)
-        _lib.call("ssf_voronoi_lut", _ptr(phase), _ptr(amp), ncol, ndir, _ptr(lut), self.stream())
+        self._call("ssf_voronoi_lut", _ptr(phase), _ptr(amp), ncol, ndir, _ptr(lut), self.stream())
         return lut
 
     def voronoi_fill(self, tmpl, lut, slab, fix_nan=True):
@@ -188,20 +235,20 @@ class Engine:
         self._check(slab, torch.float32, "slab")
         if slab.numel() != ncol * 4 * npix:
             raise ValueError("slab has the wrong size")
-        _lib.call("ssf_voronoi_fill", _ptr(tmpl), _ptr(lut), ndir, npix, ncol, _ptr(slab),
+        self._timed_call("voronoi_fill", "ssf_voronoi_fill", _ptr(tmpl), _ptr(lut), ndir, npix, ncol, _ptr(slab),
                   1 if fix_nan else 0, self.stream())
         return slab
 
     def voronoi_indicators(self, tmpl, ndir):
         npix = tmpl.numel()
         ind = self.empty((ndir,) + tuple(tmpl.shape), torch.float32)
-        _lib.call("ssf_voronoi_indicators", _ptr(tmpl), ndir, npix, _ptr(ind), self.stream())
+        self._call("ssf_voronoi_indicators", _ptr(tmpl), ndir, npix, _ptr(ind), self.stream())
         return ind
 
     def voronoi_contract(self, smoothed_ind, lut, slab, variant=-1):
         ncol, ndir, _ = lut.shape
         npix = smoothed_ind.numel() // ndir
-        _lib.call("ssf_voronoi_contract", _ptr(smoothed_ind), _ptr(lut), ndir, npix, ncol,
+        self._timed_call("voronoi_contract", "ssf_voronoi_contract", _ptr(smoothed_ind), _ptr(lut), ndir, npix, ncol,
                   _ptr(slab), variant, self.stream())
         return slab
 
@@ -212,20 +259,18 @@ class Engine:
         nimg = images.numel() // (ny * nx)
         if scratch is None:
             scratch = torch.empty_like(images)
-        _lib.call("ssf_gauss_smooth", _ptr(images), nimg, ny, nx, float(sigma), _ptr(scratch),
+        self._timed_call("gauss_smooth", "ssf_gauss_smooth", _ptr(images), nimg, ny, nx, float(sigma), _ptr(scratch),
                   self.stream())
         return images
 
     def nan_fix(self, slab, ncol, npix):
-        _lib.call("ssf_nan_fix", _ptr(slab), ncol, npix, self.stream())
+        self._call("ssf_nan_fix", _ptr(slab), ncol, npix, self.stream())
         return slab
 
 
     def bswap32(self, t):
         """In place: float32 little-endian -> big-endian (FITS storage order)."""
-        _lib.call("ssf_bswap32", _ptr(t), t.numel(), self.stream())
+        self._call("ssf_bswap32", _ptr(t), t.numel(), self.stream())
         return t
 
 
-def _lib_status_weights():
-    return -4

@@ -63,55 +63,40 @@ class KLScreen(Screen):
         self._basis = None
         self._basis_key = None
         self._c_full = None
+        self._pp_dev = None
+        self._so_dev = None
+        self.ref_ind = None
+        self.station_order = None
         self._pinv_full = None
 
     # ------------------------------------------------------------------ fit
-    def fit(self):
-        """kl_screen.py:61-155 + stationscreen.run (phase type)."""
-        if not self.phase_only:
-            raise NotImplementedError("amplitude ('gain') soltabs are not supported by this engine yet")
-        sol = self._load_solutions(self.input_phase_soltab_name)
-        if sol.val.ndim != 4:
-            raise NotImplementedError("phase soltabs with a pol axis are not supported yet")
+    def setup(self, sol, antenna_weight_sums=None):
+        """Once-per-run part of stationscreen.run (stationscreen.py:967-1053): reference
+        station, per-station orders, pierce points, and the decomposition of the full
+        structure matrix.  ``antenna_weight_sums`` lets a multi-GPU caller pass the
+        all-reduced per-antenna weight sums (the reference-station choice is global over
+        time, processing_utils.py:560-572)."""
         eng = self.engine
-        n_t, n_f, n_a, n_d = sol.val.shape
+        n_d = len(sol.dir)
         if n_d > 112:
             raise ValueError(f"{n_d} directions exceed the engine limit of 112")
-        ref_ind = reference_station(sol.weight, 10)                       # kl_screen.py:93
+        if antenna_weight_sums is None:
+            self.ref_ind = reference_station(sol.weight, 10)              # kl_screen.py:93
+        else:
+            sums = np.asarray(antenna_weight_sums, float)[:10]
+            self.ref_ind = int(np.nonzero(sums == sums.max())[0][0])
         screen_order = min(20, n_d - 1)                                   # kl_screen.py:101
-        st_order = station_orders(sol.station_positions, ref_ind, screen_order)
-
+        self.station_order = station_orders(sol.station_positions, self.ref_ind, screen_order)
         # pierce points: TAN-projected float32 source table (stationscreen.py:99-108)
         src = np.asarray(sol.source_positions, np.float32)
         ra_deg, dec_deg = np.rad2deg(src[:, 0]), np.rad2deg(src[:, 1])
         px, py, self.mid_ra, self.mid_dec = wcs.refined_screen_xy(ra_deg, dec_deg)
         self.piercepoints = np.column_stack([px, py, np.zeros(n_d)])
-        pp = eng.tensor(self.piercepoints[:, :2], torch.float64)
-
-        val = eng.tensor(sol.val, torch.float64)
-        weight = eng.tensor(sol.weight, torch.float32)
-        if ref_ind != -1:                                                 # stationscreen.py:994-997
-            val = val - val[:, :, ref_ind:ref_ind + 1, :]
-        # stations skipped by _process_single_freq (stationscreen.py:818-825)
-        skip = torch.isnan(val).all(dim=3).all(dim=0) | (weight == 0).all(dim=3).all(dim=0)  # [f, a]
-        skip[:, ref_ind] = True
-        work_w = torch.where(skip[None, :, :, None], torch.zeros_like(weight), weight).contiguous()
-        so = torch.tensor(st_order, dtype=torch.float64, device=eng.device)
-        so = so[None, None, :].expand(n_t, n_f, n_a).reshape(-1).contiguous()
-        white, resid, order = eng.kl_fit(val.reshape(-1, n_d).contiguous(), work_w.view(-1, n_d),
-                                         so, pp, niter=2, nsigma=5.0, adjust_order=True,
-                                         r0=self.r_0, beta=self.beta_val, cut=PINV_CUT)
-        order = order.view(n_t, n_f, n_a)
-        order = torch.where(skip[None], torch.zeros_like(order), order)
-        self._dev_vals = white.view(n_t, n_f, n_a, n_d)
-        self.vals_ph = self._dev_vals.cpu().numpy()
-        self.residuals = resid.view(n_t, n_f, n_a, n_d).cpu().numpy()
-        self.screen_order = order.cpu().numpy()
-        self.weights_out = torch.where(skip[None, :, :, None], weight, work_w).cpu().numpy()
+        self._pp_dev = eng.tensor(self.piercepoints[:, :2], torch.float64)
         full = torch.tensor([eng.full_mask(n_d)], dtype=torch.int64, device=eng.device)
-        c, pinv, _, _ = eng.kl_decompose(pp, full, self.r_0, self.beta_val, PINV_CUT)
+        c, pinv, _, _ = eng.kl_decompose(self._pp_dev, full, self.r_0, self.beta_val, PINV_CUT)
         self._c_full, self._pinv_full = c[0].contiguous(), pinv[0].contiguous()
-        self._pp_dev = pp
+        self._so_dev = torch.tensor(self.station_order, dtype=torch.float64, device=eng.device)
         self.times_ph = sol.time
         self.freqs_ph = sol.freq
         self.source_names = sol.dir
@@ -120,6 +105,45 @@ class KLScreen(Screen):
         self.station_names = sol.ant
         self.station_dict = sol.station_dict
         self.station_positions = sol.station_positions
+
+    def fit_device(self, val, weight, check=True):
+        """The per-system part of stationscreen.run for a device slab val [t, f, a, d] f64 /
+        weight [t, f, a, d] f32 (any number of time slots).  Returns device tensors
+        (white [t,f,a,d], resid [t,f,a,d], order [t,f,a], weights_out [t,f,a,d])."""
+        eng = self.engine
+        n_t, n_f, n_a, n_d = val.shape
+        ref_ind = self.ref_ind
+        if ref_ind != -1:                                                 # stationscreen.py:994-997
+            val = val - val[:, :, ref_ind:ref_ind + 1, :]
+        # stations skipped by _process_single_freq (stationscreen.py:818-825)
+        skip = torch.isnan(val).all(dim=3).all(dim=0) | (weight == 0).all(dim=3).all(dim=0)  # [f, a]
+        skip[:, ref_ind] = True
+        work_w = torch.where(skip[None, :, :, None], torch.zeros_like(weight), weight).contiguous()
+        so = self._so_dev[None, None, :].expand(n_t, n_f, n_a).reshape(-1).contiguous()
+        white, resid, order = eng.kl_fit(val.reshape(-1, n_d).contiguous(), work_w.view(-1, n_d),
+                                         so, self._pp_dev, niter=2, nsigma=5.0, adjust_order=True,
+                                         r0=self.r_0, beta=self.beta_val, cut=PINV_CUT, check=check)
+        order = order.view(n_t, n_f, n_a)
+        order = torch.where(skip[None], torch.zeros_like(order), order)
+        weights_out = torch.where(skip[None, :, :, None], weight, work_w)
+        return white.view(n_t, n_f, n_a, n_d), resid.view(n_t, n_f, n_a, n_d), order, weights_out
+
+    def fit(self):
+        """kl_screen.py:61-155 + stationscreen.run (phase type)."""
+        if not self.phase_only:
+            raise NotImplementedError("amplitude ('gain') soltabs are not supported by this engine yet")
+        sol = self._load_solutions(self.input_phase_soltab_name)
+        if sol.val.ndim != 4:
+            raise NotImplementedError("phase soltabs with a pol axis are not supported yet")
+        eng = self.engine
+        self.setup(sol)
+        white, resid, order, weights_out = self.fit_device(eng.tensor(sol.val, torch.float64),
+                                                           eng.tensor(sol.weight, torch.float32))
+        self._dev_vals = white
+        self.vals_ph = white.cpu().numpy()
+        self.residuals = resid.cpu().numpy()
+        self.screen_order = order.cpu().numpy()
+        self.weights_out = weights_out.cpu().numpy()
 
     # ------------------------------------------------------------------ evaluation
     def _prepare(self, cellsize_deg, out_dir):

@@ -1,0 +1,188 @@
+"""
+Parity checks shared by the emulated (``not gpu``) and the real (``gpu``) test modules: each
+takes an ``Engine`` and compares the C-ABI kernels with ``oracle.port`` on seeded inputs.
+
+Tolerances (stated once, used everywhere):
+  * template indices, Voronoi fill, NaN fix, byte swap, flags, orders: BIT-EXACT
+  * KL fit (FP64): 1e-9 absolute on white / residual (rad)
+  * KL screens: 1e-5 absolute on the phase-derived planes cos/sin (north_star: 1e-5 on phase)
+  * Gaussian smoothing: 1e-6 absolute (float32 accumulation vs scipy's float64 line buffer)
+"""
+import numpy as np
+import torch
+
+from oracle.port import klfit, screens, wcs as owcs
+
+TOL_FIT = 1e-9
+TOL_KL = 1e-5
+TOL_SMOOTH = 1e-6
+
+
+def make_directions(rng, n_d, spread=2.0):
+    return np.column_stack([np.deg2rad(126.23 + rng.uniform(-spread, spread, n_d) / np.cos(np.deg2rad(64.5))),
+                            np.deg2rad(64.5 + rng.uniform(-spread, spread, n_d))]).astype(np.float32)
+
+
+def mask_of(bits):
+    m = sum(1 << int(b) for b in bits)
+    lo, hi = m & (2 ** 64 - 1), m >> 64
+    return [lo - 2 ** 64 if lo >= 2 ** 63 else lo, hi - 2 ** 64 if hi >= 2 ** 63 else hi]
+
+
+def check_decompose(eng, n_d=9, seed=5):
+    rng = np.random.default_rng(seed)
+    pp, _, _ = klfit.piercepoints(make_directions(rng, n_d))
+    subsets = [list(range(n_d)), [i for i in range(n_d) if i not in (1, 4)], [0, 2, n_d - 1]]
+    masks = torch.tensor([mask_of(s) for s in subsets], dtype=torch.int64, device=eng.device)
+    c, p, u, sv = eng.kl_decompose(eng.tensor(pp[:, :2], torch.float64), masks)
+    for k, sub in enumerate(subsets):
+        n = len(sub)
+        c_o, p_o, u_o = klfit.calculate_svd(pp[sub])
+        sv_o = np.linalg.svd(c_o, compute_uv=False)
+        # pow() differs by an ulp or two between libm, numpy's SIMD loops and CUDA
+        assert np.allclose(c[k, :n, :n].cpu().numpy(), c_o, rtol=1e-13, atol=0)
+        assert np.allclose(sv[k, :n].cpu().numpy(), sv_o, rtol=1e-12, atol=1e-10)
+        scale = np.abs(p_o).max()
+        assert np.abs(p[k, :n, :n].cpu().numpy() - p_o).max() < 1e-10 * max(scale, 1.0)
+        u_k = u[k, :n, :n].cpu().numpy()
+        signs = np.sign(np.sum(u_k * u_o, axis=0))
+        assert np.abs(u_k * signs - u_o).max() < 1e-9
+        assert np.all(c[k, n:, :].cpu().numpy() == 0) and np.all(p[k, :, n:].cpu().numpy() == 0)
+
+
+def synthetic_fit_case(seed, n_t, n_f, n_a, n_d, flag_fraction=0.03):
+    rng = np.random.default_rng(seed)
+    dirs = make_directions(rng, n_d)
+    pos = (np.array([3826896.2, 460979.5, 5064658.0]) + rng.normal(0, 2e4, (n_a, 3))).astype(np.float32)
+    pp, _, _ = klfit.piercepoints(dirs)
+    grad = rng.normal(0, 3e-4, (n_a, 2))
+    val = (grad[None, None, :, 0, None] * pp[None, None, None, :, 0]
+           + grad[None, None, :, 1, None] * pp[None, None, None, :, 1]
+           + rng.normal(0, 0.02, (n_t, n_f, n_a, n_d)))
+    val[rng.random(val.shape) < 0.01] += 2.5                 # outliers for the 5-sigma clip
+    weight = np.ones(val.shape, np.float32)
+    weight[rng.random(val.shape) < flag_fraction] = 0.0
+    weight[:, :, 0, :] = 1.0                                 # keep station 0 the reference
+    if n_a > 3:
+        weight[:, 0, 3, :] = 0.0                             # a fully flagged (freq, station)
+    return val, weight, dirs, pos
+
+
+def run_engine_fit(eng, val, weight, dirs, pos):
+    """The KLScreen.fit recipe on raw arrays (kept here so the check does not depend on files)."""
+    from ska_sdp_screen_fitting_b200.h5parm_io import Solutions
+    from ska_sdp_screen_fitting_b200.kl_screen import KLScreen
+
+    n_t, n_f, n_a, n_d = val.shape
+    sol = Solutions.from_arrays(val, weight, np.arange(n_t) * 8.0, 1e8 + np.arange(n_f) * 1e6,
+                                [f"a{i}" for i in range(n_a)], [f"d{i}" for i in range(n_d)], dirs, pos)
+    scr = KLScreen("t", None, None, 126.23, 64.5, 1.0, 1.0)
+    scr.solutions = sol
+    scr._engine = eng
+    scr.fit()
+    return scr
+
+
+def check_fit(eng, seed=7, n_t=3, n_f=2, n_a=5, n_d=40):
+    # a 5-sigma clip over directions can only trigger with >~30 directions: (n-1)/sqrt(n) > 5
+    val, weight, dirs, pos = synthetic_fit_case(seed, n_t, n_f, n_a, n_d)
+    scr = run_engine_fit(eng, val, weight, dirs, pos)
+    ref = klfit.get_reference_station(weight, 10)
+    out = klfit.run_phase(val, weight.copy(), dirs, pos, ref, min(20, n_d - 1))
+    assert np.abs(scr.piercepoints - out["pp"]).max() < 1e-9
+    assert np.abs(scr.vals_ph - out["screen"]).max() < TOL_FIT
+    assert np.abs(scr.residuals - out["resid"]).max() < TOL_FIT
+    assert np.array_equal(scr.screen_order, out["order"])
+    assert np.array_equal(scr.weights_out, out["weights"])
+    assert (out["weights"] != weight).any(), "the case must exercise outlier flagging"
+    return scr, out
+
+
+def check_kl_eval(eng, n=24, n_d=9, ncol=11, seed=3, variant=0):
+    rng = np.random.default_rng(seed)
+    pp, mid_ra, mid_dec = klfit.piercepoints(make_directions(rng, n_d, spread=1.5))
+    width, cell = (n - 0.5) * 0.1, 0.1
+    x, y = owcs.kl_grid_coords(126.23, 64.5, width, cell, mid_ra, mid_dec)
+    assert len(x) == n
+    c_o, p_o, _ = klfit.calculate_svd(pp)
+    fit = rng.normal(0, 0.7, (ncol, n_d))
+    white = fit @ p_o.T                                      # white = pinvC fit, as the fit produces
+    ppt = eng.tensor(pp[:, :2], torch.float64)
+    full = torch.tensor([mask_of(range(n_d))], dtype=torch.int64, device=eng.device)
+    c, p, _, _ = eng.kl_decompose(ppt, full)
+    bt = eng.kl_basis(eng.tensor(x, torch.float64), eng.tensor(y, torch.float64), ppt, p[0].contiguous())
+    g = eng.kl_coeffs(eng.tensor(white, torch.float64), c[0].contiguous())
+    slab = eng.empty((ncol, 4, n, n), torch.float32)
+    eng.kl_eval(bt, g, n_d, slab, variant)
+    want = screens.kl_make_matrix(x, y, pp, white)
+    got = slab.cpu().numpy()
+    assert np.abs(got - want).max() < TOL_KL
+    assert np.array_equal(got[:, 0], got[:, 2]) and np.array_equal(got[:, 1], got[:, 3])
+    return float(np.abs(got - want).max())
+
+
+def check_voronoi(eng, n=20, n_d=7, ncol=13, seed=9):
+    rng = np.random.default_rng(seed)
+    px = rng.uniform(-2, n + 2, n_d)
+    py = rng.uniform(-2, n + 2, n_d)
+    px[1], py[1] = 4.0, 6.0                                  # exact ties along x = 5 with site 2
+    px[2], py[2] = 6.0, 6.0
+    tmpl = eng.voronoi_assign(eng.tensor(px, torch.float64), eng.tensor(py, torch.float64), n, n)
+    want_t = screens.nearest_patch_template(px, py, n)
+    assert np.array_equal(tmpl.cpu().numpy(), want_t)
+    phases = rng.normal(0, 1.0, (ncol, n_d))
+    phases[ncol - 1, n_d - 1] = np.nan
+    lut = eng.voronoi_lut(eng.tensor(phases, torch.float64))
+    for fix in (False, True):
+        slab = eng.empty((ncol, 4, n, n), torch.float32)
+        eng.voronoi_fill(tmpl, lut, slab, fix)
+        want = screens.voronoi_make_matrix(want_t, phases).astype(np.float32)
+        if fix:
+            want = screens.nan_fix(want)
+        assert np.array_equal(slab.cpu().numpy(), want, equal_nan=True)
+    return tmpl, lut, want_t, phases
+
+
+def check_smooth(eng, shape=(5, 19, 37), sigmas=(0.5, 2.0, 5.0), seed=2):
+    rng = np.random.default_rng(seed)
+    img = rng.normal(size=shape).astype(np.float32)
+    worst = 0.0
+    for sigma in sigmas:
+        got = eng.gauss_smooth(eng.tensor(img, torch.float32), sigma).cpu().numpy()
+        want = screens.smooth_block(img, sigma)
+        worst = max(worst, float(np.abs(got - want).max()))
+        assert np.abs(got - want).max() < TOL_SMOOTH * max(1.0, np.abs(img).max())
+    return worst
+
+
+def check_smoothed_voronoi(eng, n=24, n_d=6, ncol=5, sigma=1.5, seed=4):
+    rng = np.random.default_rng(seed)
+    px, py = rng.uniform(0, n, n_d), rng.uniform(0, n, n_d)
+    want_t = screens.nearest_patch_template(px, py, n)
+    tmpl = eng.tensor(want_t, torch.int32)
+    phases = rng.normal(0, 1.0, (1, 1, ncol, n_d))
+    want = screens.voronoi_cube(phases, want_t, sigma)[0, 0]
+    lut = eng.voronoi_lut(eng.tensor(phases.reshape(ncol, n_d), torch.float64))
+    slab = eng.empty((ncol, 4, n, n), torch.float32)
+    eng.voronoi_fill(tmpl, lut, slab, False)
+    eng.gauss_smooth(slab, sigma)
+    eng.nan_fix(slab, ncol, n * n)
+    assert np.abs(slab.cpu().numpy() - want).max() < TOL_SMOOTH
+    ind = eng.gauss_smooth(eng.voronoi_indicators(tmpl, n_d), sigma)
+    slab2 = eng.empty((ncol, 4, n, n), torch.float32)
+    eng.voronoi_contract(ind, lut, slab2, 0)
+    assert np.abs(slab2.cpu().numpy() - want).max() < 2 * TOL_SMOOTH
+
+
+def check_bswap_nanfix(eng, seed=1):
+    rng = np.random.default_rng(seed)
+    for count in (1, 7, 4096 + 3):
+        a = rng.normal(size=count).astype(np.float32)
+        t = eng.tensor(a, torch.float32)
+        eng.bswap32(t)
+        assert np.array_equal(t.cpu().numpy().view(np.uint32), a.view(np.uint32).byteswap())
+    slab = rng.normal(size=(3, 4, 5, 5)).astype(np.float32)
+    slab[rng.random(slab.shape) < 0.2] = np.nan
+    t = eng.tensor(slab, torch.float32)
+    eng.nan_fix(t, 3, 25)
+    assert np.array_equal(t.cpu().numpy(), screens.nan_fix(slab.copy()))

@@ -1,0 +1,84 @@
+"""Kernel LOGIC checked without a GPU: the product's .cu sources compiled by g++ against the
+CUDA emulator (tests/emu) and compared with the oracle.  The same checks run on the real
+library in test_gpu_parity.py."""
+import numpy as np
+
+import parity_checks as pc
+
+
+def test_decompose(emu_engine):
+    pc.check_decompose(emu_engine)
+
+
+def test_fit_with_flags_and_outliers(emu_engine):
+    pc.check_fit(emu_engine)
+
+
+def test_fit_repo_data_subset_against_reference_golden(emu_engine, repo_solutions, golden_dir):
+    import os
+
+    gold = np.load(os.path.join(golden_dir, "kl_c2.npz"))
+    sol = repo_solutions
+    sel_f, sel_a = [0, 11], [0, 1, 30, 61]
+    val = sol.val[:, sel_f][:, :, sel_a]
+    wt = sol.weight[:, sel_f][:, :, sel_a]
+    pos = np.asarray(sol.station_positions)
+    # station orders depend on the distance to ALL stations (max distance): compute on the full set
+    from ska_sdp_screen_fitting_b200.kl_screen import station_orders
+    orders_full = station_orders(pos, 0, 6)
+    scr = pc.run_engine_fit(emu_engine, val, wt, np.asarray(sol.source_positions), pos[sel_a])
+    want = gold["screen"][:, sel_f][:, :, sel_a]
+    same_order = [i for i, a in enumerate(sel_a) if station_orders(pos[sel_a], 0, 6)[i] == orders_full[a]]
+    assert len(same_order) >= 2
+    for i in same_order:
+        assert np.abs(scr.vals_ph[:, :, i] - want[:, :, i]).max() < pc.TOL_FIT
+
+
+def test_kl_eval(emu_engine):
+    pc.check_kl_eval(emu_engine, n=12, ncol=9)
+    pc.check_kl_eval(emu_engine, n=11, n_d=5, ncol=3, seed=8)      # ragged: npix % 4 != 0
+
+
+def test_voronoi_assign_and_fill(emu_engine):
+    pc.check_voronoi(emu_engine)
+    pc.check_voronoi(emu_engine, n=9, n_d=3, ncol=2, seed=12)      # ragged
+
+
+def test_smoothing(emu_engine):
+    pc.check_smooth(emu_engine, shape=(3, 13, 21), sigmas=(0.5, 2.0, 3.0))
+
+
+def test_smoothed_voronoi_both_forms(emu_engine):
+    pc.check_smoothed_voronoi(emu_engine, n=16, ncol=3)
+
+
+def test_bswap_and_nanfix(emu_engine):
+    pc.check_bswap_nanfix(emu_engine)
+
+
+def test_host_entry_points(emu_engine, emu_library):
+    """ssf_voronoi_cube_host / ssf_kl_cube_host: HOST buffers in, HOST slab out."""
+    import ctypes
+
+    from oracle.port import klfit, screens, wcs as owcs
+    from ska_sdp_screen_fitting_b200 import _lib
+
+    lib = _lib.load(emu_library)
+    rng = np.random.default_rng(21)
+    n, n_d, ncol = 10, 5, 4
+    tmpl = screens.nearest_patch_template(rng.uniform(0, n, n_d), rng.uniform(0, n, n_d), n)
+    phases = rng.normal(size=(ncol, n_d))
+    out = np.zeros((ncol, 4, n, n), np.float32)
+    for sigma in (0.0, 1.0):
+        _lib.call("ssf_voronoi_cube_host", tmpl.ctypes.data, phases.ctypes.data, n_d, n, n, ncol,
+                  ctypes.c_double(sigma), out.ctypes.data, lib=lib)
+        want = screens.voronoi_cube(phases.reshape(1, 1, ncol, n_d), tmpl, sigma)[0, 0]
+        assert np.abs(out - want).max() < (pc.TOL_SMOOTH if sigma else 1e-30)
+    pp, mid_ra, mid_dec = klfit.piercepoints(pc.make_directions(rng, n_d, 1.0))
+    x, y = owcs.kl_grid_coords(126.23, 64.5, (n - 0.5) * 0.2, 0.2, mid_ra, mid_dec)
+    _, p_o, _ = klfit.calculate_svd(pp)
+    white = rng.normal(0, 0.5, (ncol, n_d)) @ p_o.T
+    pp2 = np.ascontiguousarray(pp[:, :2])
+    _lib.call("ssf_kl_cube_host", x.ctypes.data, y.ctypes.data, n, n, pp2.ctypes.data, n_d,
+              white.ctypes.data, ncol, 100.0, 5.0 / 3.0, 1e-3, out.ctypes.data, lib=lib)
+    assert np.abs(out - screens.kl_make_matrix(x, y, pp, white)).max() < pc.TOL_KL

@@ -1,0 +1,172 @@
+"""Parity of the CUDA path (libssf_b200.so on a real GPU, through the C ABI) with the oracle."""
+import os
+import shutil
+
+import numpy as np
+import pytest
+import torch
+
+import parity_checks as pc
+
+pytestmark = pytest.mark.gpu
+
+
+def test_decompose(gpu_engine):
+    pc.check_decompose(gpu_engine)
+    pc.check_decompose(gpu_engine, n_d=45, seed=6)
+    pc.check_decompose(gpu_engine, n_d=100, seed=7)
+
+
+def test_fit_with_flags_and_outliers(gpu_engine):
+    pc.check_fit(gpu_engine)
+    pc.check_fit(gpu_engine, seed=17, n_t=6, n_f=3, n_a=8, n_d=45)
+
+
+def test_fit_repo_data_against_reference_golden(gpu_engine, repo_solutions, golden_dir):
+    """BASELINE.json configs[1]: the whole repo data set, all 14 880 systems."""
+    gold = np.load(os.path.join(golden_dir, "kl_c2.npz"))
+    sol = repo_solutions
+    scr = pc.run_engine_fit(gpu_engine, sol.val, sol.weight, np.asarray(sol.source_positions),
+                            np.asarray(sol.station_positions))
+    assert np.abs(scr.piercepoints - gold["piercepoints"]).max() < 1e-9
+    assert np.abs(scr.vals_ph - gold["screen"]).max() < pc.TOL_FIT
+    assert np.abs(scr.residuals - gold["resid"]).max() < pc.TOL_FIT
+    assert np.array_equal(scr.screen_order, gold["order"])
+    assert np.array_equal(scr.weights_out, gold["screen_weights"])
+
+
+def test_kl_eval(gpu_engine):
+    pc.check_kl_eval(gpu_engine, n=12, ncol=9)
+    pc.check_kl_eval(gpu_engine, n=11, n_d=5, ncol=3, seed=8)       # ragged: npix % 4 != 0
+    pc.check_kl_eval(gpu_engine, n=64, n_d=45, ncol=70, seed=9)
+    pc.check_kl_eval(gpu_engine, n=48, n_d=100, ncol=33, seed=10)
+
+
+def test_voronoi_assign_and_fill(gpu_engine):
+    pc.check_voronoi(gpu_engine)
+    pc.check_voronoi(gpu_engine, n=9, n_d=3, ncol=2, seed=12)
+    pc.check_voronoi(gpu_engine, n=128, n_d=45, ncol=40, seed=13)
+
+
+def test_template_bit_exact_at_full_size(gpu_engine):
+    """1024 x 1024, 45 patches: every index equals the float64 CPU definition."""
+    from oracle.port import screens
+
+    rng = np.random.default_rng(4)
+    px, py = rng.uniform(100, 900, 45), rng.uniform(100, 900, 45)
+    tmpl = gpu_engine.voronoi_assign(gpu_engine.tensor(px, torch.float64),
+                                     gpu_engine.tensor(py, torch.float64), 1024, 1024)
+    assert np.array_equal(tmpl.cpu().numpy(), screens.nearest_patch_template(px, py, 1024))
+
+
+def test_smoothing(gpu_engine):
+    pc.check_smooth(gpu_engine)
+    pc.check_smooth(gpu_engine, shape=(3, 130, 257), sigmas=(0.5, 2.0, 5.0, 10.0), seed=5)
+
+
+def test_smoothed_voronoi_both_forms(gpu_engine):
+    pc.check_smoothed_voronoi(gpu_engine)
+    pc.check_smoothed_voronoi(gpu_engine, n=96, n_d=20, ncol=9, sigma=5.0, seed=6)
+
+
+def test_bswap_and_nanfix(gpu_engine):
+    pc.check_bswap_nanfix(gpu_engine)
+
+
+def test_full_size_properties(gpu_engine):
+    """BASELINE-size slab (512^2, 45 directions): size-independent properties instead of an
+    oracle run -- planes 0 == 2 and 1 == 3, cos^2 + sin^2 == 1, linearity of the phase in the
+    coefficients (a column with doubled white has doubled phase), no NaN."""
+    eng = gpu_engine
+    rng = np.random.default_rng(3)
+    from oracle.port import klfit
+    n, n_d, ncol = 512, 45, 32
+    pp, mid_ra, mid_dec = klfit.piercepoints(pc.make_directions(rng, n_d, 2.0))
+    from ska_sdp_screen_fitting_b200 import wcs
+    x, y = wcs.kl_grid(126.23, 64.5, (n - 0.5) * 0.01, 0.01, mid_ra, mid_dec)
+    ppt = eng.tensor(pp[:, :2], torch.float64)
+    full = torch.tensor([pc.mask_of(range(n_d))], dtype=torch.int64, device=eng.device)
+    c, p, _, _ = eng.kl_decompose(ppt, full)
+    fit = rng.normal(0, 0.3, (ncol, n_d))
+    fit[1] = 2.0 * fit[0]
+    white = eng.tensor(fit, torch.float64) @ p[0].T
+    bt = eng.kl_basis(eng.tensor(x, torch.float64), eng.tensor(y, torch.float64), ppt, p[0].contiguous())
+    g = eng.kl_coeffs(white.contiguous(), c[0].contiguous())
+    slab = eng.empty((ncol, 4, n, n), torch.float32)
+    eng.kl_eval(bt, g, n_d, slab, -1)
+    assert torch.equal(slab[:, 0], slab[:, 2]) and torch.equal(slab[:, 1], slab[:, 3])
+    assert not torch.isnan(slab).any()
+    assert float((slab[:, 0] ** 2 + slab[:, 1] ** 2 - 1).abs().max()) < 1e-5
+    ph0 = torch.atan2(slab[0, 1].double(), slab[0, 0].double())
+    ph1 = torch.atan2(slab[1, 1].double(), slab[1, 0].double())
+    d = torch.remainder(ph1 - 2 * ph0 + np.pi, 2 * np.pi) - np.pi
+    assert float(d.abs().max()) < 5e-5
+    # sampled pixels against the float64 oracle formula K(pix, :) . white
+    from oracle.port import screens
+    sel = rng.integers(0, n, (64, 2))
+    kmat = screens.kl_kernel_matrix(x[sel[:, 0]], y[sel[:, 1]], pp)       # [64, 64, d]
+    want = np.einsum("iid,cd->ci", kmat, white.cpu().numpy())
+    got_c = slab[:, 0].cpu().numpy()[:, sel[:, 1], sel[:, 0]]
+    got_s = slab[:, 1].cpu().numpy()[:, sel[:, 1], sel[:, 0]]
+    assert np.abs(got_c - np.cos(want)).max() < pc.TOL_KL
+    assert np.abs(got_s - np.sin(want)).max() < pc.TOL_KL
+
+
+def test_host_entry_points(gpu_engine):
+    import ctypes
+
+    from oracle.port import klfit, screens, wcs as owcs
+    from ska_sdp_screen_fitting_b200 import _lib
+
+    rng = np.random.default_rng(21)
+    n, n_d, ncol = 40, 9, 24
+    tmpl = screens.nearest_patch_template(rng.uniform(0, n, n_d), rng.uniform(0, n, n_d), n)
+    phases = rng.normal(size=(ncol, n_d))
+    out = np.zeros((ncol, 4, n, n), np.float32)
+    for sigma in (0.0, 1.0):
+        _lib.call("ssf_voronoi_cube_host", tmpl.ctypes.data, phases.ctypes.data, n_d, n, n, ncol,
+                  ctypes.c_double(sigma), out.ctypes.data)
+        want = screens.voronoi_cube(phases.reshape(1, 1, ncol, n_d), tmpl, sigma)[0, 0]
+        assert np.abs(out - want).max() < (pc.TOL_SMOOTH if sigma else 1e-30)
+    pp, mid_ra, mid_dec = klfit.piercepoints(pc.make_directions(rng, n_d, 1.0))
+    x, y = owcs.kl_grid_coords(126.23, 64.5, (n - 0.5) * 0.05, 0.05, mid_ra, mid_dec)
+    _, p_o, _ = klfit.calculate_svd(pp)
+    white = rng.normal(0, 0.5, (ncol, n_d)) @ p_o.T
+    pp2 = np.ascontiguousarray(pp[:, :2])
+    _lib.call("ssf_kl_cube_host", x.ctypes.data, y.ctypes.data, n, n, pp2.ctypes.data, n_d,
+              white.ctypes.data, ncol, 100.0, 5.0 / 3.0, 1e-3, out.ctypes.data)
+    assert np.abs(out - screens.kl_make_matrix(x, y, pp, white)).max() < pc.TOL_KL
+
+
+@pytest.mark.parametrize("screen_type", ["tessellated", "kl"])
+def test_make_aterm_image_repo_configs(gpu_engine, golden_dir, tmp_path, screen_type):
+    """BASELINE.json configs[0] / configs[1] through the public API, against the cubes the
+    reference's own code produced (tests/golden, oracle/make_golden.py) and the reference's
+    own test assertions (tests/test_fit_screens.py:101-128, :190-215)."""
+    from ska_sdp_screen_fitting_b200 import fits
+    from ska_sdp_screen_fitting_b200.make_aterm_images import make_aterm_image
+
+    for f in ("solutions.h5", "skymodel.txt"):
+        shutil.copy(os.path.join(golden_dir, f), tmp_path)
+    cwd = os.getcwd()
+    os.chdir(tmp_path)
+    try:
+        make_aterm_image("solutions.h5", soltabname="phase000", screen_type=screen_type,
+                         outroot=screen_type, bounds_deg=[124.565, 66.165, 127.895, 62.835],
+                         bounds_mid_deg=[126.23, 64.50], skymodel="skymodel.txt", solsetname="sol000",
+                         padding_fraction=0, cellsize_deg=0.2, smooth_deg=0.1, ncpu=0)
+        assert os.path.exists(f"{screen_type}_0.fits") and os.path.exists(f"{screen_type}.txt")
+        header, data = fits.read(f"{screen_type}_0.fits")
+    finally:
+        os.chdir(cwd)
+    assert data.shape == (20, 12, 62, 4, 17, 17)
+    assert header["CTYPE1"] == "RA---SIN" and header["CTYPE3"] == "MATRIX" and header["CTYPE6"] == "TIME"
+    if screen_type == "tessellated":
+        assert os.path.exists(tmp_path / "tessellated_template.fits")
+        gold = np.load(os.path.join(golden_dir, "voronoi_c1.npz"))
+        want, tol = gold["cube_smooth"], pc.TOL_SMOOTH
+    else:
+        gold = np.load(os.path.join(golden_dir, "kl_c2.npz"))
+        want, tol = gold["cube"], pc.TOL_KL
+    sub = np.asarray(data)[:, list(gold["sub_f"])][:, :, list(gold["sub_a"])]
+    assert np.abs(sub - want).max() < tol

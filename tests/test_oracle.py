@@ -1,0 +1,143 @@
+"""The oracle (oracle.port) against the golden fixtures produced by the REFERENCE's own code
+(oracle/make_golden.py under oracle.refshim), and -- when /root/reference is present --
+directly against the reference modules."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+from oracle import refshim
+from oracle.port import klfit, screens, template, wcs
+
+STATIONS = (1, 30, 61)
+FREQS = (0, 11)
+
+
+@pytest.fixture(scope="module")
+def kl_golden():
+    return np.load(os.path.join(GOLDEN, "kl_c2.npz"))
+
+
+@pytest.fixture(scope="module")
+def vor_golden():
+    return np.load(os.path.join(GOLDEN, "voronoi_c1.npz"))
+
+
+def test_piercepoints_and_singular_values(repo_solutions, kl_golden):
+    pp, mid_ra, mid_dec = klfit.piercepoints(np.asarray(repo_solutions.source_positions))
+    assert np.abs(pp - kl_golden["piercepoints"]).max() < 1e-9
+    assert abs(mid_ra - float(kl_golden["midra"])) < 1e-12
+    assert abs(mid_dec - float(kl_golden["middec"])) < 1e-12
+    c, _, _ = klfit.calculate_svd(pp)
+    sv = np.linalg.svd(c, compute_uv=False)
+    # SURVEY.md appendix B known answers
+    assert np.allclose(sv, [1544.925, 744.865, 522.017, 187.373, 63.341, 18.775, 8.554], atol=2e-3)
+
+
+def test_port_fit_matches_reference_golden(repo_solutions, kl_golden):
+    sol = repo_solutions
+    ref = klfit.get_reference_station(sol.weight, 10)
+    assert ref == 0
+    out = klfit.run_phase(sol.val, sol.weight, np.asarray(sol.source_positions),
+                          np.asarray(sol.station_positions), ref, min(20, 6),
+                          stations=STATIONS, freqs=FREQS)
+    for f in FREQS:
+        for a in STATIONS:
+            assert np.abs(out["screen"][:, f, a] - kl_golden["screen"][:, f, a]).max() < 1e-12
+            assert np.abs(out["resid"][:, f, a] - kl_golden["resid"][:, f, a]).max() < 1e-12
+            assert np.array_equal(out["order"][:, f, a], kl_golden["order"][:, f, a])
+
+
+def test_port_kl_cube_matches_reference_golden(kl_golden):
+    x, y = wcs.kl_grid_coords(126.23, 64.50, 3.33, 0.2, float(kl_golden["midra"]),
+                              float(kl_golden["middec"]))
+    cube = screens.kl_cube(kl_golden["screen"], kl_golden["piercepoints"], x, y,
+                           freqs=list(kl_golden["sub_f"]), stations=list(kl_golden["sub_a"]))
+    assert np.abs(cube - kl_golden["cube"]).max() < 1e-6
+
+
+def test_port_voronoi_cube_matches_reference_golden(repo_solutions, vor_golden):
+    ph = screens.voronoi_reference_phases(repo_solutions.val, 0)
+    args = dict(freqs=list(vor_golden["sub_f"]), stations=list(vor_golden["sub_a"]))
+    cube = screens.voronoi_cube(ph, vor_golden["template"], 0.0, **args)
+    assert np.array_equal(cube, vor_golden["cube_nosmooth"])
+    cube = screens.voronoi_cube(ph, vor_golden["template"], 0.5, **args)
+    assert np.array_equal(cube, vor_golden["cube_smooth"])
+
+
+def test_restated_smoothing_equals_scipy():
+    rng = np.random.default_rng(0)
+    block = rng.normal(size=(4, 23, 31)).astype(np.float32)
+    for sigma in (0.5, 2.0, 7.0):
+        a = screens.smooth_block(block, sigma)
+        b = screens.smooth_block_restated(block, sigma)
+        assert np.abs(a - b).max() < 2e-6
+
+
+def test_port_template_matches_reference_golden(vor_golden):
+    from ska_sdp_screen_fitting_b200 import skymodel
+
+    pos = skymodel.patch_positions(os.path.join(GOLDEN, "skymodel.txt"))
+    names = ["Patch_0", "Patch_1", "Patch_10", "Patch_2", "Patch_3", "Patch_4", "Patch_8"]
+    ra = [pos[n][0] for n in names]
+    de = [pos[n][1] for n in names]
+    tmpl, px, py = template.reference_template(ra, de, 126.23, 64.50, 3.33, 0.2)
+    assert np.array_equal(tmpl, vor_golden["template"])
+    # test-geometry patch pixels
+    assert np.allclose(px, [0.80, 13.64, 10.64, 15.07, 1.67, 5.05, 8.48], atol=6e-3)
+    assert np.allclose(py, [11.32, 11.16, 7.56, 0.40, 0.40, 2.76, 5.47], atol=6e-3)
+    nearest = screens.nearest_patch_template(px, py, 17)
+    # the PIL pipeline is not a pure nearest-patch map: a few boundary pixels differ
+    assert 0 < int((nearest != tmpl).sum()) <= 8
+
+
+def test_reference_test_assertions_hold_on_golden_cubes(repo_solutions, kl_golden, vor_golden):
+    """tests/test_fit_screens.py:101-128 / :190-215 (the reference's only pins), applied to
+    the golden cubes, two-sided."""
+    from ska_sdp_screen_fitting_b200 import skymodel
+
+    pos = skymodel.patch_positions(os.path.join(GOLDEN, "skymodel.txt"))
+    val = repo_solutions.val - repo_solutions.val[:, :, 0:1, :]
+    for cube, tol, key in ((vor_golden["cube_smooth"], 1e-4, vor_golden), (kl_golden["cube"], 1e-1, kl_golden)):
+        sub = val[:, list(key["sub_f"])][:, :, list(key["sub_a"])]
+        for d, name in enumerate(repo_solutions.dir):
+            ra, de = pos[name.strip("[]")]
+            x, y = wcs.voronoi_patch_pixels(ra, de, 126.23, 64.50, 17, 0.2)
+            col, row = int(round(float(x))), int(round(float(y)))
+            if not (0 <= col < 17 and 0 <= row < 17):
+                continue
+            assert np.abs(cube[:, :, :, 0, row, col] - np.cos(sub[..., d])).max() < tol
+            assert np.abs(cube[:, :, :, 1, row, col] - np.sin(sub[..., d])).max() < tol
+            assert np.array_equal(cube[:, :, :, 0], cube[:, :, :, 2])
+
+
+@pytest.mark.skipif(not refshim.available(), reason="reference tree not mounted")
+def test_port_against_the_reference_modules_directly(repo_solutions):
+    """Pins oracle.port on a seeded synthetic case with flags, against the reference's own
+    _process_station / calculate_kl_screen run under the shim."""
+    mods = refshim.install()
+    ss = mods["stationscreen"]
+    rng = np.random.default_rng(11)
+    n_d, n_t = 9, 6
+    dirs = np.column_stack([np.deg2rad(126.23 + rng.uniform(-2, 2, n_d)),
+                            np.deg2rad(64.5 + rng.uniform(-1.5, 1.5, n_d))]).astype(np.float32)
+    pp_ref, _, _ = ss._calculate_piercepoints(np.zeros((1, 3)), dirs)
+    pp, _, _ = klfit.piercepoints(dirs)
+    assert np.abs(pp_ref - pp).max() < 1e-9
+    full_ref = ss._calculate_svd(pp_ref, 100, 5.0 / 3.0, n_d)
+    ss.FULL_MATRICES = full_ref
+    phase = rng.normal(0, 0.5, (n_d, n_t))
+    phase[3, 2] += 2.5                                      # an outlier to be flagged
+    weights = np.ones((n_d, n_t), np.float32)
+    weights[1, 0] = 0.0
+    weights[[2, 5], 4] = 0.0
+    names = np.array([f"d{i}" for i in range(n_d)])
+    scr_r, w_r, res_r, ord_r = ss._process_station(
+        phase.copy(), pp_ref, np.full(n_t, 5.0), weights.copy(), "phase", 2, 5.0, True, names,
+        full_ref, 5.0 / 3.0, 100)
+    scr_p, w_p, res_p, ord_p = klfit.process_station(
+        phase.copy(), pp, np.full(n_t, 5.0), weights.copy(), klfit.calculate_svd(pp))
+    assert np.abs(scr_r - scr_p).max() < 1e-10
+    assert np.abs(res_r - res_p).max() < 1e-10
+    assert np.array_equal(w_r, w_p) and np.array_equal(ord_r, ord_p)
