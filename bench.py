@@ -176,7 +176,9 @@ def run_ours(args):
     eng = Engine(device=f"cuda:{local}")
     slots = args.slots or auto_slots(args.workload)
     n_steps = args.warmup + args.steps
-    case = build_case(args, rank, slots * n_steps)
+    # one slab more than is evaluated: the pipelined KL path fits slab k+1 while it evaluates
+    # slab k, so the K timed steps contain exactly K slab fits and K slab evaluations
+    case = build_case(args, rank, slots * (n_steps + 1))
     sol = case.solutions
     n_t, n_f, n_a, n_d = sol.val.shape
     n = case.n_pix
@@ -194,10 +196,13 @@ def run_ours(args):
     kl, vo = make_screens(case, eng, args.variant, sums.cpu().numpy())
     ring = [eng.empty((cols, 4, n, n), torch.float32) for _ in range(2)]
 
+    kl_stream = kl.stream_slabs(val_dev, wt_dev, slots, ring, case.cellsize_deg)
+
     def kl_step(i):
-        t0 = i * slots
-        white, _, _, _ = kl.fit_device(val_dev[t0:t0 + slots], wt_dev[t0:t0 + slots], check=False)
-        kl._fill_columns(white.view(-1, n_d), ring[i % 2], case.cellsize_deg, None, 0.0, True)
+        # fit of slab i+1 (side stream) overlaps the evaluation of slab i; every timed step
+        # still contains exactly one slab fit and one slab evaluation
+        k, _ = next(kl_stream)
+        assert k == i
 
     def vo_step(i):
         t0 = i * slots

@@ -159,6 +159,7 @@ class Engine:
             s1 = min(nsys, s0 + chunk)
             ph, w = phase[s0:s1], weights[s0:s1]
             wh, rs, od, so = white[s0:s1], resid[s0:s1], order[s0:s1], station_order[s0:s1]
+            patterns, mats = None, None
             for it in range(niter):
                 masks = self.kl_flag_outliers(rs, w, nsigma if it > 0 else math.inf)
                 if it > 0 and not adjust_order:
@@ -166,12 +167,31 @@ class Engine:
                     # without order adjustment nothing is refitted (stationscreen.py:694-701)
                     continue
                 uniq, inv = torch.unique(masks, dim=0, return_inverse=True)
-                patterns = torch.cat([full, uniq]).contiguous()
-                pat = (inv + 1).to(torch.int32).contiguous()
-                c, p, u, sv = self.kl_decompose(pp, patterns, r0, beta, cut)
-                self._fit_status[1:2] += torch.isnan(sv).any().to(torch.int32)
+                if patterns is None:
+                    patterns = torch.cat([full, uniq]).contiguous()       # pattern 0 = all directions
+                    pat = (inv + 1).to(torch.int32).contiguous()
+                    c, p, u, sv = self.kl_decompose(pp, patterns, r0, beta, cut)
+                    mats = (c, p, u)
+                    self._fit_status[1:2] += torch.isnan(sv).any().to(torch.int32)
+                else:
+                    # later iterations differ from the previous one only where outliers were
+                    # flagged: decompose just the patterns that have not been seen yet
+                    n_old = patterns.shape[0]
+                    union, where = torch.unique(torch.cat([patterns, uniq]), dim=0, return_inverse=True)
+                    seen = torch.zeros(union.shape[0], dtype=torch.bool, device=self.device)
+                    seen[where[:n_old]] = True
+                    fresh = union[~seen].contiguous()
+                    slot = torch.empty(union.shape[0], dtype=torch.int64, device=self.device)
+                    slot[where[:n_old]] = torch.arange(n_old, device=self.device)
+                    slot[~seen] = n_old + torch.arange(fresh.shape[0], device=self.device)
+                    pat = slot[where[n_old:]][inv].to(torch.int32).contiguous()
+                    if fresh.shape[0]:
+                        c, p, u, sv = self.kl_decompose(pp, fresh, r0, beta, cut)
+                        self._fit_status[1:2] += torch.isnan(sv).any().to(torch.int32)
+                        mats = tuple(torch.cat([a, b]) for a, b in zip(mats, (c, p, u)))
+                        patterns = torch.cat([patterns, fresh])
                 mode = 1 if (it > 0 and adjust_order) else 0
-                self.kl_fit_pass(ph, w, pat, pp, (c, p, u), mode, od, so, wh, rs, r0, beta, cut,
+                self.kl_fit_pass(ph, w, pat, pp, mats, mode, od, so, wh, rs, r0, beta, cut,
                                  status=self._fit_status[0:1])
         if check:
             self.check_fit_status()

@@ -68,6 +68,7 @@ class KLScreen(Screen):
         self.ref_ind = None
         self.station_order = None
         self._pinv_full = None
+        self._fit_stream = None
 
     # ------------------------------------------------------------------ fit
     def setup(self, sol, antenna_weight_sums=None):
@@ -127,6 +128,49 @@ class KLScreen(Screen):
         order = torch.where(skip[None], torch.zeros_like(order), order)
         weights_out = torch.where(skip[None, :, :, None], weight, work_w)
         return white.view(n_t, n_f, n_a, n_d), resid.view(n_t, n_f, n_a, n_d), order, weights_out
+
+    def stream_slabs(self, val_dev, wt_dev, slots, ring, cellsize_deg, first=0, count=None):
+        """Streaming form of fit + evaluation for slab-at-a-time processing: yields
+        ``(k, slab)`` for k = first, first+1, ... where slab = ring[k % len(ring)] holds the
+        cube of time slots [k*slots, (k+1)*slots).  The FP64 fit of slab k+1 runs on a side
+        stream while the evaluation kernel of slab k writes the cube (the fit is latency-
+        bound and uses a fraction of the SMs; the evaluation is HBM-bound)."""
+        eng = self.engine
+        n_d = val_dev.shape[-1]
+        total = val_dev.shape[0] // slots
+        last = total if count is None else min(total, first + count)
+        if eng.device.type != "cuda":
+            for k in range(first, last):
+                white = self.fit_device(val_dev[k * slots:(k + 1) * slots],
+                                        wt_dev[k * slots:(k + 1) * slots], check=False)[0]
+                slab = ring[k % len(ring)]
+                self._fill_columns(white.view(-1, n_d), slab, cellsize_deg, None, 0.0, True)
+                yield k, slab
+            return
+        main = torch.cuda.current_stream(eng.device)
+        if self._fit_stream is None:
+            self._fit_stream = torch.cuda.Stream(eng.device)
+        side = self._fit_stream
+
+        side.wait_stream(main)                           # inputs / setup are ready
+
+        def launch_fit(k):
+            with torch.cuda.stream(side):
+                white = self.fit_device(val_dev[k * slots:(k + 1) * slots],
+                                        wt_dev[k * slots:(k + 1) * slots], check=False)[0]
+                done = torch.cuda.Event()
+                done.record(side)
+            white.record_stream(main)
+            return white, done
+
+        nxt = launch_fit(first) if first < last else None
+        for k in range(first, last):
+            white, done = nxt
+            nxt = launch_fit(k + 1) if k + 1 < last else None
+            main.wait_event(done)
+            slab = ring[k % len(ring)]
+            self._fill_columns(white.view(-1, n_d), slab, cellsize_deg, None, 0.0, True)
+            yield k, slab
 
     def fit(self):
         """kl_screen.py:61-155 + stationscreen.run (phase type)."""

@@ -97,6 +97,9 @@ static inline uint32_t __byte_perm(uint32_t a, uint32_t b, uint32_t sel) {
   for (int i = 0; i < 4; ++i) r |= (uint32_t)((v >> (8 * ((sel >> (4 * i)) & 7))) & 0xff) << (8 * i);
   return r;
 }
+// glibc declares __sinf/__cosf itself: map the CUDA intrinsics with macros (after <math.h>)
+#define __sinf(x) sinf(x)
+#define __cosf(x) cosf(x)
 static inline int __popcll(unsigned long long v) { return __builtin_popcountll(v); }
 
 // ---- the slice of the runtime API the library uses ---------------------------------------

@@ -39,6 +39,13 @@ def test_kl_eval(emu_engine):
     pc.check_kl_eval(emu_engine, n=11, n_d=5, ncol=3, seed=8)      # ragged: npix % 4 != 0
 
 
+def test_kl_eval_tiled_kernel(emu_engine):
+    """Large enough (>= 1024 pixels, >= 4 columns) to take the shared-memory tiled kernel:
+    4 pixels/thread (ndir <= 52) and 2 pixels/thread (ndir > 52) variants, ragged column tiles."""
+    pc.check_kl_eval(emu_engine, n=32, n_d=9, ncol=21, seed=4)
+    pc.check_kl_eval(emu_engine, n=36, n_d=60, ncol=19, seed=5)
+
+
 def test_voronoi_assign_and_fill(emu_engine):
     pc.check_voronoi(emu_engine)
     pc.check_voronoi(emu_engine, n=9, n_d=3, ncol=2, seed=12)      # ragged
@@ -50,6 +57,8 @@ def test_smoothing(emu_engine):
 
 def test_smoothed_voronoi_both_forms(emu_engine):
     pc.check_smoothed_voronoi(emu_engine, n=16, ncol=3)
+    pc.check_smoothed_voronoi(emu_engine, n=32, n_d=7, ncol=10, seed=7)      # tiled contraction
+    pc.check_smoothed_voronoi(emu_engine, n=32, n_d=55, ncol=9, seed=8)
 
 
 def test_bswap_and_nanfix(emu_engine):
