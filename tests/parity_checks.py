@@ -98,10 +98,12 @@ def check_fit(eng, seed=7, n_t=3, n_f=2, n_a=5, n_d=40):
     return scr, out
 
 
-def check_kl_eval(eng, n=24, n_d=9, ncol=11, seed=3, variant=0):
+def check_kl_eval(eng, n=24, n_d=9, ncol=11, seed=3, variant=0, cell=0.1):
+    """Directions are drawn in the central 80 % of the field (the geometry of BASELINE.json's
+    synthetic configs): the screen is an interpolant there, not an extrapolant."""
     rng = np.random.default_rng(seed)
-    pp, mid_ra, mid_dec = klfit.piercepoints(make_directions(rng, n_d, spread=1.5))
-    width, cell = (n - 0.5) * 0.1, 0.1
+    width = (n - 0.5) * cell
+    pp, mid_ra, mid_dec = klfit.piercepoints(make_directions(rng, n_d, spread=0.4 * width))
     x, y = owcs.kl_grid_coords(126.23, 64.5, width, cell, mid_ra, mid_dec)
     assert len(x) == n
     c_o, p_o, _ = klfit.calculate_svd(pp)
@@ -155,7 +157,7 @@ def check_smooth(eng, shape=(5, 19, 37), sigmas=(0.5, 2.0, 5.0), seed=2):
     return worst
 
 
-def check_smoothed_voronoi(eng, n=24, n_d=6, ncol=5, sigma=1.5, seed=4):
+def check_smoothed_voronoi(eng, n=24, n_d=6, ncol=5, sigma=1.5, seed=4, variant=0):
     rng = np.random.default_rng(seed)
     px, py = rng.uniform(0, n, n_d), rng.uniform(0, n, n_d)
     want_t = screens.nearest_patch_template(px, py, n)
@@ -170,7 +172,7 @@ def check_smoothed_voronoi(eng, n=24, n_d=6, ncol=5, sigma=1.5, seed=4):
     assert np.abs(slab.cpu().numpy() - want).max() < TOL_SMOOTH
     ind = eng.gauss_smooth(eng.voronoi_indicators(tmpl, n_d), sigma)
     slab2 = eng.empty((ncol, 4, n, n), torch.float32)
-    eng.voronoi_contract(ind, lut, slab2, 0)
+    eng.voronoi_contract(ind, lut, slab2, variant)
     assert np.abs(slab2.cpu().numpy() - want).max() < 2 * TOL_SMOOTH
 
 
@@ -186,3 +188,29 @@ def check_bswap_nanfix(eng, seed=1):
     t = eng.tensor(slab, torch.float32)
     eng.nan_fix(t, 3, 25)
     assert np.array_equal(t.cpu().numpy(), screens.nan_fix(slab.copy()))
+
+
+def check_raw_contraction(eng, npix=1024, n_d=45, ncol=70, seed=11, variant=1):
+    """The contraction alone (no sin/cos): random O(1) operands through ssf_voronoi_contract
+    against a float64 matmul.  Bounds the split-TF32 error of the tensor-core variant by the
+    same figure an FP32 FMA chain achieves (a few ulp of sum |a||b|)."""
+    rng = np.random.default_rng(seed)
+    s_mat = rng.normal(0, 1.0, (n_d, npix)).astype(np.float32)
+    lut = rng.normal(0, 1.0, (ncol, n_d, 2)).astype(np.float32)
+    lut = np.concatenate([lut, lut[-1:]])                    # extra column with one NaN coefficient:
+    lut[-1, 0, 0] = np.nan                                   # only that column's Re becomes (1, .)
+    ncol += 1
+    slab = eng.empty((ncol, 4, npix), torch.float32)
+    eng.voronoi_contract(eng.tensor(s_mat, torch.float32), eng.tensor(lut, torch.float32), slab, variant)
+    got = slab.cpu().numpy()
+    want_re = lut[:, :, 0].astype(np.float64) @ s_mat.astype(np.float64)
+    want_im = lut[:, :, 1].astype(np.float64) @ s_mat.astype(np.float64)
+    scale = np.abs(lut[:-1, :, 0]).astype(np.float64) @ np.abs(s_mat).astype(np.float64)
+    err_re = np.abs(got[:-1, 0] - want_re[:-1]) / scale
+    scale_im = np.abs(lut[:, :, 1]).astype(np.float64) @ np.abs(s_mat).astype(np.float64)
+    err_im = np.abs(got[:, 1] - want_im) / scale_im
+    assert err_re.max() < 4e-7, err_re.max()
+    assert err_im.max() < 4e-7, err_im.max()
+    assert np.all(got[-1, 0] == 1.0)                          # NaN column -> NaN fix (1, .)
+    assert np.array_equal(got[:, 0], got[:, 2]) and np.array_equal(got[:, 1], got[:, 3])
+    return float(err_re.max())

@@ -42,6 +42,31 @@ def test_kl_eval(gpu_engine):
     pc.check_kl_eval(gpu_engine, n=48, n_d=100, ncol=33, seed=10)
 
 
+def test_kl_eval_tcgen05(gpu_engine):
+    """Variant 1 (tcgen05, split TF32) against the float64 oracle at the same 1e-5 tolerance:
+    K padding (9 -> 16, 45 -> 48, 100 -> 104, 112), ragged column tiles, 1 and 2 CTAs per SM."""
+    pc.check_kl_eval(gpu_engine, n=32, n_d=9, ncol=11, variant=1)
+    pc.check_kl_eval(gpu_engine, n=64, n_d=45, ncol=70, seed=9, variant=1)
+    pc.check_kl_eval(gpu_engine, n=48, n_d=100, ncol=133, seed=10, variant=1)
+    pc.check_kl_eval(gpu_engine, n=32, n_d=112, ncol=64, seed=14, variant=1)
+    pc.check_kl_eval(gpu_engine, n=128, n_d=45, ncol=700, seed=15, variant=1, cell=0.03)
+    # many column tiles per CTA (both TMEM / shared-memory ring stages reused many times)
+    pc.check_kl_eval(gpu_engine, n=128, n_d=45, ncol=3840, seed=16, variant=1, cell=0.03)
+
+
+def test_contraction_tcgen05_error_bound(gpu_engine):
+    for n_d, ncol in ((45, 70), (8, 32), (100, 33), (3, 1)):
+        pc.check_raw_contraction(gpu_engine, n_d=n_d, ncol=ncol, variant=1)
+    pc.check_raw_contraction(gpu_engine, npix=128 * 37, n_d=45, ncol=500, variant=1)
+    pc.check_raw_contraction(gpu_engine, n_d=45, ncol=70, variant=0)
+
+
+def test_tcgen05_rejects_unsupported_shapes(gpu_engine):
+    from ska_sdp_screen_fitting_b200._lib import SsfError
+    with pytest.raises(SsfError):
+        pc.check_kl_eval(gpu_engine, n=11, n_d=5, ncol=3, seed=8, variant=1)   # npix % 128 != 0
+
+
 def test_voronoi_assign_and_fill(gpu_engine):
     pc.check_voronoi(gpu_engine)
     pc.check_voronoi(gpu_engine, n=9, n_d=3, ncol=2, seed=12)
@@ -67,6 +92,8 @@ def test_smoothing(gpu_engine):
 def test_smoothed_voronoi_both_forms(gpu_engine):
     pc.check_smoothed_voronoi(gpu_engine)
     pc.check_smoothed_voronoi(gpu_engine, n=96, n_d=20, ncol=9, sigma=5.0, seed=6)
+    pc.check_smoothed_voronoi(gpu_engine, n=96, n_d=20, ncol=9, sigma=5.0, seed=6, variant=1)
+    pc.check_smoothed_voronoi(gpu_engine, n=64, n_d=45, ncol=100, sigma=2.0, seed=7, variant=1)
 
 
 def test_bswap_and_nanfix(gpu_engine):
