@@ -208,59 +208,78 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ G, in
       // the MMAs of the tile that last used this stage have finished reading it
       if (use > 0) mbar_wait(bar_full + 8 * s, (use - 1) & 1);
       if (KL) {
-        for (int e0 = 0; e0 < TC_N * kc4; e0 += 32 * 8) {
-          float4 v[8];
+        // lane -> coefficient rows lane and lane + 32 (one slab column each, K contiguous in
+        // G); 4 core-matrix rows (float4) of both rows in flight per batch
+        const float *src[2];
+        bool ok[2];
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int e = e0 + u * 32 + lane;
-            const int n = e / kc4, kc = e - n * kc4;
-            const int64_t col = c0 + n;
-            v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (e < TC_N * kc4 && col < ncol && 4 * kc < ldg)
-              v[u] = __ldg(reinterpret_cast<const float4 *>(G + col * ldg + 4 * kc));
-          }
+        for (int rr = 0; rr < 2; ++rr) {
+          const int64_t col = c0 + lane + 32 * rr;
+          ok[rr] = col < ncol;
+          src[rr] = G + (ok[rr] ? col : 0) * ldg;
+        }
+        for (int kc0 = 0; kc0 < kc4; kc0 += 4) {
+          float4 v[2][4];
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int e = e0 + u * 32 + lane;
-            if (e >= TC_N * kc4) continue;
-            const int n = e / kc4, kc = e - n * kc4;
-            float4 x = v[u];
-            if (4 * kc + 0 >= ndir) x.x = 0.f;
-            if (4 * kc + 1 >= ndir) x.y = 0.f;
-            if (4 * kc + 2 >= ndir) x.z = 0.f;
-            if (4 * kc + 3 >= ndir) x.w = 0.f;
-            const float4 h = make_float4(to_tf32(x.x), to_tf32(x.y), to_tf32(x.z), to_tf32(x.w));
-            const float4 l = make_float4(to_tf32(x.x - h.x), to_tf32(x.y - h.y), to_tf32(x.z - h.z),
-                                         to_tf32(x.w - h.w));
-            const int o = canon(n, 4 * kc, kc4);
-            *reinterpret_cast<float4 *>(bh + o) = h;
-            *reinterpret_cast<float4 *>(bl + o) = l;
+          for (int rr = 0; rr < 2; ++rr)
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int kc = kc0 + u;
+              v[rr][u] = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (ok[rr] && kc < kc4 && 4 * kc < ldg)
+                v[rr][u] = __ldg(reinterpret_cast<const float4 *>(src[rr]) + kc);
+            }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int kc = kc0 + u;
+            if (kc >= kc4) break;                              // warp-uniform
+            const bool tail = 4 * kc + 3 >= ndir;              // warp-uniform: zero the K padding
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr) {
+              float4 x = v[rr][u];
+              if (tail) {
+                if (4 * kc + 0 >= ndir) x.x = 0.f;
+                if (4 * kc + 1 >= ndir) x.y = 0.f;
+                if (4 * kc + 2 >= ndir) x.z = 0.f;
+                x.w = 0.f;
+              }
+              const float4 hv = make_float4(to_tf32(x.x), to_tf32(x.y), to_tf32(x.z), to_tf32(x.w));
+              const float4 lv = make_float4(to_tf32(x.x - hv.x), to_tf32(x.y - hv.y), to_tf32(x.z - hv.z),
+                                            to_tf32(x.w - hv.w));
+              const int o = canon(lane + 32 * rr, 4 * kc, kc4);
+              *reinterpret_cast<float4 *>(bh + o) = hv;
+              *reinterpret_cast<float4 *>(bl + o) = lv;
+            }
           }
         }
       } else {
-        // lut [col][d][2]: row c = Re of column c0 + c, row 32 + c = Im
-        for (int e0 = 0; e0 < CT * Kp; e0 += 32 * 8) {
+        // lut [col][d][2]: lane -> slab column c0 + lane; row lane = Re, row 32 + lane = Im
+        const int64_t col = c0 + lane;
+        const bool ok = col < ncol;
+        const float2 *src = reinterpret_cast<const float2 *>(G) + (ok ? col : 0) * ndir;
+        for (int kc0 = 0; kc0 < kc4; kc0 += 2) {
           float2 v[8];
 #pragma unroll
           for (int u = 0; u < 8; ++u) {
-            const int e = e0 + u * 32 + lane;
-            const int c = e / Kp, k = e - c * Kp;
-            const int64_t col = c0 + c;
-            v[u] = make_float2(0.f, 0.f);
-            if (e < CT * Kp && col < ncol && k < ndir)
-              v[u] = __ldg(reinterpret_cast<const float2 *>(G) + col * ndir + k);
+            const int k = 4 * kc0 + u;
+            v[u] = (ok && k < ndir) ? __ldg(src + k) : make_float2(0.f, 0.f);
           }
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int e = e0 + u * 32 + lane;
-            if (e >= CT * Kp) continue;
-            const int c = e / Kp, k = e - c * Kp;
-            const float hr = to_tf32(v[u].x), hi_ = to_tf32(v[u].y);
-            const int o_re = canon(c, k, kc4), o_im = canon(CT + c, k, kc4);
-            bh[o_re] = hr;
-            bl[o_re] = to_tf32(v[u].x - hr);
-            bh[o_im] = hi_;
-            bl[o_im] = to_tf32(v[u].y - hi_);
+          for (int u = 0; u < 2; ++u) {
+            const int kc = kc0 + u;                            // kc4 is even: always < kc4
+            const float4 re = make_float4(v[4 * u].x, v[4 * u + 1].x, v[4 * u + 2].x, v[4 * u + 3].x);
+            const float4 im = make_float4(v[4 * u].y, v[4 * u + 1].y, v[4 * u + 2].y, v[4 * u + 3].y);
+            const float4 rh = make_float4(to_tf32(re.x), to_tf32(re.y), to_tf32(re.z), to_tf32(re.w));
+            const float4 ih = make_float4(to_tf32(im.x), to_tf32(im.y), to_tf32(im.z), to_tf32(im.w));
+            const float4 rl = make_float4(to_tf32(re.x - rh.x), to_tf32(re.y - rh.y), to_tf32(re.z - rh.z),
+                                          to_tf32(re.w - rh.w));
+            const float4 il = make_float4(to_tf32(im.x - ih.x), to_tf32(im.y - ih.y), to_tf32(im.z - ih.z),
+                                          to_tf32(im.w - ih.w));
+            const int o_re = canon(lane, 4 * kc, kc4), o_im = canon(CT + lane, 4 * kc, kc4);
+            *reinterpret_cast<float4 *>(bh + o_re) = rh;
+            *reinterpret_cast<float4 *>(bl + o_re) = rl;
+            *reinterpret_cast<float4 *>(bh + o_im) = ih;
+            *reinterpret_cast<float4 *>(bl + o_im) = il;
           }
         }
       }
@@ -308,9 +327,11 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ G, in
       if (lane == 0) mbar_arrive(bar_empty + 8 * s);
       if (KL) {
         float *out = slab + (c0 + 32 * h) * 4 * npix + pix;
-#pragma unroll 4
-        for (int j = 0; j < 32; ++j) {
-          if (c0 + 32 * h + j >= ncol) break;
+        const int64_t left = ncol - (c0 + 32 * h);
+        const int nvalid = left < 32 ? (int)left : 32;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {                       // fully unrolled: v[j] stays in registers
+          if (j >= nvalid) break;
           float sn, cs;
           sincos_reduced(v[j], &sn, &cs);
           cs = ssf::fix_re(cs);
@@ -324,9 +345,11 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ G, in
       } else {
         // h = 0: Re rows -> planes 0, 2; h = 1: Im rows -> planes 1, 3
         float *out = slab + c0 * 4 * npix + (int64_t)h * npix + pix;
-#pragma unroll 4
+        const int64_t left = ncol - c0;
+        const int nvalid = left < 32 ? (int)left : 32;
+#pragma unroll
         for (int j = 0; j < 32; ++j) {
-          if (c0 + j >= ncol) break;
+          if (j >= nvalid) break;
           const float x = h == 0 ? ssf::fix_re(v[j]) : ssf::fix_im(v[j]);
           __stcs(out, x);
           __stcs(out + 2 * npix, x);
