@@ -42,7 +42,8 @@ namespace {
 constexpr int TC_M = 128;                       // pixels per CTA tile = TMEM lanes
 constexpr int TC_N = 64;                        // accumulator columns per tile
 constexpr int EPI_WARPS = 8;
-constexpr int TC_THREADS = (EPI_WARPS + 1) * 32;
+constexpr int PROD_WARPS = 2;                     // one producer / MMA-issuing warp per ring stage
+constexpr int TC_THREADS = (EPI_WARPS + PROD_WARPS) * 32;
 constexpr int TMEM_COLS = 2 * TC_N;             // 2 accumulator stages (power of two >= 32)
 
 // ------------------------------------------------------------------------------------ PTX
@@ -143,6 +144,38 @@ __device__ __forceinline__ void sincos_reduced(float x, float *s, float *c) {
   *c = __cosf(r);
 }
 
+// Epilogue stores of one thread's 32 accumulator columns (its pixel, 32 slab columns): the 32
+// lanes of the warp write 128 contiguous bytes per plane.  CHECK = ragged last tile.
+template <bool CHECK>
+__device__ __forceinline__ void store_kl(const float (&v)[32], float *out, int64_t npix, int nvalid) {
+  const int64_t p2 = 2 * npix, p3 = 3 * npix, p4 = 4 * npix;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {                             // fully unrolled: v[j] stays in registers
+    if (CHECK && j >= nvalid) break;
+    float sn, cs;
+    sincos_reduced(v[j], &sn, &cs);
+    cs = ssf::fix_re(cs);
+    sn = ssf::fix_im(sn);
+    __stcs(out, cs);
+    __stcs(out + npix, sn);
+    __stcs(out + p2, cs);
+    __stcs(out + p3, sn);
+    out += p4;
+  }
+}
+template <bool CHECK>
+__device__ __forceinline__ void store_vo(const float (&v)[32], float *out, int64_t npix, int nvalid, int h) {
+  const int64_t p2 = 2 * npix, p4 = 4 * npix;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    if (CHECK && j >= nvalid) break;
+    const float x = h == 0 ? ssf::fix_re(v[j]) : ssf::fix_im(v[j]);
+    __stcs(out, x);
+    __stcs(out + p2, x);
+    out += p4;
+  }
+}
+
 // ------------------------------------------------------------------------------------ kernel
 // Shared memory (floats): A_hi[128 Kp] A_lo[128 Kp] B[2 stages][hi, lo][64 Kp], then 4
 // mbarriers (tmem_full[2], tmem_empty[2]) and the TMEM base address.
@@ -183,13 +216,24 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ G, in
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   // basis tile: coalesced reads (pixel fastest), split, canonical layout
-  for (int i = tid; i < TC_M * Kp; i += TC_THREADS) {
-    const int r = i & (TC_M - 1), k = i >> 7;
-    const float x = k < ndir ? __ldg(Bt + (int64_t)k * npix + pix0 + r) : 0.0f;
-    const float hi = to_tf32(x);
-    const int o = canon(r, k, kc4);
-    a_hi[o] = hi;
-    a_lo[o] = to_tf32(x - hi);
+  // (8 loads in flight per thread: under a saturated store stream a dependent load costs us)
+  for (int i0 = tid; i0 < TC_M * Kp; i0 += TC_THREADS * 8) {
+    float x[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = i0 + u * TC_THREADS;
+      const int r = i & (TC_M - 1), k = i >> 7;
+      x[u] = k < ndir ? __ldg(Bt + (int64_t)k * npix + pix0 + r) : 0.0f;   // k >= ndir also covers i >= 128 Kp
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = i0 + u * TC_THREADS;
+      if (i >= TC_M * Kp) break;
+      const float hi = to_tf32(x[u]);
+      const int o = canon(i & (TC_M - 1), i >> 7, kc4);
+      a_hi[o] = hi;
+      a_lo[o] = to_tf32(x[u] - hi);
+    }
   }
   fence_proxy_async();
   tc_fence_before();
@@ -197,12 +241,13 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ G, in
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
 
-  if (warp == EPI_WARPS) {
-    // ===== producer + MMA issuer =====
+  if (warp >= EPI_WARPS) {
+    // ===== producers + MMA issuers: warp EPI_WARPS + s owns ring stage s (tiles it = s, s + 2, ..) =====
     const uint32_t lbo = 128, sbo = (uint32_t)kc4 * 128;
     const uint64_t da_hi = make_desc(smem_u32(a_hi), lbo, sbo), da_lo = make_desc(smem_u32(a_lo), lbo, sbo);
-    for (int it = 0; it < n_tiles; ++it) {
-      const int s = it & 1, use = it >> 1;
+    const int s = warp - EPI_WARPS;
+    for (int it = s; it < n_tiles; it += 2) {
+      const int use = it >> 1;
       const int64_t c0 = (ct_begin + it) * CT;
       float *bh = b_base + (size_t)s * 2 * TC_N * Kp, *bl = bh + TC_N * Kp;
       // the MMAs of the tile that last used this stage have finished reading it
@@ -218,19 +263,19 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ G, in
           ok[rr] = col < ncol;
           src[rr] = G + (ok[rr] ? col : 0) * ldg;
         }
-        for (int kc0 = 0; kc0 < kc4; kc0 += 4) {
-          float4 v[2][4];
+        for (int kc0 = 0; kc0 < kc4; kc0 += 6) {
+          float4 v[2][6];
 #pragma unroll
           for (int rr = 0; rr < 2; ++rr)
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < 6; ++u) {
               const int kc = kc0 + u;
               v[rr][u] = make_float4(0.f, 0.f, 0.f, 0.f);
               if (ok[rr] && kc < kc4 && 4 * kc < ldg)
                 v[rr][u] = __ldg(reinterpret_cast<const float4 *>(src[rr]) + kc);
             }
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
+          for (int u = 0; u < 6; ++u) {
             const int kc = kc0 + u;
             if (kc >= kc4) break;                              // warp-uniform
             const bool tail = 4 * kc + 3 >= ndir;              // warp-uniform: zero the K padding
@@ -328,33 +373,14 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ G, in
       if (KL) {
         float *out = slab + (c0 + 32 * h) * 4 * npix + pix;
         const int64_t left = ncol - (c0 + 32 * h);
-        const int nvalid = left < 32 ? (int)left : 32;
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {                       // fully unrolled: v[j] stays in registers
-          if (j >= nvalid) break;
-          float sn, cs;
-          sincos_reduced(v[j], &sn, &cs);
-          cs = ssf::fix_re(cs);
-          sn = ssf::fix_im(sn);
-          __stcs(out, cs);
-          __stcs(out + npix, sn);
-          __stcs(out + 2 * npix, cs);
-          __stcs(out + 3 * npix, sn);
-          out += 4 * npix;
-        }
+        if (left >= 32) store_kl<false>(v, out, npix, 32);    // branch-free common case
+        else store_kl<true>(v, out, npix, (int)left);
       } else {
         // h = 0: Re rows -> planes 0, 2; h = 1: Im rows -> planes 1, 3
         float *out = slab + c0 * 4 * npix + (int64_t)h * npix + pix;
         const int64_t left = ncol - c0;
-        const int nvalid = left < 32 ? (int)left : 32;
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          if (j >= nvalid) break;
-          const float x = h == 0 ? ssf::fix_re(v[j]) : ssf::fix_im(v[j]);
-          __stcs(out, x);
-          __stcs(out + 2 * npix, x);
-          out += 4 * npix;
-        }
+        if (left >= 32) store_vo<false>(v, out, npix, 32, h);
+        else store_vo<true>(v, out, npix, (int)left, h);
       }
     }
   }
