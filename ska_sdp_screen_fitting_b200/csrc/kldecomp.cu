@@ -13,6 +13,11 @@ namespace {
 constexpr int THREADS = 256;
 constexpr int MAX_SWEEPS = 40;
 
+#ifdef SSF_CPU_EMU
+inline double rsqrt(double x) { return 1.0 / sqrt(x); }
+inline double __drcp_rn(double x) { return 1.0 / x; }
+#endif
+
 __global__ void __launch_bounds__(THREADS)
 decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__restrict__ masks,
                  double r0sq, double half_beta, double cut, double *__restrict__ Cout,
@@ -23,8 +28,10 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
   __shared__ int s_p[SSF_MAX_DIR / 2 + 1], s_q[SSF_MAX_DIR / 2 + 1];
   __shared__ int s_rank[SSF_MAX_DIR];
   __shared__ int s_n;
-  __shared__ double s_red[THREADS / 32];
+  __shared__ double s_red[THREADS / 32], s_red2[THREADS / 32];
+  __shared__ uchar2 s_blk[(SSF_MAX_DIR / 2) * (SSF_MAX_DIR / 2 + 1) / 2];
   __shared__ double s_off, s_tot;
+  __shared__ double s_inv[SSF_MAX_DIR];
 
   const int pat = blockIdx.x;
   const int tid = threadIdx.x;
@@ -37,8 +44,11 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
   }
   __syncthreads();
   const int n = s_n;
-  double *A = sm;           // [n][n]
-  double *V = sm + n * n;   // [n][n]
+  const int m = (n + 1) & ~1;   // padded to an even size: the extra row / column is zero, so every
+                                // rotation that touches it is the identity (apq == 0)
+  const int npairs = m / 2;
+  double *A = sm;               // [m][m]
+  double *V = sm + m * m;       // [m][m]
   double *C = Cout + (size_t)pat * ndir * ndir;
   double *P = Pout + (size_t)pat * ndir * ndir;
   double *U = Uout + (size_t)pat * ndir * ndir;
@@ -51,96 +61,152 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
     U[i] = 0.0;
   }
   for (int i = tid; i < ndir; i += THREADS) sv[i] = 0.0;
+  // upper-triangular list of pair blocks (k1 <= k2), built once
+  for (int e = tid; e < npairs * npairs; e += THREADS) {
+    const int k1 = e / npairs, k2 = e - k1 * npairs;
+    if (k1 <= k2) s_blk[k1 * npairs - k1 * (k1 - 1) / 2 + (k2 - k1)] = make_uchar2((unsigned char)k1, (unsigned char)k2);
+  }
   __syncthreads();
   if (n == 0) return;
+  const int nblocks = npairs * (npairs + 1) / 2;
 
   // C_S (stationscreen.py:417-426); same association as numpy: dx^2 + dy^2 (+ 0)
-  for (int e = tid; e < n * n; e += THREADS) {
-    int i = e / n, j = e - i * n;
-    double dx = pp[2 * s_idx[i]] - pp[2 * s_idx[j]];
-    double dy = pp[2 * s_idx[i] + 1] - pp[2 * s_idx[j] + 1];
-    double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
-    double q = d2 / r0sq;
-    double v = q > 0.0 ? -0.5 * pow(q, half_beta) : 0.0;
+  for (int e = tid; e < m * m; e += THREADS) {
+    int i = e / m, j = e - i * m;
+    double v = 0.0;
+    if (i < n && j < n) {
+      double dx = pp[2 * s_idx[i]] - pp[2 * s_idx[j]];
+      double dy = pp[2 * s_idx[i] + 1] - pp[2 * s_idx[j] + 1];
+      double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+      double q = d2 / r0sq;
+      v = q > 0.0 ? -0.5 * pow(q, half_beta) : 0.0;
+      C[i * ndir + j] = v;
+    }
     A[e] = v;
     V[e] = (i == j) ? 1.0 : 0.0;
-    C[i * ndir + j] = v;
   }
   __syncthreads();
 
-  const int m = (n + 1) & ~1;  // players (last one is a dummy when n is odd)
-  const int npairs = m / 2;
   // Quadratic convergence: once the off-diagonal energy is below 1e-24 of the total, one
   // more sweep takes it to rounding level.
   bool converged = (n == 1);
   bool last = false;
+  const int warp = tid >> 5, lane = tid & 31;
   for (int sweep = 0; sweep < MAX_SWEEPS && !converged; ++sweep) {
     for (int r = 0; r < m - 1; ++r) {
-      if (tid < npairs) {
-        int p, q;
-        if (tid == 0) {
-          p = m - 1;
-          q = r;
-        } else {
-          p = (r + tid) % (m - 1);
-          q = (r - tid + (m - 1)) % (m - 1);
-        }
-        if (p > q) {
-          int t = p;
-          p = q;
-          q = t;
-        }
-        double c = 1.0, s = 0.0;
-        if (q < n) {
-          double apq = A[p * n + q];
-          if (apq != 0.0) {
-            double app = A[p * n + p], aqq = A[q * n + q];
-            double tau = (aqq - app) / (2.0 * apq);
-            double t = (tau >= 0.0 ? 1.0 : -1.0) / (fabs(tau) + sqrt(1.0 + tau * tau));
-            c = 1.0 / sqrt(1.0 + t * t);
-            s = t * c;
+      // round-robin pairing: m / 2 disjoint rotations.  Every warp computes the rotation of
+      // pair k = lane (+ 32) for itself, so its V rows can be updated from registers without
+      // waiting for anybody; warp 0 also publishes the rotations for the A block update.
+      int pk[2], qk[2];
+      double ck[2], sk[2];
+#pragma unroll
+      for (int g = 0; g < 2; ++g) {
+        const int k = lane + 32 * g;
+        pk[g] = qk[g] = 0;
+        ck[g] = 1.0;
+        sk[g] = 0.0;
+        if (k < npairs) {
+          int p, q;
+          if (k == 0) {
+            p = m - 1;
+            q = r;
+          } else {
+            p = r + k;
+            if (p >= m - 1) p -= m - 1;
+            q = r - k;
+            if (q < 0) q += m - 1;
           }
-        } else {
-          q = -1;
+          if (p > q) {
+            int t = p;
+            p = q;
+            q = t;
+          }
+          double c = 1.0, sn = 0.0;
+          const double apq = A[p * m + q];
+          if (apq != 0.0) {
+            // t = sgn(tau) / (|tau| + sqrt(1 + tau^2)), tau = (aqq - app) / (2 apq), written
+            // without the slow FP64 divide / sqrt: t = apq / (d + sgn(d) hypot(d, apq))
+            const double d = 0.5 * (A[q * m + q] - A[p * m + p]);
+            const double r2 = fma(d, d, apq * apq);
+            if (r2 > 0.0) {
+              const double den = d + copysign(r2 * rsqrt(r2), d);
+              const double t = apq * __drcp_rn(den);
+              c = rsqrt(fma(t, t, 1.0));
+              sn = t * c;
+            }
+          }
+          pk[g] = p;
+          qk[g] = q;
+          ck[g] = c;
+          sk[g] = sn;
+          if (warp == 0) {
+            s_p[k] = p;
+            s_q[k] = q;
+            s_c[k] = c;
+            s_s[k] = sn;
+          }
         }
-        s_p[tid] = p;
-        s_q[tid] = q;
-        s_c[tid] = c;
-        s_s[tid] = s;
       }
-      __syncthreads();
-      // column update of A and V:  X <- X J
-      for (int e = tid; e < n * npairs; e += THREADS) {
-        int i = e / npairs, k = e - i * npairs;
-        int q = s_q[k];
-        if (q < 0) continue;
-        int p = s_p[k];
-        double c = s_c[k], s = s_s[k];
-        double aip = A[i * n + p], aiq = A[i * n + q];
-        A[i * n + p] = c * aip - s * aiq;
-        A[i * n + q] = s * aip + c * aiq;
-        double vip = V[i * n + p], viq = V[i * n + q];
-        V[i * n + p] = c * vip - s * viq;
-        V[i * n + q] = s * vip + c * viq;
+      // V <- V J (columns).  Rows are owned by warps (row = warp, warp + 8, ..): no other warp
+      // ever touches them, so this needs no barrier.  4 rows in flight per lane.
+#pragma unroll
+      for (int g = 0; g < 2; ++g) {
+        if (lane + 32 * g >= npairs) break;
+        double *vp = V + pk[g], *vq = V + qk[g];
+        const double c = ck[g], sn = sk[g];
+        for (int i0 = warp; i0 < m; i0 += 4 * (THREADS / 32)) {
+          double x[4], y[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int i = i0 + u * (THREADS / 32);
+            if (i < m) {
+              x[u] = vp[i * m];
+              y[u] = vq[i * m];
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int i = i0 + u * (THREADS / 32);
+            if (i < m) {
+              vp[i * m] = c * x[u] - sn * y[u];
+              vq[i * m] = sn * x[u] + c * y[u];
+            }
+          }
+        }
       }
-      __syncthreads();
-      // row update of A:  A <- J^T A
-      for (int e = tid; e < n * npairs; e += THREADS) {
-        int k = e / n, j = e - k * n;
-        int q = s_q[k];
-        if (q < 0) continue;
-        int p = s_p[k];
-        double c = s_c[k], s = s_s[k];
-        double apj = A[p * n + j], aqj = A[q * n + j];
-        A[p * n + j] = c * apj - s * aqj;
-        A[q * n + j] = s * apj + c * aqj;
+      __syncthreads();   // every warp has read A for its rotations; s_p.. are published
+      // A <- J^T A J by 2 x 2 pair blocks: the thread of block (k1, k2), k1 <= k2, reads its 4
+      // elements, applies the column rotation of pair k2 and the row rotation of pair k1,
+      // and writes them and their mirror images.  No element is touched by two threads.
+      for (int e = tid; e < nblocks; e += THREADS) {
+        const uchar2 kk = s_blk[e];
+        const int p1 = s_p[kk.x], q1 = s_q[kk.x], p2 = s_p[kk.y], q2 = s_q[kk.y];
+        const double c1 = s_c[kk.x], s1 = s_s[kk.x], c2 = s_c[kk.y], s2 = s_s[kk.y];
+        const double a00 = A[p1 * m + p2], a01 = A[p1 * m + q2], a10 = A[q1 * m + p2], a11 = A[q1 * m + q2];
+        const double b00 = c2 * a00 - s2 * a01, b01 = s2 * a00 + c2 * a01;
+        const double b10 = c2 * a10 - s2 * a11, b11 = s2 * a10 + c2 * a11;
+        const double r00 = c1 * b00 - s1 * b10, r10 = s1 * b00 + c1 * b10;
+        const double r01 = c1 * b01 - s1 * b11, r11 = s1 * b01 + c1 * b11;
+        A[p1 * m + p2] = r00;
+        A[q1 * m + q2] = r11;
+        if (kk.x == kk.y) {
+          A[p1 * m + q1] = r01;                     // the annihilated element (rounding level)
+          A[q1 * m + p1] = r01;
+        } else {
+          A[p1 * m + q2] = r01;
+          A[q1 * m + p2] = r10;
+          A[p2 * m + p1] = r00;
+          A[q2 * m + p1] = r01;
+          A[p2 * m + q1] = r10;
+          A[q2 * m + q1] = r11;
+        }
       }
       __syncthreads();
     }
     // convergence: off-diagonal energy against total energy
     double off = 0.0, tot = 0.0;
-    for (int e = tid; e < n * n; e += THREADS) {
-      int i = e / n, j = e - i * n;
+    for (int e = tid; e < m * m; e += THREADS) {
+      int i = e / m, j = e - i * m;
       double v = A[e] * A[e];
       tot += v;
       if (i != j) off += v;
@@ -149,20 +215,19 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
       off += __shfl_xor_sync(0xffffffffu, off, o);
       tot += __shfl_xor_sync(0xffffffffu, tot, o);
     }
-    if ((tid & 31) == 0) s_red[tid >> 5] = off;
-    __syncthreads();
-    if (tid == 0) {
-      double a = 0.0;
-      for (int w = 0; w < THREADS / 32; ++w) a += s_red[w];
-      s_off = a;
+    if (lane == 0) {
+      s_red[warp] = off;
+      s_red2[warp] = tot;
     }
     __syncthreads();
-    if ((tid & 31) == 0) s_red[tid >> 5] = tot;
-    __syncthreads();
     if (tid == 0) {
-      double a = 0.0;
-      for (int w = 0; w < THREADS / 32; ++w) a += s_red[w];
-      s_tot = a;
+      double a = 0.0, b = 0.0;
+      for (int w = 0; w < THREADS / 32; ++w) {
+        a += s_red[w];
+        b += s_red2[w];
+      }
+      s_off = a;
+      s_tot = b;
     }
     __syncthreads();
     if (last) converged = true;
@@ -171,29 +236,27 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
 
   // order by |lambda| descending (ties: lower index first)
   for (int i = tid; i < n; i += THREADS) {
-    double li = fabs(A[i * n + i]);
+    double li = fabs(A[i * m + i]);
     int rank = 0;
     for (int j = 0; j < n; ++j) {
-      double lj = fabs(A[j * n + j]);
+      double lj = fabs(A[j * m + j]);
       rank += (lj > li) || (lj == li && j < i);
     }
     s_rank[i] = rank;
     sv[rank] = converged ? li : nan("");
+    s_inv[i] = li > cut ? 1.0 / A[i * m + i] : 0.0;
   }
   __syncthreads();
   for (int e = tid; e < n * n; e += THREADS) {
     int a = e / n, i = e - a * n;
-    U[a * ndir + s_rank[i]] = V[e];
+    U[a * ndir + s_rank[i]] = V[a * m + i];
   }
   // pinv(C_S) = sum_{|lambda_i| > cut} v_i v_i^T / lambda_i
   for (int e = tid; e < n * n; e += THREADS) {
     int a = e / n, b = e - a * n;
     if (b < a) continue;
     double acc = 0.0;
-    for (int i = 0; i < n; ++i) {
-      double lam = A[i * n + i];
-      if (fabs(lam) > cut) acc += V[a * n + i] * V[b * n + i] / lam;
-    }
+    for (int i = 0; i < n; ++i) acc = fma(V[a * m + i] * V[b * m + i], s_inv[i], acc);
     P[a * ndir + b] = acc;
     P[b * ndir + a] = acc;
   }
@@ -207,7 +270,8 @@ extern "C" int ssf_kl_decompose(const double *pp, int ndir, const uint64_t *mask
   SSF_REQUIRE(pp && masks && C && pinvC && U && sv, "ssf_kl_decompose: null pointer");
   SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR, "ssf_kl_decompose: ndir=%d out of range [1,%d]", ndir, SSF_MAX_DIR);
   if (npat <= 0) return SSF_OK;
-  size_t smem = sizeof(double) * 2 * (size_t)ndir * ndir;
+  const int mmax = (ndir + 1) & ~1;
+  size_t smem = sizeof(double) * 2 * (size_t)mmax * mmax;
   if (smem > 48 * 1024)
     SSF_CUDA(cudaFuncSetAttribute(decompose_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   SSF_LAUNCH(decompose_kernel, npat, THREADS, smem, (cudaStream_t)stream, pp, ndir, masks, r0 * r0,

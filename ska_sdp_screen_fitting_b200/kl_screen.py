@@ -149,7 +149,7 @@ class KLScreen(Screen):
             return
         main = torch.cuda.current_stream(eng.device)
         if self._fit_stream is None:
-            self._fit_stream = torch.cuda.Stream(eng.device)
+            self._fit_stream = torch.cuda.Stream(eng.device, priority=-1)   # the fit fills freed SM slots first
         side = self._fit_stream
 
         side.wait_stream(main)                           # inputs / setup are ready
