@@ -97,16 +97,24 @@ class Engine:
         # torch has no uint64 arithmetic: masks travel as int64 bit patterns
         return [lo - 2**64 if lo >= 2**63 else lo, hi - 2**64 if hi >= 2**63 else hi]
 
-    def kl_decompose(self, pp, masks, r0=R_0, beta=BETA, cut=PINV_CUT):
+    def kl_decompose(self, pp, masks, r0=R_0, beta=BETA, cut=PINV_CUT, out=None):
         """ssf_kl_decompose: pp [ndir, 2] f64, masks [npat, 2] int64 bit patterns.
-        Returns C, pinvC, U [npat, ndir, ndir] and sv [npat, ndir]."""
+        Returns C, pinvC, U [npat, ndir, ndir] and sv [npat, ndir] (``out``: the same four as
+        preallocated contiguous tensors)."""
         self._check(pp, torch.float64, "pp")
         self._check(masks, torch.int64, "masks")
         ndir, npat = pp.shape[0], masks.shape[0]
-        c = self.empty((npat, ndir, ndir), torch.float64)
-        p = self.empty((npat, ndir, ndir), torch.float64)
-        u = self.empty((npat, ndir, ndir), torch.float64)
-        sv = self.empty((npat, ndir), torch.float64)
+        if out is not None:
+            c, p, u, sv = out
+            for t, nm in ((c, "C"), (p, "pinvC"), (u, "U"), (sv, "sv")):
+                self._check(t, torch.float64, nm)
+                if t.shape[0] != npat:
+                    raise ValueError("decompose output has the wrong number of patterns")
+        else:
+            c = self.empty((npat, ndir, ndir), torch.float64)
+            p = self.empty((npat, ndir, ndir), torch.float64)
+            u = self.empty((npat, ndir, ndir), torch.float64)
+            sv = self.empty((npat, ndir), torch.float64)
         self._call("ssf_kl_decompose", _ptr(pp), ndir, _ptr(masks), npat, r0, beta, cut,
                   _ptr(c), _ptr(p), _ptr(u), _ptr(sv), self.stream())
         return c, p, u, sv
@@ -139,60 +147,33 @@ class Engine:
         return status
 
     def kl_fit(self, phase, weights, station_order, pp, niter=2, nsigma=5.0, adjust_order=True,
-               r0=R_0, beta=BETA, cut=PINV_CUT, pattern_budget_bytes=4 << 30, check=True):
+               r0=R_0, beta=BETA, cut=PINV_CUT, cache=None, check=True):
         """The iteration structure of _process_station (stationscreen.py:658-779) for a batch
         of independent systems.  phase [nsys, ndir] f64 (already referenced), weights
         [nsys, ndir] f32 (modified in place by the flagging), station_order [nsys] f64.
         Returns (white, resid, order) with shapes [nsys, ndir], [nsys, ndir], [nsys].
+        ``cache``: a PatternCache for these pierce points (decompositions of flag patterns are
+        kept across calls); a temporary one is made if absent.
         ``check=False`` defers the convergence / weight-range checks: the caller must call
-        ``check_fit_status()`` later (avoids a host sync per slab in streaming loops)."""
+        ``check_fit_status()`` later."""
         nsys, ndir = phase.shape
         white = self.zeros((nsys, ndir), torch.float64)
         resid = self.zeros((nsys, ndir), torch.float64)
         order = station_order.clone()
-        full = torch.tensor([self.full_mask(ndir)], dtype=torch.int64, device=self.device)
-        per_pattern = 3 * ndir * ndir * 8 + ndir * 8
-        chunk = max(1024, pattern_budget_bytes // per_pattern)
+        if cache is None:
+            cache = PatternCache(self, pp, r0, beta, cut)
         if self._fit_status is None:
             self._fit_status = self.zeros((2,), torch.int32)     # [weights out of range, no convergence]
-        for s0 in range(0, nsys, chunk):
-            s1 = min(nsys, s0 + chunk)
-            ph, w = phase[s0:s1], weights[s0:s1]
-            wh, rs, od, so = white[s0:s1], resid[s0:s1], order[s0:s1], station_order[s0:s1]
-            patterns, mats = None, None
-            for it in range(niter):
-                masks = self.kl_flag_outliers(rs, w, nsigma if it > 0 else math.inf)
-                if it > 0 and not adjust_order:
-                    # the flagged weights alias the "previous" weights in the reference, so
-                    # without order adjustment nothing is refitted (stationscreen.py:694-701)
-                    continue
-                uniq, inv = torch.unique(masks, dim=0, return_inverse=True)
-                if patterns is None:
-                    patterns = torch.cat([full, uniq]).contiguous()       # pattern 0 = all directions
-                    pat = (inv + 1).to(torch.int32).contiguous()
-                    c, p, u, sv = self.kl_decompose(pp, patterns, r0, beta, cut)
-                    mats = (c, p, u)
-                    self._fit_status[1:2] += torch.isnan(sv).any().to(torch.int32)
-                else:
-                    # later iterations differ from the previous one only where outliers were
-                    # flagged: decompose just the patterns that have not been seen yet
-                    n_old = patterns.shape[0]
-                    union, where = torch.unique(torch.cat([patterns, uniq]), dim=0, return_inverse=True)
-                    seen = torch.zeros(union.shape[0], dtype=torch.bool, device=self.device)
-                    seen[where[:n_old]] = True
-                    fresh = union[~seen].contiguous()
-                    slot = torch.empty(union.shape[0], dtype=torch.int64, device=self.device)
-                    slot[where[:n_old]] = torch.arange(n_old, device=self.device)
-                    slot[~seen] = n_old + torch.arange(fresh.shape[0], device=self.device)
-                    pat = slot[where[n_old:]][inv].to(torch.int32).contiguous()
-                    if fresh.shape[0]:
-                        c, p, u, sv = self.kl_decompose(pp, fresh, r0, beta, cut)
-                        self._fit_status[1:2] += torch.isnan(sv).any().to(torch.int32)
-                        mats = tuple(torch.cat([a, b]) for a, b in zip(mats, (c, p, u)))
-                        patterns = torch.cat([patterns, fresh])
-                mode = 1 if (it > 0 and adjust_order) else 0
-                self.kl_fit_pass(ph, w, pat, pp, mats, mode, od, so, wh, rs, r0, beta, cut,
-                                 status=self._fit_status[0:1])
+        for it in range(niter):
+            masks = self.kl_flag_outliers(resid, weights, nsigma if it > 0 else math.inf)
+            if it > 0 and not adjust_order:
+                # the flagged weights alias the "previous" weights in the reference, so
+                # without order adjustment nothing is refitted (stationscreen.py:694-701)
+                continue
+            pat = cache.index(masks)
+            mode = 1 if (it > 0 and adjust_order) else 0
+            self.kl_fit_pass(phase, weights, pat, pp, cache.mats, mode, order, station_order, white,
+                             resid, r0, beta, cut, status=self._fit_status[0:1])
         if check:
             self.check_fit_status()
         return white, resid, order
@@ -294,3 +275,88 @@ class Engine:
         return t
 
 
+
+
+class PatternCache:
+    """Decompositions (C_S, pinv C_S, U_S) of the flag patterns seen so far for one set of
+    pierce points, kept on the device across fit calls.
+
+    The reference recomputes the SVD for every system with a flagged direction
+    (stationscreen.py:493-499); systems that share a flag pattern share the result, within a
+    slab and across slabs, so each distinct pattern is decomposed once per run.  The dedupe is
+    host-side marshalling: the [nsys, 2] masks come back once per fit pass, a dict maps a
+    pattern to its slot, and only patterns never seen before go to ``ssf_kl_decompose``.
+    Slot 0 is the full pattern."""
+
+    def __init__(self, engine, pp, r0=R_0, beta=BETA, cut=PINV_CUT, max_bytes=4 << 30):
+        self.eng = engine
+        self.pp = pp
+        self.ndir = pp.shape[0]
+        self.params = (r0, beta, cut)
+        self.full = tuple(Engine.full_mask(self.ndir))
+        per = (3 * self.ndir * self.ndir + self.ndir) * 8
+        self.max_slots = max(2, int(max_bytes // per))
+        self.slots = {}
+        self.count = 0
+        self.capacity = 0
+        self.c = self.p = self.u = self.sv = None
+        self.decomposed = 0
+        self._reserve(min(self.max_slots, 256))
+        self._add([self.full])
+
+    @property
+    def mats(self):
+        return self.c, self.p, self.u
+
+    def _reserve(self, capacity):
+        eng, n = self.eng, self.ndir
+        new = [eng.empty((capacity, n, n), torch.float64) for _ in range(3)] + [eng.empty((capacity, n), torch.float64)]
+        if self.count:
+            for dst, src in zip(new, (self.c, self.p, self.u, self.sv)):
+                dst[:self.count].copy_(src[:self.count])
+            if eng.device.type == "cuda":
+                torch.cuda.synchronize(eng.device)       # growth is rare; old stores may be in use on another stream
+        self.c, self.p, self.u, self.sv = new
+        self.capacity = capacity
+
+    def _add(self, keys):
+        """Decomposes new patterns into the next free slots."""
+        eng = self.eng
+        n_new = len(keys)
+        if self.count + n_new > self.capacity:
+            self._reserve(min(self.max_slots, max(2 * self.capacity, self.count + n_new)))
+        base = self.count
+        masks = torch.tensor(keys, dtype=torch.int64).reshape(n_new, 2).to(eng.device)
+        out = tuple(t[base:base + n_new] for t in (self.c, self.p, self.u, self.sv))
+        eng.kl_decompose(self.pp, masks, *self.params, out=out)
+        if eng._fit_status is None:
+            eng._fit_status = eng.zeros((2,), torch.int32)
+        eng._fit_status[1:2] += torch.isnan(out[3]).any().to(torch.int32)
+        for i, key in enumerate(keys):
+            self.slots[key] = base + i
+        self.count += n_new
+        self.decomposed += n_new
+
+    def index(self, masks):
+        """masks: device [nsys, 2] int64 bit patterns -> device int32 [nsys] slot of each
+        system's pattern (decomposing the ones not seen before)."""
+        m = masks.cpu().numpy()
+        nsys = m.shape[0]
+        pat = np.zeros(nsys, np.int32)
+        rows = np.nonzero((m[:, 0] != self.full[0]) | (m[:, 1] != self.full[1]))[0]
+        if rows.size:
+            uniq, inv = np.unique(m[rows], axis=0, return_inverse=True)
+            keys = [(int(a), int(b)) for a, b in uniq]
+            fresh = [k for k in keys if k not in self.slots]
+            if self.count + len(fresh) > self.max_slots:
+                # out of budget: forget everything but the full pattern and start over
+                self.slots = {self.full: 0}
+                self.count = 1
+                fresh = keys
+                if 1 + len(fresh) > self.max_slots:
+                    raise MemoryError("pattern cache budget too small for one fit pass")
+            if fresh:
+                self._add(fresh)
+            slot = np.fromiter((self.slots[k] for k in keys), np.int32, len(keys))
+            pat[rows] = slot[inv.reshape(-1)]
+        return torch.from_numpy(pat).to(self.eng.device)

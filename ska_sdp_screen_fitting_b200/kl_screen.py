@@ -14,7 +14,7 @@ import numpy as np
 import torch
 
 from . import wcs
-from .engine import BETA, PINV_CUT, R_0
+from .engine import BETA, PINV_CUT, R_0, PatternCache
 from .screen import Screen
 
 
@@ -69,6 +69,7 @@ class KLScreen(Screen):
         self.station_order = None
         self._pinv_full = None
         self._fit_stream = None
+        self._patterns = None
 
     # ------------------------------------------------------------------ fit
     def setup(self, sol, antenna_weight_sums=None):
@@ -97,6 +98,7 @@ class KLScreen(Screen):
         full = torch.tensor([eng.full_mask(n_d)], dtype=torch.int64, device=eng.device)
         c, pinv, _, _ = eng.kl_decompose(self._pp_dev, full, self.r_0, self.beta_val, PINV_CUT)
         self._c_full, self._pinv_full = c[0].contiguous(), pinv[0].contiguous()
+        self._patterns = PatternCache(eng, self._pp_dev, self.r_0, self.beta_val, PINV_CUT)
         self._so_dev = torch.tensor(self.station_order, dtype=torch.float64, device=eng.device)
         self.times_ph = sol.time
         self.freqs_ph = sol.freq
@@ -123,7 +125,8 @@ class KLScreen(Screen):
         so = self._so_dev[None, None, :].expand(n_t, n_f, n_a).reshape(-1).contiguous()
         white, resid, order = eng.kl_fit(val.reshape(-1, n_d).contiguous(), work_w.view(-1, n_d),
                                          so, self._pp_dev, niter=2, nsigma=5.0, adjust_order=True,
-                                         r0=self.r_0, beta=self.beta_val, cut=PINV_CUT, check=check)
+                                         r0=self.r_0, beta=self.beta_val, cut=PINV_CUT,
+                                         cache=self._patterns, check=check)
         order = order.view(n_t, n_f, n_a)
         order = torch.where(skip[None], torch.zeros_like(order), order)
         weights_out = torch.where(skip[None, :, :, None], weight, work_w)
@@ -166,10 +169,12 @@ class KLScreen(Screen):
         nxt = launch_fit(first) if first < last else None
         for k in range(first, last):
             white, done = nxt
-            nxt = launch_fit(k + 1) if k + 1 < last else None
             main.wait_event(done)
             slab = ring[k % len(ring)]
             self._fill_columns(white.view(-1, n_d), slab, cellsize_deg, None, 0.0, True)
+            # the evaluation of slab k is queued before the fit of slab k + 1 is issued: the
+            # fit's host-side pattern lookup (one small D2H per pass) then never starves the GPU
+            nxt = launch_fit(k + 1) if k + 1 < last else None
             yield k, slab
 
     def fit(self):
