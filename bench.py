@@ -252,8 +252,28 @@ def run_ours(args):
         ms, launches, kern, clocks = timed(kl_step, ["kl_eval"])
         n_launch, k_ms = kern["kl_eval"]
         achieved = voxels_per_step * BYTES_PER_VOXEL / (k_ms * 1e-3) / 1e9
+        # the same kernel timed alone (no fit running beside it on the side stream): explains
+        # how much of the in-step duration is sharing SMs with the overlapped FP64 fit
+        white0 = kl.fit_device(val_dev[:slots], wt_dev[:slots], check=False)[0].view(-1, n_d)
+        coeffs0 = eng.kl_coeffs(white0, kl._c_full)
+        torch.cuda.synchronize()
+        alone = []
+        for _ in range(3):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            eng.kl_eval(kl._basis, coeffs0, n_d, ring[0], args.variant)
+            b.record()
+            torch.cuda.synchronize()
+            alone.append(a.elapsed_time(b))
+        alone_ms = sorted(alone)[1]
+        tc = args.variant != 0 and (n * n) % 128 == 0
+        kname = ("contract_tc_kernel<KL> (ssf_kl_eval, tcgen05 split-TF32)" if tc
+                 else "contract_tile_kernel<KL> (ssf_kl_eval, FP32 SIMT)")
         out["kl"] = dict(ms=ms, launches=launches, clocks=clocks,
-                         roofline={"bound": "hbm", "kernel": "contract_simt_kernel<KL> (ssf_kl_eval)",
+                         roofline={"bound": "hbm", "kernel": kname,
+                                   "alone": {"kernel_ms": alone_ms,
+                                             "achieved": voxels_per_step * BYTES_PER_VOXEL / (alone_ms * 1e-3) / 1e9,
+                                             "frac": voxels_per_step * BYTES_PER_VOXEL / (alone_ms * 1e-3) / 1e9 / peak},
                                    "achieved": achieved, "peak": peak, "unit": "GB/s",
                                    "frac": achieved / peak, "traffic": recorded_traffic("kl_eval"),
                                    "kernel_ms": k_ms, "kernel_launches": n_launch, "peak_source": peak_src,

@@ -15,11 +15,12 @@
 // representable in TF32, so the tensor core's own operand conversion is the identity and
 // every product is exact; the only rounding left is the accumulator's (see the issue loop).
 //
-// CTA = 8 epilogue warps + 1 producer/MMA warp, one 128-pixel tile, a run of column tiles:
+// CTA = 8 epilogue warps + 2 producer/MMA warps (one per ring stage), one 128-pixel tile, a
+// run of column tiles:
 //   * the basis tile is split once and kept in shared memory in the canonical K-major
 //     no-swizzle UMMA layout (8 x 16 B core matrices);
-//   * the producer warp splits the next coefficient tile into a 2-stage shared-memory ring,
-//     fences it to the async proxy and one elected lane issues the 4 * K/8 tcgen05.mma into
+//   * producer warp s splits every second coefficient tile into stage s of a 2-stage
+//     shared-memory ring, fences it to the async proxy and its lane 0 issues the 4 * K/8 tcgen05.mma into
 //     a 2-stage TMEM accumulator ring, tcgen05.commit signalling an mbarrier;
 //   * epilogue warp w reads TMEM lanes 32 (w % 4).. (its pixel = lane) and accumulator columns
 //     32 (w / 4).. with tcgen05.ld, releases the TMEM stage, and streams the planes out: for a
