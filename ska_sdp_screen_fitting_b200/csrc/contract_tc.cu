@@ -25,6 +25,8 @@
 //   * epilogue warp w reads TMEM lanes 32 (w % 4).. (its pixel = lane) and accumulator columns
 //     32 (w / 4).. with tcgen05.ld, releases the TMEM stage, and streams the planes out: for a
 //     fixed column the 32 lanes of a warp store 128 contiguous bytes per plane.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 #ifdef SSF_CPU_EMU
@@ -395,22 +397,22 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ G, in
   }
 }
 
-// Column chunks per pixel tile: enough CTAs for >= 8 waves of the resident capacity, with the
-// smallest last-wave waste among nearby counts.
+// Column chunks per pixel tile.  A CTA stages its basis tile once (worth about 3 column tiles
+// of time) and then walks `per` column tiles, so the launch takes about
+// waves * (3 + per) tile times; take the chunk count that minimises that.  Few, long CTAs
+// win unless the grid would leave SMs idle or the last wave nearly empty.
 int pick_chunks(int pix_tiles, int64_t n_ct, int capacity) {
-  int64_t want = ((int64_t)capacity * 8 + pix_tiles - 1) / pix_tiles;
-  if (want < 1) want = 1;
-  if (want > n_ct) want = n_ct;
-  int best = (int)want;
-  double best_waste = 2.0;
-  for (int64_t ch = want; ch <= n_ct && ch < want + 64; ++ch) {
+  int best = 1;
+  double best_cost = 1e300;
+  const int64_t max_ch = n_ct < 256 ? n_ct : 256;
+  for (int64_t ch = 1; ch <= max_ch; ++ch) {
     const int64_t per = (n_ct + ch - 1) / ch;
-    const int64_t real = (n_ct + per - 1) / per;
+    const int64_t real = (n_ct + per - 1) / per;      // chunks that actually have work
     const int64_t ctas = real * pix_tiles;
     const int64_t waves = (ctas + capacity - 1) / capacity;
-    const double waste = 1.0 - (double)ctas / (double)(waves * capacity);
-    if (waste < best_waste - 1e-9) {
-      best_waste = waste;
+    const double cost = (double)waves * (3.0 + (double)per);
+    if (cost < best_cost - 1e-9) {
+      best_cost = cost;
       best = (int)ch;
     }
   }
@@ -428,7 +430,12 @@ int launch_tc(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, 
   const int pix_tiles = (int)(npix / TC_M);
   const int64_t n_ct = (ncol + CT - 1) / CT;
   const int per_sm = 2 * (smem + 1024) <= 227 * 1024 ? 2 : 1;
-  const int chunks = pick_chunks(pix_tiles, n_ct, 148 * per_sm);
+  int chunks = pick_chunks(pix_tiles, n_ct, 148 * per_sm);
+  if (const char *e = getenv("SSF_TC_CHUNKS")) {   // experiment hook
+    chunks = atoi(e);
+    if (chunks < 1) chunks = 1;
+    if (chunks > n_ct) chunks = (int)n_ct;
+  }
   const int per = (int)((n_ct + chunks - 1) / chunks);
   const int gx = (int)((n_ct + per - 1) / per);
   dim3 grid(gx, pix_tiles);
