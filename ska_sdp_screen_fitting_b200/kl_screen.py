@@ -10,6 +10,10 @@ Unlike the reference, the fit results stay in memory: nothing is appended to the
 h5parm (the reference's ``remove_soltabs`` never succeeds, so a second run would read a stale
 table -- SURVEY.md section 5).
 """
+import queue
+import threading
+import time
+
 import numpy as np
 import torch
 
@@ -70,6 +74,7 @@ class KLScreen(Screen):
         self._pinv_full = None
         self._fit_stream = None
         self._patterns = None
+        self.fit_ahead = 2                # slabs the streaming fit runs ahead of the evaluation
 
     # ------------------------------------------------------------------ fit
     def setup(self, sol, antenna_weight_sums=None):
@@ -158,24 +163,55 @@ class KLScreen(Screen):
         side.wait_stream(main)                           # inputs / setup are ready
 
         def launch_fit(k):
+            t_host = time.perf_counter()
             with torch.cuda.stream(side):
                 white = self.fit_device(val_dev[k * slots:(k + 1) * slots],
                                         wt_dev[k * slots:(k + 1) * slots], check=False)[0]
                 done = torch.cuda.Event()
                 done.record(side)
             white.record_stream(main)
+            self.timings["fit_host_s"] = self.timings.get("fit_host_s", 0.0) + time.perf_counter() - t_host
+            self.timings["fit_calls"] = self.timings.get("fit_calls", 0) + 1
             return white, done
 
-        nxt = launch_fit(first) if first < last else None
-        for k in range(first, last):
-            white, done = nxt
-            main.wait_event(done)
-            slab = ring[k % len(ring)]
-            self._fill_columns(white.view(-1, n_d), slab, cellsize_deg, None, 0.0, True)
-            # the evaluation of slab k is queued before the fit of slab k + 1 is issued: the
-            # fit's host-side pattern lookup (one small D2H per pass) then never starves the GPU
-            nxt = launch_fit(k + 1) if k + 1 < last else None
-            yield k, slab
+        # The fits are issued by a helper thread that runs up to `ahead` slabs in front of the
+        # evaluation: the host-side part of a fit (pattern lookup: one small blocking D2H per
+        # pass) then never keeps the evaluation stream waiting for its next launch.
+        ahead = max(1, int(self.fit_ahead))
+        ready = queue.Queue(maxsize=ahead)
+        stop = threading.Event()
+
+        def issue_fits():
+            try:
+                torch.cuda.set_device(eng.device)
+                for k in range(first, last):
+                    item = launch_fit(k)
+                    while not stop.is_set():
+                        try:
+                            ready.put(item, timeout=0.05)
+                            break
+                        except queue.Full:
+                            continue
+                    if stop.is_set():
+                        return
+            except BaseException as exc:  # surfaced in the consumer
+                ready.put(exc)
+
+        helper = threading.Thread(target=issue_fits, name="ssf-fit", daemon=True)
+        helper.start()
+        try:
+            for k in range(first, last):
+                item = ready.get()
+                if isinstance(item, BaseException):
+                    raise item
+                white, done = item
+                main.wait_event(done)
+                slab = ring[k % len(ring)]
+                self._fill_columns(white.view(-1, n_d), slab, cellsize_deg, None, 0.0, True)
+                yield k, slab
+        finally:
+            stop.set()
+            helper.join(timeout=30)
 
     def fit(self):
         """kl_screen.py:61-155 + stationscreen.run (phase type)."""
