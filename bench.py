@@ -31,6 +31,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 FIT_AHEAD = 2
+FIT_GROUP = 4      # slabs per fit call of the streaming KL path
 METRIC = "screen voxels/s (pix*ant*time*freq), KL & Voronoi"
 UNIT = "voxel/s"
 BYTES_PER_VOXEL = 16
@@ -144,6 +145,7 @@ def make_screens(case, eng, variant, weight_sums):
     kl._engine = eng
     kl.eval_variant = variant
     kl.fit_ahead = FIT_AHEAD
+    kl.fit_group = FIT_GROUP
     kl.setup(case.solutions, antenna_weight_sums=weight_sums)
     kl._prepare(case.cellsize_deg, None)
     vo = VoronoiScreen("bench_vo", None, None, case.rad, case.dec, case.width_deg, case.width_deg)
@@ -179,10 +181,11 @@ def run_ours(args):
     eng = Engine(device=f"cuda:{local}")
     slots = args.slots or auto_slots(args.workload)
     n_steps = args.warmup + args.steps
-    # FIT_AHEAD + 1 slabs more than are evaluated: the pipelined KL path keeps the fits
-    # FIT_AHEAD slabs (+ the one in flight) in front of the evaluation through a bounded queue,
-    # so in steady state the K timed steps contain exactly K slab fits and K slab evaluations
-    case = build_case(args, rank, slots * (n_steps + FIT_AHEAD + 1))
+    # (FIT_AHEAD + 2) fit groups more than are evaluated: the pipelined KL path fits FIT_GROUP
+    # slabs per call and keeps FIT_AHEAD groups (+ the one in flight) in front of the evaluation
+    # through a bounded queue, so in steady state the fit never runs out of slabs during the K
+    # timed steps: they contain K slab evaluations and (to within one group) K slab fits
+    case = build_case(args, rank, slots * (n_steps + (FIT_AHEAD + 2) * FIT_GROUP))
     sol = case.solutions
     n_t, n_f, n_a, n_d = sol.val.shape
     n = case.n_pix
@@ -203,8 +206,7 @@ def run_ours(args):
     kl_stream = kl.stream_slabs(val_dev, wt_dev, slots, ring, case.cellsize_deg)
 
     def kl_step(i):
-        # fit of slab i+1 (side stream) overlaps the evaluation of slab i; every timed step
-        # still contains exactly one slab fit and one slab evaluation
+        # the fits of the next group of slabs (side stream) overlap the evaluation of slab i
         k, _ = next(kl_stream)
         assert k == i
 
@@ -228,12 +230,18 @@ def run_ours(args):
         eng.timers = {}
         kl.timings.pop("fit_host_s", None)
         kl.timings.pop("fit_calls", None)
+        kl.timings.pop("fit_slabs", None)
         launches0 = eng.launch_count()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        # the streamed KL fit runs a fixed number of slab groups ahead of the evaluation: bring
+        # that lead to its steady-state value on both sides of the timed region (and order the
+        # main stream after it), so the region holds as many slab fits as slab evaluations
+        kl.settle_fit_lead()
         t_begin = time.time()
         ev0.record()
         for i in range(args.warmup, n_steps):
             step_fn(i)
+        kl.settle_fit_lead()
         ev1.record()
         torch.cuda.synchronize()
         t_end = time.time()
@@ -255,7 +263,13 @@ def run_ours(args):
     peak, peak_src = measured_peaks()
     out = {}
     if args.workload != "voronoi1k":
-        ms, launches, kern, clocks = timed(kl_step, ["kl_eval"])
+        eng.host_times = {}
+        ms, launches, kern, clocks = timed(kl_step, ["kl_eval", "kl_patterns_update", "kl_flag_outliers", "kl_fit_pass"])
+        # side-stream spans (queueing behind the evaluation's CTAs + execution), whole run incl. warm-up for the host part
+        fit_breakdown = {k: {"calls": kern[k][0], "mean_ms": kern[k][1]} for k in kern if k != "kl_eval"}
+        fit_breakdown["pattern_slots_in_use"] = kl._patterns.stats()[0]
+        fit_breakdown["host_s"] = dict(eng.host_times)
+        fit_breakdown["torch_device_allocs_total"] = torch.cuda.memory_stats().get("num_device_alloc", None)
         kl_stream.close()                     # stops the fit helper thread
         torch.cuda.synchronize()
         n_launch, k_ms = kern["kl_eval"]
@@ -278,7 +292,8 @@ def run_ours(args):
         kname = ("contract_tc_kernel<KL> (ssf_kl_eval, tcgen05 split-TF32)" if tc
                  else "contract_tile_kernel<KL> (ssf_kl_eval, FP32 SIMT)")
         out["kl"] = dict(ms=ms, launches=launches, clocks=clocks,
-                         fit_host_ms=kl.timings.get("fit_host_s", 0.0) / max(kl.timings.get("fit_calls", 1), 1) * 1e3,
+                         fit_host_ms=kl.timings.get("fit_host_s", 0.0) / max(kl.timings.get("fit_slabs", 1), 1) * 1e3,
+                         fit_slabs=kl.timings.get("fit_slabs", 0), fit_breakdown=fit_breakdown,
                          roofline={"bound": "hbm", "kernel": kname,
                                    "alone": {"kernel_ms": alone_ms,
                                              "achieved": voxels_per_step * BYTES_PER_VOXEL / (alone_ms * 1e-3) / 1e9,
@@ -507,6 +522,8 @@ def main():
                 "clocks": out[head]["clocks"]}
         if "fit_host_ms" in out[head]:
             line["fit_host_ms_per_slab"] = out[head]["fit_host_ms"]
+            line["fit_slabs_in_timed_region"] = out[head]["fit_slabs"]
+            line["fit_breakdown"] = out[head]["fit_breakdown"]
         if head == "kl":
             vms = out["voronoi"]["ms"]
             line["voronoi"] = {"value": world * args.steps * res["voxels_per_step"] / (vms * 1e-3),

@@ -61,6 +61,29 @@ int ssf_kl_decompose(const double *pp, int ndir, const uint64_t *masks, int npat
                      double r0, double beta, double pinv_cut,
                      double *C, double *pinvC, double *U, double *sv, void *stream);
 
+/* Device-resident cache of decompositions, so that a fit pass needs no host round trip
+ * (the reference recomputes the SVD for every system with a flagged direction,
+ * stationscreen.py:493-499; systems that share a flag pattern share the result here).
+ * For the masks [nsys, 2] of one pass (ssf_kl_flag_outliers) it finds or creates the slot
+ * of every system's pattern (pat [nsys], slot 0 = the full pattern, which the caller
+ * decomposes into slot 0 beforehand with ssf_kl_decompose) and decomposes the slots that
+ * are new, all stream-ordered:
+ *   table_keys [hash_cap, 2] u64, table_slots [hash_cap] i32 (initialised to -1):
+ *       open-addressing hash table, hash_cap = power of two >= 2 * max_slots
+ *   slot_masks [max_slots, 2] u64; C, pinvC, U [max_slots, ndir, ndir], sv [max_slots, ndir]
+ *   counters [4] i32 = {slots in use (start at 1), slots decomposed (start at 1),
+ *       overflow flag, scratch}.  When a pass could run out of slots the cache forgets
+ *       everything but slot 0 first; counters[2] = 1 only if one pass alone has more
+ *       distinct patterns than max_slots - 1 (results are then invalid).
+ *   status [1] i32: set to 1 if a Jacobi solve did not converge.
+ */
+int ssf_kl_patterns_update(const uint64_t *masks, int64_t nsys, int ndir, const double *pp,
+                           double r0, double beta, double pinv_cut,
+                           uint64_t *table_keys, int32_t *table_slots, int hash_cap,
+                           uint64_t *slot_masks, int max_slots,
+                           double *C, double *pinvC, double *U, double *sv,
+                           int32_t *counters, int32_t *status, int32_t *pat, void *stream);
+
 /* ------------------------------------------------------------------------------------
  * KL fit, one pass over all systems.  Replaces _fit_screen (stationscreen.py:433-594) and
  * the per-time body of _process_station (:681-779) for phase screens.

@@ -15,17 +15,24 @@
 // representable in TF32, so the tensor core's own operand conversion is the identity and
 // every product is exact; the only rounding left is the accumulator's (see the issue loop).
 //
-// CTA = 8 epilogue warps + 2 producer/MMA warps (one per ring stage), one 128-pixel tile, a
-// run of column tiles:
-//   * the basis tile is split once and kept in shared memory in the canonical K-major
-//     no-swizzle UMMA layout (8 x 16 B core matrices);
-//   * producer warp s splits every second coefficient tile into stage s of a 2-stage
-//     shared-memory ring, fences it to the async proxy and its lane 0 issues the 4 * K/8 tcgen05.mma into
-//     a 2-stage TMEM accumulator ring, tcgen05.commit signalling an mbarrier;
+// Coefficient operand: a small pre-pass (split_b_kernel) splits G / the LUT once per launch into
+// hi/lo tiles stored in global memory in exactly the shared-memory image the MMA reads (canonical
+// K-major no-swizzle UMMA layout, 8 x 16 B core matrices), so the hot kernel stages a tile with
+// ONE bulk-async copy (cp.async.bulk, the TMA engine, mbarrier complete_tx) and no thread touches it.
+//
+// CTA = NEPI epilogue warps + 1 TMA warp + 1 MMA warp, one 128-pixel tile, a run of column tiles:
+//   * the basis tile is split once and kept in shared memory in the canonical layout;
+//   * TMA warp (one lane): bulk copies of the coefficient tiles into a 2-stage shared-memory ring,
+//     each stage re-armed as soon as the MMAs that read it have retired (tcgen05.commit);
+//   * MMA warp (one lane): issues the 4 * K/8 tcgen05.mma of a tile into a 4-stage TMEM accumulator
+//     ring (256 columns), tcgen05.commit signalling the epilogue's mbarrier;
 //   * epilogue warp w reads TMEM lanes 32 (w % 4).. (its pixel = lane) and accumulator columns
-//     32 (w / 4).. with tcgen05.ld, releases the TMEM stage, and streams the planes out: for a
-//     fixed column the 32 lanes of a warp store 128 contiguous bytes per plane.
+//     32 ((w / 4) % 2).. with tcgen05.ld, releases the TMEM stage, and streams the planes out: for a
+//     fixed column the 32 lanes of a warp store 128 contiguous bytes per plane.  NEPI = 8 with two
+//     CTAs per SM, or 16 (two groups taking alternate tiles) when only one CTA fits (ndir > 56).
 #include <stdlib.h>
+
+#include <mutex>
 
 #include "common.cuh"
 
@@ -44,10 +51,10 @@ namespace {
 
 constexpr int TC_M = 128;                       // pixels per CTA tile = TMEM lanes
 constexpr int TC_N = 64;                        // accumulator columns per tile
-constexpr int EPI_WARPS = 8;
-constexpr int PROD_WARPS = 2;                     // one producer / MMA-issuing warp per ring stage
-constexpr int TC_THREADS = (EPI_WARPS + PROD_WARPS) * 32;
-constexpr int TMEM_COLS = 2 * TC_N;             // 2 accumulator stages (power of two >= 32)
+constexpr int B_STAGES = 2;                     // shared-memory ring of coefficient tiles
+constexpr int T_STAGES = 4;                     // TMEM accumulator ring
+constexpr int TMEM_COLS = T_STAGES * TC_N;      // 256 columns (two resident CTAs use all 512)
+constexpr int N_BARS = 2 * B_STAGES + 2 * T_STAGES;
 
 // ------------------------------------------------------------------------------------ PTX
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -70,6 +77,15 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "memory");
     if (!done && spin > (1 << 22)) __trap();
   }
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// Bulk-async (TMA engine) copy global -> shared, completion counted in bytes on an mbarrier.
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -179,22 +195,62 @@ __device__ __forceinline__ void store_vo(const float (&v)[32], float *out, int64
   }
 }
 
-// ------------------------------------------------------------------------------------ kernel
-// Shared memory (floats): A_hi[128 Kp] A_lo[128 Kp] B[2 stages][hi, lo][64 Kp], then 4
-// mbarriers (tmem_full[2], tmem_empty[2]) and the TMEM base address.
+// ------------------------------------------------------------------------------------ pre-pass
+// Coefficient tiles, split and laid out as the MMA wants them:
+//   Bs[tile][hi | lo][canon(row, k)]   (64 rows x Kp, zero padded)
+// KL:      row r of tile t = slab column 64 t + r               (G[col, d], leading dimension ldg)
+// Voronoi: rows r < 32 = Re, r >= 32 = Im of column 32 t + (r & 31)   (lut[col, d, 0/1])
 template <bool KL>
-__global__ void __launch_bounds__(TC_THREADS, 2)
-contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ G, int ndir, int ldg,
-                   int64_t npix, int64_t ncol, float *__restrict__ slab, int tiles_per_chunk, int Kp) {
+__global__ void split_b_kernel(const float *__restrict__ G, int ndir, int ldg, int64_t ncol, int Kp,
+                               int64_t n_ct, float *__restrict__ Bs) {
+  const int kc4 = Kp >> 2;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n_ct * TC_N * kc4) return;
+  const int kc = (int)(idx % kc4);
+  const int r = (int)((idx / kc4) % TC_N);
+  const int64_t tile = idx / ((int64_t)kc4 * TC_N);
+  float x[4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const int k = 4 * kc + u;
+    float v = 0.0f;
+    if (KL) {
+      const int64_t col = tile * TC_N + r;
+      if (col < ncol && k < ndir) v = G[col * ldg + k];
+    } else {
+      const int64_t col = tile * (TC_N / 2) + (r & 31);
+      if (col < ncol && k < ndir) v = G[(col * ndir + k) * 2 + (r >> 5)];
+    }
+    x[u] = v;
+  }
+  const float4 hv = make_float4(to_tf32(x[0]), to_tf32(x[1]), to_tf32(x[2]), to_tf32(x[3]));
+  const float4 lv = make_float4(to_tf32(x[0] - hv.x), to_tf32(x[1] - hv.y), to_tf32(x[2] - hv.z),
+                                to_tf32(x[3] - hv.w));
+  float *dst = Bs + tile * (2 * TC_N * Kp) + canon(r, 4 * kc, kc4);
+  *reinterpret_cast<float4 *>(dst) = hv;
+  *reinterpret_cast<float4 *>(dst + TC_N * Kp) = lv;
+}
+
+// ------------------------------------------------------------------------------------ kernel
+// Shared memory (floats): A_hi[128 Kp] A_lo[128 Kp] B[2 stages][hi, lo][64 Kp], then the
+// mbarriers b_full[2] b_empty[2] t_full[4] t_empty[4] and the TMEM base address.
+template <bool KL, int NEPI>
+__global__ void __launch_bounds__((NEPI + 2) * 32, NEPI == 8 ? 2 : 1)
+contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, int ndir, int64_t npix,
+                   int64_t ncol, float *__restrict__ slab, int tiles_per_chunk, int Kp) {
   constexpr int CT = KL ? TC_N : TC_N / 2;       // slab columns per tile (Voronoi: re + im rows)
+  constexpr int THREADS = (NEPI + 2) * 32;
+  constexpr int GROUPS = NEPI / 8;               // epilogue groups taking alternate tiles
   SSF_DYN_SMEM(float, sm);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int kc4 = Kp >> 2;
   float *a_hi = sm, *a_lo = sm + TC_M * Kp;
   float *b_base = sm + 2 * TC_M * Kp;            // stage s: hi at s*2*64*Kp, lo right after
-  uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (2 * TC_M + 4 * TC_N) * Kp);
-  uint32_t *tmem_holder = reinterpret_cast<uint32_t *>(bars + 4);
-  const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + 2);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (2 * TC_M + 2 * B_STAGES * TC_N) * Kp);
+  uint32_t *tmem_holder = reinterpret_cast<uint32_t *>(bars + N_BARS);
+  const uint32_t b_full = smem_u32(bars), b_empty = smem_u32(bars + B_STAGES);
+  const uint32_t t_full = smem_u32(bars + 2 * B_STAGES), t_empty = smem_u32(bars + 2 * B_STAGES + T_STAGES);
+  const uint32_t stage_bytes = (uint32_t)(2 * TC_N * Kp * sizeof(float));
 
   const int64_t pix0 = (int64_t)blockIdx.y * TC_M;
   const int64_t n_ct = (ncol + CT - 1) / CT;
@@ -203,15 +259,27 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ G, in
   if (ct_end > n_ct) ct_end = n_ct;
   if (ct_begin >= ct_end) return;                // whole CTA, before any barrier / allocation
   const int n_tiles = (int)(ct_end - ct_begin);
+  const float *b_src = Bs + ct_begin * (2 * TC_N * Kp);
 
-  if (tid == 0) {
-    mbar_init(bar_full, 1);
-    mbar_init(bar_full + 8, 1);
-    mbar_init(bar_empty, EPI_WARPS);
-    mbar_init(bar_empty + 8, EPI_WARPS);
+  if (tid == NEPI * 32) {
+    // the TMA lane initialises the barriers and starts the first coefficient tiles at once, so
+    // their latency runs under the staging of the basis tile below
+    for (int i = 0; i < B_STAGES; ++i) {
+      mbar_init(b_full + 8 * i, 1);
+      mbar_init(b_empty + 8 * i, 1);
+    }
+    for (int i = 0; i < T_STAGES; ++i) {
+      mbar_init(t_full + 8 * i, 1);
+      mbar_init(t_empty + 8 * i, 8);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    for (int it = 0; it < B_STAGES && it < n_tiles; ++it) {
+      mbar_expect_tx(b_full + 8 * it, stage_bytes);
+      bulk_g2s(smem_u32(b_base + (size_t)it * 2 * TC_N * Kp), b_src + (size_t)it * 2 * TC_N * Kp, stage_bytes,
+               b_full + 8 * it);
+    }
   }
-  if (warp == EPI_WARPS) {
+  if (warp == NEPI + 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
                      smem_u32(tmem_holder)),
                  "n"(TMEM_COLS)
@@ -220,17 +288,17 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ G, in
   }
   // basis tile: coalesced reads (pixel fastest), split, canonical layout
   // (8 loads in flight per thread: under a saturated store stream a dependent load costs us)
-  for (int i0 = tid; i0 < TC_M * Kp; i0 += TC_THREADS * 8) {
+  for (int i0 = tid; i0 < TC_M * Kp; i0 += THREADS * 8) {
     float x[8];
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
-      const int i = i0 + u * TC_THREADS;
+      const int i = i0 + u * THREADS;
       const int r = i & (TC_M - 1), k = i >> 7;
       x[u] = k < ndir ? __ldg(Bt + (int64_t)k * npix + pix0 + r) : 0.0f;   // k >= ndir also covers i >= 128 Kp
     }
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
-      const int i = i0 + u * TC_THREADS;
+      const int i = i0 + u * THREADS;
       if (i >= TC_M * Kp) break;
       const float hi = to_tf32(x[u]);
       const int o = canon(i & (TC_M - 1), i >> 7, kc4);
@@ -244,102 +312,31 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ G, in
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
 
-  if (warp >= EPI_WARPS) {
-    // ===== producers + MMA issuers: warp EPI_WARPS + s owns ring stage s (tiles it = s, s + 2, ..) =====
-    const uint32_t lbo = 128, sbo = (uint32_t)kc4 * 128;
-    const uint64_t da_hi = make_desc(smem_u32(a_hi), lbo, sbo), da_lo = make_desc(smem_u32(a_lo), lbo, sbo);
-    const int s = warp - EPI_WARPS;
-    for (int it = s; it < n_tiles; it += 2) {
-      const int use = it >> 1;
-      const int64_t c0 = (ct_begin + it) * CT;
-      float *bh = b_base + (size_t)s * 2 * TC_N * Kp, *bl = bh + TC_N * Kp;
-      // the MMAs of the tile that last used this stage have finished reading it
-      if (use > 0) mbar_wait(bar_full + 8 * s, (use - 1) & 1);
-      if (KL) {
-        // lane -> coefficient rows lane and lane + 32 (one slab column each, K contiguous in
-        // G); 4 core-matrix rows (float4) of both rows in flight per batch
-        const float *src[2];
-        bool ok[2];
-#pragma unroll
-        for (int rr = 0; rr < 2; ++rr) {
-          const int64_t col = c0 + lane + 32 * rr;
-          ok[rr] = col < ncol;
-          src[rr] = G + (ok[rr] ? col : 0) * ldg;
-        }
-        for (int kc0 = 0; kc0 < kc4; kc0 += 6) {
-          float4 v[2][6];
-#pragma unroll
-          for (int rr = 0; rr < 2; ++rr)
-#pragma unroll
-            for (int u = 0; u < 6; ++u) {
-              const int kc = kc0 + u;
-              v[rr][u] = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (ok[rr] && kc < kc4 && 4 * kc < ldg)
-                v[rr][u] = __ldg(reinterpret_cast<const float4 *>(src[rr]) + kc);
-            }
-#pragma unroll
-          for (int u = 0; u < 6; ++u) {
-            const int kc = kc0 + u;
-            if (kc >= kc4) break;                              // warp-uniform
-            const bool tail = 4 * kc + 3 >= ndir;              // warp-uniform: zero the K padding
-#pragma unroll
-            for (int rr = 0; rr < 2; ++rr) {
-              float4 x = v[rr][u];
-              if (tail) {
-                if (4 * kc + 0 >= ndir) x.x = 0.f;
-                if (4 * kc + 1 >= ndir) x.y = 0.f;
-                if (4 * kc + 2 >= ndir) x.z = 0.f;
-                x.w = 0.f;
-              }
-              const float4 hv = make_float4(to_tf32(x.x), to_tf32(x.y), to_tf32(x.z), to_tf32(x.w));
-              const float4 lv = make_float4(to_tf32(x.x - hv.x), to_tf32(x.y - hv.y), to_tf32(x.z - hv.z),
-                                            to_tf32(x.w - hv.w));
-              const int o = canon(lane + 32 * rr, 4 * kc, kc4);
-              *reinterpret_cast<float4 *>(bh + o) = hv;
-              *reinterpret_cast<float4 *>(bl + o) = lv;
-            }
-          }
-        }
-      } else {
-        // lut [col][d][2]: lane -> slab column c0 + lane; row lane = Re, row 32 + lane = Im
-        const int64_t col = c0 + lane;
-        const bool ok = col < ncol;
-        const float2 *src = reinterpret_cast<const float2 *>(G) + (ok ? col : 0) * ndir;
-        for (int kc0 = 0; kc0 < kc4; kc0 += 2) {
-          float2 v[8];
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int k = 4 * kc0 + u;
-            v[u] = (ok && k < ndir) ? __ldg(src + k) : make_float2(0.f, 0.f);
-          }
-#pragma unroll
-          for (int u = 0; u < 2; ++u) {
-            const int kc = kc0 + u;                            // kc4 is even: always < kc4
-            const float4 re = make_float4(v[4 * u].x, v[4 * u + 1].x, v[4 * u + 2].x, v[4 * u + 3].x);
-            const float4 im = make_float4(v[4 * u].y, v[4 * u + 1].y, v[4 * u + 2].y, v[4 * u + 3].y);
-            const float4 rh = make_float4(to_tf32(re.x), to_tf32(re.y), to_tf32(re.z), to_tf32(re.w));
-            const float4 ih = make_float4(to_tf32(im.x), to_tf32(im.y), to_tf32(im.z), to_tf32(im.w));
-            const float4 rl = make_float4(to_tf32(re.x - rh.x), to_tf32(re.y - rh.y), to_tf32(re.z - rh.z),
-                                          to_tf32(re.w - rh.w));
-            const float4 il = make_float4(to_tf32(im.x - ih.x), to_tf32(im.y - ih.y), to_tf32(im.z - ih.z),
-                                          to_tf32(im.w - ih.w));
-            const int o_re = canon(lane, 4 * kc, kc4), o_im = canon(CT + lane, 4 * kc, kc4);
-            *reinterpret_cast<float4 *>(bh + o_re) = rh;
-            *reinterpret_cast<float4 *>(bl + o_re) = rl;
-            *reinterpret_cast<float4 *>(bh + o_im) = ih;
-            *reinterpret_cast<float4 *>(bl + o_im) = il;
-          }
-        }
+  if (warp == NEPI) {
+    // ===== TMA lane: refill stage s once the MMAs of the tile that used it have retired =====
+    if (lane == 0) {
+      for (int it = B_STAGES; it < n_tiles; ++it) {
+        const int s = it % B_STAGES, use = it / B_STAGES;
+        mbar_wait(b_empty + 8 * s, (use - 1) & 1);
+        mbar_expect_tx(b_full + 8 * s, stage_bytes);
+        bulk_g2s(smem_u32(b_base + (size_t)s * 2 * TC_N * Kp), b_src + (size_t)it * 2 * TC_N * Kp, stage_bytes,
+                 b_full + 8 * s);
       }
-      fence_proxy_async();
-      __syncwarp();
-      if (lane == 0) {
-        // the epilogue has drained the accumulator stage this tile writes
-        if (use > 0) mbar_wait(bar_empty + 8 * s, (use - 1) & 1);
+    }
+  } else if (warp == NEPI + 1) {
+    // ===== MMA lane =====
+    if (lane == 0) {
+      const uint32_t lbo = 128, sbo = (uint32_t)kc4 * 128;
+      const uint64_t da_hi = make_desc(smem_u32(a_hi), lbo, sbo), da_lo = make_desc(smem_u32(a_lo), lbo, sbo);
+      const int ksteps = Kp >> 3;
+      for (int it = 0; it < n_tiles; ++it) {
+        const int s = it % B_STAGES, t = it % T_STAGES;
+        mbar_wait(b_full + 8 * s, (it / B_STAGES) & 1);                  // coefficient tile landed
+        if (it >= T_STAGES) mbar_wait(t_empty + 8 * t, (it / T_STAGES - 1) & 1);   // accumulator drained
         tc_fence_after();
-        const uint64_t db_hi = make_desc(smem_u32(bh), lbo, sbo), db_lo = make_desc(smem_u32(bl), lbo, sbo);
-        const uint32_t d_tmem = tmem_base + (uint32_t)(s * TC_N);
-        const int ksteps = Kp >> 3;
+        const float *bh = b_base + (size_t)s * 2 * TC_N * Kp;
+        const uint64_t db_hi = make_desc(smem_u32(bh), lbo, sbo), db_lo = make_desc(smem_u32(bh + TC_N * Kp), lbo, sbo);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(t * TC_N);
         // The tensor core truncates (round toward zero) once per accumulating instruction
         // (measured: -0.4 ulp of |D| per tcgen05.mma).  So the small correction products go
         // first, while |D| is ~2^-11 of its final size and the truncation is harmless, and
@@ -355,24 +352,24 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ G, in
           const uint64_t adv = (uint64_t)(ks * 16);
           tc_mma_tf32(d_tmem, da_hi + adv, db_hi + adv, IDESC, 1);
         }
-        tc_commit(bar_full + 8 * s);
+        tc_commit(b_empty + 8 * s);                  // shared-memory stage free for the next copy
+        tc_commit(t_full + 8 * t);                   // accumulator ready for the epilogue
       }
-      __syncwarp();
     }
   } else {
     // ===== epilogue warps =====
-    const int q = warp & 3, h = warp >> 2;
+    const int g = warp >> 3, q = warp & 3, h = (warp >> 2) & 1;
     const int64_t pix = pix0 + 32 * q + lane;
-    for (int it = 0; it < n_tiles; ++it) {
-      const int s = it & 1, use = it >> 1;
+    for (int it = g; it < n_tiles; it += GROUPS) {
+      const int t = it % T_STAGES;
       const int64_t c0 = (ct_begin + it) * CT;
-      mbar_wait(bar_full + 8 * s, use & 1);
+      mbar_wait(t_full + 8 * t, (it / T_STAGES) & 1);
       tc_fence_after();
       float v[32];
-      tmem_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(s * TC_N + 32 * h), v);
+      tmem_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TC_N + 32 * h), v);
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_empty + 8 * s);
+      if (lane == 0) mbar_arrive(t_empty + 8 * t);
       if (KL) {
         float *out = slab + (c0 + 32 * h) * 4 * npix + pix;
         const int64_t left = ncol - (c0 + 32 * h);
@@ -390,33 +387,69 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ G, in
 
   tc_fence_before();
   __syncthreads();
-  if (warp == EPI_WARPS) {
+  if (warp == NEPI + 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS)
                  : "memory");
   }
 }
 
-// Column chunks per pixel tile.  A CTA stages its basis tile once (worth about 3 column tiles
-// of time) and then walks `per` column tiles, so the launch takes about
-// waves * (3 + per) tile times; take the chunk count that minimises that.  Few, long CTAs
-// win unless the grid would leave SMs idle or the last wave nearly empty.
-int pick_chunks(int pix_tiles, int64_t n_ct, int capacity) {
-  int best = 1;
-  double best_cost = 1e300;
-  const int64_t max_ch = n_ct < 256 ? n_ct : 256;
-  for (int64_t ch = 1; ch <= max_ch; ++ch) {
-    const int64_t per = (n_ct + ch - 1) / ch;
-    const int64_t real = (n_ct + per - 1) / per;      // chunks that actually have work
-    const int64_t ctas = real * pix_tiles;
-    const int64_t waves = (ctas + capacity - 1) / capacity;
-    const double cost = (double)waves * (3.0 + (double)per);
-    if (cost < best_cost - 1e-9) {
-      best_cost = cost;
-      best = (int)ch;
-    }
+// Column tiles per CTA.  Measured on B200 (profiles/r01c chunk sweeps): with the coefficient
+// tiles arriving by TMA the launch is fastest when a CTA covers about 256 slab columns (4 KL
+// tiles / 8 Voronoi tiles, 0.5 MB of cube): 0.93 of the measured HBM peak against 0.78 for CTAs
+// that walk all 93 column tiles, and 0.67 for one-tile CTAs.  Short CTAs let the dynamic CTA
+// scheduler even out SMs of unequal speed; the floor is the cost of staging the basis tile
+// (128 x Kp x 4 B per CTA, an L2 hit for all but the first chunk of a pixel tile), which
+// grows with the direction count -- hence the Kp / 12 term.
+int pick_tiles_per_cta(int ct, int Kp, int64_t n_ct) {
+  int64_t per = 256 / ct;
+  if (per < Kp / 12) per = Kp / 12;
+  if (per > n_ct) per = n_ct;
+  return (int)(per < 1 ? 1 : per);
+}
+
+// Stream-ordered scratch for the split coefficient tiles, from a library-private memory pool
+// (kept warm: release threshold = max), one per device.
+cudaMemPool_t scratch_pool(int device) {
+  static std::mutex mu;
+  static cudaMemPool_t pools[64] = {};
+  std::lock_guard<std::mutex> lock(mu);
+  if (device < 0 || device >= 64) return nullptr;
+  if (!pools[device]) {
+    cudaMemPoolProps props = {};
+    props.allocType = cudaMemAllocationTypePinned;
+    props.handleTypes = cudaMemHandleTypeNone;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = device;
+    cudaMemPool_t pool = nullptr;
+    if (cudaMemPoolCreate(&pool, &props) != cudaSuccess) return nullptr;
+    uint64_t keep = UINT64_MAX;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    pools[device] = pool;
   }
-  return best;
+  return pools[device];
+}
+
+template <bool KL, int NEPI>
+int launch_kernel(const float *Bt, const float *Bs, int ndir, int64_t npix, int64_t ncol, float *slab, int Kp,
+                  size_t smem, int per_sm, cudaStream_t stream) {
+  constexpr int CT = KL ? TC_N : TC_N / 2;
+  auto kfn = contract_tc_kernel<KL, NEPI>;
+  SSF_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int pix_tiles = (int)(npix / TC_M);
+  const int64_t n_ct = (ncol + CT - 1) / CT;
+  (void)per_sm;
+  int per = pick_tiles_per_cta(CT, Kp, n_ct);
+  if (const char *e = getenv("SSF_TC_PER")) {      // experiment hook: column tiles per CTA
+    per = atoi(e);
+    if (per < 1) per = 1;
+    if (per > n_ct) per = (int)n_ct;
+  }
+  const int gx = (int)((n_ct + per - 1) / per);
+  dim3 grid(gx, pix_tiles);
+  SSF_LAUNCH(kfn, grid, (NEPI + 2) * 32, smem, stream, Bt, Bs, ndir, npix, ncol, slab, per, Kp);
+  SSF_LAUNCHED();
+  return SSF_OK;
 }
 
 template <bool KL>
@@ -424,24 +457,26 @@ int launch_tc(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, 
               cudaStream_t stream) {
   constexpr int CT = KL ? TC_N : TC_N / 2;
   const int Kp = (ndir + 7) / 8 * 8;
-  const size_t smem = sizeof(float) * (size_t)(2 * TC_M + 4 * TC_N) * Kp + 64;
-  auto kfn = contract_tc_kernel<KL>;
-  SSF_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int pix_tiles = (int)(npix / TC_M);
   const int64_t n_ct = (ncol + CT - 1) / CT;
+  if (n_ct == 0) return SSF_OK;
+  const size_t smem = sizeof(float) * (size_t)(2 * TC_M + 2 * B_STAGES * TC_N) * Kp + 128;
   const int per_sm = 2 * (smem + 1024) <= 227 * 1024 ? 2 : 1;
-  int chunks = pick_chunks(pix_tiles, n_ct, 148 * per_sm);
-  if (const char *e = getenv("SSF_TC_CHUNKS")) {   // experiment hook
-    chunks = atoi(e);
-    if (chunks < 1) chunks = 1;
-    if (chunks > n_ct) chunks = (int)n_ct;
-  }
-  const int per = (int)((n_ct + chunks - 1) / chunks);
-  const int gx = (int)((n_ct + per - 1) / per);
-  dim3 grid(gx, pix_tiles);
-  SSF_LAUNCH(kfn, grid, TC_THREADS, smem, stream, Bt, G, ndir, ldg, npix, ncol, slab, per, Kp);
+
+  int device = 0;
+  SSF_CUDA(cudaGetDevice(&device));
+  cudaMemPool_t pool = scratch_pool(device);
+  SSF_REQUIRE(pool != nullptr, "tcgen05 contraction: could not create the scratch memory pool");
+  float *Bs = nullptr;
+  const size_t bs_bytes = sizeof(float) * (size_t)n_ct * 2 * TC_N * Kp;
+  SSF_CUDA(cudaMallocFromPoolAsync(reinterpret_cast<void **>(&Bs), bs_bytes, pool, stream));
+  const int64_t n_thr = n_ct * TC_N * (Kp >> 2);
+  SSF_LAUNCH(split_b_kernel<KL>, ssf::div_up(n_thr, 256), 256, 0, stream, G, ndir, ldg, ncol, Kp, n_ct, Bs);
   SSF_LAUNCHED();
-  return SSF_OK;
+  int rc = per_sm == 2 ? launch_kernel<KL, 8>(Bt, Bs, ndir, npix, ncol, slab, Kp, smem, per_sm, stream)
+                       : launch_kernel<KL, 16>(Bt, Bs, ndir, npix, ncol, slab, Kp, smem, per_sm, stream);
+  cudaError_t fe = cudaFreeAsync(Bs, stream);
+  if (rc == SSF_OK) SSF_CUDA(fe);
+  return rc;
 }
 
 }  // namespace

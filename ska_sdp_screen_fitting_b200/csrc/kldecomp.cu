@@ -21,7 +21,8 @@ inline double __drcp_rn(double x) { return 1.0 / x; }
 __global__ void __launch_bounds__(THREADS)
 decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__restrict__ masks,
                  double r0sq, double half_beta, double cut, double *__restrict__ Cout,
-                 double *__restrict__ Pout, double *__restrict__ Uout, double *__restrict__ svout) {
+                 double *__restrict__ Pout, double *__restrict__ Uout, double *__restrict__ svout,
+                 const int32_t *__restrict__ range, int32_t *__restrict__ status) {
   SSF_DYN_SMEM(double, sm);
   __shared__ int s_idx[SSF_MAX_DIR];
   __shared__ double s_c[SSF_MAX_DIR / 2 + 1], s_s[SSF_MAX_DIR / 2 + 1];
@@ -33,7 +34,10 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
   __shared__ double s_off, s_tot;
   __shared__ double s_inv[SSF_MAX_DIR];
 
-  const int pat = blockIdx.x;
+  // range != null: device-resident pattern cache -- this launch covers the slots
+  // [range[1], range[0]) that ssf_kl_patterns_update has just handed out (grid = upper bound)
+  const int pat = range ? range[1] + (int)blockIdx.x : (int)blockIdx.x;
+  if (range && pat >= range[0]) return;
   const int tid = threadIdx.x;
   const uint64_t m0 = masks[2 * pat], m1 = masks[2 * pat + 1];
   if (tid == 0) {
@@ -244,6 +248,7 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
     }
     s_rank[i] = rank;
     sv[rank] = converged ? li : nan("");
+    if (!converged && status) *status = 1;
     s_inv[i] = li > cut ? 1.0 / A[i * m + i] : 0.0;
   }
   __syncthreads();
@@ -262,6 +267,104 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
   }
 }
 
+
+// ------------------------------------------------------------------------------------ pattern cache
+// Device-resident map  flag pattern (128-bit mask) -> slot of its decomposition, so that a fit
+// pass needs no host round trip: open-addressing hash table, slots handed out by an atomic
+// counter, new slots decomposed by the same launch sequence.
+//   counters[0] = slots in use (slot 0 = the full pattern, decomposed by the caller)
+//   counters[1] = slots already decomposed
+//   counters[2] = 1 after an unrecoverable overflow (one pass has more patterns than slots)
+//   counters[3] = flagged systems of the current pass (scratch)
+constexpr int PC_EMPTY = -1, PC_BUSY = -2;
+
+__device__ __forceinline__ bool pc_is_full(uint64_t lo, uint64_t hi, int ndir) {
+  const uint64_t f0 = ndir >= 64 ? ~0ull : ((1ull << ndir) - 1);
+  const uint64_t f1 = ndir <= 64 ? 0ull : (ndir >= 128 ? ~0ull : ((1ull << (ndir - 64)) - 1));
+  return lo == f0 && hi == f1;
+}
+
+__global__ void pc_count_kernel(const uint64_t *__restrict__ masks, int64_t nsys, int ndir,
+                                int32_t *__restrict__ counters) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int flagged = 0;
+  if (i < nsys) flagged = pc_is_full(masks[2 * i], masks[2 * i + 1], ndir) ? 0 : 1;
+#ifndef SSF_CPU_EMU
+  flagged = __reduce_add_sync(0xffffffffu, flagged);
+  if ((threadIdx.x & 31) == 0 && flagged) atomicAdd(&counters[3], flagged);
+#else
+  if (flagged) atomicAdd(&counters[3], flagged);
+#endif
+}
+
+// If this pass could run out of slots, forget every cached pattern but the full one.  Every
+// thread evaluates the same condition (nobody writes the counters during this kernel).
+__global__ void pc_reset_kernel(int32_t *__restrict__ table_slots, int hash_cap, int max_slots,
+                                const int32_t *__restrict__ counters) {
+  if (counters[0] + counters[3] <= max_slots) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < hash_cap) table_slots[i] = PC_EMPTY;
+}
+__global__ void pc_reset_commit_kernel(int max_slots, int32_t *__restrict__ counters) {
+  if (counters[0] + counters[3] > max_slots) {
+    counters[0] = 1;
+    counters[1] = 1;
+    if (1 + counters[3] > max_slots) counters[2] = 1;
+  }
+  counters[3] = 0;
+}
+
+__global__ void pc_lookup_kernel(const uint64_t *__restrict__ masks, int64_t nsys, int ndir,
+                                 uint64_t *table_keys, int32_t *table_slots, int hash_cap,
+                                 uint64_t *__restrict__ slot_masks, int max_slots, int32_t *counters,
+                                 int32_t *__restrict__ pat) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nsys) return;
+  const uint64_t lo = masks[2 * i], hi = masks[2 * i + 1];
+  if (pc_is_full(lo, hi, ndir)) {
+    pat[i] = 0;
+    return;
+  }
+  uint64_t h = (lo ^ (hi * 0x9E3779B97F4A7C15ull)) * 0xD6E8FEB86659FD93ull;
+  h ^= h >> 32;
+  int pos = (int)(h & (uint64_t)(hash_cap - 1));
+  volatile int32_t *vslots = table_slots;
+  volatile uint64_t *vkeys = table_keys;
+  int result = 0;
+  for (int probes = 0; probes < hash_cap;) {
+    const int32_t s = vslots[pos];
+    if (s == PC_EMPTY) {
+      if (atomicCAS(&table_slots[pos], PC_EMPTY, PC_BUSY) == PC_EMPTY) {
+        const int slot = atomicAdd(&counters[0], 1);
+        if (slot >= max_slots) {                 // cannot happen after pc_reset unless one pass overflows
+          counters[2] = 1;
+          atomicExch(&table_slots[pos], PC_EMPTY);
+          break;
+        }
+        vkeys[2 * pos] = lo;
+        vkeys[2 * pos + 1] = hi;
+        slot_masks[2 * slot] = lo;
+        slot_masks[2 * slot + 1] = hi;
+        __threadfence();
+        atomicExch(&table_slots[pos], slot);     // publish
+        result = slot;
+        break;
+      }
+      continue;                                  // somebody else claimed it: look again
+    }
+    if (s == PC_BUSY) continue;                  // being filled in: the key is published with the slot
+    if (vkeys[2 * pos] == lo && vkeys[2 * pos + 1] == hi) {
+      result = s;
+      break;
+    }
+    pos = (pos + 1) & (hash_cap - 1);
+    ++probes;
+  }
+  pat[i] = result;
+}
+
+__global__ void pc_commit_kernel(int32_t *__restrict__ counters) { counters[1] = counters[0]; }
+
 }  // namespace
 
 extern "C" int ssf_kl_decompose(const double *pp, int ndir, const uint64_t *masks, int npat,
@@ -275,7 +378,46 @@ extern "C" int ssf_kl_decompose(const double *pp, int ndir, const uint64_t *mask
   if (smem > 48 * 1024)
     SSF_CUDA(cudaFuncSetAttribute(decompose_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   SSF_LAUNCH(decompose_kernel, npat, THREADS, smem, (cudaStream_t)stream, pp, ndir, masks, r0 * r0,
-             beta / 2.0, pinv_cut, C, pinvC, U, sv);
+             beta / 2.0, pinv_cut, C, pinvC, U, sv, (const int32_t *)nullptr, (int32_t *)nullptr);
+  SSF_LAUNCHED();
+  return SSF_OK;
+}
+
+
+extern "C" int ssf_kl_patterns_update(const uint64_t *masks, int64_t nsys, int ndir, const double *pp,
+                                      double r0, double beta, double pinv_cut, uint64_t *table_keys,
+                                      int32_t *table_slots, int hash_cap, uint64_t *slot_masks,
+                                      int max_slots, double *C, double *pinvC, double *U, double *sv,
+                                      int32_t *counters, int32_t *status, int32_t *pat, void *stream) {
+  SSF_REQUIRE(masks && pp && table_keys && table_slots && slot_masks && C && pinvC && U && sv && counters && pat,
+              "ssf_kl_patterns_update: null pointer");
+  SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR, "ssf_kl_patterns_update: ndir=%d out of range [1,%d]", ndir,
+              SSF_MAX_DIR);
+  SSF_REQUIRE(hash_cap >= 2 && (hash_cap & (hash_cap - 1)) == 0 && hash_cap >= 2 * max_slots && max_slots >= 2,
+              "ssf_kl_patterns_update: hash_cap must be a power of two >= 2 * max_slots");
+  if (nsys <= 0) return SSF_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nb = ssf::div_up(nsys, 256);
+  SSF_LAUNCH(pc_count_kernel, nb, 256, 0, st, masks, nsys, ndir, counters);
+  SSF_LAUNCHED();
+  SSF_LAUNCH(pc_reset_kernel, ssf::div_up(hash_cap, 256), 256, 0, st, table_slots, hash_cap, max_slots, counters);
+  SSF_LAUNCHED();
+  SSF_LAUNCH(pc_reset_commit_kernel, 1, 1, 0, st, max_slots, counters);
+  SSF_LAUNCHED();
+  SSF_LAUNCH(pc_lookup_kernel, nb, 256, 0, st, masks, nsys, ndir, table_keys, table_slots, hash_cap, slot_masks,
+             max_slots, counters, pat);
+  SSF_LAUNCHED();
+  // decompose the slots handed out by this pass: the grid is an upper bound, CTAs beyond
+  // counters[0] return at once
+  const int mmax = (ndir + 1) & ~1;
+  size_t smem = sizeof(double) * 2 * (size_t)mmax * mmax;
+  if (smem > 48 * 1024)
+    SSF_CUDA(cudaFuncSetAttribute(decompose_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t bound = nsys < max_slots ? nsys : max_slots;
+  SSF_LAUNCH(decompose_kernel, (int)bound, THREADS, smem, st, pp, ndir, slot_masks, r0 * r0, beta / 2.0, pinv_cut,
+             C, pinvC, U, sv, (const int32_t *)counters, status);
+  SSF_LAUNCHED();
+  SSF_LAUNCH(pc_commit_kernel, 1, 1, 0, st, counters);
   SSF_LAUNCHED();
   return SSF_OK;
 }

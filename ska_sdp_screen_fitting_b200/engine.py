@@ -6,6 +6,9 @@ torch is plumbing only (allocation, views, ``unique`` over flag masks); nothing 
 computes a screen in Python or falls back to the CPU.
 """
 import math
+import threading
+import time
+import weakref
 
 import numpy as np
 import torch
@@ -31,6 +34,9 @@ class Engine:
         self._lib = _lib.load(path)
         self._fit_status = None
         self.timers = None
+        self.host_times = {}
+        self._cpu_mark = {}
+        self._caches = weakref.WeakSet()
         emulated = path != _lib.LIB_PATH
         if device is None:
             device = "cpu" if emulated else "cuda"
@@ -64,6 +70,17 @@ class Engine:
             ms = [a.elapsed_time(b) for a, b in pairs]
             out[key] = (len(ms), sum(ms) / max(len(ms), 1))
         return out
+
+    def host_tick(self, label, t0):
+        """Accumulates host wall time per label (diagnostics of the fit's host path)."""
+        t1 = time.perf_counter()
+        self.host_times[label] = self.host_times.get(label, 0.0) + t1 - t0
+        # thread CPU time next to it tells "computing" from "blocked" (GIL, driver lock, sync)
+        c1 = time.thread_time()
+        c0 = self._cpu_mark.get(threading.get_ident(), c1)
+        self._cpu_mark[threading.get_ident()] = c1
+        self.host_times[label + ":cpu"] = self.host_times.get(label + ":cpu", 0.0) + c1 - c0
+        return t1
 
     def launch_count(self):
         return _lib.launch_count(self._lib)
@@ -115,7 +132,7 @@ class Engine:
             p = self.empty((npat, ndir, ndir), torch.float64)
             u = self.empty((npat, ndir, ndir), torch.float64)
             sv = self.empty((npat, ndir), torch.float64)
-        self._call("ssf_kl_decompose", _ptr(pp), ndir, _ptr(masks), npat, r0, beta, cut,
+        self._timed_call("kl_decompose", "ssf_kl_decompose", _ptr(pp), ndir, _ptr(masks), npat, r0, beta, cut,
                   _ptr(c), _ptr(p), _ptr(u), _ptr(sv), self.stream())
         return c, p, u, sv
 
@@ -126,7 +143,7 @@ class Engine:
         self._check(resid, torch.float64, "resid")
         self._check(weights, torch.float32, "weights")
         masks = self.empty((nsys, 2), torch.int64)
-        self._call("ssf_kl_flag_outliers", _ptr(resid), _ptr(weights), ndir, nsys, float(nsigma),
+        self._timed_call("kl_flag_outliers", "ssf_kl_flag_outliers", _ptr(resid), _ptr(weights), ndir, nsys, float(nsigma),
                   _ptr(masks), self.stream())
         return masks
 
@@ -141,7 +158,7 @@ class Engine:
             self._check(t, dt, nm)
         if status is None:
             status = self.zeros((1,), torch.int32)
-        self._call("ssf_kl_fit_pass", _ptr(phase), _ptr(weights), _ptr(pat), _ptr(pp), ndir, nsys,
+        self._timed_call("kl_fit_pass", "ssf_kl_fit_pass", _ptr(phase), _ptr(weights), _ptr(pat), _ptr(pp), ndir, nsys,
                    _ptr(c), _ptr(p), _ptr(u), r0, beta, cut, mode, _ptr(order), _ptr(station_order),
                    _ptr(white), _ptr(resid), _ptr(status), self.stream())
         return status
@@ -161,19 +178,24 @@ class Engine:
         resid = self.zeros((nsys, ndir), torch.float64)
         order = station_order.clone()
         if cache is None:
-            cache = PatternCache(self, pp, r0, beta, cut)
+            cache = PatternCache(self, pp, r0, beta, cut, max_bytes=256 << 20)
+        self._caches.add(cache)
         if self._fit_status is None:
             self._fit_status = self.zeros((2,), torch.int32)     # [weights out of range, no convergence]
         for it in range(niter):
+            t0 = time.perf_counter()
             masks = self.kl_flag_outliers(resid, weights, nsigma if it > 0 else math.inf)
+            t0 = self.host_tick("flag_launch", t0)
             if it > 0 and not adjust_order:
                 # the flagged weights alias the "previous" weights in the reference, so
                 # without order adjustment nothing is refitted (stationscreen.py:694-701)
                 continue
-            pat = cache.index(masks)
+            pat = cache.lookup(masks)
+            t0 = self.host_tick("pattern_lookup", t0)
             mode = 1 if (it > 0 and adjust_order) else 0
             self.kl_fit_pass(phase, weights, pat, pp, cache.mats, mode, order, station_order, white,
                              resid, r0, beta, cut, status=self._fit_status[0:1])
+            self.host_tick("fit_pass_launch", t0)
         if check:
             self.check_fit_status()
         return white, resid, order
@@ -183,6 +205,10 @@ class Engine:
             return
         bad_w, no_conv = (int(v) for v in self._fit_status.tolist())
         self._fit_status.zero_()
+        for cache in list(self._caches):
+            if cache.counters[2].item():
+                raise _lib.SsfError("ssf_kl_patterns_update", -5, "one fit pass has more distinct flag patterns "
+                                    "than the pattern cache has slots: raise PatternCache(max_bytes=...)")
         if no_conv:
             raise _lib.SsfError("ssf_kl_decompose", -3, "Jacobi eigen-solver did not converge")
         if bad_w:
@@ -279,84 +305,58 @@ class Engine:
 
 class PatternCache:
     """Decompositions (C_S, pinv C_S, U_S) of the flag patterns seen so far for one set of
-    pierce points, kept on the device across fit calls.
+    pierce points, kept on the device across fit calls -- together with the map from a
+    pattern to its slot (``ssf_kl_patterns_update``: device hash table, atomic slot counter,
+    new slots decomposed in the same launch sequence).
 
     The reference recomputes the SVD for every system with a flagged direction
     (stationscreen.py:493-499); systems that share a flag pattern share the result, within a
-    slab and across slabs, so each distinct pattern is decomposed once per run.  The dedupe is
-    host-side marshalling: the [nsys, 2] masks come back once per fit pass, a dict maps a
-    pattern to its slot, and only patterns never seen before go to ``ssf_kl_decompose``.
-    Slot 0 is the full pattern."""
+    slab and across slabs.  Nothing here reads anything back: a fit pass is a pure sequence of
+    stream-ordered launches, so the host never waits for the GPU and the fit of the next slabs
+    can be issued while the evaluation kernel owns the device.  Slot 0 is the full pattern.
+    When the slots run out the device forgets all patterns but slot 0 and starts over."""
 
-    def __init__(self, engine, pp, r0=R_0, beta=BETA, cut=PINV_CUT, max_bytes=4 << 30):
+    def __init__(self, engine, pp, r0=R_0, beta=BETA, cut=PINV_CUT, max_bytes=2 << 30):
         self.eng = engine
         self.pp = pp
-        self.ndir = pp.shape[0]
+        self.ndir = n = pp.shape[0]
         self.params = (r0, beta, cut)
-        self.full = tuple(Engine.full_mask(self.ndir))
-        per = (3 * self.ndir * self.ndir + self.ndir) * 8
-        self.max_slots = max(2, int(max_bytes // per))
-        self.slots = {}
-        self.count = 0
-        self.capacity = 0
-        self.c = self.p = self.u = self.sv = None
-        self.decomposed = 0
-        self._reserve(min(self.max_slots, 256))
-        self._add([self.full])
+        per = (3 * n * n + n) * 8 + 16
+        self.max_slots = int(max(2, min(max_bytes // per, 1 << 16)))
+        self.hash_cap = 1 << int(math.ceil(math.log2(2 * self.max_slots)))
+        self.c, self.p, self.u = (engine.empty((self.max_slots, n, n), torch.float64) for _ in range(3))
+        self.sv = engine.empty((self.max_slots, n), torch.float64)
+        self.slot_masks = engine.zeros((self.max_slots, 2), torch.int64)
+        self.table_keys = engine.zeros((self.hash_cap, 2), torch.int64)
+        self.table_slots = torch.full((self.hash_cap,), -1, dtype=torch.int32, device=engine.device)
+        self.counters = torch.tensor([1, 1, 0, 0], dtype=torch.int32, device=engine.device)
+        full = torch.tensor([Engine.full_mask(n)], dtype=torch.int64, device=engine.device)
+        self.slot_masks[0:1].copy_(full)
+        engine.kl_decompose(pp, full, r0, beta, cut,
+                            out=(self.c[0:1], self.p[0:1], self.u[0:1], self.sv[0:1]))
+        if engine._fit_status is None:
+            engine._fit_status = engine.zeros((2,), torch.int32)
+        engine._fit_status[1:2] += torch.isnan(self.sv[0]).any().to(torch.int32)
 
     @property
     def mats(self):
         return self.c, self.p, self.u
 
-    def _reserve(self, capacity):
-        eng, n = self.eng, self.ndir
-        new = [eng.empty((capacity, n, n), torch.float64) for _ in range(3)] + [eng.empty((capacity, n), torch.float64)]
-        if self.count:
-            for dst, src in zip(new, (self.c, self.p, self.u, self.sv)):
-                dst[:self.count].copy_(src[:self.count])
-            if eng.device.type == "cuda":
-                torch.cuda.synchronize(eng.device)       # growth is rare; old stores may be in use on another stream
-        self.c, self.p, self.u, self.sv = new
-        self.capacity = capacity
-
-    def _add(self, keys):
-        """Decomposes new patterns into the next free slots."""
-        eng = self.eng
-        n_new = len(keys)
-        if self.count + n_new > self.capacity:
-            self._reserve(min(self.max_slots, max(2 * self.capacity, self.count + n_new)))
-        base = self.count
-        masks = torch.tensor(keys, dtype=torch.int64).reshape(n_new, 2).to(eng.device)
-        out = tuple(t[base:base + n_new] for t in (self.c, self.p, self.u, self.sv))
-        eng.kl_decompose(self.pp, masks, *self.params, out=out)
-        if eng._fit_status is None:
-            eng._fit_status = eng.zeros((2,), torch.int32)
-        eng._fit_status[1:2] += torch.isnan(out[3]).any().to(torch.int32)
-        for i, key in enumerate(keys):
-            self.slots[key] = base + i
-        self.count += n_new
-        self.decomposed += n_new
-
-    def index(self, masks):
+    def lookup(self, masks, out=None):
         """masks: device [nsys, 2] int64 bit patterns -> device int32 [nsys] slot of each
-        system's pattern (decomposing the ones not seen before)."""
-        m = masks.cpu().numpy()
-        nsys = m.shape[0]
-        pat = np.zeros(nsys, np.int32)
-        rows = np.nonzero((m[:, 0] != self.full[0]) | (m[:, 1] != self.full[1]))[0]
-        if rows.size:
-            uniq, inv = np.unique(m[rows], axis=0, return_inverse=True)
-            keys = [(int(a), int(b)) for a, b in uniq]
-            fresh = [k for k in keys if k not in self.slots]
-            if self.count + len(fresh) > self.max_slots:
-                # out of budget: forget everything but the full pattern and start over
-                self.slots = {self.full: 0}
-                self.count = 1
-                fresh = keys
-                if 1 + len(fresh) > self.max_slots:
-                    raise MemoryError("pattern cache budget too small for one fit pass")
-            if fresh:
-                self._add(fresh)
-            slot = np.fromiter((self.slots[k] for k in keys), np.int32, len(keys))
-            pat[rows] = slot[inv.reshape(-1)]
-        return torch.from_numpy(pat).to(self.eng.device)
+        system's pattern; the patterns not seen before are decomposed (stream-ordered)."""
+        eng = self.eng
+        nsys = masks.shape[0]
+        pat = out if out is not None else eng.empty((nsys,), torch.int32)
+        r0, beta, cut = self.params
+        eng._timed_call("kl_patterns_update", "ssf_kl_patterns_update", _ptr(masks), nsys, self.ndir,
+                        _ptr(self.pp), r0, beta, cut, _ptr(self.table_keys), _ptr(self.table_slots),
+                        self.hash_cap, _ptr(self.slot_masks), self.max_slots, _ptr(self.c), _ptr(self.p),
+                        _ptr(self.u), _ptr(self.sv), _ptr(self.counters), _ptr(eng._fit_status[1:2]),
+                        _ptr(pat), eng.stream())
+        return pat
+
+    def stats(self):
+        """(slots in use, overflow flag) -- reads the counters back (synchronises)."""
+        c = self.counters.tolist()
+        return c[0], c[2]

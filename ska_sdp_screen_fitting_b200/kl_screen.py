@@ -74,7 +74,9 @@ class KLScreen(Screen):
         self._pinv_full = None
         self._fit_stream = None
         self._patterns = None
-        self.fit_ahead = 2                # slabs the streaming fit runs ahead of the evaluation
+        self.fit_ahead = 2                # fit groups the streaming fit runs ahead of the evaluation
+        self.fit_group = 4                # slabs fitted per fit call (amortises the per-call host work)
+        self._settle = None
 
     # ------------------------------------------------------------------ fit
     def setup(self, sol, antenna_weight_sums=None):
@@ -119,6 +121,7 @@ class KLScreen(Screen):
         weight [t, f, a, d] f32 (any number of time slots).  Returns device tensors
         (white [t,f,a,d], resid [t,f,a,d], order [t,f,a], weights_out [t,f,a,d])."""
         eng = self.engine
+        t_host = time.perf_counter()
         n_t, n_f, n_a, n_d = val.shape
         ref_ind = self.ref_ind
         if ref_ind != -1:                                                 # stationscreen.py:994-997
@@ -128,6 +131,7 @@ class KLScreen(Screen):
         skip[:, ref_ind] = True
         work_w = torch.where(skip[None, :, :, None], torch.zeros_like(weight), weight).contiguous()
         so = self._so_dev[None, None, :].expand(n_t, n_f, n_a).reshape(-1).contiguous()
+        eng.host_tick("fit_prelude", t_host)
         white, resid, order = eng.kl_fit(val.reshape(-1, n_d).contiguous(), work_w.view(-1, n_d),
                                          so, self._pp_dev, niter=2, nsigma=5.0, adjust_order=True,
                                          r0=self.r_0, beta=self.beta_val, cut=PINV_CUT,
@@ -162,21 +166,28 @@ class KLScreen(Screen):
 
         side.wait_stream(main)                           # inputs / setup are ready
 
-        def launch_fit(k):
+        group = max(1, int(self.fit_group))
+        state = {"last_done": None, "blocked": False}
+
+        def launch_fit(k0, k1):
+            """One fit call over the time slots of slabs [k0, k1)."""
             t_host = time.perf_counter()
             with torch.cuda.stream(side):
-                white = self.fit_device(val_dev[k * slots:(k + 1) * slots],
-                                        wt_dev[k * slots:(k + 1) * slots], check=False)[0]
+                white = self.fit_device(val_dev[k0 * slots:k1 * slots],
+                                        wt_dev[k0 * slots:k1 * slots], check=False)[0]
                 done = torch.cuda.Event()
                 done.record(side)
+            state["last_done"] = done
             white.record_stream(main)
             self.timings["fit_host_s"] = self.timings.get("fit_host_s", 0.0) + time.perf_counter() - t_host
             self.timings["fit_calls"] = self.timings.get("fit_calls", 0) + 1
-            return white, done
+            self.timings["fit_slabs"] = self.timings.get("fit_slabs", 0) + (k1 - k0)
+            return k0, k1, white, done
 
-        # The fits are issued by a helper thread that runs up to `ahead` slabs in front of the
-        # evaluation: the host-side part of a fit (pattern lookup: one small blocking D2H per
-        # pass) then never keeps the evaluation stream waiting for its next launch.
+        # The fits are issued by a helper thread that runs up to `ahead` groups of `group` slabs
+        # in front of the evaluation: the host-side part of a fit (pattern lookup: one small
+        # blocking D2H per pass, a fixed cost per call whatever the number of systems) is paid
+        # once per group and never keeps the evaluation stream waiting for its next launch.
         ahead = max(1, int(self.fit_ahead))
         ready = queue.Queue(maxsize=ahead)
         stop = threading.Event()
@@ -184,34 +195,58 @@ class KLScreen(Screen):
         def issue_fits():
             try:
                 torch.cuda.set_device(eng.device)
-                for k in range(first, last):
-                    item = launch_fit(k)
+                for k0 in range(first, last, group):
+                    item = launch_fit(k0, min(last, k0 + group))
                     while not stop.is_set():
                         try:
-                            ready.put(item, timeout=0.05)
+                            ready.put_nowait(item)
                             break
                         except queue.Full:
-                            continue
+                            state["blocked"] = True       # as far ahead as allowed
+                            time.sleep(0.0002)
+                    state["blocked"] = False
                     if stop.is_set():
                         return
             except BaseException as exc:  # surfaced in the consumer
                 ready.put(exc)
 
+        def settle():
+            """Blocks until the helper has issued every fit it may run ahead (or all of them) and
+            orders the main stream after the last one: benchmarks call this on both sides of a
+            timed region so that the region contains as many slab fits as slab evaluations."""
+            time.sleep(0.001)            # let the helper notice a slot the consumer just freed
+            while helper.is_alive() and not state["blocked"]:
+                time.sleep(0.0002)
+            if state["last_done"] is not None:
+                main.wait_event(state["last_done"])
+
+        self._settle = settle
+
         helper = threading.Thread(target=issue_fits, name="ssf-fit", daemon=True)
         helper.start()
         try:
-            for k in range(first, last):
+            k = first
+            while k < last:
                 item = ready.get()
                 if isinstance(item, BaseException):
                     raise item
-                white, done = item
+                k0, k1, white, done = item
                 main.wait_event(done)
-                slab = ring[k % len(ring)]
-                self._fill_columns(white.view(-1, n_d), slab, cellsize_deg, None, 0.0, True)
-                yield k, slab
+                white = white.view(k1 - k0, -1, n_d)
+                for k in range(k0, k1):
+                    slab = ring[k % len(ring)]
+                    self._fill_columns(white[k - k0], slab, cellsize_deg, None, 0.0, True)
+                    yield k, slab
+                k = k1
         finally:
             stop.set()
             helper.join(timeout=30)
+            self._settle = None
+
+    def settle_fit_lead(self):
+        """See ``stream_slabs``: no-op unless a streamed run is active."""
+        if self._settle is not None:
+            self._settle()
 
     def fit(self):
         """kl_screen.py:61-155 + stationscreen.run (phase type)."""

@@ -93,6 +93,8 @@ static inline float __int_as_float(int i) { float f; memcpy(&f, &i, 4); return f
 static inline int __float_as_int(float f) { int i; memcpy(&i, &f, 4); return i; }
 template <typename T> static inline T atomicExch(T *p, T v) { T o = *p; *p = v; return o; }
 template <typename T> static inline T atomicAdd(T *p, T v) { T o = *p; *p = o + v; return o; }
+template <typename T> static inline T atomicCAS(T *p, T cmp, T v) { T o = *p; if (o == cmp) *p = v; return o; }
+static inline void __threadfence() {}
 static inline uint32_t __byte_perm(uint32_t a, uint32_t b, uint32_t sel) {
   uint64_t v = ((uint64_t)b << 32) | a;
   uint32_t r = 0;

@@ -165,6 +165,42 @@ def test_host_entry_points(gpu_engine):
     assert np.abs(out - screens.kl_make_matrix(x, y, pp, white)).max() < pc.TOL_KL
 
 
+def test_streamed_kl_slabs_match_the_whole_fit(gpu_engine):
+    """KLScreen.stream_slabs (grouped fits on a side stream issued by a helper thread, ragged
+    last group) gives the same cube slabs as one fit over all time slots followed by the
+    evaluation -- the fit systems are independent across time (stationscreen.py:681-722)."""
+    from ska_sdp_screen_fitting_b200 import synthetic
+    from ska_sdp_screen_fitting_b200.kl_screen import KLScreen
+
+    case = synthetic.make_case("small", seed=11, n_times=10, flag_fraction=0.05)
+    sol = case.solutions
+    eng = gpu_engine
+    kl = KLScreen("t", None, None, case.rad, case.dec, case.width_deg, case.width_deg)
+    kl._engine = eng
+    kl.setup(sol)
+    val, wt = eng.tensor(sol.val, torch.float64), eng.tensor(sol.weight, torch.float32)
+    n_t, n_f, n_a, n_d = sol.val.shape
+    n, slots = case.n_pix, 2
+    cols = slots * n_f * n_a
+    white = kl.fit_device(val, wt)[0]
+    want = []
+    for k in range(n_t // slots):
+        slab = eng.empty((cols, 4, n, n), torch.float32)
+        kl._fill_columns(white[k * slots:(k + 1) * slots].reshape(-1, n_d), slab, case.cellsize_deg, None, 0.0, True)
+        want.append(slab.cpu().numpy())
+    for group in (1, 2, 4):
+        kl.fit_group = group
+        ring = [eng.empty((cols, 4, n, n), torch.float32) for _ in range(2)]
+        seen = 0
+        for k, slab in kl.stream_slabs(val, wt, slots, ring, case.cellsize_deg):
+            assert k == seen
+            got = slab.cpu().numpy()
+            assert np.abs(got - want[k]).max() < 2e-6, (group, k)
+            seen += 1
+        assert seen == n_t // slots
+        eng.check_fit_status()
+
+
 @pytest.mark.parametrize("screen_type", ["tessellated", "kl"])
 def test_make_aterm_image_repo_configs(gpu_engine, golden_dir, tmp_path, screen_type):
     """BASELINE.json configs[0] / configs[1] through the public API, against the cubes the
