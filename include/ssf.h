@@ -156,6 +156,14 @@ int ssf_voronoi_lut(const double *phase, const double *amp, int64_t ncol, int nd
 int ssf_voronoi_fill(const int32_t *tmpl, const float *lut, int ndir, int64_t npix,
                      int64_t ncol, float *slab, int fix_nan, void *stream);
 
+/* Gain solutions (scalar phase + XX/YY amplitudes, voronoi_screen.py:177-214):
+ * amp [ncol, ndir, 2] f64 = (XX, YY) amplitudes; lut4 [ncol, ndir, 4] f32 =
+ * (axx cos, axx sin, ayy cos, ayy sin); slab[col, p, pix] = lut4[col, tmpl[pix]-1, p]. */
+int ssf_voronoi_lut_gain(const double *phase, const double *amp, int64_t ncol, int ndir,
+                         float *lut4, void *stream);
+int ssf_voronoi_fill_gain(const int32_t *tmpl, const float *lut4, int ndir, int64_t npix,
+                          int64_t ncol, float *slab, int fix_nan, void *stream);
+
 /* Smoothed Voronoi through linearity: slab[col, p, pix] = sum_d S[d, pix] * lut[col, d, p&1]
  * where S[d, :] is the Gaussian-smoothed indicator image of cell d (built with
  * ssf_voronoi_indicators + ssf_gauss_smooth).  Same result as fill -> gaussian_filter

@@ -47,6 +47,8 @@ SIGNATURES = {
     "ssf_voronoi_assign": (c_int, [_P, _P, c_int, c_int, c_int, _P, _P]),
     "ssf_voronoi_lut": (c_int, [_P, _P, c_int64, c_int, _P, _P]),
     "ssf_voronoi_fill": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, c_int, _P]),
+    "ssf_voronoi_lut_gain": (c_int, [_P, _P, c_int64, c_int, _P, _P]),
+    "ssf_voronoi_fill_gain": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, c_int, _P]),
     "ssf_voronoi_indicators": (c_int, [_P, c_int, c_int64, _P, _P]),
     "ssf_voronoi_contract": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, c_int, _P]),
     "ssf_gauss_smooth": (c_int, [_P, c_int64, c_int, c_int, c_double, _P, _P]),

@@ -89,6 +89,60 @@ __global__ void fill_kernel(const int32_t *__restrict__ tmpl, const float2 *__re
   }
 }
 
+// Gain (amplitude + phase) solutions: planes 0/1 carry the XX amplitude, planes 2/3 the YY one
+// (voronoi_screen.py:177-214).  lut4[col, d] = (axx cos, axx sin, ayy cos, ayy sin), the FP64
+// products rounded once to float32.
+__global__ void lut_gain_kernel(const double *__restrict__ phase, const double *__restrict__ amp,
+                                int64_t n, float4 *__restrict__ lut) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    double s, c;
+    sincos(phase[i], &s, &c);
+    const double ax = amp[2 * i], ay = amp[2 * i + 1];
+    lut[i] = make_float4((float)(ax * c), (float)(ax * s), (float)(ay * c), (float)(ay * s));
+  }
+}
+
+template <bool VEC4>
+__global__ void fill_gain_kernel(const int32_t *__restrict__ tmpl, const float4 *__restrict__ lut,
+                                 int ndir, int64_t npix, int64_t ncol, float *__restrict__ slab,
+                                 int fix_nan) {
+  const int64_t per_col = VEC4 ? npix / 4 : npix;
+  const int64_t total = per_col * ncol;
+  for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < total;
+       w += (int64_t)gridDim.x * blockDim.x) {
+    int64_t col = w / per_col;
+    int64_t q = w - col * per_col;
+    const float4 *row = lut + col * ndir;
+    float *out = slab + col * 4 * npix;
+    if (VEC4) {
+      int4 t = __ldg(reinterpret_cast<const int4 *>(tmpl) + q);
+      float4 a = __ldg(row + (t.x - 1)), b = __ldg(row + (t.y - 1));
+      float4 c = __ldg(row + (t.z - 1)), d = __ldg(row + (t.w - 1));
+      float4 p0 = make_float4(a.x, b.x, c.x, d.x), p1 = make_float4(a.y, b.y, c.y, d.y);
+      float4 p2 = make_float4(a.z, b.z, c.z, d.z), p3 = make_float4(a.w, b.w, c.w, d.w);
+      if (fix_nan) {
+        p0 = make_float4(ssf::fix_re(p0.x), ssf::fix_re(p0.y), ssf::fix_re(p0.z), ssf::fix_re(p0.w));
+        p1 = make_float4(ssf::fix_im(p1.x), ssf::fix_im(p1.y), ssf::fix_im(p1.z), ssf::fix_im(p1.w));
+        p2 = make_float4(ssf::fix_re(p2.x), ssf::fix_re(p2.y), ssf::fix_re(p2.z), ssf::fix_re(p2.w));
+        p3 = make_float4(ssf::fix_im(p3.x), ssf::fix_im(p3.y), ssf::fix_im(p3.z), ssf::fix_im(p3.w));
+      }
+      float4 *o = reinterpret_cast<float4 *>(out) + q;
+      const int64_t ps = npix / 4;
+      __stcs(o, p0);
+      __stcs(o + ps, p1);
+      __stcs(o + 2 * ps, p2);
+      __stcs(o + 3 * ps, p3);
+    } else {
+      float4 a = __ldg(row + (__ldg(tmpl + q) - 1));
+      out[q] = fix_nan ? ssf::fix_re(a.x) : a.x;
+      out[npix + q] = fix_nan ? ssf::fix_im(a.y) : a.y;
+      out[2 * npix + q] = fix_nan ? ssf::fix_re(a.z) : a.z;
+      out[3 * npix + q] = fix_nan ? ssf::fix_im(a.w) : a.w;
+    }
+  }
+}
+
 __global__ void indicator_kernel(const int32_t *__restrict__ tmpl, int ndir, int64_t npix,
                                  float *__restrict__ ind) {
   // ind[d, pix] = (tmpl[pix] == d + 1)
@@ -170,6 +224,36 @@ extern "C" int ssf_voronoi_fill(const int32_t *tmpl, const float *lut, int ndir,
   } else {
     SSF_LAUNCH(fill_kernel<false>, grid_for(npix * ncol, 256, 8), 256, 0, (cudaStream_t)stream,
                tmpl, (const float2 *)lut, ndir, npix, ncol, slab, fix_nan);
+  }
+  SSF_LAUNCHED();
+  return SSF_OK;
+}
+
+extern "C" int ssf_voronoi_lut_gain(const double *phase, const double *amp, int64_t ncol, int ndir,
+                                    float *lut4, void *stream) {
+  SSF_REQUIRE(phase && amp && lut4, "ssf_voronoi_lut_gain: null pointer");
+  SSF_REQUIRE(ncol >= 0 && ndir >= 1, "ssf_voronoi_lut_gain: bad sizes");
+  SSF_REQUIRE((uintptr_t)lut4 % 16 == 0, "ssf_voronoi_lut_gain: lut4 must be 16-byte aligned");
+  if (ncol == 0) return SSF_OK;
+  int64_t n = ncol * ndir;
+  SSF_LAUNCH(lut_gain_kernel, grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream, phase, amp, n, (float4 *)lut4);
+  SSF_LAUNCHED();
+  return SSF_OK;
+}
+
+extern "C" int ssf_voronoi_fill_gain(const int32_t *tmpl, const float *lut4, int ndir, int64_t npix,
+                                     int64_t ncol, float *slab, int fix_nan, void *stream) {
+  SSF_REQUIRE(tmpl && lut4 && slab, "ssf_voronoi_fill_gain: null pointer");
+  SSF_REQUIRE(ndir >= 1 && npix >= 1 && ncol >= 0, "ssf_voronoi_fill_gain: bad sizes");
+  SSF_REQUIRE((uintptr_t)lut4 % 16 == 0, "ssf_voronoi_fill_gain: lut4 must be 16-byte aligned");
+  if (ncol == 0) return SSF_OK;
+  bool vec = (npix % 4 == 0) && ((uintptr_t)slab % 16 == 0) && ((uintptr_t)tmpl % 16 == 0);
+  if (vec) {
+    SSF_LAUNCH(fill_gain_kernel<true>, grid_for(npix / 4 * ncol, 256, 8), 256, 0, (cudaStream_t)stream,
+               tmpl, (const float4 *)lut4, ndir, npix, ncol, slab, fix_nan);
+  } else {
+    SSF_LAUNCH(fill_gain_kernel<false>, grid_for(npix * ncol, 256, 8), 256, 0, (cudaStream_t)stream,
+               tmpl, (const float4 *)lut4, ndir, npix, ncol, slab, fix_nan);
   }
   SSF_LAUNCHED();
   return SSF_OK;

@@ -266,6 +266,28 @@ class Engine:
                   1 if fix_nan else 0, self.stream())
         return slab
 
+    def voronoi_lut_gain(self, phase, amp):
+        """phase [ncol, ndir] f64, amp [ncol, ndir, 2] f64 (XX, YY) -> lut4 [ncol, ndir, 4] f32."""
+        ncol, ndir = phase.shape
+        self._check(phase, torch.float64, "phase")
+        self._check(amp, torch.float64, "amp")
+        if tuple(amp.shape) != (ncol, ndir, 2):
+            raise ValueError("amp must be [ncol, ndir, 2]")
+        lut = self.empty((ncol, ndir, 4), torch.float32)
+        self._call("ssf_voronoi_lut_gain", _ptr(phase), _ptr(amp), ncol, ndir, _ptr(lut), self.stream())
+        return lut
+
+    def voronoi_fill_gain(self, tmpl, lut4, slab, fix_nan=True):
+        ncol, ndir, _ = lut4.shape
+        npix = tmpl.numel()
+        self._check(tmpl, torch.int32, "tmpl")
+        self._check(slab, torch.float32, "slab")
+        if slab.numel() != ncol * 4 * npix:
+            raise ValueError("slab has the wrong size")
+        self._timed_call("voronoi_fill", "ssf_voronoi_fill_gain", _ptr(tmpl), _ptr(lut4), ndir, npix, ncol,
+                         _ptr(slab), 1 if fix_nan else 0, self.stream())
+        return slab
+
     def voronoi_indicators(self, tmpl, ndir):
         npix = tmpl.numel()
         ind = self.empty((ndir,) + tuple(tmpl.shape), torch.float32)
