@@ -10,7 +10,8 @@
 
 namespace {
 
-constexpr int THREADS = 256;
+// threads per CTA: 256 for up to 64 directions; 512 above, where a pattern's two 100 x 100
+// FP64 matrices leave room for only one CTA per SM and more warps hide the latency
 constexpr int MAX_SWEEPS = 40;
 
 #ifdef SSF_CPU_EMU
@@ -18,6 +19,7 @@ inline double rsqrt(double x) { return 1.0 / sqrt(x); }
 inline double __drcp_rn(double x) { return 1.0 / x; }
 #endif
 
+template <int THREADS>
 __global__ void __launch_bounds__(THREADS)
 decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__restrict__ masks,
                  double r0sq, double half_beta, double cut, double *__restrict__ Cout,
@@ -375,10 +377,15 @@ extern "C" int ssf_kl_decompose(const double *pp, int ndir, const uint64_t *mask
   if (npat <= 0) return SSF_OK;
   const int mmax = (ndir + 1) & ~1;
   size_t smem = sizeof(double) * 2 * (size_t)mmax * mmax;
-  if (smem > 48 * 1024)
-    SSF_CUDA(cudaFuncSetAttribute(decompose_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  SSF_LAUNCH(decompose_kernel, npat, THREADS, smem, (cudaStream_t)stream, pp, ndir, masks, r0 * r0,
-             beta / 2.0, pinv_cut, C, pinvC, U, sv, (const int32_t *)nullptr, (int32_t *)nullptr);
+  SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
+  SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
+  if (ndir > 64) {
+    SSF_LAUNCH(decompose_kernel<512>, npat, 512, smem, (cudaStream_t)stream, pp, ndir, masks, r0 * r0,
+               beta / 2.0, pinv_cut, C, pinvC, U, sv, (const int32_t *)nullptr, (int32_t *)nullptr);
+  } else {
+    SSF_LAUNCH(decompose_kernel<256>, npat, 256, smem, (cudaStream_t)stream, pp, ndir, masks, r0 * r0,
+               beta / 2.0, pinv_cut, C, pinvC, U, sv, (const int32_t *)nullptr, (int32_t *)nullptr);
+  }
   SSF_LAUNCHED();
   return SSF_OK;
 }
@@ -411,11 +418,16 @@ extern "C" int ssf_kl_patterns_update(const uint64_t *masks, int64_t nsys, int n
   // counters[0] return at once
   const int mmax = (ndir + 1) & ~1;
   size_t smem = sizeof(double) * 2 * (size_t)mmax * mmax;
-  if (smem > 48 * 1024)
-    SSF_CUDA(cudaFuncSetAttribute(decompose_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t bound = nsys < max_slots ? nsys : max_slots;
-  SSF_LAUNCH(decompose_kernel, (int)bound, THREADS, smem, st, pp, ndir, slot_masks, r0 * r0, beta / 2.0, pinv_cut,
-             C, pinvC, U, sv, (const int32_t *)counters, status);
+  if (ndir > 64) {
+    SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
+    SSF_LAUNCH(decompose_kernel<512>, (int)bound, 512, smem, st, pp, ndir, slot_masks, r0 * r0, beta / 2.0, pinv_cut,
+               C, pinvC, U, sv, (const int32_t *)counters, status);
+  } else {
+    SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
+    SSF_LAUNCH(decompose_kernel<256>, (int)bound, 256, smem, st, pp, ndir, slot_masks, r0 * r0, beta / 2.0, pinv_cut,
+               C, pinvC, U, sv, (const int32_t *)counters, status);
+  }
   SSF_LAUNCHED();
   SSF_LAUNCH(pc_commit_kernel, 1, 1, 0, st, counters);
   SSF_LAUNCHED();
