@@ -72,19 +72,41 @@ def recorded_traffic(kernel):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    """SM clocks / throttle reasons sampled DURING the timed region: in-process NVML
+    (nvidia_ml_py) every 50 ms from a helper thread; `nvidia-smi -lms` as the fallback.  One
+    nvidia-smi process per rank on an 8-GPU box takes seconds to start and contends for the
+    driver with the ranks' launches, NVML in-process does neither."""
 
     QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
              "clocks_event_reasons.sw_power_cap")
+    # nvmlClocksEventReason* bit masks
+    REASONS = {"sw_power_cap": 0x4, "hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20,
+               "hw_thermal_slowdown": 0x40}
 
     def __init__(self, index):
         self.index = index
-        self.rows = []
+        self.rows = []          # (stamp, sm_mhz, sm_max_mhz, [reason names])
         self._proc = None
         self._thread = None
+        self._stop = threading.Event()
+        self._nvml = None
 
     def start(self):
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(visible.split(",")[self.index]) if visible and visible.replace(",", "").isdigit() else self.index
+            handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            smax = float(pynvml.nvmlDeviceGetMaxClockInfo(handle, pynvml.NVML_CLOCK_SM))
+            self._nvml = (pynvml, handle, smax)
+            self._thread = threading.Thread(target=self._poll_nvml, daemon=True)
+            self._thread.start()
+            return
+        except Exception:  # noqa: BLE001 - any NVML problem -> nvidia-smi
+            self._nvml = None
         try:
             self._proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.QUERY}",
@@ -95,31 +117,48 @@ class ClockSampler:
         self._thread = threading.Thread(target=self._pump, daemon=True)
         self._thread.start()
 
-    def _pump(self):
-        for line in self._proc.stdout:
-            self.rows.append((time.time(), line.strip()))
-
-    def stop(self, t_begin, t_end):
-        if self._proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self._proc.terminate()
-        sm, smax, reasons = [], None, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for stamp, line in self.rows:
-            if not t_begin - 0.05 <= stamp <= t_end + 0.15:
-                continue
-            cells = [c.strip() for c in line.split(",")]
+    def _poll_nvml(self):
+        pynvml, handle, smax = self._nvml
+        while not self._stop.is_set():
             try:
-                sm.append(float(cells[0]))
-                smax = float(cells[1])
+                sm = float(pynvml.nvmlDeviceGetClockInfo(handle, pynvml.NVML_CLOCK_SM))
+                try:
+                    bits = pynvml.nvmlDeviceGetCurrentClocksEventReasons(handle)
+                except Exception:  # noqa: BLE001 - older binding name
+                    bits = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(handle)
+                self.rows.append((time.time(), sm, smax, [n for n, m in self.REASONS.items() if bits & m]))
+            except Exception:  # noqa: BLE001
+                pass
+            self._stop.wait(0.05)
+
+    def _pump(self):
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self._proc.stdout:
+            cells = [c.strip() for c in line.strip().split(",")]
+            try:
+                sm, smax = float(cells[0]), float(cells[1])
             except (ValueError, IndexError):
                 continue
-            for name, cell in zip(names, cells[3:7]):
-                if cell.lower().startswith("active"):
-                    reasons.add(name)
+            why = [n for n, c in zip(names, cells[3:7]) if c.lower().startswith("active")]
+            self.rows.append((time.time(), sm, smax, why))
+
+    def stop(self, t_begin, t_end):
+        if self._thread is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no clock source (NVML, nvidia-smi) available"]}
+        if self._nvml is None:
+            time.sleep(0.15)
+            self._proc.terminate()
+        self._stop.set()
+        sm, smax, reasons = [], None, set()
+        for stamp, mhz, mx, why in list(self.rows):
+            if not t_begin - 0.05 <= stamp <= t_end + 0.15:
+                continue
+            sm.append(mhz)
+            smax = mx
+            reasons.update(why)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "reasons": sorted(reasons),
+                "source": "nvml" if self._nvml is not None else "nvidia-smi"}
 
 
 # ---------------------------------------------------------------------------- workload
@@ -228,6 +267,7 @@ def run_ours(args):
         sampler.start()
         time.sleep(0.25)
         eng.timers = {}
+        eng.host_times = {}
         kl.timings.pop("fit_host_s", None)
         kl.timings.pop("fit_calls", None)
         kl.timings.pop("fit_slabs", None)
@@ -263,7 +303,6 @@ def run_ours(args):
     peak, peak_src = measured_peaks()
     out = {}
     if args.workload != "voronoi1k":
-        eng.host_times = {}
         ms, launches, kern, clocks = timed(kl_step, ["kl_eval", "kl_patterns_update", "kl_flag_outliers", "kl_fit_pass"])
         # side-stream spans (queueing behind the evaluation's CTAs + execution), whole run incl. warm-up for the host part
         fit_breakdown = {k: {"calls": kern[k][0], "mean_ms": kern[k][1]} for k in kern if k != "kl_eval"}

@@ -1,0 +1,97 @@
+"""
+TEST INFRASTRUCTURE (oracle): golden vectors for the gain ("amplitude + phase") path,
+produced by the REFERENCE's own code under ``oracle.refshim``.
+
+The repo's ``solutions.h5`` is phase-only, and there is no HDF5 writer in this image, so a
+seeded synthetic ``amplitude000`` soltab (slow grid: 5 times x 3 freqs, XX/YY) is overlaid on
+the real file in memory (``fake_h5parm.add_soltab``) and the reference is run with
+``soltabname="gain000"`` (make_aterm_images.py:71-74) for both screen types.  The amplitude
+inputs are stored in the fixture so the product reads exactly the same numbers.
+
+    python -m oracle.make_golden --only gain
+"""
+import os
+import shutil
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+SUB_F = (0, 5, 11)
+SUB_A = (0, 1, 30, 61)
+
+TEST_ARGS = dict(
+    bounds_deg=[124.565, 66.165, 127.895, 62.835],
+    bounds_mid_deg=[126.23, 64.50],
+    skymodel="skymodel.txt",
+    solsetname="sol000",
+    padding_fraction=0,
+    cellsize_deg=0.2,
+    ncpu=0,
+)
+
+
+def synthetic_amplitudes(times_ph, freqs_ph, n_ant, n_dir, seed=17):
+    """Slow XX/YY amplitudes on a coarser grid than the phases: smooth over direction and
+    station, a few flagged solutions and a few gross outliers (exercise _flag_outliers)."""
+    rng = np.random.default_rng(seed)
+    t_amp = np.linspace(times_ph[0] + 3.0, times_ph[-1] - 5.0, 5)
+    f_amp = np.array([freqs_ph[1], freqs_ph[5], freqs_ph[10]]) + 1.0e3
+    d_slope = rng.normal(0.0, 0.05, (n_dir, 2))
+    a_gain = rng.normal(0.0, 0.03, (n_ant, 1, 2))
+    val = (1.0 + a_gain[None, None] + d_slope[None, None, None]
+           + 0.02 * np.sin(np.arange(5))[:, None, None, None, None]
+           + 0.01 * np.arange(3)[None, :, None, None, None]
+           + rng.normal(0.0, 0.01, (5, 3, n_ant, n_dir, 2)))
+    weight = np.ones(val.shape, np.float32)
+    weight[rng.random(val.shape) < 0.02] = 0.0
+    out = rng.random(val.shape) < 0.004
+    val[out] *= 3.0
+    return t_amp, f_amp, val, weight
+
+
+def golden_gain(mods):
+    from oracle.refshim import fake_astropy, fake_h5parm
+
+    tmp = tempfile.mkdtemp(prefix="ssf_golden_")
+    for f in ("solutions.h5", "skymodel.txt"):
+        shutil.copy(os.path.join(GOLDEN, f), tmp)
+    cwd = os.getcwd()
+    os.chdir(tmp)
+    try:
+        fake_h5parm.reset()
+        h5 = fake_h5parm.H5parm("solutions.h5")
+        ph = h5.get_solset("sol000").get_soltab("phase000")
+        t_amp, f_amp, val, weight = synthetic_amplitudes(ph.time, ph.freq, len(ph.ant), len(ph.dir))
+        fake_h5parm.add_soltab("solutions.h5", "sol000", "amplitude000", "amplitude",
+                               ["time", "freq", "ant", "dir", "pol"],
+                               [t_amp, f_amp, ph.ant, ph.dir, np.array(["XX", "YY"])], val, weight)
+        out = dict(amp_time=t_amp, amp_freq=f_amp, amp_val=val, amp_weight=weight,
+                   sub_f=SUB_F, sub_a=SUB_A)
+        for screen_type in ("tessellated", "kl"):
+            args = dict(TEST_ARGS, bounds_deg=list(TEST_ARGS["bounds_deg"]))
+            mods["make_aterm_images"].make_aterm_image(
+                "solutions.h5", soltabname="gain000", screen_type=screen_type, outroot=screen_type,
+                smooth_deg=0.1 if screen_type == "tessellated" else 0.0, **args)
+            cube = fake_astropy.open(f"{screen_type}_0.fits")[0].data
+            out[f"cube_{screen_type}"] = cube[:, SUB_F][:, :, SUB_A].copy()
+        args = dict(TEST_ARGS, bounds_deg=list(TEST_ARGS["bounds_deg"]))
+        mods["make_aterm_images"].make_aterm_image(
+            "solutions.h5", soltabname="gain000", screen_type="tessellated", outroot="plain",
+            smooth_deg=0.0, **args)
+        out["cube_tessellated_nosmooth"] = fake_astropy.open("plain_0.fits")[0].data[:, SUB_F][:, :, SUB_A].copy()
+        store = fake_h5parm._CREATED["solutions.h5"]["sol000"]
+        scr = store["amplitude_screen000"]._soltab
+        res = store["amplitude_screen000resid"]._soltab
+        out.update(amp_screen=scr._val, amp_screen_weights=scr._weight, amp_resid=res._val,
+                   amp_order=res._weight[:, :, :, 0, :])
+        np.savez_compressed(os.path.join(GOLDEN, "gain_c1.npz"), **out)
+    finally:
+        os.chdir(cwd)
+        shutil.rmtree(tmp)
+        fake_h5parm.reset()
+
+
+JOBS = {"gain": golden_gain}

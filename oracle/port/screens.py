@@ -56,18 +56,53 @@ def nearest_patch_template(px, py, n):
 
 
 def voronoi_make_matrix(template, phases_td, amp_td=None):
-    """voronoi_screen.py:169-216 (phase-only: amplitudes are ones, :88)."""
+    """voronoi_screen.py:169-216.  Phase-only: amplitudes are ones (:88); gain solutions:
+    ``amp_td`` [t, d, 2] = (XX, YY) amplitudes on planes 0-1 / 2-3 (:179-214)."""
     n_t, n_d = phases_td.shape
     data = np.zeros((n_t, 4) + template.shape)
     for d in range(n_d):
         ind = np.where(template == d + 1)
         for t in range(n_t):
-            amp = 1.0 if amp_td is None else amp_td[t, d]
-            data[t, 0, ind[0], ind[1]] = amp * np.cos(phases_td[t, d])
-            data[t, 2, ind[0], ind[1]] = amp * np.cos(phases_td[t, d])
-            data[t, 1, ind[0], ind[1]] = amp * np.sin(phases_td[t, d])
-            data[t, 3, ind[0], ind[1]] = amp * np.sin(phases_td[t, d])
+            axx, ayy = (1.0, 1.0) if amp_td is None else (amp_td[t, d, 0], amp_td[t, d, 1])
+            data[t, 0, ind[0], ind[1]] = axx * np.cos(phases_td[t, d])
+            data[t, 2, ind[0], ind[1]] = ayy * np.cos(phases_td[t, d])
+            data[t, 1, ind[0], ind[1]] = axx * np.sin(phases_td[t, d])
+            data[t, 3, ind[0], ind[1]] = ayy * np.sin(phases_td[t, d])
     return data
+
+
+def interpolate_amplitudes(vals_amp, times_amp, freqs_amp, times_ph, freqs_ph, log_amps,
+                           interp_kind="nearest"):
+    """screen.py:108-154 (Screen.interpolate) for vals_amp [t', f', a, d, pol]."""
+    from scipy import interpolate as si
+
+    vals_amp = np.asarray(vals_amp)
+    n_t, n_f = len(times_ph), len(freqs_ph)
+    if len(times_amp) == 1:
+        new_shape = list(vals_amp.shape)
+        new_shape[0], new_shape[1] = n_t, n_f
+        return np.resize(vals_amp, new_shape)
+    logvals = vals_amp if log_amps else np.log10(vals_amp)
+    if vals_amp.shape[0] != n_t:
+        logvals = si.interp1d(times_amp, logvals, axis=0, kind=interp_kind, fill_value="extrapolate")(times_ph)
+    if vals_amp.shape[1] != n_f:
+        logvals = si.interp1d(freqs_amp, logvals, axis=1, kind=interp_kind, fill_value="extrapolate")(freqs_ph)
+    return logvals if log_amps else 10 ** logvals
+
+
+def voronoi_gain_cube(phases_tfad, amp_tfadp, template, smooth_pix=0.0, freqs=None, stations=None):
+    """screen.py:328-383 for Voronoi gain solutions: fill, float32 store, smooth, NaN fix."""
+    n_t, n_f, n_a, _ = phases_tfad.shape
+    freqs = range(n_f) if freqs is None else freqs
+    stations = range(n_a) if stations is None else stations
+    cube = np.zeros((n_t, len(freqs), len(stations), 4) + template.shape, np.float32)
+    for fi, f in enumerate(freqs):
+        for ai, a in enumerate(stations):
+            cube[:, fi, ai] = voronoi_make_matrix(template, phases_tfad[:, f, a, :], amp_tfadp[:, f, a, :, :2])
+            if smooth_pix > 0:
+                for t in range(n_t):
+                    cube[t, fi, ai] = smooth_block(cube[t, fi, ai], smooth_pix)
+    return nan_fix(cube)
 
 
 # ---------------------------------------------------------------------------- smoothing

@@ -12,6 +12,15 @@ import numpy as np
 from ska_sdp_screen_fitting_b200.utils import h5min
 
 _CREATED = {}  # filename -> {solset: {soltab_name: _Obj}}
+_EXTRA = {}    # filename -> {solset: {soltab_name: dict(type, axes, axes_vals, val, weight)}}:
+               # in-memory soltabs overlaid on a real file (synthetic amplitude tables)
+
+
+def add_soltab(filename, solset, name, soltype, axes, axes_vals, val, weight):
+    """Overlay an in-memory soltab on ``filename`` (there is no HDF5 writer in this image)."""
+    _EXTRA.setdefault(filename, {}).setdefault(solset, {})[name] = dict(
+        type=soltype, axes=list(axes), axes_vals=[np.asarray(v) for v in axes_vals],
+        val=np.asarray(val), weight=np.asarray(weight))
 
 
 class _VFile:
@@ -88,6 +97,12 @@ class Solset:
         created = self._h5._store.setdefault(self.name, {})
         if name in created:
             return created[name]._soltab
+        extra = _EXTRA.get(self._h5.filename, {}).get(self.name, {})
+        if name in extra:
+            e = extra[name]
+            obj = _Obj(name, e["type"], self._h5._store)
+            return Soltab(self, name, e["type"], e["axes"], e["axes_vals"], e["val"].copy(),
+                          e["weight"].copy(), obj)
         grp = self._file_group()
         if name not in grp:
             raise Exception(f"Solution-table {name}  not found in solset {self.name}.")
@@ -147,3 +162,4 @@ class H5parm:
 
 def reset():
     _CREATED.clear()
+    _EXTRA.clear()

@@ -174,9 +174,11 @@ class Engine:
         ``check=False`` defers the convergence / weight-range checks: the caller must call
         ``check_fit_status()`` later."""
         nsys, ndir = phase.shape
+        t0 = time.perf_counter()
         white = self.zeros((nsys, ndir), torch.float64)
         resid = self.zeros((nsys, ndir), torch.float64)
         order = station_order.clone()
+        self.host_tick("fit_alloc", t0)
         if cache is None:
             cache = PatternCache(self, pp, r0, beta, cut, max_bytes=256 << 20)
         self._caches.add(cache)

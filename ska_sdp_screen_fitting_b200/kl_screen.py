@@ -136,9 +136,11 @@ class KLScreen(Screen):
                                          so, self._pp_dev, niter=2, nsigma=5.0, adjust_order=True,
                                          r0=self.r_0, beta=self.beta_val, cut=PINV_CUT,
                                          cache=self._patterns, check=check)
+        t_host = time.perf_counter()
         order = order.view(n_t, n_f, n_a)
         order = torch.where(skip[None], torch.zeros_like(order), order)
         weights_out = torch.where(skip[None, :, :, None], weight, work_w)
+        eng.host_tick("fit_post", t_host)
         return white.view(n_t, n_f, n_a, n_d), resid.view(n_t, n_f, n_a, n_d), order, weights_out
 
     def stream_slabs(self, val_dev, wt_dev, slots, ring, cellsize_deg, first=0, count=None):
@@ -277,7 +279,7 @@ class KLScreen(Screen):
                                    self._pp_dev, self._pinv_full, self.r_0, self.beta_val)
         self._basis_key = key
 
-    def _fill_columns(self, cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan):
+    def _fill_columns(self, cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan, amp=None):
         # smooth_pix is forced to 0 for KL screens by make_aterm_image (make_aterm_images.py:101-103);
         # NaN -> (1, 0) is fused into the store of ssf_kl_eval either way.
         self._prepare(cellsize_deg, out_dir)

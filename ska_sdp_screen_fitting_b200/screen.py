@@ -44,6 +44,24 @@ def split_range(start, stop, parts, index):
     return lo, lo + base + (1 if index < extra else 0)
 
 
+def _interp_axis(x_old, values, axis, x_new, kind):
+    """``scipy.interpolate.interp1d(x_old, values, axis=axis, kind=kind,
+    fill_value="extrapolate")(x_new)`` (screen.py:134-150).  "nearest" is restated (sorted
+    abscissae, ties at a midpoint go to the lower sample, ends clamp -- scipy's rule); any other
+    kind is handed to scipy itself."""
+    x_old = np.asarray(x_old, np.float64)
+    x_new = np.asarray(x_new, np.float64)
+    if kind == "nearest":
+        order = np.argsort(x_old, kind="mergesort")
+        xs = x_old[order]
+        mids = 0.5 * (xs[1:] + xs[:-1])
+        idx = np.clip(np.searchsorted(mids, x_new, side="left"), 0, len(xs) - 1)
+        return np.take(np.take(values, order, axis=axis), idx, axis=axis)
+    from scipy import interpolate as si
+
+    return si.interp1d(x_old, values, axis=axis, kind=kind, fill_value="extrapolate")(x_new)
+
+
 def time_chunks(times):
     """Output-file boundaries (screen.py:283-294): a new file wherever the time step exceeds
     1.2 x the smallest step.  Returns the list of stop indices.  The reference's further,
@@ -103,6 +121,7 @@ class Screen:
         self.timings = {}
         self._engine = None
         self._dev_vals = None            # device [t, f, a, d] float64: what make_matrix consumes
+        self._dev_amp = None             # device [t, f, a, d, 2] float64 (gain solutions only)
 
     # ------------------------------------------------------------------ plumbing
     @property
@@ -112,6 +131,8 @@ class Screen:
         return self._engine
 
     def _load_solutions(self, soltab_name):
+        if isinstance(self.solutions, dict):         # {soltab name: Solutions} (phase + amplitude)
+            return self.solutions[soltab_name]
         if self.solutions is not None:
             return self.solutions
         from .h5parm_io import read_solutions
@@ -127,12 +148,28 @@ class Screen:
         """Fits screens to the input solutions (implemented in the subclasses)."""
 
     def interpolate(self, interp_kind="nearest"):
-        """screen.py:108-154: resample slow amplitudes onto the phase grid.  Phase-only
-        solutions (the only kind the engine accepts so far) return immediately, as in the
-        reference (:118-119)."""
+        """screen.py:108-154: resample the slow amplitudes (in log space) onto the fast-phase
+        time and frequency grid; phase-only solutions return immediately (:118-119).  Host
+        marshalling, once per run; the result is uploaded as the device tensor the cube
+        kernels read ([time, freq, ant, dir, pol])."""
         if self.phase_only:
             return
-        raise NotImplementedError("amplitude ('gain') soltabs are not supported by this engine yet")
+        vals_amp = np.asarray(self.vals_amp)
+        n_t, n_f = self.vals_ph.shape[0], self.vals_ph.shape[1]
+        if len(self.times_amp) == 1:
+            # a single time: the values are repeated as needed (numpy.resize semantics, :121-126)
+            new_shape = list(vals_amp.shape)
+            new_shape[0], new_shape[1] = n_t, n_f
+            vals_amp = np.resize(vals_amp, new_shape)
+        else:
+            logvals = vals_amp if self.log_amps else np.log10(vals_amp)
+            if vals_amp.shape[0] != n_t:
+                logvals = _interp_axis(self.times_amp, logvals, 0, self.times_ph, interp_kind)
+            if vals_amp.shape[1] != n_f:
+                logvals = _interp_axis(self.freqs_amp, logvals, 1, self.freqs_ph, interp_kind)
+            vals_amp = logvals if self.log_amps else 10 ** logvals
+        self.vals_amp = vals_amp
+        self._dev_amp = self.engine.tensor(np.ascontiguousarray(vals_amp[..., :2]), torch.float64)
 
     def get_memory_usage(self, cellsize_deg):
         """GB of HOST memory per time slot.  The reference's estimates (kl_screen.py:157-190,
@@ -146,12 +183,16 @@ class Screen:
         the same device path as write() (reference: screen.py:197-245)."""
         n_y, n_x = self.image_shape(cellsize_deg)
         cols = self._dev_vals[t_start_index:t_stop_index, freq_ind, stat_ind, :].contiguous()
+        amp = None
+        if not self.phase_only:
+            amp = self._dev_amp[t_start_index:t_stop_index, freq_ind, stat_ind].contiguous()
         slab = self.engine.empty((cols.shape[0], 4, n_y, n_x), torch.float32)
-        self._fill_columns(cols, slab, cellsize_deg, out_dir, smooth_pix=0.0, fix_nan=False)
+        self._fill_columns(cols, slab, cellsize_deg, out_dir, smooth_pix=0.0, fix_nan=False, amp=amp)
         return slab.double().cpu().numpy()
 
-    def _fill_columns(self, cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan):
-        """cols: device [ncol, ndir] float64; slab: device float32 [ncol, 4, ny, nx]."""
+    def _fill_columns(self, cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan, amp=None):
+        """cols: device [ncol, ndir] float64; amp: device [ncol, ndir, 2] float64 (XX, YY) for
+        gain solutions; slab: device float32 [ncol, 4, ny, nx]."""
         raise NotImplementedError
 
     def _prepare(self, cellsize_deg, out_dir):
@@ -200,9 +241,11 @@ class Screen:
             buf = 0
             for t0 in range(my0, my1, step):
                 t1 = min(my1, t0 + step)
-                cols = self._dev_vals[t0:t1].reshape(-1, self._dev_vals.shape[-1])
+                n_d = self._dev_vals.shape[-1]
+                cols = self._dev_vals[t0:t1].reshape(-1, n_d)
+                amp = None if self.phase_only else self._dev_amp[t0:t1].reshape(-1, n_d, 2)
                 slab = eng.empty((cols.shape[0], 4, n_y, n_x), torch.float32)
-                self._fill_columns(cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan=True)
+                self._fill_columns(cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan=True, amp=amp)
                 eng.bswap32(slab)
                 if pinned[buf] is None or pinned[buf].numel() < slab.numel():
                     pinned[buf] = torch.empty(slab.numel(), dtype=torch.float32,

@@ -43,11 +43,10 @@ class VoronoiScreen(Screen):
 
     def fit(self):
         """voronoi_screen.py:57-102: no fitting, the phases are referenced to one station."""
-        if not self.phase_only:
-            raise NotImplementedError("amplitude ('gain') soltabs are not supported by this engine yet")
         sol = self._load_solutions(self.input_phase_soltab_name)
         if sol.val.ndim != 4:
-            raise NotImplementedError("phase soltabs with a pol axis are not supported yet")
+            raise NotImplementedError("phase soltabs with a pol axis are not supported (scalarphase only, "
+                                      "as in the reference: voronoi_screen.py:69-70)")
         eng = self.engine
         ref_ind = reference_station(sol.weight, 10)
         val = eng.tensor(sol.val, torch.float64)
@@ -56,9 +55,18 @@ class VoronoiScreen(Screen):
         self.vals_ph = self._dev_vals.cpu().numpy()
         self.times_ph = sol.time
         self.freqs_ph = sol.freq
-        self.vals_amp = np.ones_like(self.vals_ph)
-        self.times_amp = self.times_ph
-        self.freqs_amp = self.freqs_ph
+        if self.phase_only:
+            self.vals_amp = np.ones_like(self.vals_ph)
+            self.times_amp = self.times_ph
+            self.freqs_amp = self.freqs_ph
+        else:
+            amp = self._load_solutions(self.input_amplitude_soltab_name)      # voronoi_screen.py:84-88
+            if amp.val.ndim != 5 or amp.val.shape[-1] < 2:
+                raise ValueError("amplitude soltab must be [time, freq, ant, dir, pol] with XX and YY")
+            self.log_amps = False
+            self.vals_amp = np.array(amp.val, dtype=np.float64)
+            self.times_amp = amp.time
+            self.freqs_amp = amp.freq
         self.source_names = sol.dir
         self.source_dict = sol.source_dict
         self.source_positions = sol.source_positions
@@ -118,12 +126,22 @@ class VoronoiScreen(Screen):
         return self._ind_dev
 
     # ------------------------------------------------------------------ fill
-    def _fill_columns(self, cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan):
+    def _fill_columns(self, cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan, amp=None):
         self._prepare(cellsize_deg, out_dir)
         eng = self.engine
-        lut = eng.voronoi_lut(cols)
         npix = self._tmpl_dev.numel()
         smooth = bool(smooth_pix) and smooth_pix > 0
+        if amp is not None:
+            # gain solutions: XX / YY amplitudes on planes 0-1 / 2-3 (voronoi_screen.py:177-214);
+            # smoothing in the reference's own order of operations (screen.py:353-378)
+            lut4 = eng.voronoi_lut_gain(cols.contiguous(), amp.contiguous())
+            eng.voronoi_fill_gain(self._tmpl_dev, lut4, slab, fix_nan=fix_nan and not smooth)
+            if smooth:
+                eng.gauss_smooth(slab, smooth_pix)
+                if fix_nan:
+                    eng.nan_fix(slab, cols.shape[0], npix)
+            return
+        lut = eng.voronoi_lut(cols)
         linear = self.smooth_mode == "linear"
         if smooth and self.smooth_mode == "auto":
             has_nan = self._has_nan if self._has_nan is not None else bool(torch.isnan(cols).any().item())

@@ -145,6 +145,70 @@ def check_voronoi(eng, n=20, n_d=7, ncol=13, seed=9):
     return tmpl, lut, want_t, phases
 
 
+def check_voronoi_gain(eng, n=20, n_d=7, ncol=13, seed=19):
+    """ssf_voronoi_lut_gain + ssf_voronoi_fill_gain: bit-exact against the oracle."""
+    rng = np.random.default_rng(seed)
+    want_t = screens.nearest_patch_template(rng.uniform(0, n, n_d), rng.uniform(0, n, n_d), n)
+    tmpl = eng.tensor(want_t, torch.int32)
+    phases = rng.normal(0, 1.0, (ncol, n_d))
+    amp = rng.uniform(0.5, 1.5, (ncol, n_d, 2))
+    phases[ncol - 1, n_d - 1] = np.nan
+    amp[0, 0, 1] = np.nan
+    lut4 = eng.voronoi_lut_gain(eng.tensor(phases, torch.float64), eng.tensor(amp, torch.float64))
+    for fix in (False, True):
+        slab = eng.empty((ncol, 4, n, n), torch.float32)
+        eng.voronoi_fill_gain(tmpl, lut4, slab, fix)
+        want = screens.voronoi_make_matrix(want_t, phases, amp).astype(np.float32)
+        if fix:
+            want = screens.nan_fix(want)
+        assert np.array_equal(slab.cpu().numpy(), want, equal_nan=True)
+
+
+def gain_solutions(golden_dir, repo_solutions):
+    """{soltab name: Solutions} of the gain fixture: the repo's phase000 plus the synthetic
+    amplitude000 stored in tests/golden/gain_c1.npz (oracle/make_golden_synth.py)."""
+    import os
+
+    from ska_sdp_screen_fitting_b200.h5parm_io import Solutions
+
+    gold = np.load(os.path.join(golden_dir, "gain_c1.npz"))
+    ph = repo_solutions
+    amp = Solutions("amplitude", gold["amp_val"], gold["amp_weight"], gold["amp_time"], gold["amp_freq"],
+                    list(ph.ant), list(ph.dir), ["XX", "YY"], dict(ph.source_dict), dict(ph.station_dict))
+    return {"phase000": ph, "amplitude000": amp}, gold
+
+
+def check_voronoi_gain_golden(eng, golden_dir, repo_solutions, tmp_path, full=True):
+    """VoronoiScreen on gain solutions through process() + write(): against the cube the
+    reference's own code produced (smoothed and unsmoothed)."""
+    from ska_sdp_screen_fitting_b200 import fits
+    from ska_sdp_screen_fitting_b200.voronoi_screen import VoronoiScreen
+
+    sols, gold = gain_solutions(golden_dir, repo_solutions)
+    import os
+
+    for smooth_pix, key, tol in ((0.0, "cube_tessellated_nosmooth", 1e-30), (0.5, "cube_tessellated", TOL_SMOOTH)):
+        scr = VoronoiScreen("gain", None, os.path.join(golden_dir, "skymodel.txt"), 126.23, 64.50, 3.33, 3.33,
+                            phase_soltab_name="phase000", amplitude_soltab_name="amplitude000")
+        scr._engine = eng
+        scr.solutions = sols
+        scr.process()
+        if not full:
+            # emulator-sized: two (freq, station) pairs through make_matrix, unsmoothed, bit-exact
+            for fi, ai in ((0, 1), (2, 3)):
+                one = scr.make_matrix(0, 20, int(gold["sub_f"][fi]), int(gold["sub_a"][ai]), 0.2, None, 0)
+                assert np.array_equal(one.astype(np.float32), gold["cube_tessellated_nosmooth"][:, fi, ai])
+            return
+        scr.write(str(tmp_path), 0.2, smooth_pix=smooth_pix)
+        _, data = fits.read(os.path.join(str(tmp_path), "gain_0.fits"))
+        sub = np.asarray(data)[:, list(gold["sub_f"])][:, :, list(gold["sub_a"])]
+        assert sub.shape == gold[key].shape
+        assert np.abs(sub - gold[key]).max() <= tol, (key, np.abs(sub - gold[key]).max())
+        one = scr.make_matrix(0, 20, int(gold["sub_f"][1]), int(gold["sub_a"][2]), 0.2, None, 0)
+        if smooth_pix == 0.0:
+            assert np.array_equal(one.astype(np.float32), gold[key][:, 1, 2])
+
+
 def check_smooth(eng, shape=(5, 19, 37), sigmas=(0.5, 2.0, 5.0), seed=2):
     rng = np.random.default_rng(seed)
     img = rng.normal(size=shape).astype(np.float32)

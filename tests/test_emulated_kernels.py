@@ -51,6 +51,15 @@ def test_voronoi_assign_and_fill(emu_engine):
     pc.check_voronoi(emu_engine, n=9, n_d=3, ncol=2, seed=12)      # ragged
 
 
+def test_voronoi_gain_fill(emu_engine):
+    pc.check_voronoi_gain(emu_engine)
+    pc.check_voronoi_gain(emu_engine, n=9, n_d=3, ncol=2, seed=12)     # ragged (scalar stores)
+
+
+def test_voronoi_gain_against_reference_golden(emu_engine, golden_dir, repo_solutions, tmp_path):
+    pc.check_voronoi_gain_golden(emu_engine, golden_dir, repo_solutions, tmp_path, full=False)
+
+
 def test_smoothing(emu_engine):
     pc.check_smooth(emu_engine, shape=(3, 13, 21), sigmas=(0.5, 2.0, 3.0))
 

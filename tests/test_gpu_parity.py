@@ -73,6 +73,13 @@ def test_voronoi_assign_and_fill(gpu_engine):
     pc.check_voronoi(gpu_engine, n=128, n_d=45, ncol=40, seed=13)
 
 
+def test_voronoi_gain(gpu_engine, golden_dir, repo_solutions, tmp_path):
+    pc.check_voronoi_gain(gpu_engine)
+    pc.check_voronoi_gain(gpu_engine, n=9, n_d=3, ncol=2, seed=12)
+    pc.check_voronoi_gain(gpu_engine, n=256, n_d=45, ncol=40, seed=13)
+    pc.check_voronoi_gain_golden(gpu_engine, golden_dir, repo_solutions, tmp_path)
+
+
 def test_template_bit_exact_at_full_size(gpu_engine):
     """1024 x 1024, 45 patches: every index equals the float64 CPU definition."""
     from oracle.port import screens
