@@ -96,6 +96,8 @@ int ssf_kl_patterns_update(const uint64_t *masks, int64_t nsys, int ndir, const 
  *   mode 0: iteration 0       -> one fit at min(order, n_unfl-1)         (:681-722)
  *   mode 1: iteration > 0     -> order-adjust state machine, first order iteration skips
  *                                the fit (reference quirk, :694-705), <= 3 refits (:692-779)
+ *   mode + 2: amplitude type  -> `phase` holds amplitudes; log10 fit (:535-548), residual
+ *                                amp - 10^fit (:576-590), log-residual chi^2 (:732-744)
  *   white, resid [nsys, ndir] f64 in/out (mode 1 reads the residual of the previous pass)
  * Systems with no unflagged direction are left untouched (:683-684).
  *   status  [1] i32 in/out     set to 1 if any system had a weight in (0, pinv_cut] (the
@@ -115,6 +117,15 @@ int ssf_kl_fit_pass(const double *phase, const float *weights, const int32_t *pa
  * Also emits each system's new 128-bit flag mask (masks_out [nsys, 2]).  */
 int ssf_kl_flag_outliers(const double *resid, float *weights, int ndir, int64_t nsys,
                          double nsigma, uint64_t *masks_out, void *stream);
+
+/* Amplitude-type flagging (_flag_outliers :341-348 on the log residual of :664-668):
+ * systems are time-major with `ngroups` = freq*station*pol systems per time slot
+ * (sys = t*ngroups + g); one weighted rms per group over all directions and times
+ * (group_std [ngroups] scratch), weights of |log resid| > nsigma*rms set to 0 in place.
+ * nsigma = inf flags nothing and only emits the masks. */
+int ssf_kl_flag_outliers_amp(const double *val, const double *resid, float *weights, int ndir,
+                             int64_t nsys, int64_t ngroups, double nsigma, double *group_std,
+                             uint64_t *masks_out, void *stream);
 
 /* ------------------------------------------------------------------------------------
  * KL evaluation.  Replaces KLScreen.make_matrix + calculate_kl_screen
@@ -140,6 +151,13 @@ int ssf_kl_coeffs(const double *white, int64_t ncol, int ndir, const double *C,
 /* variant: 0 = FP32 SIMT, 1 = tcgen05 (3xTF32 split, FP32 accumulate in TMEM), -1 = auto */
 int ssf_kl_eval(const float *Bt, const float *G, int ndir, int ldg, int64_t npix,
                 int64_t ncol, float *slab, int variant, void *stream);
+
+/* Gain solutions (scalar phase + log10 XX/YY amplitude screens, kl_screen.py:319-378):
+ * G3 [ncol, 3, ldg] f32 = coefficients (phase, Axx, Ayy) from ssf_kl_coeffs on the stacked
+ * white vectors; slab[col] = (10^Axx cos Phi, 10^Axx sin Phi, 10^Ayy cos Phi, 10^Ayy sin Phi),
+ * NaN -> (1, 0, 1, 0) fused into the store. */
+int ssf_kl_eval_gain(const float *Bt, const float *G3, int ndir, int ldg, int64_t npix,
+                     int64_t ncol, float *slab, void *stream);
 
 /* ------------------------------------------------------------------------------------
  * Voronoi.  ssf_voronoi_assign: float64 nearest patch per integer pixel, lowest index

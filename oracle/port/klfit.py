@@ -46,8 +46,8 @@ def piercepoints(source_dirs_rad):
     return pp, mid_ra, mid_dec
 
 
-def fit_screen(full, pp, phase, weights, order, r_0=R_0, beta=BETA):
-    """stationscreen.py:433-594 (_fit_screen, screen_type == "phase")."""
+def fit_screen(full, pp, phase, weights, order, r_0=R_0, beta=BETA, screen_type="phase"):
+    """stationscreen.py:433-594 (_fit_screen, screen_type "phase" or "amplitude")."""
     n_all = len(phase)
     unfl = np.where(weights > 0.0)[0]
     n = len(unfl)
@@ -58,13 +58,19 @@ def fit_screen(full, pp, phase, weights, order, r_0=R_0, beta=BETA):
     w = np.diag(weights[unfl].astype(weights.dtype))
     uk = u[:, :order]
     inv_u = pinv_abs(uk.T @ (w @ u)[:, :order])                  # :501-504
-    fits = []
-    for r in (np.cos(phase[unfl]), np.sin(phase[unfl])):         # :509-528
-        rr1 = uk.T @ (w @ r)
-        fits.append(pinv_c @ (uk @ (inv_u @ rr1)))
-    real_fit, imag_fit = fits
-    screen_fit = np.arctan2(c @ imag_fit, c @ real_fit)          # :531-533
-    white = pinv_c @ screen_fit                                  # :534
+    if screen_type == "amplitude":                               # :535-548
+        with np.errstate(all="ignore"):
+            rr1 = uk.T @ (w @ np.log10(phase[unfl]))
+        amp_fit_log = pinv_c @ (uk @ (inv_u @ rr1))
+        screen_fit = c @ amp_fit_log
+    else:
+        fits = []
+        for r in (np.cos(phase[unfl]), np.sin(phase[unfl])):     # :509-528
+            rr1 = uk.T @ (w @ r)
+            fits.append(pinv_c @ (uk @ (inv_u @ rr1)))
+        real_fit, imag_fit = fits
+        screen_fit = np.arctan2(c @ imag_fit, c @ real_fit)      # :531-533
+    white = pinv_c @ screen_fit                                  # :534 / :548
     if n != n_all:                                               # :565-582
         fit_all = np.zeros(n_all)
         fit_all[unfl] = screen_fit
@@ -73,10 +79,11 @@ def fit_screen(full, pp, phase, weights, order, r_0=R_0, beta=BETA):
             cval = structure_matrix(pp[fi:fi + 1], pp[unfl], r_0, beta)[0]
             fit_all[fi] = cval @ white
         white_all = full[1] @ fit_all
-        resid = phase - fit_all
+        resid = phase - (10 ** fit_all if screen_type == "amplitude" else fit_all)     # :576-583
     else:
         white_all = white
-        resid = phase - c @ white                                # :590
+        model = c @ white
+        resid = phase - (10 ** model if screen_type == "amplitude" else model)        # :584-590
     return white_all, resid
 
 
@@ -91,10 +98,17 @@ def normalize_phase(phase):
     return out
 
 
-def flag_outliers(weights, residual, nsigma):
-    """stationscreen.py:303-350 (phase): 5-sigma clip on the circular std over directions.
+def flag_outliers(weights, residual, nsigma, screen_type="phase"):
+    """stationscreen.py:303-350: 5-sigma clip -- phase: circular std over directions per time;
+    amplitude: ONE weighted rms over all directions and times of the station (:341-346).
     Mutates and returns ``weights`` ([ndir, nt]), as the reference does."""
     if not (weights > 0.0).any():
+        return weights
+    if screen_type == "amplitude":
+        nonfl = weights > 0.0
+        with np.errstate(all="ignore"):
+            std = np.sqrt(np.average(residual[nonfl] ** 2, weights=weights[nonfl], axis=0))
+            weights[np.abs(residual) > nsigma * std] = 0.0
         return weights
     res = normalize_phase(residual)
     res_nan = res.copy()
@@ -118,8 +132,14 @@ def circ_chi2(samples, weights):
     return (1.0 - np.hypot(m1, m2)) * sumw
 
 
+def log_residual(values, residual):
+    """stationscreen.py:664-668, :732-741: log10(a) - log10(|a - resid|)."""
+    with np.errstate(all="ignore"):
+        return np.log10(values) - np.log10(np.abs(values - residual))
+
+
 def process_station(phase, pp, screen_order, station_weights, full, niter=2, nsigma=5.0,
-                    adjust_order=True, r_0=R_0, beta=BETA):
+                    adjust_order=True, r_0=R_0, beta=BETA, screen_type="phase"):
     """stationscreen.py:597-782 (_process_station, phase).  ``phase``/``station_weights`` are
     [ndir, nt]; ``screen_order`` [nt] is updated in place.  Quirks kept:
     the flagged weights alias the "previous" weights so the first order iteration of every
@@ -131,7 +151,8 @@ def process_station(phase, pp, screen_order, station_weights, full, niter=2, nsi
     init_w = station_weights.copy()
     for it in range(niter):
         if it > 0:
-            station_weights = flag_outliers(init_w, residual.copy(), nsigma)
+            diff = residual.copy() if screen_type == "phase" else log_residual(phase, residual)
+            station_weights = flag_outliers(init_w, diff, nsigma, screen_type)
         prev_w = init_w
         prev_redchi2 = 0
         norderiter = 4 if (adjust_order and it > 0) else 1
@@ -152,14 +173,19 @@ def process_station(phase, pp, screen_order, station_weights, full, niter=2, nsi
                         skip_fit = True
                 if not np.all(station_weights[:, t] == 0.0) and not skip_fit:
                     scr, res = fit_screen(full, pp, phase[:, t], station_weights[:, t],
-                                          int(screen_order[t]), r_0, beta)
+                                          int(screen_order[t]), r_0, beta, screen_type)
                     screen[:, t] = scr
                     residual[:, t] = res
                 if hit_lower2 or hit_upper2:
                     break
                 if adjust_order and it > 0:
-                    redchi2 = circ_chi2(residual[:, t], station_weights[:, t]) / (
-                        n_unfl - screen_order[t])
+                    if screen_type == "phase":
+                        redchi2 = circ_chi2(residual[:, t], station_weights[:, t]) / (
+                            n_unfl - screen_order[t])
+                    else:                                                        # :732-744
+                        diff = log_residual(phase[:, t], residual[:, t])
+                        redchi2 = np.sum(np.square(diff) * station_weights[:, t]) / (
+                            n_unfl - screen_order[t])
                     if oi > 0:
                         if redchi2 > 1.0 and prev_redchi2 < redchi2:
                             sign *= -1
@@ -250,3 +276,35 @@ def run_phase(val_tfad, weight_tfad, source_dirs_rad, station_pos, ref_ant, orde
             order_out[:, f, a] = so
     return dict(screen=screen, weights=w_out, resid=resid, order=order_out, pp=pp,
                 midra=mid_ra, middec=mid_dec, full=full, station_order=st_order)
+
+
+def run_amplitude(val_tfadp, weight_tfadp, source_dirs_rad, order, niter=3, nsigma=5.0,
+                  adjust_order=True, stations=None, freqs=None):
+    """stationscreen.py:858-1161 (run) for an amplitude soltab [time, freq, ant, dir, pol] as
+    KLScreen.fit calls it (kl_screen.py:114-126): niter=3, scale_order=False, ref_ant=-1 (no
+    referencing, no station skipped for being the reference).  The screens are log10 values,
+    the residuals are not (:1090)."""
+    val = np.array(val_tfadp, dtype=np.float64)
+    n_t, n_f, n_a, n_d, n_p = val.shape
+    wts = np.array(weight_tfadp)
+    pp, mid_ra, mid_dec = piercepoints(source_dirs_rad)
+    full = calculate_svd(pp)
+    screen = np.zeros(val.shape)
+    resid = np.zeros(val.shape)
+    order_out = np.zeros((n_t, n_f, n_a, n_p))
+    w_out = wts.copy()
+    for f in (range(n_f) if freqs is None else freqs):
+        for p in range(n_p):
+            for a in (range(n_a) if stations is None else stations):
+                arr = val[:, f, a, :, p].T
+                sw = wts[:, f, a, :, p].T.copy()
+                if np.all(np.isnan(arr)) or np.all(sw == 0):
+                    continue
+                so = np.full(n_t, float(order))
+                scr, wgt, res, so = process_station(arr, pp, so, sw, full, niter, nsigma, adjust_order,
+                                                    screen_type="amplitude")
+                screen[:, f, a, :, p] = scr.T
+                resid[:, f, a, :, p] = res.T
+                w_out[:, f, a, :, p] = wgt.T
+                order_out[:, f, a, p] = so
+    return dict(screen=screen, weights=w_out, resid=resid, order=order_out, pp=pp, full=full)

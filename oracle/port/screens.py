@@ -25,15 +25,26 @@ def kl_phase_images(kmat, white_td):
     return np.einsum("ijd,td->ijt", kmat, white_td)
 
 
-def kl_make_matrix(x_coord, y_coord, pp, white_td):
-    """kl_screen.py:192-380 (phase-only): data[t, 4, ny, nx] float64."""
-    val_phase = kl_phase_images(kl_kernel_matrix(x_coord, y_coord, pp), white_td)
+def kl_make_matrix(x_coord, y_coord, pp, white_td, amp_xx_td=None, amp_yy_td=None):
+    """kl_screen.py:192-380: data[t, 4, ny, nx] float64.  Gain solutions: ``amp_xx_td`` /
+    ``amp_yy_td`` are the log10 amplitude screens (white values), evaluated with the same
+    kernel and raised to the power of ten (:319-365, :374-378)."""
+    kmat = kl_kernel_matrix(x_coord, y_coord, pp)
+    val_phase = kl_phase_images(kmat, white_td)
     n_t = white_td.shape[0]
     data = np.zeros((n_t, 4, len(y_coord), len(x_coord)))
-    data[:, 0] = np.cos(val_phase.T)                          # :368-373 (note the .T)
-    data[:, 2] = data[:, 0]
-    data[:, 1] = np.sin(val_phase.T)
-    data[:, 3] = data[:, 1]
+    if amp_xx_td is None:
+        data[:, 0] = np.cos(val_phase.T)                      # :368-373 (note the .T)
+        data[:, 2] = data[:, 0]
+        data[:, 1] = np.sin(val_phase.T)
+        data[:, 3] = data[:, 1]
+        return data
+    val_amp_xx = 10 ** kl_phase_images(kmat, amp_xx_td)
+    val_amp_yy = 10 ** kl_phase_images(kmat, amp_yy_td)
+    data[:, 0] = val_amp_xx.T * np.cos(val_phase.T)
+    data[:, 2] = val_amp_yy.T * np.cos(val_phase.T)
+    data[:, 1] = val_amp_xx.T * np.sin(val_phase.T)
+    data[:, 3] = val_amp_yy.T * np.sin(val_phase.T)
     return data
 
 

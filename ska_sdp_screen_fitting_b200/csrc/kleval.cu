@@ -75,6 +75,78 @@ coeffs_kernel(const double *__restrict__ white, int64_t ncol, int ndir, const do
   }
 }
 
+
+// Gain solutions (kl_screen.py:319-378): three contractions per voxel against the same basis --
+// the phase screen and the log10 XX / YY amplitude screens -- and
+//   slab = (10^Axx cos Phi, 10^Axx sin Phi, 10^Ayy cos Phi, 10^Ayy sin Phi).
+// G3 [ncol][3][ldg] = coefficients (phase, Axx, Ayy).  FP32 SIMT: a CTA owns a 512-pixel basis
+// tile (L1-resident across its columns), a thread 4 consecutive pixels.
+constexpr int GAIN_THREADS = 128;
+
+template <bool VEC>
+__global__ void __launch_bounds__(GAIN_THREADS)
+kl_gain_kernel(const float *__restrict__ Bt, const float *__restrict__ G3, int ndir, int ldg, int64_t npix,
+               int64_t ncol, float *__restrict__ slab, int64_t cols_per_cta) {
+  SSF_DYN_SMEM(float, gs);                       // [3][ndir] of the current column
+  const int64_t p0 = ((int64_t)blockIdx.x * GAIN_THREADS + threadIdx.x) * 4;
+  const int64_t c_begin = (int64_t)blockIdx.y * cols_per_cta;
+  int64_t c_end = c_begin + cols_per_cta;
+  if (c_end > ncol) c_end = ncol;
+  for (int64_t col = c_begin; col < c_end; ++col) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < 3 * ndir; i += GAIN_THREADS) {
+      const int k = i / ndir, d = i - k * ndir;
+      gs[i] = G3[(col * 3 + k) * ldg + d];
+    }
+    __syncthreads();
+    if (p0 >= npix) continue;
+    float acc[3][4];
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[k][j] = 0.0f;
+    for (int d = 0; d < ndir; ++d) {
+      float b[4];
+      if (VEC) {
+        const float4 v = __ldg(reinterpret_cast<const float4 *>(Bt + (int64_t)d * npix + p0));
+        b[0] = v.x; b[1] = v.y; b[2] = v.z; b[3] = v.w;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) b[j] = (p0 + j < npix) ? __ldg(Bt + (int64_t)d * npix + p0 + j) : 0.0f;
+      }
+      const float g0 = gs[d], g1 = gs[ndir + d], g2 = gs[2 * ndir + d];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        acc[0][j] = fmaf(b[j], g0, acc[0][j]);
+        acc[1][j] = fmaf(b[j], g1, acc[1][j]);
+        acc[2][j] = fmaf(b[j], g2, acc[2][j]);
+      }
+    }
+    float pl[4][4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float sn, cs;
+      sincosf(acc[0][j], &sn, &cs);
+      const float ax = exp10f(acc[1][j]), ay = exp10f(acc[2][j]);
+      pl[0][j] = ssf::fix_re(ax * cs);
+      pl[1][j] = ssf::fix_im(ax * sn);
+      pl[2][j] = ssf::fix_re(ay * cs);
+      pl[3][j] = ssf::fix_im(ay * sn);
+    }
+    float *out = slab + col * 4 * npix + p0;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      if (VEC) {
+        __stcs(reinterpret_cast<float4 *>(out + p * npix), make_float4(pl[p][0], pl[p][1], pl[p][2], pl[p][3]));
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (p0 + j < npix) out[p * npix + j] = pl[p][j];
+      }
+    }
+  }
+}
+
 }  // namespace
 
 extern "C" int ssf_kl_basis(const double *x_coord, const double *y_coord, int nx, int ny,
@@ -137,4 +209,29 @@ extern "C" int ssf_voronoi_contract(const float *S, const float *lut, int ndir, 
   if (variant == 1 || (variant < 0 && tc_ok))
     return ssf::contract_tc(false, S, lut, ndir, ndir, npix, ncol, slab, (cudaStream_t)stream);
   return ssf::voronoi_contract_simt(S, lut, ndir, npix, ncol, slab, (cudaStream_t)stream);
+}
+
+
+extern "C" int ssf_kl_eval_gain(const float *Bt, const float *G3, int ndir, int ldg, int64_t npix,
+                                int64_t ncol, float *slab, void *stream) {
+  SSF_REQUIRE(Bt && G3 && slab, "ssf_kl_eval_gain: null pointer");
+  SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR && ldg >= ndir && npix >= 1, "ssf_kl_eval_gain: bad sizes");
+  if (ncol <= 0) return SSF_OK;
+  const int64_t pix_tiles = (npix + 4 * GAIN_THREADS - 1) / (4 * GAIN_THREADS);
+  // enough column chunks for ~8 CTAs per SM; a chunk keeps its basis tile in L1 across columns
+  int64_t chunks = (148 * 8 + pix_tiles - 1) / pix_tiles;
+  if (chunks > ncol) chunks = ncol;
+  if (chunks > 65535) chunks = 65535;
+  const int64_t per = (ncol + chunks - 1) / chunks;
+  dim3 grid((unsigned)pix_tiles, (unsigned)((ncol + per - 1) / per));
+  const size_t smem = sizeof(float) * 3 * (size_t)ndir;
+  const bool vec = npix % 4 == 0 && (uintptr_t)Bt % 16 == 0 && (uintptr_t)slab % 16 == 0;
+  if (vec)
+    SSF_LAUNCH(kl_gain_kernel<true>, grid, GAIN_THREADS, smem, (cudaStream_t)stream, Bt, G3, ndir, ldg, npix, ncol,
+               slab, per);
+  else
+    SSF_LAUNCH(kl_gain_kernel<false>, grid, GAIN_THREADS, smem, (cudaStream_t)stream, Bt, G3, ndir, ldg, npix, ncol,
+               slab, per);
+  SSF_LAUNCHED();
+  return SSF_OK;
 }

@@ -61,14 +61,15 @@ __host__ __device__ inline size_t smem_doubles(int nall) {
 // (0, cut]) -- not supported by the Cholesky path.
 __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restrict__ pp, int nall,
                          int n, int k, double r0sq, double half_beta, double cut,
-                         double *__restrict__ white_out, double *__restrict__ resid_out) {
+                         double *__restrict__ white_out, double *__restrict__ resid_out, bool amp) {
   __shared__ int sh_uniform, sh_ok;
   const int tid = threadIdx.x;
   const int ld = pt.ld;
   if (tid < n) {
     double phi = s.ph[s.idx[tid]];
-    double sn, cs;
-    sincos(phi, &sn, &cs);
+    double sn = 0.0, cs;
+    if (amp) cs = log10(phi);          // amplitude type fits log10(amp) (:535-541); one right-hand side
+    else sincos(phi, &sn, &cs);
     s.rc[tid] = cs;
     s.rs[tid] = sn;
     s.wc[tid] = s.w[s.idx[tid]];
@@ -176,7 +177,7 @@ __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restr
       ac = fma(c, s.gc[e], ac);
       as = fma(c, s.gs_[e], as);
     }
-    s.fit[tid] = atan2(as, ac);
+    s.fit[tid] = amp ? ac : atan2(as, ac);        // amplitude: screen_fit = C amp_fit_log (:547)
   }
   __syncthreads();
   // white = pinvC fit   (:534)
@@ -192,7 +193,7 @@ __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restr
       double a = 0.0;
       for (int e = 0; e < n; ++e) a = fma(pt.C[e * ld + tid], s.wh[e], a);
       white_out[tid] = s.wh[tid];
-      resid_out[tid] = s.ph[tid] - a;
+      resid_out[tid] = s.ph[tid] - (amp ? pow(10.0, a) : a);     // :584-590
     }
   } else {
     // flagged directions are predicted from the unflagged screen   (:565-574)
@@ -217,7 +218,7 @@ __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restr
       double a = 0.0;
       for (int e = 0; e < nall; ++e) a = fma(pt.Pfull[e * ld + tid], s.fall[e], a);
       white_out[tid] = a;
-      resid_out[tid] = s.ph[tid] - s.fall[tid];
+      resid_out[tid] = s.ph[tid] - (amp ? pow(10.0, s.fall[tid]) : s.fall[tid]);   // :576-583
     }
   }
   __syncthreads();
@@ -267,8 +268,9 @@ fit_pass_kernel(const double *__restrict__ phase, const float *__restrict__ weig
     if (ord > (double)(n - 1)) ord = (double)(n - 1);  // :685-686
     const double st_order = station_order[sys];
 
-    if (mode == 0) {
-      bool ok = fit_once(s, pt, pp, nall, n, (int)ord, r0sq, half_beta, cut, w_out, r_out);
+    const bool amp = (mode & 2) != 0;
+    if ((mode & 1) == 0) {
+      bool ok = fit_once(s, pt, pp, nall, n, (int)ord, r0sq, half_beta, cut, w_out, r_out, amp);
       if (!ok && tid == 0) atomicExch(status, 1);
       if (tid == 0) order[sys] = ord;
       continue;
@@ -280,7 +282,7 @@ fit_pass_kernel(const double *__restrict__ phase, const float *__restrict__ weig
     double sign = 1.0, prev_redchi2 = 0.0;
     for (int oi = 0; oi < 4; ++oi) {
       if (oi > 0) {
-        bool ok = fit_once(s, pt, pp, nall, n, (int)ord, r0sq, half_beta, cut, w_out, r_out);
+        bool ok = fit_once(s, pt, pp, nall, n, (int)ord, r0sq, half_beta, cut, w_out, r_out, amp);
         if (!ok && tid == 0) atomicExch(status, 1);
       }
       if (hit_lower2 || hit_upper2) break;
@@ -288,21 +290,34 @@ fit_pass_kernel(const double *__restrict__ phase, const float *__restrict__ weig
       __syncthreads();
       if (tid < nall) {
         double r = r_out[tid];
-        double sn, cs;
-        sincos(r, &sn, &cs);
-        sh_t1[tid] = s.w[tid] * sn * sn;
-        sh_t2[tid] = s.w[tid] * cs * cs;
+        if (amp) {
+          // log residual (:732-741): over ALL directions, NaN/inf times a zero weight included
+          const double v = s.ph[tid];
+          const double diff = log10(v) - log10(fabs(v - r));
+          sh_t1[tid] = diff * diff * s.w[tid];
+        } else {
+          double sn, cs;
+          sincos(r, &sn, &cs);
+          sh_t1[tid] = s.w[tid] * sn * sn;
+          sh_t2[tid] = s.w[tid] * cs * cs;
+        }
       }
       __syncthreads();
       if (tid == 0) {
-        double a1 = 0.0, a2 = 0.0, sw = 0.0;
-        for (int i = 0; i < n; ++i) {
-          int d = s.idx[i];
-          a1 += sh_t1[d];
-          a2 += sh_t2[d];
-          sw += s.w[d];
+        double chi2;
+        if (amp) {
+          chi2 = 0.0;
+          for (int d = 0; d < nall; ++d) chi2 += sh_t1[d];
+        } else {
+          double a1 = 0.0, a2 = 0.0, sw = 0.0;
+          for (int i = 0; i < n; ++i) {
+            int d = s.idx[i];
+            a1 += sh_t1[d];
+            a2 += sh_t2[d];
+            sw += s.w[d];
+          }
+          chi2 = (1.0 - hypot(a1 / sw, a2 / sw)) * sw;
         }
-        double chi2 = (1.0 - hypot(a1 / sw, a2 / sw)) * sw;
         double redchi2 = chi2 / ((double)n - ord);
         if (oi > 0) {
           if (redchi2 > 1.0 && prev_redchi2 < redchi2) sign = -sign;
@@ -417,6 +432,79 @@ flag_kernel(const double *__restrict__ resid, float *__restrict__ weights, int n
   }
 }
 
+
+// Amplitude type (_flag_outliers, stationscreen.py:341-348, with the log residual of :664-668):
+// ONE weighted rms per (freq, station, pol) group over all directions and times.  Systems are
+// time-major: sys = t * ngroups + g.  One warp per group, fixed summation order.
+__device__ __forceinline__ double amp_log_resid(double v, double r) { return log10(v) - log10(fabs(v - r)); }
+
+__global__ void __launch_bounds__(128)
+amp_std_kernel(const double *__restrict__ val, const double *__restrict__ resid,
+               const float *__restrict__ weights, int nall, int64_t nsys, int64_t ngroups,
+               double *__restrict__ group_std) {
+  const int lane = threadIdx.x & 31;
+  const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (g >= ngroups) return;
+  const int64_t nt = nsys / ngroups;
+  double acc = 0.0, sw = 0.0;
+  int cnt = 0;
+  for (int64_t t = 0; t < nt; ++t) {
+    const int64_t base = (t * ngroups + g) * nall;
+    for (int d = lane; d < nall; d += 32) {
+      const double w = (double)weights[base + d];
+      if (w > 0.0) {
+        const double diff = amp_log_resid(val[base + d], resid[base + d]);
+        acc = fma(diff * diff, w, acc);
+        sw += w;
+        ++cnt;
+      }
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    sw += __shfl_xor_sync(0xffffffffu, sw, o);
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  }
+  // no unflagged solution: _flag_outliers returns early (:329-330) -> nothing can exceed +inf
+  if (lane == 0) group_std[g] = cnt > 0 ? sqrt(acc / sw) : INFINITY;
+}
+
+__global__ void __launch_bounds__(128)
+amp_flag_kernel(const double *__restrict__ val, const double *__restrict__ resid, float *__restrict__ weights,
+                int nall, int64_t nsys, int64_t ngroups, double nsigma, const double *__restrict__ group_std,
+                uint64_t *__restrict__ masks) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t sys = warp; sys < nsys; sys += nwarps) {
+    float *w = weights + sys * nall;
+    const double lim = group_std ? nsigma * group_std[sys % ngroups] : INFINITY;
+    uint64_t m0 = 0, m1 = 0;
+    for (int d = lane; d < nall; d += 32) {
+      float wd = w[d];
+      if (group_std) {
+        const double diff = amp_log_resid(val[sys * nall + d], resid[sys * nall + d]);
+        if (fabs(diff) > lim) {
+          wd = 0.0f;
+          w[d] = 0.0f;
+        }
+      }
+      if (wd > 0.0f) {
+        if (d < 64) m0 |= 1ull << d;
+        else m1 |= 1ull << (d - 64);
+      }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      m0 |= __shfl_xor_sync(0xffffffffu, m0, o);
+      m1 |= __shfl_xor_sync(0xffffffffu, m1, o);
+    }
+    if (lane == 0) {
+      masks[2 * sys] = m0;
+      masks[2 * sys + 1] = m1;
+    }
+  }
+}
+
 }  // namespace
 
 extern "C" int ssf_kl_fit_pass(const double *phase, const float *weights, const int32_t *pat,
@@ -428,7 +516,7 @@ extern "C" int ssf_kl_fit_pass(const double *phase, const float *weights, const 
                   resid && status,
               "ssf_kl_fit_pass: null pointer");
   SSF_REQUIRE(ndir >= 2 && ndir <= SSF_MAX_DIR, "ssf_kl_fit_pass: ndir=%d out of range [2,%d]", ndir, SSF_MAX_DIR);
-  SSF_REQUIRE(mode == 0 || mode == 1, "ssf_kl_fit_pass: mode must be 0 or 1");
+  SSF_REQUIRE(mode >= 0 && mode <= 3, "ssf_kl_fit_pass: mode must be in 0..3");
   if (nsys <= 0) return SSF_OK;
   size_t smem = sizeof(double) * smem_doubles(ndir);
   if (smem > 48 * 1024)
@@ -450,6 +538,29 @@ extern "C" int ssf_kl_flag_outliers(const double *resid, float *weights, int ndi
   if (blocks > 148 * 16) blocks = 148 * 16;
   SSF_LAUNCH(flag_kernel, (int)blocks, 128, 0, (cudaStream_t)stream, resid, weights, ndir, nsys, nsigma,
              masks_out);
+  SSF_LAUNCHED();
+  return SSF_OK;
+}
+
+
+extern "C" int ssf_kl_flag_outliers_amp(const double *val, const double *resid, float *weights, int ndir,
+                                        int64_t nsys, int64_t ngroups, double nsigma, double *group_std,
+                                        uint64_t *masks_out, void *stream) {
+  SSF_REQUIRE(val && resid && weights && masks_out, "ssf_kl_flag_outliers_amp: null pointer");
+  SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR, "ssf_kl_flag_outliers_amp: ndir out of range");
+  if (nsys <= 0) return SSF_OK;
+  SSF_REQUIRE(ngroups >= 1 && nsys % ngroups == 0, "ssf_kl_flag_outliers_amp: nsys must be a multiple of ngroups");
+  const bool flag = nsigma < INFINITY;
+  SSF_REQUIRE(!flag || group_std, "ssf_kl_flag_outliers_amp: group_std scratch needed when flagging");
+  if (flag) {
+    SSF_LAUNCH(amp_std_kernel, ssf::div_up(ngroups * 32, 128), 128, 0, (cudaStream_t)stream, val, resid, weights,
+               ndir, nsys, ngroups, group_std);
+    SSF_LAUNCHED();
+  }
+  int64_t blocks = (nsys + 3) / 4;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  SSF_LAUNCH(amp_flag_kernel, (int)blocks, 128, 0, (cudaStream_t)stream, val, resid, weights, ndir, nsys, ngroups,
+             nsigma, flag ? (const double *)group_std : (const double *)nullptr, masks_out);
   SSF_LAUNCHED();
   return SSF_OK;
 }

@@ -147,6 +147,19 @@ class Engine:
                   _ptr(masks), self.stream())
         return masks
 
+    def kl_flag_outliers_amp(self, val, resid, weights, ngroups, nsigma):
+        """ssf_kl_flag_outliers_amp in place on ``weights`` (amplitude type: one rms per
+        (freq, station, pol) group over all directions and times); returns the masks."""
+        nsys, ndir = resid.shape
+        self._check(val, torch.float64, "val")
+        self._check(resid, torch.float64, "resid")
+        self._check(weights, torch.float32, "weights")
+        masks = self.empty((nsys, 2), torch.int64)
+        std = self.empty((ngroups,), torch.float64)
+        self._timed_call("kl_flag_outliers", "ssf_kl_flag_outliers_amp", _ptr(val), _ptr(resid), _ptr(weights),
+                         ndir, nsys, ngroups, float(nsigma), _ptr(std), _ptr(masks), self.stream())
+        return masks
+
     def kl_fit_pass(self, phase, weights, pat, pp, mats, mode, order, station_order, white, resid,
                     r0=R_0, beta=BETA, cut=PINV_CUT, status=None):
         nsys, ndir = phase.shape
@@ -164,7 +177,8 @@ class Engine:
         return status
 
     def kl_fit(self, phase, weights, station_order, pp, niter=2, nsigma=5.0, adjust_order=True,
-               r0=R_0, beta=BETA, cut=PINV_CUT, cache=None, check=True):
+               r0=R_0, beta=BETA, cut=PINV_CUT, cache=None, check=True, screen_type="phase",
+               ngroups=None):
         """The iteration structure of _process_station (stationscreen.py:658-779) for a batch
         of independent systems.  phase [nsys, ndir] f64 (already referenced), weights
         [nsys, ndir] f32 (modified in place by the flagging), station_order [nsys] f64.
@@ -172,8 +186,16 @@ class Engine:
         ``cache``: a PatternCache for these pierce points (decompositions of flag patterns are
         kept across calls); a temporary one is made if absent.
         ``check=False`` defers the convergence / weight-range checks: the caller must call
-        ``check_fit_status()`` later."""
+        ``check_fit_status()`` later.
+        ``screen_type="amplitude"``: ``phase`` holds amplitudes, rows are time-major with
+        ``ngroups`` = freq * station * pol systems per time slot (the outlier rms is taken per
+        group over all times, stationscreen.py:341-346); ``white`` are log10 screens."""
         nsys, ndir = phase.shape
+        amp = screen_type == "amplitude"
+        if screen_type not in ("phase", "amplitude"):
+            raise ValueError("screen_type must be 'phase' or 'amplitude'")
+        if amp and (not ngroups or nsys % ngroups):
+            raise ValueError("amplitude fits need ngroups (systems per time slot) dividing nsys")
         t0 = time.perf_counter()
         white = self.zeros((nsys, ndir), torch.float64)
         resid = self.zeros((nsys, ndir), torch.float64)
@@ -186,7 +208,10 @@ class Engine:
             self._fit_status = self.zeros((2,), torch.int32)     # [weights out of range, no convergence]
         for it in range(niter):
             t0 = time.perf_counter()
-            masks = self.kl_flag_outliers(resid, weights, nsigma if it > 0 else math.inf)
+            if amp:
+                masks = self.kl_flag_outliers_amp(phase, resid, weights, ngroups, nsigma if it > 0 else math.inf)
+            else:
+                masks = self.kl_flag_outliers(resid, weights, nsigma if it > 0 else math.inf)
             t0 = self.host_tick("flag_launch", t0)
             if it > 0 and not adjust_order:
                 # the flagged weights alias the "previous" weights in the reference, so
@@ -194,7 +219,7 @@ class Engine:
                 continue
             pat = cache.lookup(masks)
             t0 = self.host_tick("pattern_lookup", t0)
-            mode = 1 if (it > 0 and adjust_order) else 0
+            mode = (1 if (it > 0 and adjust_order) else 0) | (2 if amp else 0)
             self.kl_fit_pass(phase, weights, pat, pp, cache.mats, mode, order, station_order, white,
                              resid, r0, beta, cut, status=self._fit_status[0:1])
             self.host_tick("fit_pass_launch", t0)
@@ -241,6 +266,18 @@ class Engine:
             raise ValueError("slab has the wrong size")
         self._timed_call("kl_eval", "ssf_kl_eval", _ptr(bt), _ptr(g), ndir, ldg, npix, ncol, _ptr(slab), variant,
                   self.stream())
+        return slab
+
+    def kl_eval_gain(self, bt, g3, ndir, slab):
+        """g3 [ncol, 3, ldg] f32 (phase, Axx, Ayy coefficients) -> gain cube slab."""
+        ncol, _, ldg = g3.shape
+        npix = bt.shape[1]
+        self._check(slab, torch.float32, "slab")
+        self._check(g3, torch.float32, "g3")
+        if slab.numel() != ncol * 4 * npix:
+            raise ValueError("slab has the wrong size")
+        self._timed_call("kl_eval", "ssf_kl_eval_gain", _ptr(bt), _ptr(g3), ndir, ldg, npix, ncol, _ptr(slab),
+                         self.stream())
         return slab
 
     # ------------------------------------------------------------------ Voronoi

@@ -46,6 +46,11 @@ def station_orders(station_positions, ref_ant, order, min_order=5):
     return [max(min_order, min(order, int(np.float32(order) * np.sqrt(d / scale)))) for d in dist]
 
 
+def amplitude_order(n_dir):
+    """Order of the amplitude screens (kl_screen.py:95-97)."""
+    return min(12, max(3, int(np.round(n_dir / 2))))
+
+
 class KLScreen(Screen):
     """Class for KL (Karhunen-Lo`eve) screens (reference: kl_screen.py:22-59)."""
 
@@ -142,6 +147,34 @@ class KLScreen(Screen):
         weights_out = torch.where(skip[None, :, :, None], weight, work_w)
         eng.host_tick("fit_post", t_host)
         return white.view(n_t, n_f, n_a, n_d), resid.view(n_t, n_f, n_a, n_d), order, weights_out
+
+    def fit_amplitude_device(self, val, weight, check=True):
+        """stationscreen.run on an amplitude soltab as KLScreen.fit calls it (kl_screen.py:114-126:
+        niter=3, scale_order=False, no reference station) for device tensors val
+        [t, f, a, d, pol] f64 / weight f32.  Returns (white = log10 screens, resid, order
+        [t, f, a, pol], weights_out), in the input layout.  The outlier rms of the amplitude
+        type spans all time slots of a (freq, station, pol) (stationscreen.py:341-346), so this
+        takes the whole (slow) amplitude table at once."""
+        eng = self.engine
+        n_t, n_f, n_a, n_d, n_p = val.shape
+        v = val.permute(0, 1, 2, 4, 3).contiguous()                        # systems [t, f, a, pol] x dir
+        w = weight.permute(0, 1, 2, 4, 3).contiguous()
+        # (freq, station, pol) groups skipped by _process_single_freq (stationscreen.py:821-825)
+        skip = torch.isnan(v).all(dim=4).all(dim=0) | (w == 0).all(dim=4).all(dim=0)
+        work_w = torch.where(skip[None, ..., None], torch.zeros_like(w), w).contiguous()
+        groups = n_f * n_a * n_p
+        so = torch.full((n_t * groups,), float(amplitude_order(n_d)), dtype=torch.float64, device=eng.device)
+        white, resid, order = eng.kl_fit(v.view(-1, n_d), work_w.view(-1, n_d), so, self._pp_dev, niter=3,
+                                         nsigma=5.0, adjust_order=True, r0=self.r_0, beta=self.beta_val,
+                                         cut=PINV_CUT, cache=self._patterns, check=check,
+                                         screen_type="amplitude", ngroups=groups)
+        shape = (n_t, n_f, n_a, n_p, n_d)
+        order = order.view(n_t, n_f, n_a, n_p)
+        order = torch.where(skip[None], torch.zeros_like(order), order)
+        weights_out = torch.where(skip[None, ..., None], w, work_w)
+        back = (0, 1, 2, 4, 3)
+        return (white.view(shape).permute(back).contiguous(), resid.view(shape).permute(back).contiguous(),
+                order, weights_out.permute(back).contiguous())
 
     def stream_slabs(self, val_dev, wt_dev, slots, ring, cellsize_deg, first=0, count=None):
         """Streaming form of fit + evaluation for slab-at-a-time processing: yields
@@ -252,11 +285,10 @@ class KLScreen(Screen):
 
     def fit(self):
         """kl_screen.py:61-155 + stationscreen.run (phase type)."""
-        if not self.phase_only:
-            raise NotImplementedError("amplitude ('gain') soltabs are not supported by this engine yet")
         sol = self._load_solutions(self.input_phase_soltab_name)
         if sol.val.ndim != 4:
-            raise NotImplementedError("phase soltabs with a pol axis are not supported yet")
+            raise NotImplementedError("phase soltabs with a pol axis are not supported (scalarphase only, "
+                                      "as the reference's make_matrix assumes: kl_screen.py:263-271)")
         eng = self.engine
         self.setup(sol)
         white, resid, order, weights_out = self.fit_device(eng.tensor(sol.val, torch.float64),
@@ -266,6 +298,19 @@ class KLScreen(Screen):
         self.residuals = resid.cpu().numpy()
         self.screen_order = order.cpu().numpy()
         self.weights_out = weights_out.cpu().numpy()
+        if not self.phase_only:                                           # kl_screen.py:113-126, :135-139
+            amp = self._load_solutions(self.input_amplitude_soltab_name)
+            if amp.val.ndim != 5 or amp.val.shape[-1] < 2:
+                raise ValueError("amplitude soltab must be [time, freq, ant, dir, pol] with XX and YY")
+            a_white, a_resid, a_order, a_w = self.fit_amplitude_device(eng.tensor(amp.val, torch.float64),
+                                                                       eng.tensor(amp.weight, torch.float32))
+            self.log_amps = True
+            self.vals_amp = a_white.cpu().numpy()
+            self.times_amp = amp.time
+            self.freqs_amp = amp.freq
+            self.amp_residuals = a_resid.cpu().numpy()
+            self.amp_screen_order = a_order.cpu().numpy()
+            self.amp_weights_out = a_w.cpu().numpy()
 
     # ------------------------------------------------------------------ evaluation
     def _prepare(self, cellsize_deg, out_dir):
@@ -284,6 +329,13 @@ class KLScreen(Screen):
         # NaN -> (1, 0) is fused into the store of ssf_kl_eval either way.
         self._prepare(cellsize_deg, out_dir)
         eng = self.engine
+        if amp is not None:
+            # gain solutions: phase, log10 XX and log10 YY amplitude screens share the basis
+            n_col, n_d = cols.shape
+            stacked = torch.stack([cols, amp[..., 0], amp[..., 1]], dim=1).reshape(-1, n_d).contiguous()
+            g3 = eng.kl_coeffs(stacked, self._c_full)
+            eng.kl_eval_gain(self._basis, g3.view(n_col, 3, -1), n_d, slab)
+            return
         coeffs = eng.kl_coeffs(cols, self._c_full)
         eng.kl_eval(self._basis, coeffs, cols.shape[1], slab, self.eval_variant)
         if smooth_pix and smooth_pix > 0:

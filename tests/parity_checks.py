@@ -98,6 +98,65 @@ def check_fit(eng, seed=7, n_t=3, n_f=2, n_a=5, n_d=40):
     return scr, out
 
 
+def check_fit_amplitude(eng, seed=23, n_t=6, n_f=2, n_a=4, n_d=24):
+    """Amplitude-type fit (log10 screens, per-station rms clip over all times, niter=3)
+    against the port of stationscreen.run / _process_station / _fit_screen."""
+    from ska_sdp_screen_fitting_b200.h5parm_io import Solutions
+    from ska_sdp_screen_fitting_b200.kl_screen import KLScreen, amplitude_order
+
+    rng = np.random.default_rng(seed)
+    dirs = make_directions(rng, n_d)
+    pos = (np.array([3826896.2, 460979.5, 5064658.0]) + rng.normal(0, 2e4, (n_a, 3))).astype(np.float32)
+    pp, _, _ = klfit.piercepoints(dirs)
+    grad = rng.normal(0, 2e-4, (n_a, 2, 2))
+    log_amp = (grad[None, None, :, None, 0, :] * pp[None, None, None, :, 0, None]
+               + grad[None, None, :, None, 1, :] * pp[None, None, None, :, 1, None]
+               + rng.normal(0, 0.004, (n_t, n_f, n_a, n_d, 2)))
+    val = 10 ** log_amp
+    out_mask = rng.random(val.shape) < 0.004
+    val[out_mask] *= 1.6                                     # gross outliers for the 5-sigma clip
+    weight = np.ones(val.shape, np.float32)
+    weight[rng.random(val.shape) < 0.03] = 0.0
+    weight[:, 1, 2, :, 0] = 0.0                              # a fully flagged (freq, station, pol)
+    sol = Solutions.from_arrays(np.zeros((n_t, n_f, n_a, n_d)), np.ones((n_t, n_f, n_a, n_d), np.float32),
+                                np.arange(n_t) * 8.0, 1e8 + np.arange(n_f) * 1e6,
+                                [f"a{i}" for i in range(n_a)], [f"d{i}" for i in range(n_d)], dirs, pos)
+    scr = KLScreen("t", None, None, 126.23, 64.5, 1.0, 1.0)
+    scr._engine = eng
+    scr.setup(sol)
+    white, resid, order, w_out = scr.fit_amplitude_device(eng.tensor(val, torch.float64),
+                                                          eng.tensor(weight, torch.float32))
+    want = klfit.run_amplitude(val, weight.copy(), dirs, amplitude_order(n_d))
+    assert np.array_equal(w_out.cpu().numpy(), want["weights"])
+    assert (want["weights"] != weight).any(), "the case must exercise outlier flagging"
+    assert np.array_equal(order.cpu().numpy(), want["order"])
+    assert np.abs(white.cpu().numpy() - want["screen"]).max() < TOL_FIT
+    # the residuals are amplitudes (not logs) and scale with them: relative above 1
+    assert (np.abs(resid.cpu().numpy() - want["resid"]) <= TOL_FIT * np.maximum(1.0, np.abs(want["resid"]))).all()
+    return want
+
+
+def check_kl_gain_eval(eng, n=24, n_d=9, ncol=7, seed=31, cell=0.1):
+    """ssf_kl_eval_gain against the float64 oracle: 10^Axx / 10^Ayy times cos / sin."""
+    rng = np.random.default_rng(seed)
+    width = (n - 0.5) * cell
+    pp, mid_ra, mid_dec = klfit.piercepoints(make_directions(rng, n_d, spread=0.4 * width))
+    x, y = owcs.kl_grid_coords(126.23, 64.5, width, cell, mid_ra, mid_dec)
+    c_o, p_o, _ = klfit.calculate_svd(pp)
+    white = [rng.normal(0, s, (ncol, n_d)) @ p_o.T for s in (0.7, 0.05, 0.05)]
+    ppt = eng.tensor(pp[:, :2], torch.float64)
+    full = torch.tensor([mask_of(range(n_d))], dtype=torch.int64, device=eng.device)
+    c, p, _, _ = eng.kl_decompose(ppt, full)
+    bt = eng.kl_basis(eng.tensor(x, torch.float64), eng.tensor(y, torch.float64), ppt, p[0].contiguous())
+    stacked = np.stack(white, axis=1).reshape(-1, n_d)
+    g3 = eng.kl_coeffs(eng.tensor(stacked, torch.float64), c[0].contiguous()).view(ncol, 3, -1)
+    slab = eng.empty((ncol, 4, n, n), torch.float32)
+    eng.kl_eval_gain(bt, g3, n_d, slab)
+    want = screens.kl_make_matrix(x, y, pp, white[0], white[1], white[2])
+    got = slab.cpu().numpy()
+    assert (np.abs(got - want) <= TOL_KL * np.maximum(1.0, np.abs(want))).all()
+
+
 def check_kl_eval(eng, n=24, n_d=9, ncol=11, seed=3, variant=0, cell=0.1):
     """Directions are drawn in the central 80 % of the field (the geometry of BASELINE.json's
     synthetic configs): the screen is an interpolant there, not an extrapolant."""
@@ -207,6 +266,44 @@ def check_voronoi_gain_golden(eng, golden_dir, repo_solutions, tmp_path, full=Tr
         one = scr.make_matrix(0, 20, int(gold["sub_f"][1]), int(gold["sub_a"][2]), 0.2, None, 0)
         if smooth_pix == 0.0:
             assert np.array_equal(one.astype(np.float32), gold[key][:, 1, 2])
+
+
+def check_kl_gain_golden(eng, golden_dir, repo_solutions, full=True):
+    """KLScreen on gain solutions against what the reference's own code produced: the
+    amplitude screen soltab (values, residuals, orders, weights) and the a-term cube."""
+    import os
+
+    from ska_sdp_screen_fitting_b200.kl_screen import KLScreen
+
+    sols, gold = gain_solutions(golden_dir, repo_solutions)
+    scr = KLScreen("gain", None, os.path.join(golden_dir, "skymodel.txt"), 126.23, 64.50, 3.33, 3.33,
+                   phase_soltab_name="phase000", amplitude_soltab_name="amplitude000")
+    scr._engine = eng
+    scr.solutions = sols
+    sub_a = [int(a) for a in gold["sub_a"]]
+    if not full:
+        # emulator-sized: the amplitude fit of the four fixture stations (stations are independent)
+        scr.setup(sols["phase000"])
+        amp = sols["amplitude000"]
+        white, resid, order, w_out = scr.fit_amplitude_device(
+            eng.tensor(amp.val[:, :, sub_a], torch.float64), eng.tensor(amp.weight[:, :, sub_a], torch.float32))
+        assert np.abs(white.cpu().numpy() - gold["amp_screen"][:, :, sub_a]).max() < TOL_FIT
+        assert np.abs(resid.cpu().numpy() - gold["amp_resid"][:, :, sub_a]).max() < TOL_FIT
+        assert np.array_equal(order.cpu().numpy(), gold["amp_order"][:, :, sub_a])
+        assert np.array_equal(w_out.cpu().numpy(), gold["amp_screen_weights"][:, :, sub_a])
+        return
+    scr.fit()
+    assert np.abs(scr.vals_amp - gold["amp_screen"]).max() < TOL_FIT
+    assert np.abs(scr.amp_residuals - gold["amp_resid"]).max() < TOL_FIT
+    assert np.array_equal(scr.amp_screen_order, gold["amp_order"])
+    assert np.array_equal(scr.amp_weights_out, gold["amp_screen_weights"])
+    scr.interpolate()
+    assert scr.vals_amp.shape[:2] == scr.vals_ph.shape[:2]
+    for fi, f in enumerate(gold["sub_f"]):
+        for ai, a in enumerate(sub_a):
+            got = scr.make_matrix(0, 20, int(f), a, 0.2, None, 0)
+            want = gold["cube_kl"][:, fi, ai].astype(np.float64)
+            assert (np.abs(got - want) <= TOL_KL * np.maximum(1.0, np.abs(want))).all(), (fi, ai)
 
 
 def check_smooth(eng, shape=(5, 19, 37), sigmas=(0.5, 2.0, 5.0), seed=2):

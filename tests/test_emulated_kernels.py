@@ -34,6 +34,19 @@ def test_fit_repo_data_subset_against_reference_golden(emu_engine, repo_solution
         assert np.abs(scr.vals_ph[:, :, i] - want[:, :, i]).max() < pc.TOL_FIT
 
 
+def test_fit_amplitude_type(emu_engine):
+    pc.check_fit_amplitude(emu_engine)
+
+
+def test_kl_gain_fit_against_reference_golden(emu_engine, golden_dir, repo_solutions):
+    pc.check_kl_gain_golden(emu_engine, golden_dir, repo_solutions, full=False)
+
+
+def test_kl_gain_eval(emu_engine):
+    pc.check_kl_gain_eval(emu_engine)
+    pc.check_kl_gain_eval(emu_engine, n=11, n_d=5, ncol=3, seed=8)      # ragged: npix % 4 != 0
+
+
 def test_kl_eval(emu_engine):
     pc.check_kl_eval(emu_engine, n=12, ncol=9)
     pc.check_kl_eval(emu_engine, n=11, n_d=5, ncol=3, seed=8)      # ragged: npix % 4 != 0

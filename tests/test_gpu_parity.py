@@ -73,6 +73,15 @@ def test_voronoi_assign_and_fill(gpu_engine):
     pc.check_voronoi(gpu_engine, n=128, n_d=45, ncol=40, seed=13)
 
 
+def test_kl_gain(gpu_engine, golden_dir, repo_solutions):
+    pc.check_fit_amplitude(gpu_engine)
+    pc.check_fit_amplitude(gpu_engine, seed=29, n_t=9, n_f=3, n_a=6, n_d=45)
+    pc.check_kl_gain_eval(gpu_engine)
+    pc.check_kl_gain_eval(gpu_engine, n=11, n_d=5, ncol=3, seed=8)
+    pc.check_kl_gain_eval(gpu_engine, n=128, n_d=45, ncol=33, seed=9, cell=0.02)
+    pc.check_kl_gain_golden(gpu_engine, golden_dir, repo_solutions)
+
+
 def test_voronoi_gain(gpu_engine, golden_dir, repo_solutions, tmp_path):
     pc.check_voronoi_gain(gpu_engine)
     pc.check_voronoi_gain(gpu_engine, n=9, n_d=3, ncol=2, seed=12)
