@@ -141,3 +141,63 @@ def test_port_against_the_reference_modules_directly(repo_solutions):
     assert np.abs(scr_r - scr_p).max() < 1e-10
     assert np.abs(res_r - res_p).max() < 1e-10
     assert np.array_equal(w_r, w_p) and np.array_equal(ord_r, ord_p)
+
+
+# ------------------------------------------------------------------------------ gain fixture
+@pytest.fixture(scope="module")
+def gain_golden():
+    return np.load(os.path.join(GOLDEN, "gain_c1.npz"))
+
+
+def test_port_amplitude_fit_matches_reference_golden(repo_solutions, gain_golden):
+    """stationscreen.run on the amplitude soltab (kl_screen.py:114-126): log10 screens,
+    non-log residuals, orders and weights of the reference's amplitude_screen000 soltabs."""
+    g = gain_golden
+    sub_a = [int(a) for a in g["sub_a"]]
+    out = klfit.run_amplitude(g["amp_val"], g["amp_weight"], np.asarray(repo_solutions.source_positions),
+                              order=4, stations=sub_a)
+    assert np.abs(out["screen"][:, :, sub_a] - g["amp_screen"][:, :, sub_a]).max() < 1e-12
+    assert np.abs(out["resid"][:, :, sub_a] - g["amp_resid"][:, :, sub_a]).max() < 1e-12
+    assert np.array_equal(out["order"][:, :, sub_a], g["amp_order"][:, :, sub_a])
+    assert np.array_equal(out["weights"][:, :, sub_a], g["amp_screen_weights"][:, :, sub_a])
+
+
+def test_port_gain_cubes_match_reference_golden(repo_solutions, gain_golden, kl_golden, vor_golden):
+    """Screen.interpolate + the gain branches of both make_matrix implementations."""
+    g, sol = gain_golden, repo_solutions
+    sub_f, sub_a = [int(f) for f in g["sub_f"]], [int(a) for a in g["sub_a"]]
+    # Voronoi: amplitudes interpolated in log space from the raw soltab (log_amps False)
+    amp = screens.interpolate_amplitudes(g["amp_val"], g["amp_time"], g["amp_freq"], sol.time, sol.freq, False)
+    phases = screens.voronoi_reference_phases(sol.val, 0)
+    for key, sigma in (("cube_tessellated_nosmooth", 0.0), ("cube_tessellated", 0.5)):
+        cube = screens.voronoi_gain_cube(phases, amp, vor_golden["template"], sigma, freqs=sub_f, stations=sub_a)
+        assert np.abs(cube - g[key]).max() <= (1e-6 if sigma else 0.0), key
+    # KL: the log10 amplitude screens are interpolated as they are (log_amps True)
+    amp_w = screens.interpolate_amplitudes(g["amp_screen"], g["amp_time"], g["amp_freq"], sol.time, sol.freq, True)
+    x, y = wcs.kl_grid_coords(126.23, 64.50, 3.33, 0.2, float(kl_golden["midra"]), float(kl_golden["middec"]))
+    pp = kl_golden["piercepoints"]
+    for fi, f in enumerate(sub_f):
+        for ai, a in enumerate(sub_a):
+            data = screens.kl_make_matrix(x, y, pp, kl_golden["screen"][:, f, a], amp_w[:, f, a, :, 0],
+                                          amp_w[:, f, a, :, 1])
+            want = g["cube_kl"][:, fi, ai]
+            assert (np.abs(data.astype(np.float32) - want) <= 2e-6 * np.maximum(1.0, np.abs(want))).all()
+
+
+def test_product_interpolation_matches_scipy(gain_golden, repo_solutions):
+    """Screen.interpolate's restated nearest-neighbour rule against scipy's interp1d, including
+    exact midpoints and out-of-range abscissae."""
+    from ska_sdp_screen_fitting_b200.screen import _interp_axis
+
+    rng = np.random.default_rng(3)
+    x_old = np.array([0.0, 2.0, 4.0, 7.0])
+    vals = rng.normal(size=(4, 3, 2))
+    x_new = np.array([-5.0, 0.0, 1.0, 1.0000001, 3.0, 5.5, 6.9, 7.0, 30.0])
+    want = screens.interpolate_amplitudes(vals[:, None], x_old, np.array([1.0]), x_new, np.array([1.0]), True)
+    got = _interp_axis(x_old, vals[:, None], 0, x_new, "nearest")
+    assert np.array_equal(got, want)
+    g, sol = gain_golden, repo_solutions
+    want = screens.interpolate_amplitudes(g["amp_val"], g["amp_time"], g["amp_freq"], sol.time, sol.freq, False)
+    got = 10 ** _interp_axis(g["amp_freq"], _interp_axis(g["amp_time"], np.log10(g["amp_val"]), 0, sol.time, "nearest"),
+                             1, sol.freq, "nearest")
+    assert np.array_equal(got, want)
