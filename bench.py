@@ -161,6 +161,42 @@ class ClockSampler:
                 "source": "nvml" if self._nvml is not None else "nvidia-smi"}
 
 
+_ORIG_AFFINITY = None
+
+
+def bind_to_gpu_numa_node(index):
+    """Pin this rank's threads to the CPUs NVML names as local to its GPU, before any pinned
+    host buffer is allocated: first-touch then places the e2e staging buffers on the GPU's own
+    NUMA node instead of sending every D2H byte across the socket interconnect.  Undone by
+    ``restore_affinity`` before the CPU baseline (which wants all cores)."""
+    global _ORIG_AFFINITY
+    try:
+        import pynvml
+
+        if _ORIG_AFFINITY is None:
+            _ORIG_AFFINITY = os.sched_getaffinity(0)
+        pynvml.nvmlInit()
+        visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+        phys = int(visible.split(",")[index]) if visible and visible.replace(",", "").isdigit() else index
+        handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (os.cpu_count() + 63) // 64)
+        cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1}
+        cpus &= _ORIG_AFFINITY
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return sorted(cpus)
+    except Exception:  # noqa: BLE001 - affinity is an optimisation, never a requirement
+        return None
+
+
+def restore_affinity():
+    if _ORIG_AFFINITY is not None:
+        try:
+            os.sched_setaffinity(0, _ORIG_AFFINITY)
+        except OSError:
+            pass
+
+
 # ---------------------------------------------------------------------------- workload
 def auto_slots(workload):
     return {"lofar": 4, "voronoi1k": 1, "skalow": 1, "small": 4}[workload]
@@ -208,6 +244,7 @@ def run_ours(args):
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    bind_to_gpu_numa_node(local)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -574,6 +611,7 @@ def main():
         if res["e2e"] is not None:
             line["e2e"] = res["e2e"]
         if world == 1 and not args.no_cpu_baseline:
+            restore_affinity()
             ncpu = os.cpu_count() or 1
             use_kl = head == "kl"
             from ska_sdp_screen_fitting_b200 import synthetic
