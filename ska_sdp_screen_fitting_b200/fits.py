@@ -125,6 +125,25 @@ class CubeWriter:
         while done < nbytes:                         # pwrite caps at ~2 GiB per call
             done += os.pwrite(self._fd, view[done:done + (1 << 30)], off + done)
 
+    def write_columns(self, c0, slab, already_big_endian=False):
+        """slab: whole (time, freq, antenna) columns -- [ncol, 4, ny, nx] -- starting at the flat
+        column index ``c0`` = (t * n_freq + f) * n_ant + a.  The cube is column-major in exactly
+        that order (processing_utils.py:190-194), so any run of columns is one byte range."""
+        arr = np.ascontiguousarray(slab)
+        if arr.dtype.itemsize != 4:
+            raise TypeError("slab must be a 4-byte type")
+        if not already_big_endian:
+            arr = arr.astype(">f4", copy=False)
+        col_bytes = int(np.prod(self.shape[3:])) * 4
+        nbytes = arr.nbytes
+        if nbytes % col_bytes or c0 * col_bytes + nbytes > self.shape[0] * self._row_bytes:
+            raise ValueError("slab does not fit the cube")
+        view = memoryview(arr).cast("B")
+        off = len(self._head) + c0 * col_bytes
+        done = 0
+        while done < nbytes:
+            done += os.pwrite(self._fd, view[done:done + (1 << 30)], off + done)
+
     def close(self):
         if self._fd is not None:
             os.close(self._fd)

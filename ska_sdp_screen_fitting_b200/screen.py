@@ -205,10 +205,11 @@ class Screen:
         self.interpolate()
 
     # ------------------------------------------------------------------ write
-    def slab_times(self, cellsize_deg):
+    def slab_columns(self, cellsize_deg):
+        """(time, freq, antenna) columns per device slab.  A slab is a run of whole columns, not
+        of whole time slots: one SKA-Low time slot (32 freqs x 512 stations x 2048^2) is 1.1 TB."""
         n_y, n_x = self.image_shape(cellsize_deg)
-        per_time = len(self.freqs_ph) * len(self.station_names) * 16 * n_y * n_x
-        return max(1, int(self.slab_bytes // per_time))
+        return max(1, int(self.slab_bytes // (16 * n_y * n_x)))
 
     def write(self, out_dir, cellsize_deg, smooth_pix=0, ncpu=0):
         """Writes ``{name}_{g}.fits`` per gap-free time chunk and ``{name}.txt``
@@ -220,7 +221,11 @@ class Screen:
         n_f, n_a = len(self.freqs_ph), len(self.station_names)
         times = np.asarray(self.times_ph, np.float64)
         self._prepare(cellsize_deg, out_dir)
-        step = self.slab_times(cellsize_deg)
+        step = self.slab_columns(cellsize_deg)
+        per_t = n_f * n_a
+        n_d = self._dev_vals.shape[-1]
+        flat_vals = self._dev_vals.reshape(-1, n_d)
+        flat_amp = None if self.phase_only else self._dev_amp.reshape(-1, n_d, 2)
         pinned = [None, None]
         outfiles = []
         g_start = 0
@@ -239,11 +244,10 @@ class Screen:
             my0, my1 = split_range(g_start, g_stop, world, rank)
             pending = None
             buf = 0
-            for t0 in range(my0, my1, step):
-                t1 = min(my1, t0 + step)
-                n_d = self._dev_vals.shape[-1]
-                cols = self._dev_vals[t0:t1].reshape(-1, n_d)
-                amp = None if self.phase_only else self._dev_amp[t0:t1].reshape(-1, n_d, 2)
+            for c0 in range(my0 * per_t, my1 * per_t, step):
+                c1 = min(my1 * per_t, c0 + step)
+                cols = flat_vals[c0:c1]
+                amp = None if flat_amp is None else flat_amp[c0:c1]
                 slab = eng.empty((cols.shape[0], 4, n_y, n_x), torch.float32)
                 self._fill_columns(cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan=True, amp=amp)
                 eng.bswap32(slab)
@@ -258,7 +262,7 @@ class Screen:
                     event.record()
                 if pending is not None:
                     self._flush(writer, *pending)
-                pending = (t0 - g_start, host, event)
+                pending = (c0 - g_start * per_t, host, event)
                 buf ^= 1
                 voxels += cols.shape[0] * n_y * n_x
             if pending is not None:
@@ -275,7 +279,7 @@ class Screen:
         return outfiles
 
     @staticmethod
-    def _flush(writer, t_rel, host, event):
+    def _flush(writer, col_rel, host, event):
         if event is not None:
             event.synchronize()
-        writer.write_times(t_rel, host.numpy().view(">f4"), already_big_endian=True)
+        writer.write_columns(col_rel, host.numpy().view(">f4"), already_big_endian=True)

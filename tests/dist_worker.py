@@ -44,6 +44,9 @@ def main():
         if cls is VoronoiScreen:
             scr.patch_radec = radec
         scr.process()
+        if world > 1:
+            # 3 columns per device slab: slabs end in the middle of a time slot (10 columns each)
+            scr.slab_bytes = 3 * 16 * 17 * 17
         files = scr.write(out_dir, 0.2, smooth_pix=smooth)
         assert len(files) == 2
     if world > 1:
