@@ -292,6 +292,8 @@ def run_ours(args):
         ph = (v - v[:, :, kl.ref_ind:kl.ref_ind + 1, :]).reshape(-1, n_d)
         vo._fill_columns(ph, ring[i % 2], case.cellsize_deg, None, smooth_pix, True)
 
+    kept_timers = None
+
     def timed(step_fn, timer_keys):
         for i in range(args.warmup):
             step_fn(i)
@@ -329,6 +331,8 @@ def run_ours(args):
         ms = ev0.elapsed_time(ev1)
         launches = eng.launch_count() - launches0
         kern = eng.timer_summary()
+        nonlocal kept_timers
+        kept_timers = eng.timers
         eng.timers = None
         eng.check_fit_status()
         if dist is not None:
@@ -344,6 +348,8 @@ def run_ours(args):
         # side-stream spans (queueing behind the evaluation's CTAs + execution), whole run incl. warm-up for the host part
         fit_breakdown = {k: {"calls": kern[k][0], "mean_ms": kern[k][1]} for k in kern if k != "kl_eval"}
         fit_breakdown["pattern_slots_in_use"] = kl._patterns.stats()[0]
+        fit_breakdown["patterns_update_spans_ms"] = [round(a.elapsed_time(b), 3) for a, b in
+                                                     (kept_timers or {}).get("kl_patterns_update", [])]
         fit_breakdown["host_s"] = dict(eng.host_times)
         fit_breakdown["torch_device_allocs_total"] = torch.cuda.memory_stats().get("num_device_alloc", None)
         kl_stream.close()                     # stops the fit helper thread

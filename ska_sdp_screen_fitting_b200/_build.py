@@ -25,7 +25,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC",
-]
+] + os.environ.get("SSF_NVCC_EXTRA", "").split()      # experiment hook (e.g. -DSSF_DECOMP_BIG=1024)
 
 
 def _nvcc():

@@ -51,6 +51,14 @@ namespace {
 
 constexpr int TC_M = 128;                       // pixels per CTA tile = TMEM lanes
 constexpr int TC_N = 64;                        // accumulator columns per tile
+// Register cap of the two-CTAs-per-SM variant.  The kernel needs no more than 64 (no spills);
+// what is left of the 64 K register file decides whether the FP64 fit kernels of the next slabs
+// (fit_pass: 128 x 80 registers, decompose: 256 x 70) can be resident NEXT TO two evaluation
+// CTAs and run in their idle issue slots, or have to wait for an evaluation CTA to retire and
+// take its place.
+#ifndef SSF_TC_MAXREG
+#define SSF_TC_MAXREG 72
+#endif
 constexpr int B_STAGES = 2;                     // shared-memory ring of coefficient tiles
 constexpr int T_STAGES = 4;                     // TMEM accumulator ring
 constexpr int TMEM_COLS = T_STAGES * TC_N;      // 256 columns (two resident CTAs use all 512)
@@ -235,7 +243,7 @@ __global__ void split_b_kernel(const float *__restrict__ G, int ndir, int ldg, i
 // Shared memory (floats): A_hi[128 Kp] A_lo[128 Kp] B[2 stages][hi, lo][64 Kp], then the
 // mbarriers b_full[2] b_empty[2] t_full[4] t_empty[4] and the TMEM base address.
 template <bool KL, int NEPI>
-__global__ void __launch_bounds__((NEPI + 2) * 32, NEPI == 8 ? 2 : 1)
+__global__ void __maxnreg__(NEPI == 8 ? SSF_TC_MAXREG : 96)
 contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, int ndir, int64_t npix,
                    int64_t ncol, float *__restrict__ slab, int tiles_per_chunk, int Kp) {
   constexpr int CT = KL ? TC_N : TC_N / 2;       // slab columns per tile (Voronoi: re + im rows)

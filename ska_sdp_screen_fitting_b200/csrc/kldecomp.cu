@@ -13,6 +13,10 @@ namespace {
 // threads per CTA: 256 for up to 64 directions; 512 above, where a pattern's two 100 x 100
 // FP64 matrices leave room for only one CTA per SM and more warps hide the latency
 constexpr int MAX_SWEEPS = 40;
+#ifndef SSF_DECOMP_BIG
+#define SSF_DECOMP_BIG 512
+#endif
+constexpr int BIG = SSF_DECOMP_BIG;   // threads per CTA above 64 directions
 
 #ifdef SSF_CPU_EMU
 inline double rsqrt(double x) { return 1.0 / sqrt(x); }
@@ -377,10 +381,10 @@ extern "C" int ssf_kl_decompose(const double *pp, int ndir, const uint64_t *mask
   if (npat <= 0) return SSF_OK;
   const int mmax = (ndir + 1) & ~1;
   size_t smem = sizeof(double) * 2 * (size_t)mmax * mmax;
-  SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
+  SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
   SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
   if (ndir > 64) {
-    SSF_LAUNCH(decompose_kernel<512>, npat, 512, smem, (cudaStream_t)stream, pp, ndir, masks, r0 * r0,
+    SSF_LAUNCH(decompose_kernel<BIG>, npat, BIG, smem, (cudaStream_t)stream, pp, ndir, masks, r0 * r0,
                beta / 2.0, pinv_cut, C, pinvC, U, sv, (const int32_t *)nullptr, (int32_t *)nullptr);
   } else {
     SSF_LAUNCH(decompose_kernel<256>, npat, 256, smem, (cudaStream_t)stream, pp, ndir, masks, r0 * r0,
@@ -420,8 +424,8 @@ extern "C" int ssf_kl_patterns_update(const uint64_t *masks, int64_t nsys, int n
   size_t smem = sizeof(double) * 2 * (size_t)mmax * mmax;
   const int64_t bound = nsys < max_slots ? nsys : max_slots;
   if (ndir > 64) {
-    SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
-    SSF_LAUNCH(decompose_kernel<512>, (int)bound, 512, smem, st, pp, ndir, slot_masks, r0 * r0, beta / 2.0, pinv_cut,
+    SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
+    SSF_LAUNCH(decompose_kernel<BIG>, (int)bound, BIG, smem, st, pp, ndir, slot_masks, r0 * r0, beta / 2.0, pinv_cut,
                C, pinvC, U, sv, (const int32_t *)counters, status);
   } else {
     SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
