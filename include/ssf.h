@@ -155,9 +155,10 @@ int ssf_kl_eval(const float *Bt, const float *G, int ndir, int ldg, int64_t npix
 /* Gain solutions (scalar phase + log10 XX/YY amplitude screens, kl_screen.py:319-378):
  * G3 [ncol, 3, ldg] f32 = coefficients (phase, Axx, Ayy) from ssf_kl_coeffs on the stacked
  * white vectors; slab[col] = (10^Axx cos Phi, 10^Axx sin Phi, 10^Ayy cos Phi, 10^Ayy sin Phi),
- * NaN -> (1, 0, 1, 0) fused into the store. */
+ * NaN -> (1, 0, 1, 0) fused into the store.  variant: -1 auto, 0 FP32 SIMT, 1 tcgen05
+ * (16 columns x 3 accumulator groups per 64-wide tile; same kernel as ssf_kl_eval). */
 int ssf_kl_eval_gain(const float *Bt, const float *G3, int ndir, int ldg, int64_t npix,
-                     int64_t ncol, float *slab, void *stream);
+                     int64_t ncol, float *slab, int variant, void *stream);
 
 /* ------------------------------------------------------------------------------------
  * Voronoi.  ssf_voronoi_assign: float64 nearest patch per integer pixel, lowest index

@@ -45,7 +45,7 @@ SIGNATURES = {
     "ssf_kl_basis": (c_int, [_P, _P, c_int, c_int, _P, c_int, _P, c_double, c_double, _P, _P]),
     "ssf_kl_coeffs": (c_int, [_P, c_int64, c_int, _P, _P, c_int, _P]),
     "ssf_kl_eval": (c_int, [_P, _P, c_int, c_int, c_int64, c_int64, _P, c_int, _P]),
-    "ssf_kl_eval_gain": (c_int, [_P, _P, c_int, c_int, c_int64, c_int64, _P, _P]),
+    "ssf_kl_eval_gain": (c_int, [_P, _P, c_int, c_int, c_int64, c_int64, _P, c_int, _P]),
     "ssf_voronoi_assign": (c_int, [_P, _P, c_int, c_int, c_int, _P, _P]),
     "ssf_voronoi_lut": (c_int, [_P, _P, c_int64, c_int, _P, _P]),
     "ssf_voronoi_fill": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, c_int, _P]),

@@ -44,6 +44,10 @@ int contract_tc(bool, const float *, const float *, int, int, int64_t, int64_t, 
   set_error("tcgen05 contraction variant is not available in the CPU emulator");
   return SSF_ENOTSUP;
 }
+int contract_tc_gain(const float *, const float *, int, int, int64_t, int64_t, float *, cudaStream_t) {
+  set_error("tcgen05 contraction variant is not available in the CPU emulator");
+  return SSF_ENOTSUP;
+}
 }  // namespace ssf
 #else
 
@@ -63,6 +67,9 @@ constexpr int B_STAGES = 2;                     // shared-memory ring of coeffic
 constexpr int T_STAGES = 4;                     // TMEM accumulator ring
 constexpr int TMEM_COLS = T_STAGES * TC_N;      // 256 columns (two resident CTAs use all 512)
 constexpr int N_BARS = 2 * B_STAGES + 2 * T_STAGES;
+// Slab columns per 64-row coefficient tile.  MODE 0 = Voronoi (Re + Im rows per column),
+// 1 = KL phase screens (one row per column), 2 = KL gain (phase + log10 Axx + log10 Ayy rows).
+__host__ __device__ constexpr int tile_columns(int mode) { return mode == 1 ? TC_N : mode == 0 ? TC_N / 2 : 16; }
 
 // ------------------------------------------------------------------------------------ PTX
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -141,6 +148,18 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float *v) {
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// 32 lanes x 8 consecutive accumulator columns -> 8 registers per thread.
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float *v) {
+  uint32_t r[8];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
+}
+
 // Shared-memory matrix descriptor, K-major, no swizzle (cute::UMMA::SmemDescriptor):
 //   [0,14) start address >> 4, [16,30) leading byte offset >> 4 (core matrix to core matrix
 //   along K), [32,46) stride byte offset >> 4 (8-row group to 8-row group), [46,48) version = 1,
@@ -203,12 +222,32 @@ __device__ __forceinline__ void store_vo(const float (&v)[32], float *out, int64
   }
 }
 
+// Gain tiles: 8 slab columns per epilogue warp; phase, log10 Axx and log10 Ayy accumulators.
+__device__ __forceinline__ void store_gain(const float (&ph)[8], const float (&ax)[8], const float (&ay)[8],
+                                           float *out, int64_t npix, int nvalid) {
+  const int64_t p2 = 2 * npix, p3 = 3 * npix, p4 = 4 * npix;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (j >= nvalid) break;
+    float sn, cs;
+    sincos_reduced(ph[j], &sn, &cs);
+    const float axx = exp10f(ax[j]), ayy = exp10f(ay[j]);
+    __stcs(out, ssf::fix_re(axx * cs));
+    __stcs(out + npix, ssf::fix_im(axx * sn));
+    __stcs(out + p2, ssf::fix_re(ayy * cs));
+    __stcs(out + p3, ssf::fix_im(ayy * sn));
+    out += p4;
+  }
+}
+
 // ------------------------------------------------------------------------------------ pre-pass
 // Coefficient tiles, split and laid out as the MMA wants them:
 //   Bs[tile][hi | lo][canon(row, k)]   (64 rows x Kp, zero padded)
 // KL:      row r of tile t = slab column 64 t + r               (G[col, d], leading dimension ldg)
 // Voronoi: rows r < 32 = Re, r >= 32 = Im of column 32 t + (r & 31)   (lut[col, d, 0/1])
-template <bool KL>
+// Gain:    rows 16 g + r, g = 0 (phase), 1 (log10 Axx), 2 (log10 Ayy) of column 16 t + r;
+//          rows 48.. are zero                                   (G3[col, g, d], leading dimension ldg)
+template <int MODE>
 __global__ void split_b_kernel(const float *__restrict__ G, int ndir, int ldg, int64_t ncol, int Kp,
                                int64_t n_ct, float *__restrict__ Bs) {
   const int kc4 = Kp >> 2;
@@ -222,7 +261,10 @@ __global__ void split_b_kernel(const float *__restrict__ G, int ndir, int ldg, i
   for (int u = 0; u < 4; ++u) {
     const int k = 4 * kc + u;
     float v = 0.0f;
-    if (KL) {
+    if (MODE == 2) {
+      const int64_t col = tile * 16 + (r & 15);
+      if (r < 48 && col < ncol && k < ndir) v = G[(col * 3 + (r >> 4)) * ldg + k];
+    } else if (MODE == 1) {
       const int64_t col = tile * TC_N + r;
       if (col < ncol && k < ndir) v = G[col * ldg + k];
     } else {
@@ -242,11 +284,12 @@ __global__ void split_b_kernel(const float *__restrict__ G, int ndir, int ldg, i
 // ------------------------------------------------------------------------------------ kernel
 // Shared memory (floats): A_hi[128 Kp] A_lo[128 Kp] B[2 stages][hi, lo][64 Kp], then the
 // mbarriers b_full[2] b_empty[2] t_full[4] t_empty[4] and the TMEM base address.
-template <bool KL, int NEPI>
+template <int MODE, int NEPI>
 __global__ void __maxnreg__(NEPI == 8 ? SSF_TC_MAXREG : 96)
 contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, int ndir, int64_t npix,
                    int64_t ncol, float *__restrict__ slab, int tiles_per_chunk, int Kp) {
-  constexpr int CT = KL ? TC_N : TC_N / 2;       // slab columns per tile (Voronoi: re + im rows)
+  constexpr bool KL = MODE == 1;
+  constexpr int CT = tile_columns(MODE);         // slab columns per tile
   constexpr int THREADS = (NEPI + 2) * 32;
   constexpr int GROUPS = NEPI / 8;               // epilogue groups taking alternate tiles
   SSF_DYN_SMEM(float, sm);
@@ -373,6 +416,20 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, i
       const int64_t c0 = (ct_begin + it) * CT;
       mbar_wait(t_full + 8 * t, (it / T_STAGES) & 1);
       tc_fence_after();
+      if (MODE == 2) {
+        // this warp: its 32 pixels x slab columns c0 + 8 h .. + 7, three accumulator groups
+        float ph[8], ax[8], ay[8];
+        const uint32_t ta = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TC_N + 8 * h);
+        tmem_ld8(ta, ph);
+        tmem_ld8(ta + 16, ax);
+        tmem_ld8(ta + 32, ay);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(t_empty + 8 * t);
+        const int64_t left = ncol - (c0 + 8 * h);
+        if (left > 0) store_gain(ph, ax, ay, slab + (c0 + 8 * h) * 4 * npix + pix, npix, left >= 8 ? 8 : (int)left);
+        continue;
+      }
       float v[32];
       tmem_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TC_N + 32 * h), v);
       tc_fence_before();
@@ -438,11 +495,11 @@ cudaMemPool_t scratch_pool(int device) {
   return pools[device];
 }
 
-template <bool KL, int NEPI>
+template <int MODE, int NEPI>
 int launch_kernel(const float *Bt, const float *Bs, int ndir, int64_t npix, int64_t ncol, float *slab, int Kp,
                   size_t smem, int per_sm, cudaStream_t stream) {
-  constexpr int CT = KL ? TC_N : TC_N / 2;
-  auto kfn = contract_tc_kernel<KL, NEPI>;
+  constexpr int CT = tile_columns(MODE);
+  auto kfn = contract_tc_kernel<MODE, NEPI>;
   SSF_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int pix_tiles = (int)(npix / TC_M);
   const int64_t n_ct = (ncol + CT - 1) / CT;
@@ -460,10 +517,10 @@ int launch_kernel(const float *Bt, const float *Bs, int ndir, int64_t npix, int6
   return SSF_OK;
 }
 
-template <bool KL>
+template <int MODE>
 int launch_tc(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
               cudaStream_t stream) {
-  constexpr int CT = KL ? TC_N : TC_N / 2;
+  constexpr int CT = tile_columns(MODE);
   const int Kp = (ndir + 7) / 8 * 8;
   const int64_t n_ct = (ncol + CT - 1) / CT;
   if (n_ct == 0) return SSF_OK;
@@ -478,10 +535,10 @@ int launch_tc(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, 
   const size_t bs_bytes = sizeof(float) * (size_t)n_ct * 2 * TC_N * Kp;
   SSF_CUDA(cudaMallocFromPoolAsync(reinterpret_cast<void **>(&Bs), bs_bytes, pool, stream));
   const int64_t n_thr = n_ct * TC_N * (Kp >> 2);
-  SSF_LAUNCH(split_b_kernel<KL>, ssf::div_up(n_thr, 256), 256, 0, stream, G, ndir, ldg, ncol, Kp, n_ct, Bs);
+  SSF_LAUNCH(split_b_kernel<MODE>, ssf::div_up(n_thr, 256), 256, 0, stream, G, ndir, ldg, ncol, Kp, n_ct, Bs);
   SSF_LAUNCHED();
-  int rc = per_sm == 2 ? launch_kernel<KL, 8>(Bt, Bs, ndir, npix, ncol, slab, Kp, smem, per_sm, stream)
-                       : launch_kernel<KL, 16>(Bt, Bs, ndir, npix, ncol, slab, Kp, smem, per_sm, stream);
+  int rc = per_sm == 2 ? launch_kernel<MODE, 8>(Bt, Bs, ndir, npix, ncol, slab, Kp, smem, per_sm, stream)
+                       : launch_kernel<MODE, 16>(Bt, Bs, ndir, npix, ncol, slab, Kp, smem, per_sm, stream);
   cudaError_t fe = cudaFreeAsync(Bs, stream);
   if (rc == SSF_OK) SSF_CUDA(fe);
   return rc;
@@ -500,10 +557,14 @@ int contract_tc(bool kl, const float *Bt, const float *G, int ndir, int ldg, int
                 float *slab, cudaStream_t stream) {
   if (kl) {
     SSF_REQUIRE(ldg % 4 == 0 && (uintptr_t)G % 16 == 0, "tcgen05 KL contraction: G must be 16 B aligned, ldg %% 4 == 0");
-    return launch_tc<true>(Bt, G, ndir, ldg, npix, ncol, slab, stream);
+    return launch_tc<1>(Bt, G, ndir, ldg, npix, ncol, slab, stream);
   }
   SSF_REQUIRE((uintptr_t)G % 8 == 0, "tcgen05 Voronoi contraction: lut must be 8 B aligned");
-  return launch_tc<false>(Bt, G, ndir, ldg, npix, ncol, slab, stream);
+  return launch_tc<0>(Bt, G, ndir, ldg, npix, ncol, slab, stream);
+}
+int contract_tc_gain(const float *Bt, const float *G3, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
+                     cudaStream_t stream) {
+  return launch_tc<2>(Bt, G3, ndir, ldg, npix, ncol, slab, stream);
 }
 }  // namespace ssf
 #endif  // SSF_CPU_EMU

@@ -8,6 +8,7 @@ int kl_eval_simt(const float *, const float *, int, int, int64_t, int64_t, float
 int voronoi_contract_simt(const float *, const float *, int, int64_t, int64_t, float *, cudaStream_t);
 int contract_tc(bool kl, const float *, const float *, int, int, int64_t, int64_t, float *, cudaStream_t);
 bool contract_tc_supported(bool kl, int ndir, int64_t npix, int64_t ncol, const void *bt, const void *slab);
+int contract_tc_gain(const float *, const float *, int, int, int64_t, int64_t, float *, cudaStream_t);
 }  // namespace ssf
 
 namespace {
@@ -213,10 +214,17 @@ extern "C" int ssf_voronoi_contract(const float *S, const float *lut, int ndir, 
 
 
 extern "C" int ssf_kl_eval_gain(const float *Bt, const float *G3, int ndir, int ldg, int64_t npix,
-                                int64_t ncol, float *slab, void *stream) {
+                                int64_t ncol, float *slab, int variant, void *stream) {
   SSF_REQUIRE(Bt && G3 && slab, "ssf_kl_eval_gain: null pointer");
   SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR && ldg >= ndir && npix >= 1, "ssf_kl_eval_gain: bad sizes");
   if (ncol <= 0) return SSF_OK;
+  const bool tc_ok = ssf::contract_tc_supported(true, ndir, npix, ncol, Bt, slab);
+  if (variant == 1 && !tc_ok) {
+    ssf::set_error("ssf_kl_eval_gain: tcgen05 variant needs npix %% 128 == 0 and 16 B aligned buffers");
+    return SSF_ENOTSUP;
+  }
+  if (variant == 1 || (variant < 0 && tc_ok))
+    return ssf::contract_tc_gain(Bt, G3, ndir, ldg, npix, ncol, slab, (cudaStream_t)stream);
   const int64_t pix_tiles = (npix + 4 * GAIN_THREADS - 1) / (4 * GAIN_THREADS);
   // enough column chunks for ~8 CTAs per SM; a chunk keeps its basis tile in L1 across columns
   int64_t chunks = (148 * 8 + pix_tiles - 1) / pix_tiles;

@@ -268,7 +268,7 @@ class Engine:
                   self.stream())
         return slab
 
-    def kl_eval_gain(self, bt, g3, ndir, slab):
+    def kl_eval_gain(self, bt, g3, ndir, slab, variant=-1):
         """g3 [ncol, 3, ldg] f32 (phase, Axx, Ayy coefficients) -> gain cube slab."""
         ncol, _, ldg = g3.shape
         npix = bt.shape[1]
@@ -277,7 +277,7 @@ class Engine:
         if slab.numel() != ncol * 4 * npix:
             raise ValueError("slab has the wrong size")
         self._timed_call("kl_eval", "ssf_kl_eval_gain", _ptr(bt), _ptr(g3), ndir, ldg, npix, ncol, _ptr(slab),
-                         self.stream())
+                         variant, self.stream())
         return slab
 
     # ------------------------------------------------------------------ Voronoi

@@ -334,7 +334,7 @@ class KLScreen(Screen):
             n_col, n_d = cols.shape
             stacked = torch.stack([cols, amp[..., 0], amp[..., 1]], dim=1).reshape(-1, n_d).contiguous()
             g3 = eng.kl_coeffs(stacked, self._c_full)
-            eng.kl_eval_gain(self._basis, g3.view(n_col, 3, -1), n_d, slab)
+            eng.kl_eval_gain(self._basis, g3.view(n_col, 3, -1), n_d, slab, self.eval_variant)
             return
         coeffs = eng.kl_coeffs(cols, self._c_full)
         eng.kl_eval(self._basis, coeffs, cols.shape[1], slab, self.eval_variant)

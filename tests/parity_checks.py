@@ -136,7 +136,7 @@ def check_fit_amplitude(eng, seed=23, n_t=6, n_f=2, n_a=4, n_d=24):
     return want
 
 
-def check_kl_gain_eval(eng, n=24, n_d=9, ncol=7, seed=31, cell=0.1):
+def check_kl_gain_eval(eng, n=24, n_d=9, ncol=7, seed=31, cell=0.1, variant=0):
     """ssf_kl_eval_gain against the float64 oracle: 10^Axx / 10^Ayy times cos / sin."""
     rng = np.random.default_rng(seed)
     width = (n - 0.5) * cell
@@ -151,7 +151,7 @@ def check_kl_gain_eval(eng, n=24, n_d=9, ncol=7, seed=31, cell=0.1):
     stacked = np.stack(white, axis=1).reshape(-1, n_d)
     g3 = eng.kl_coeffs(eng.tensor(stacked, torch.float64), c[0].contiguous()).view(ncol, 3, -1)
     slab = eng.empty((ncol, 4, n, n), torch.float32)
-    eng.kl_eval_gain(bt, g3, n_d, slab)
+    eng.kl_eval_gain(bt, g3, n_d, slab, variant)
     want = screens.kl_make_matrix(x, y, pp, white[0], white[1], white[2])
     got = slab.cpu().numpy()
     assert (np.abs(got - want) <= TOL_KL * np.maximum(1.0, np.abs(want))).all()

@@ -79,6 +79,10 @@ def test_kl_gain(gpu_engine, golden_dir, repo_solutions):
     pc.check_kl_gain_eval(gpu_engine)
     pc.check_kl_gain_eval(gpu_engine, n=11, n_d=5, ncol=3, seed=8)
     pc.check_kl_gain_eval(gpu_engine, n=128, n_d=45, ncol=33, seed=9, cell=0.02)
+    # tcgen05 variant: ragged column tiles (16 per tile), one- and two-CTA-per-SM shapes
+    pc.check_kl_gain_eval(gpu_engine, n=128, n_d=45, ncol=33, seed=9, cell=0.02, variant=1)
+    pc.check_kl_gain_eval(gpu_engine, n=64, n_d=9, ncol=7, seed=10, cell=0.05, variant=1)
+    pc.check_kl_gain_eval(gpu_engine, n=64, n_d=100, ncol=50, seed=11, cell=0.05, variant=1)
     pc.check_kl_gain_golden(gpu_engine, golden_dir, repo_solutions)
 
 
