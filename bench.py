@@ -403,6 +403,29 @@ def run_ours(args):
         out["voronoi"]["smooth"] = {"sigma_pix": smooth_pix, "kernel_ms": g_ms,
                                     "achieved": voxels_per_step * 64 / (g_ms * 1e-3) / 1e9,
                                     "unit": "GB/s", "algorithmic_bytes_per_voxel": 64}
+    if args.workload != "voronoi1k":
+        # gain solutions (scalar phase + XX/YY amplitude screens, kl_screen.py:319-378): the
+        # evaluation of three screens per voxel on the same kernel.  The amplitude fit runs once
+        # per run on the slow amplitude grid, so the per-slab work is this evaluation next to the
+        # phase fit measured above; the screens here are seeded log10 amplitudes of +-5 %.
+        gen = torch.Generator(device=eng.device).manual_seed(7)
+        white_g = kl.fit_device(val_dev[:slots], wt_dev[:slots], check=False)[0].view(-1, n_d)
+        amp_fit = 0.02 * torch.randn((cols, n_d, 2), dtype=torch.float64, device=eng.device, generator=gen)
+        amp_white = torch.einsum("de,cep->cdp", kl._pinv_full, amp_fit).contiguous()
+
+        def gain_step(i):
+            kl._fill_columns(white_g, ring[i % 2], case.cellsize_deg, None, 0.0, True, amp=amp_white)
+
+        ms_g, launches_g, kern_g, clocks_g = timed(gain_step, ["kl_eval"])
+        n_launch, k_ms = kern_g["kl_eval"]
+        achieved_g = voxels_per_step * BYTES_PER_VOXEL / (k_ms * 1e-3) / 1e9
+        out["gain"] = dict(ms=ms_g, launches=launches_g, clocks=clocks_g,
+                           roofline={"bound": "hbm", "kernel": "contract_tc_kernel<gain> (ssf_kl_eval_gain: phase + "
+                                     "log10 Axx + log10 Ayy screens, tcgen05 split-TF32)",
+                                     "achieved": achieved_g, "peak": peak, "unit": "GB/s", "frac": achieved_g / peak,
+                                     "traffic": recorded_traffic("kl_eval_gain"), "kernel_ms": k_ms,
+                                     "kernel_launches": n_launch, "peak_source": peak_src,
+                                     "kernel_share_of_step": k_ms * n_launch / ms_g})
     e2e = None
     if not args.no_e2e:
         e2e = run_e2e(args, eng, case, kl, vo, dist, smooth_pix)
@@ -614,6 +637,11 @@ def main():
                                "gpu_launches": out["voronoi"]["launches"], "clocks": out["voronoi"]["clocks"]}
         elif "smooth" in out["voronoi"]:
             line["smooth"] = out["voronoi"]["smooth"]
+        if "gain" in out:
+            gms = out["gain"]["ms"]
+            line["kl_gain_eval"] = {"value": world * args.steps * res["voxels_per_step"] / (gms * 1e-3),
+                                    "unit": UNIT, "ms_per_step": gms / args.steps,
+                                    "roofline": out["gain"]["roofline"], "gpu_launches": out["gain"]["launches"]}
         if res["e2e"] is not None:
             line["e2e"] = res["e2e"]
         if world == 1 and not args.no_cpu_baseline:
