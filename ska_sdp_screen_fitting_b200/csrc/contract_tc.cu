@@ -50,6 +50,7 @@ int contract_tc_gain(const float *, const float *, int, int, int64_t, int64_t, f
 }
 }  // namespace ssf
 #else
+#include <cuda.h>
 
 namespace {
 
@@ -100,6 +101,12 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
                "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+// TMA tiled 2-D load (tensor map): box at element coordinates (x, y) -> dense rows in shared memory.
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, int x, int y, uint32_t bar) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
+               "l"(map), "r"(x), "r"(y), "r"(bar)
                : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() {
@@ -459,6 +466,224 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, i
   }
 }
 
+// ------------------------------------------------------------------------------------ big-K kernel
+// More than 56 directions: the split basis tile alone is > 57 KB x 2, so only one CTA fits an SM
+// and the kernel above cannot hide the staging of its basis tile behind a second CTA (0.68-0.72 of
+// the measured HBM peak at 100 directions).  This variant is PERSISTENT (one CTA per SM walks a list
+// of (pixel tile, column chunk) items) and keeps the split basis operand in TENSOR MEMORY
+// (tcgen05.mma with A from TMEM: lane = pixel row, one TF32 per 32-bit column, 2 Kp columns next to
+// the 4 x 64 accumulator columns).  Shared memory then only holds the coefficient ring (3 stages)
+// and the RAW basis tile of the NEXT item, which the TMA lane prefetches with one tensor-map copy
+// while the current item is being contracted; four converter warps split it into TMEM
+// (tcgen05.st) as soon as the last MMA of the current item has retired, while the 16 epilogue warps
+// still have accumulator stages to drain.
+//   shared memory (floats): raw[Kp][128]  B[nb stages][hi, lo][64 Kp]
+//   tensor memory (columns): D[4][64] | A_hi[Kp] | A_lo[Kp]
+constexpr int BK_EPI = 16, BK_CONV = 4;
+constexpr int BK_THREADS = (BK_EPI + 2 + BK_CONV) * 32;
+constexpr int BK_MAXB = 3;
+constexpr int BK_NBARS = 2 * BK_MAXB + 2 * T_STAGES + 4;
+constexpr int BK_ACOL = T_STAGES * TC_N;         // first TMEM column of A_hi
+
+// D[tmem] (+)= A[tmem] * B[smem desc], kind::tf32, issued by ONE thread.
+__device__ __forceinline__ void tc_mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                               uint32_t accumulate) {
+  asm volatile(
+      "{ .reg .pred p; setp.ne.b32 p, %4, 0;\n"
+      "  tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p; }"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 32 lanes x 8 consecutive columns <- 8 registers per thread.
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const float *v) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr),
+               "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])),
+               "r"(__float_as_uint(v[3])), "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])),
+               "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7]))
+               : "memory");
+}
+
+__global__ void __launch_bounds__(BK_THREADS, 1)
+contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float *__restrict__ Bs, int ndir,
+                        int64_t npix, int64_t ncol, float *__restrict__ slab, int tiles_per_chunk, int chunks,
+                        int Kp, int nb, int64_t n_items) {
+  SSF_DYN_SMEM(float, sm);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int kc4 = Kp >> 2;
+  float *raw = sm;
+  float *b_base = sm + TC_M * Kp;                // stage s: hi at s*2*64*Kp, lo right after
+  uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (TC_M + 2 * nb * TC_N) * Kp);
+  uint32_t *tmem_holder = reinterpret_cast<uint32_t *>(bars + BK_NBARS);
+  const uint32_t b_full = smem_u32(bars), b_empty = smem_u32(bars + BK_MAXB);
+  const uint32_t t_full = smem_u32(bars + 2 * BK_MAXB), t_empty = smem_u32(bars + 2 * BK_MAXB + T_STAGES);
+  const uint32_t raw_full = smem_u32(bars + 2 * BK_MAXB + 2 * T_STAGES), raw_free = raw_full + 8;
+  const uint32_t a_ready = raw_full + 16, a_free = raw_full + 24;
+  const uint32_t stage_bytes = (uint32_t)(2 * TC_N * Kp * sizeof(float));
+  const int64_t n_ct = (ncol + TC_N - 1) / TC_N;
+
+  if (tid == BK_EPI * 32) {
+    for (int i = 0; i < BK_MAXB; ++i) {
+      mbar_init(b_full + 8 * i, 1);
+      mbar_init(b_empty + 8 * i, 1);
+    }
+    for (int i = 0; i < T_STAGES; ++i) {
+      mbar_init(t_full + 8 * i, 1);
+      mbar_init(t_empty + 8 * i, 8);
+    }
+    mbar_init(raw_full, 1);
+    mbar_init(raw_free, BK_CONV * 32);
+    mbar_init(a_ready, BK_CONV * 32);
+    mbar_init(a_free, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == BK_EPI + 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(tmem_holder)),
+                 "n"(512)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+
+  // every role walks the same list of items: item -> (pixel tile, first column tile, tile count)
+#define BK_ITEM(item, pix0, ct0, nt)                                                   \
+  const int64_t pix0 = ((item) / chunks) * TC_M;                                       \
+  const int64_t ct0 = ((item) % chunks) * (int64_t)tiles_per_chunk;                    \
+  const int nt = (int)((ct0 + tiles_per_chunk <= n_ct ? ct0 + tiles_per_chunk : n_ct) - ct0)
+
+  if (warp == BK_EPI) {
+    // ===== TMA lane: raw basis tile of the NEXT item, then the coefficient tiles of this one =====
+    if (lane == 0) {
+      auto load_raw = [&](int64_t item) {
+        // one tensor-map copy: box = Kp direction rows x 128 pixels of Bt[ndir][npix]; rows beyond
+        // ndir are out of bounds and arrive as zeros
+        const int64_t p0 = (item / chunks) * TC_M;
+        mbar_expect_tx(raw_full, (uint32_t)Kp * TC_M * (uint32_t)sizeof(float));
+        tma_load_2d(smem_u32(raw), &bt_map, (int)p0, 0, raw_full);
+      };
+      load_raw(blockIdx.x);
+      uint32_t T = 0;
+      int j = 0;
+      for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++j) {
+        BK_ITEM(item, pix0, ct0, nt);
+        (void)pix0;
+        if (item + gridDim.x < n_items) {
+          mbar_wait(raw_free, j & 1);                 // the converters have read this item's raw tile
+          load_raw(item + gridDim.x);
+        }
+        for (int it = 0; it < nt; ++it, ++T) {
+          const int s = T % nb;
+          if (T >= (uint32_t)nb) mbar_wait(b_empty + 8 * s, (T / nb - 1) & 1);
+          mbar_expect_tx(b_full + 8 * s, stage_bytes);
+          bulk_g2s(smem_u32(b_base + (size_t)s * 2 * TC_N * Kp), Bs + (ct0 + it) * (2 * TC_N * Kp), stage_bytes,
+                   b_full + 8 * s);
+        }
+      }
+    }
+  } else if (warp == BK_EPI + 1) {
+    // ===== MMA lane: A from tensor memory =====
+    if (lane == 0) {
+      const uint32_t lbo = 128, sbo = (uint32_t)kc4 * 128;
+      const uint32_t ta_hi = tmem_base + BK_ACOL, ta_lo = ta_hi + (uint32_t)Kp;
+      const int ksteps = Kp >> 3;
+      uint32_t T = 0;
+      int j = 0;
+      for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++j) {
+        BK_ITEM(item, pix0, ct0, nt);
+        (void)pix0;
+        (void)ct0;
+        mbar_wait(a_ready, j & 1);                    // split basis tile of this item is in TMEM
+        tc_fence_after();
+        for (int it = 0; it < nt; ++it, ++T) {
+          const int s = T % nb, t = T % T_STAGES;
+          mbar_wait(b_full + 8 * s, (T / nb) & 1);
+          if (T >= T_STAGES) mbar_wait(t_empty + 8 * t, (T / T_STAGES - 1) & 1);
+          tc_fence_after();
+          const float *bh = b_base + (size_t)s * 2 * TC_N * Kp;
+          const uint64_t db_hi = make_desc(smem_u32(bh), lbo, sbo), db_lo = make_desc(smem_u32(bh + TC_N * Kp), lbo, sbo);
+          const uint32_t d_tmem = tmem_base + (uint32_t)(t * TC_N);
+          for (int ks = 0; ks < ksteps; ++ks) {       // corrections first (see the kernel above)
+            const uint64_t adv = (uint64_t)(ks * 16);
+            const uint32_t ac = (uint32_t)(ks * 8);   // one K step = 8 TF32 = 8 TMEM columns of A
+            tc_mma_tf32_ts(d_tmem, ta_lo + ac, db_lo + adv, IDESC, ks > 0);
+            tc_mma_tf32_ts(d_tmem, ta_lo + ac, db_hi + adv, IDESC, 1);
+            tc_mma_tf32_ts(d_tmem, ta_hi + ac, db_lo + adv, IDESC, 1);
+          }
+          for (int ks = 0; ks < ksteps; ++ks)
+            tc_mma_tf32_ts(d_tmem, ta_hi + (uint32_t)(ks * 8), db_hi + (uint64_t)(ks * 16), IDESC, 1);
+          tc_commit(b_empty + 8 * s);
+          tc_commit(t_full + 8 * t);
+        }
+        tc_commit(a_free);                            // the basis operand may be overwritten
+      }
+    }
+  } else if (warp >= BK_EPI + 2) {
+    // ===== converter warps: raw[k][row] -> split operand in TMEM, thread = pixel row = TMEM lane =====
+    const int cw = warp & 3;                          // the TMEM lane quadrant this warp may touch
+    const int r = 32 * cw + lane;
+    const uint32_t ta_hi = tmem_base + ((uint32_t)(32 * cw) << 16) + BK_ACOL, ta_lo = ta_hi + (uint32_t)Kp;
+    int j = 0;
+    for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++j) {
+      mbar_wait(raw_full, j & 1);
+      if (j > 0) mbar_wait(a_free, (j - 1) & 1);
+      tc_fence_after();
+      for (int k0 = 0; k0 < Kp; k0 += 8) {
+        float hi[8], lo[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const float x = (k0 + u < ndir) ? raw[(k0 + u) * TC_M + r] : 0.0f;
+          hi[u] = to_tf32(x);
+          lo[u] = to_tf32(x - hi[u]);
+        }
+        tmem_st8(ta_hi + (uint32_t)k0, hi);
+        tmem_st8(ta_lo + (uint32_t)k0, lo);
+      }
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      tc_fence_before();
+      mbar_arrive(raw_free);
+      mbar_arrive(a_ready);
+    }
+  } else {
+    // ===== epilogue warps: group g = warp / 8 takes the tiles T with T % 2 == g =====
+    const int g = warp >> 3, q = warp & 3, h = (warp >> 2) & 1;
+    uint32_t T = 0;
+    for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x) {
+      BK_ITEM(item, pix0, ct0, nt);
+      const int64_t pix = pix0 + 32 * q + lane;
+      for (int it = 0; it < nt; ++it, ++T) {
+        if ((int)(T & 1) != g) continue;
+        const int t = T % T_STAGES;
+        mbar_wait(t_full + 8 * t, (T / T_STAGES) & 1);
+        tc_fence_after();
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TC_N + 32 * h), v);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(t_empty + 8 * t);
+        const int64_t c0 = (ct0 + it) * TC_N + 32 * h;
+        float *out = slab + c0 * 4 * npix + pix;
+        const int64_t left = ncol - c0;
+        if (left >= 32) store_kl<false>(v, out, npix, 32);
+        else if (left > 0) store_kl<true>(v, out, npix, (int)left);
+      }
+    }
+  }
+#undef BK_ITEM
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == BK_EPI + 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
+  }
+}
+
+int launch_bigk(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
+                cudaMemPool_t pool, cudaStream_t stream);
+
 // Column tiles per CTA.  Measured on B200 (profiles/r01c chunk sweeps): with the coefficient
 // tiles arriving by TMA the launch is fastest when a CTA covers about 256 slab columns (4 KL
 // tiles / 8 Voronoi tiles, 0.5 MB of cube): 0.93 of the measured HBM peak against 0.78 for CTAs
@@ -471,6 +696,65 @@ int pick_tiles_per_cta(int ct, int Kp, int64_t n_ct) {
   if (per < Kp / 12) per = Kp / 12;
   if (per > n_ct) per = n_ct;
   return (int)(per < 1 ? 1 : per);
+}
+
+int launch_bigk(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
+                cudaMemPool_t pool, cudaStream_t stream) {
+  const int Kp = (ndir + 7) / 8 * 8;
+  const int64_t n_ct = (ncol + TC_N - 1) / TC_N;
+  // 3 coefficient stages when they fit next to the raw basis tile (Kp <= 104), else 2
+  int nb = BK_MAXB;
+  size_t smem = sizeof(float) * (size_t)(TC_M + 2 * nb * TC_N) * Kp + 256;
+  if (smem > 227 * 1024) {
+    nb = 2;
+    smem = sizeof(float) * (size_t)(TC_M + 2 * nb * TC_N) * Kp + 256;
+  }
+  float *Bs = nullptr;
+  SSF_CUDA(cudaMallocFromPoolAsync(reinterpret_cast<void **>(&Bs), sizeof(float) * (size_t)n_ct * 2 * TC_N * Kp, pool,
+                                   stream));
+  SSF_LAUNCH(split_b_kernel<1>, ssf::div_up(n_ct * TC_N * (Kp >> 2), 256), 256, 0, stream, G, ndir, ldg, ncol, Kp,
+             n_ct, Bs);
+  SSF_LAUNCHED();
+  // items: one per pixel tile, or column chunks of >= 4 tiles when there are few pixel tiles
+  const int64_t pix_tiles = npix / TC_M;
+  int64_t chunks = 1;
+  if (pix_tiles < 4 * 148) {
+    chunks = (4 * 148 + pix_tiles - 1) / pix_tiles;
+    if (chunks > (n_ct + 3) / 4) chunks = (n_ct + 3) / 4;
+    if (chunks < 1) chunks = 1;
+  }
+  const int per = (int)((n_ct + chunks - 1) / chunks);
+  chunks = (n_ct + per - 1) / per;
+  const int64_t n_items = pix_tiles * chunks;
+  // tensor map of the basis: [ndir rows][npix] float32, box = Kp rows x 128 pixels, no swizzle
+  typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                               const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                               CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static EncodeFn encode = nullptr;
+  if (!encode) {
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    SSF_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    SSF_REQUIRE(fn != nullptr && qres == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled is not available");
+    encode = reinterpret_cast<EncodeFn>(fn);
+  }
+  CUtensorMap bt_map;
+  const cuuint64_t gdim[2] = {(cuuint64_t)npix, (cuuint64_t)ndir};
+  const cuuint64_t gstride[1] = {(cuuint64_t)npix * sizeof(float)};
+  const cuuint32_t box[2] = {(cuuint32_t)TC_M, (cuuint32_t)Kp};
+  const cuuint32_t estride[2] = {1, 1};
+  const CUresult cr = encode(&bt_map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(Bt), gdim, gstride, box,
+                             estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  SSF_REQUIRE(cr == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d)", (int)cr);
+  SSF_CUDA(cudaFuncSetAttribute(contract_tc_bigk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int grid = (int)(n_items < 148 ? n_items : 148);
+  SSF_LAUNCH(contract_tc_bigk_kernel, grid, BK_THREADS, smem, stream, bt_map, Bs, ndir, npix, ncol, slab, per,
+             (int)chunks, Kp, nb, n_items);
+  SSF_LAUNCHED();
+  cudaError_t fe = cudaFreeAsync(Bs, stream);
+  SSF_CUDA(fe);
+  return SSF_OK;
 }
 
 // Stream-ordered scratch for the split coefficient tiles, from a library-private memory pool
@@ -531,6 +815,11 @@ int launch_tc(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, 
   SSF_CUDA(cudaGetDevice(&device));
   cudaMemPool_t pool = scratch_pool(device);
   SSF_REQUIRE(pool != nullptr, "tcgen05 contraction: could not create the scratch memory pool");
+  if (MODE == 1 && per_sm == 1) {
+    // more than 56 directions: persistent kernel with basis-tile prefetch (SSF_TC_BIGK=0: experiment hook)
+    const char *e = getenv("SSF_TC_BIGK");
+    if (!(e && e[0] == '0')) return launch_bigk(Bt, G, ndir, ldg, npix, ncol, slab, pool, stream);
+  }
   float *Bs = nullptr;
   const size_t bs_bytes = sizeof(float) * (size_t)n_ct * 2 * TC_N * Kp;
   SSF_CUDA(cudaMallocFromPoolAsync(reinterpret_cast<void **>(&Bs), bs_bytes, pool, stream));

@@ -52,6 +52,11 @@ def test_kl_eval_tcgen05(gpu_engine):
     pc.check_kl_eval(gpu_engine, n=128, n_d=45, ncol=700, seed=15, variant=1, cell=0.03)
     # many column tiles per CTA (both TMEM / shared-memory ring stages reused many times)
     pc.check_kl_eval(gpu_engine, n=128, n_d=45, ncol=3840, seed=16, variant=1, cell=0.03)
+    # more than 56 directions -> persistent kernel: several items per CTA (basis tile prefetch and
+    # re-split, all ring phases wrap), ragged last column tile, column chunks
+    pc.check_kl_eval(gpu_engine, n=160, n_d=100, ncol=77, seed=17, variant=1, cell=0.02)
+    pc.check_kl_eval(gpu_engine, n=256, n_d=60, ncol=300, seed=18, variant=1, cell=0.015)
+    pc.check_kl_eval(gpu_engine, n=64, n_d=112, ncol=1500, seed=19, variant=1, cell=0.05)
 
 
 def test_contraction_tcgen05_error_bound(gpu_engine):
