@@ -61,12 +61,12 @@ def measured_peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def recorded_traffic(kernel):
-    """DRAM bytes per launch of `kernel` from the committed ncu capture, if any."""
+def recorded_traffic(kernel, workload="lofar"):
+    """DRAM bytes per launch of `kernel` on `workload` from the committed ncu capture, if any."""
     path = os.path.join(ROOT, "profiles", "traffic.json")
     try:
         with open(path, encoding="utf8") as fh:
-            return json.load(fh).get(kernel)
+            return json.load(fh).get(f"{workload}:{kernel}")
     except (OSError, ValueError):
         return None
 
@@ -381,7 +381,7 @@ def run_ours(args):
                                              "achieved": voxels_per_step * BYTES_PER_VOXEL / (alone_ms * 1e-3) / 1e9,
                                              "frac": voxels_per_step * BYTES_PER_VOXEL / (alone_ms * 1e-3) / 1e9 / peak},
                                    "achieved": achieved, "peak": peak, "unit": "GB/s",
-                                   "frac": achieved / peak, "traffic": recorded_traffic("kl_eval"),
+                                   "frac": achieved / peak, "traffic": recorded_traffic("kl_eval", args.workload),
                                    "kernel_ms": k_ms, "kernel_launches": n_launch, "peak_source": peak_src,
                                    "kernel_share_of_step": k_ms * n_launch / ms})
     ms_v, launches_v, kern_v, clocks_v = timed(vo_step, ["voronoi_fill", "gauss_smooth", "voronoi_contract"])
@@ -394,7 +394,7 @@ def run_ours(args):
                                                "indicators x cos/sin LUT, tcgen05 split-TF32)"
                                                if vkey == "voronoi_contract" else "fill_kernel (ssf_voronoi_fill)"),
                                     "achieved": achieved_v, "peak": peak, "unit": "GB/s",
-                                    "frac": achieved_v / peak, "traffic": recorded_traffic(vkey),
+                                    "frac": achieved_v / peak, "traffic": recorded_traffic(vkey, args.workload),
                                     "kernel_ms": k_ms, "kernel_launches": n_launch, "peak_source": peak_src,
                                     "kernel_share_of_step": k_ms * n_launch / ms_v})
     if "gauss_smooth" in kern_v:
@@ -423,7 +423,7 @@ def run_ours(args):
                            roofline={"bound": "hbm", "kernel": "contract_tc_kernel<gain> (ssf_kl_eval_gain: phase + "
                                      "log10 Axx + log10 Ayy screens, tcgen05 split-TF32)",
                                      "achieved": achieved_g, "peak": peak, "unit": "GB/s", "frac": achieved_g / peak,
-                                     "traffic": recorded_traffic("kl_eval_gain"), "kernel_ms": k_ms,
+                                     "traffic": recorded_traffic("kl_eval_gain", args.workload), "kernel_ms": k_ms,
                                      "kernel_launches": n_launch, "peak_source": peak_src,
                                      "kernel_share_of_step": k_ms * n_launch / ms_g})
     e2e = None
