@@ -371,7 +371,8 @@ def run_ours(args):
             alone.append(a.elapsed_time(b))
         alone_ms = sorted(alone)[1]
         tc = args.variant != 0 and (n * n) % 128 == 0
-        kname = ("contract_tc_kernel<KL> (ssf_kl_eval, tcgen05 split-TF32)" if tc
+        kname = (("contract_tc_bigk_kernel (ssf_kl_eval, tcgen05 split-TF32, persistent, basis operand in TMEM)"
+                  if n_d > 56 else "contract_tc_kernel<KL> (ssf_kl_eval, tcgen05 split-TF32)") if tc
                  else "contract_tile_kernel<KL> (ssf_kl_eval, FP32 SIMT)")
         out["kl"] = dict(ms=ms, launches=launches, clocks=clocks,
                          fit_host_ms=kl.timings.get("fit_host_s", 0.0) / max(kl.timings.get("fit_slabs", 1), 1) * 1e3,

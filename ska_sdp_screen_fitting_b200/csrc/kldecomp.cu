@@ -13,6 +13,10 @@ namespace {
 // threads per CTA: 256 for up to 64 directions; 512 above, where a pattern's two 100 x 100
 // FP64 matrices leave room for only one CTA per SM and more warps hide the latency
 constexpr int MAX_SWEEPS = 40;
+// off-diagonal / total ENERGY below which one more sweep is the last (see the sweep loop)
+#ifndef SSF_JACOBI_LAST
+#define SSF_JACOBI_LAST 1e-24
+#endif
 #ifndef SSF_DECOMP_BIG
 #define SSF_DECOMP_BIG 512
 #endif
@@ -241,7 +245,7 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
     }
     __syncthreads();
     if (last) converged = true;
-    if (s_off <= 1e-24 * s_tot) last = true;
+    if (s_off <= SSF_JACOBI_LAST * s_tot) last = true;
   }
 
   // order by |lambda| descending (ties: lower index first)
