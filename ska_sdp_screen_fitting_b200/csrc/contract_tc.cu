@@ -503,6 +503,7 @@ __device__ __forceinline__ void tmem_st8(uint32_t taddr, const float *v) {
                : "memory");
 }
 
+template <int MODE>
 __global__ void __launch_bounds__(BK_THREADS, 1)
 contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float *__restrict__ Bs, int ndir,
                         int64_t npix, int64_t ncol, float *__restrict__ slab, int tiles_per_chunk, int chunks,
@@ -519,7 +520,8 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
   const uint32_t raw_full = smem_u32(bars + 2 * BK_MAXB + 2 * T_STAGES), raw_free = raw_full + 8;
   const uint32_t a_ready = raw_full + 16, a_free = raw_full + 24;
   const uint32_t stage_bytes = (uint32_t)(2 * TC_N * Kp * sizeof(float));
-  const int64_t n_ct = (ncol + TC_N - 1) / TC_N;
+  constexpr int CT = tile_columns(MODE);         // slab columns per 64-row coefficient tile
+  const int64_t n_ct = (ncol + CT - 1) / CT;
 
   if (tid == BK_EPI * 32) {
     for (int i = 0; i < BK_MAXB; ++i) {
@@ -658,16 +660,38 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
         const int t = T % T_STAGES;
         mbar_wait(t_full + 8 * t, (T / T_STAGES) & 1);
         tc_fence_after();
+        const int64_t c0 = (ct0 + it) * CT;
+        if (MODE == 2) {
+          // gain: this warp's 32 pixels x slab columns c0 + 8 h .. + 7, three accumulator groups
+          float ph[8], ax[8], ay[8];
+          const uint32_t ta = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TC_N + 8 * h);
+          tmem_ld8(ta, ph);
+          tmem_ld8(ta + 16, ax);
+          tmem_ld8(ta + 32, ay);
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(t_empty + 8 * t);
+          const int64_t left = ncol - (c0 + 8 * h);
+          if (left > 0) store_gain(ph, ax, ay, slab + (c0 + 8 * h) * 4 * npix + pix, npix, left >= 8 ? 8 : (int)left);
+          continue;
+        }
         float v[32];
         tmem_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TC_N + 32 * h), v);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(t_empty + 8 * t);
-        const int64_t c0 = (ct0 + it) * TC_N + 32 * h;
-        float *out = slab + c0 * 4 * npix + pix;
-        const int64_t left = ncol - c0;
-        if (left >= 32) store_kl<false>(v, out, npix, 32);
-        else if (left > 0) store_kl<true>(v, out, npix, (int)left);
+        if (MODE == 1) {
+          float *out = slab + (c0 + 32 * h) * 4 * npix + pix;
+          const int64_t left = ncol - (c0 + 32 * h);
+          if (left >= 32) store_kl<false>(v, out, npix, 32);
+          else if (left > 0) store_kl<true>(v, out, npix, (int)left);
+        } else {
+          // Voronoi: h = 0: Re rows -> planes 0, 2; h = 1: Im rows -> planes 1, 3
+          float *out = slab + c0 * 4 * npix + (int64_t)h * npix + pix;
+          const int64_t left = ncol - c0;
+          if (left >= 32) store_vo<false>(v, out, npix, 32, h);
+          else store_vo<true>(v, out, npix, (int)left, h);
+        }
       }
     }
   }
@@ -681,6 +705,7 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
   }
 }
 
+template <int MODE>
 int launch_bigk(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
                 cudaMemPool_t pool, cudaStream_t stream);
 
@@ -698,10 +723,12 @@ int pick_tiles_per_cta(int ct, int Kp, int64_t n_ct) {
   return (int)(per < 1 ? 1 : per);
 }
 
+template <int MODE>
 int launch_bigk(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
                 cudaMemPool_t pool, cudaStream_t stream) {
+  constexpr int CT = tile_columns(MODE);
   const int Kp = (ndir + 7) / 8 * 8;
-  const int64_t n_ct = (ncol + TC_N - 1) / TC_N;
+  const int64_t n_ct = (ncol + CT - 1) / CT;
   // 3 coefficient stages when they fit next to the raw basis tile (Kp <= 104), else 2
   int nb = BK_MAXB;
   size_t smem = sizeof(float) * (size_t)(TC_M + 2 * nb * TC_N) * Kp + 256;
@@ -712,7 +739,7 @@ int launch_bigk(const float *Bt, const float *G, int ndir, int ldg, int64_t npix
   float *Bs = nullptr;
   SSF_CUDA(cudaMallocFromPoolAsync(reinterpret_cast<void **>(&Bs), sizeof(float) * (size_t)n_ct * 2 * TC_N * Kp, pool,
                                    stream));
-  SSF_LAUNCH(split_b_kernel<1>, ssf::div_up(n_ct * TC_N * (Kp >> 2), 256), 256, 0, stream, G, ndir, ldg, ncol, Kp,
+  SSF_LAUNCH(split_b_kernel<MODE>, ssf::div_up(n_ct * TC_N * (Kp >> 2), 256), 256, 0, stream, G, ndir, ldg, ncol, Kp,
              n_ct, Bs);
   SSF_LAUNCHED();
   // items: one per pixel tile, or column chunks of >= 4 tiles when there are few pixel tiles
@@ -747,9 +774,9 @@ int launch_bigk(const float *Bt, const float *G, int ndir, int ldg, int64_t npix
                              estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   SSF_REQUIRE(cr == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d)", (int)cr);
-  SSF_CUDA(cudaFuncSetAttribute(contract_tc_bigk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  SSF_CUDA(cudaFuncSetAttribute(contract_tc_bigk_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int grid = (int)(n_items < 148 ? n_items : 148);
-  SSF_LAUNCH(contract_tc_bigk_kernel, grid, BK_THREADS, smem, stream, bt_map, Bs, ndir, npix, ncol, slab, per,
+  SSF_LAUNCH(contract_tc_bigk_kernel<MODE>, grid, BK_THREADS, smem, stream, bt_map, Bs, ndir, npix, ncol, slab, per,
              (int)chunks, Kp, nb, n_items);
   SSF_LAUNCHED();
   cudaError_t fe = cudaFreeAsync(Bs, stream);
@@ -815,10 +842,10 @@ int launch_tc(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, 
   SSF_CUDA(cudaGetDevice(&device));
   cudaMemPool_t pool = scratch_pool(device);
   SSF_REQUIRE(pool != nullptr, "tcgen05 contraction: could not create the scratch memory pool");
-  if (MODE == 1 && per_sm == 1) {
+  if (per_sm == 1) {
     // more than 56 directions: persistent kernel with basis-tile prefetch (SSF_TC_BIGK=0: experiment hook)
     const char *e = getenv("SSF_TC_BIGK");
-    if (!(e && e[0] == '0')) return launch_bigk(Bt, G, ndir, ldg, npix, ncol, slab, pool, stream);
+    if (!(e && e[0] == '0')) return launch_bigk<MODE>(Bt, G, ndir, ldg, npix, ncol, slab, pool, stream);
   }
   float *Bs = nullptr;
   const size_t bs_bytes = sizeof(float) * (size_t)n_ct * 2 * TC_N * Kp;

@@ -63,6 +63,8 @@ def test_contraction_tcgen05_error_bound(gpu_engine):
     for n_d, ncol in ((45, 70), (8, 32), (100, 33), (3, 1)):
         pc.check_raw_contraction(gpu_engine, n_d=n_d, ncol=ncol, variant=1)
     pc.check_raw_contraction(gpu_engine, npix=128 * 37, n_d=45, ncol=500, variant=1)
+    # persistent TMEM-operand kernel, Voronoi rows (Re/Im), several items per CTA, ragged tile
+    pc.check_raw_contraction(gpu_engine, npix=128 * 200, n_d=64, ncol=100, seed=12, variant=1)
     pc.check_raw_contraction(gpu_engine, n_d=45, ncol=70, variant=0)
 
 
@@ -88,6 +90,7 @@ def test_kl_gain(gpu_engine, golden_dir, repo_solutions):
     pc.check_kl_gain_eval(gpu_engine, n=128, n_d=45, ncol=33, seed=9, cell=0.02, variant=1)
     pc.check_kl_gain_eval(gpu_engine, n=64, n_d=9, ncol=7, seed=10, cell=0.05, variant=1)
     pc.check_kl_gain_eval(gpu_engine, n=64, n_d=100, ncol=50, seed=11, cell=0.05, variant=1)
+    pc.check_kl_gain_eval(gpu_engine, n=160, n_d=100, ncol=21, seed=12, cell=0.02, variant=1)   # persistent, multi-item
     pc.check_kl_gain_golden(gpu_engine, golden_dir, repo_solutions)
 
 
