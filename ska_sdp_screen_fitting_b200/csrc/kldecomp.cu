@@ -35,8 +35,8 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
                  const int32_t *__restrict__ range, int32_t *__restrict__ status) {
   SSF_DYN_SMEM(double, sm);
   __shared__ int s_idx[SSF_MAX_DIR];
-  __shared__ double s_c[SSF_MAX_DIR / 2 + 1], s_s[SSF_MAX_DIR / 2 + 1];
-  __shared__ int s_p[SSF_MAX_DIR / 2 + 1], s_q[SSF_MAX_DIR / 2 + 1];
+  __shared__ double s_c[2][SSF_MAX_DIR / 2 + 1], s_s[2][SSF_MAX_DIR / 2 + 1];   // double-buffered rotations
+  __shared__ int s_p[2][SSF_MAX_DIR / 2 + 1], s_q[2][SSF_MAX_DIR / 2 + 1];
   __shared__ int s_rank[SSF_MAX_DIR];
   __shared__ int s_n;
   __shared__ double s_red[THREADS / 32], s_red2[THREADS / 32];
@@ -61,8 +61,11 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
   const int m = (n + 1) & ~1;   // padded to an even size: the extra row / column is zero, so every
                                 // rotation that touches it is the identity (apq == 0)
   const int npairs = m / 2;
-  double *A = sm;               // [m][m]
-  double *V = sm + m * m;       // [m][m]
+  const int ld = m + 1;         // odd leading dimension: column walks (the mirror stores of the
+                                // A update) hit every bank instead of 4 of them
+  double *A = sm;               // [m][ld]
+  double *V = sm + m * ld;      // [m][ld]
+  const int warp = tid >> 5, lane = tid & 31;
   double *C = Cout + (size_t)pat * ndir * ndir;
   double *P = Pout + (size_t)pat * ndir * ndir;
   double *U = Uout + (size_t)pat * ndir * ndir;
@@ -96,123 +99,115 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
       v = q > 0.0 ? -0.5 * pow(q, half_beta) : 0.0;
       C[i * ndir + j] = v;
     }
-    A[e] = v;
-    V[e] = (i == j) ? 1.0 : 0.0;
+    A[i * ld + j] = v;
+    V[i * ld + j] = (i == j) ? 1.0 : 0.0;
   }
   __syncthreads();
+
+  // Rotation of pair k of round-robin step r (m / 2 disjoint pairs), published in buffer `buf`.
+  auto publish = [&](int r, int buf) {
+    const int k = lane + 32 * warp;       // called by warps 0 and 1
+    if (k >= npairs) return;
+    int p, q;
+    if (k == 0) {
+      p = m - 1;
+      q = r;
+    } else {
+      p = r + k;
+      if (p >= m - 1) p -= m - 1;
+      q = r - k;
+      if (q < 0) q += m - 1;
+    }
+    if (p > q) {
+      int t = p;
+      p = q;
+      q = t;
+    }
+    double c = 1.0, sn = 0.0;
+    const double apq = A[p * ld + q];
+    if (apq != 0.0) {
+      // t = sgn(tau) / (|tau| + sqrt(1 + tau^2)), tau = (aqq - app) / (2 apq), written
+      // without the slow FP64 divide / sqrt: t = apq / (d + sgn(d) hypot(d, apq))
+      const double d = 0.5 * (A[q * ld + q] - A[p * ld + p]);
+      const double r2 = fma(d, d, apq * apq);
+      if (r2 > 0.0) {
+        const double den = d + copysign(r2 * rsqrt(r2), d);
+        const double t = apq * __drcp_rn(den);
+        c = rsqrt(fma(t, t, 1.0));
+        sn = t * c;
+      }
+    }
+    s_p[buf][k] = p;
+    s_q[buf][k] = q;
+    s_c[buf][k] = c;
+    s_s[buf][k] = sn;
+  };
 
   // Quadratic convergence: once the off-diagonal energy is below 1e-24 of the total, one
   // more sweep takes it to rounding level.
   bool converged = (n == 1);
   bool last = false;
-  const int warp = tid >> 5, lane = tid & 31;
+  if (!converged && warp < 2) publish(0, 0);
+  __syncthreads();
+  int buf = 0;
   for (int sweep = 0; sweep < MAX_SWEEPS && !converged; ++sweep) {
-    for (int r = 0; r < m - 1; ++r) {
-      // round-robin pairing: m / 2 disjoint rotations.  Every warp computes the rotation of
-      // pair k = lane (+ 32) for itself, so its V rows can be updated from registers without
-      // waiting for anybody; warp 0 also publishes the rotations for the A block update.
-      int pk[2], qk[2];
-      double ck[2], sk[2];
+    for (int r = 0; r < m - 1; ++r, buf ^= 1) {
+      // A <- J^T A J by 2 x 2 pair blocks: the thread of block (k1, k2), k1 <= k2, reads its 4
+      // elements, applies the column rotation of pair k2 and the row rotation of pair k1,
+      // and writes them and their mirror images.  No element is touched by two threads.
+      for (int e = tid; e < nblocks; e += THREADS) {
+        const uchar2 kk = s_blk[e];
+        const int p1 = s_p[buf][kk.x], q1 = s_q[buf][kk.x], p2 = s_p[buf][kk.y], q2 = s_q[buf][kk.y];
+        const double c1 = s_c[buf][kk.x], s1 = s_s[buf][kk.x], c2 = s_c[buf][kk.y], s2 = s_s[buf][kk.y];
+        const double a00 = A[p1 * ld + p2], a01 = A[p1 * ld + q2], a10 = A[q1 * ld + p2], a11 = A[q1 * ld + q2];
+        const double b00 = c2 * a00 - s2 * a01, b01 = s2 * a00 + c2 * a01;
+        const double b10 = c2 * a10 - s2 * a11, b11 = s2 * a10 + c2 * a11;
+        const double r00 = c1 * b00 - s1 * b10, r10 = s1 * b00 + c1 * b10;
+        const double r01 = c1 * b01 - s1 * b11, r11 = s1 * b01 + c1 * b11;
+        A[p1 * ld + p2] = r00;
+        A[q1 * ld + q2] = r11;
+        if (kk.x == kk.y) {
+          A[p1 * ld + q1] = r01;                     // the annihilated element (rounding level)
+          A[q1 * ld + p1] = r01;
+        } else {
+          A[p1 * ld + q2] = r01;
+          A[q1 * ld + p2] = r10;
+          A[p2 * ld + p1] = r00;
+          A[q2 * ld + p1] = r01;
+          A[p2 * ld + q1] = r10;
+          A[q2 * ld + q1] = r11;
+        }
+      }
+      __syncthreads();
+      // A is final for this step: warps 0 and 1 work out the NEXT step's rotations (a long
+      // dependent FP64 chain) while the others apply this step's to V.
+      if (warp < 2) publish(r + 1 < m - 1 ? r + 1 : 0, buf ^ 1);
+      // V <- V J (columns).  Rows are owned by warps (row = warp, warp + THREADS / 32, ..): no
+      // other warp ever touches them.  Lane = pair, 4 rows in flight per lane.
 #pragma unroll
       for (int g = 0; g < 2; ++g) {
         const int k = lane + 32 * g;
-        pk[g] = qk[g] = 0;
-        ck[g] = 1.0;
-        sk[g] = 0.0;
-        if (k < npairs) {
-          int p, q;
-          if (k == 0) {
-            p = m - 1;
-            q = r;
-          } else {
-            p = r + k;
-            if (p >= m - 1) p -= m - 1;
-            q = r - k;
-            if (q < 0) q += m - 1;
-          }
-          if (p > q) {
-            int t = p;
-            p = q;
-            q = t;
-          }
-          double c = 1.0, sn = 0.0;
-          const double apq = A[p * m + q];
-          if (apq != 0.0) {
-            // t = sgn(tau) / (|tau| + sqrt(1 + tau^2)), tau = (aqq - app) / (2 apq), written
-            // without the slow FP64 divide / sqrt: t = apq / (d + sgn(d) hypot(d, apq))
-            const double d = 0.5 * (A[q * m + q] - A[p * m + p]);
-            const double r2 = fma(d, d, apq * apq);
-            if (r2 > 0.0) {
-              const double den = d + copysign(r2 * rsqrt(r2), d);
-              const double t = apq * __drcp_rn(den);
-              c = rsqrt(fma(t, t, 1.0));
-              sn = t * c;
-            }
-          }
-          pk[g] = p;
-          qk[g] = q;
-          ck[g] = c;
-          sk[g] = sn;
-          if (warp == 0) {
-            s_p[k] = p;
-            s_q[k] = q;
-            s_c[k] = c;
-            s_s[k] = sn;
-          }
-        }
-      }
-      // V <- V J (columns).  Rows are owned by warps (row = warp, warp + 8, ..): no other warp
-      // ever touches them, so this needs no barrier.  4 rows in flight per lane.
-#pragma unroll
-      for (int g = 0; g < 2; ++g) {
-        if (lane + 32 * g >= npairs) break;
-        double *vp = V + pk[g], *vq = V + qk[g];
-        const double c = ck[g], sn = sk[g];
+        if (k >= npairs) break;
+        double *vp = V + s_p[buf][k], *vq = V + s_q[buf][k];
+        const double c = s_c[buf][k], sn = s_s[buf][k];
         for (int i0 = warp; i0 < m; i0 += 4 * (THREADS / 32)) {
           double x[4], y[4];
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             const int i = i0 + u * (THREADS / 32);
             if (i < m) {
-              x[u] = vp[i * m];
-              y[u] = vq[i * m];
+              x[u] = vp[i * ld];
+              y[u] = vq[i * ld];
             }
           }
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             const int i = i0 + u * (THREADS / 32);
             if (i < m) {
-              vp[i * m] = c * x[u] - sn * y[u];
-              vq[i * m] = sn * x[u] + c * y[u];
+              vp[i * ld] = c * x[u] - sn * y[u];
+              vq[i * ld] = sn * x[u] + c * y[u];
             }
           }
-        }
-      }
-      __syncthreads();   // every warp has read A for its rotations; s_p.. are published
-      // A <- J^T A J by 2 x 2 pair blocks: the thread of block (k1, k2), k1 <= k2, reads its 4
-      // elements, applies the column rotation of pair k2 and the row rotation of pair k1,
-      // and writes them and their mirror images.  No element is touched by two threads.
-      for (int e = tid; e < nblocks; e += THREADS) {
-        const uchar2 kk = s_blk[e];
-        const int p1 = s_p[kk.x], q1 = s_q[kk.x], p2 = s_p[kk.y], q2 = s_q[kk.y];
-        const double c1 = s_c[kk.x], s1 = s_s[kk.x], c2 = s_c[kk.y], s2 = s_s[kk.y];
-        const double a00 = A[p1 * m + p2], a01 = A[p1 * m + q2], a10 = A[q1 * m + p2], a11 = A[q1 * m + q2];
-        const double b00 = c2 * a00 - s2 * a01, b01 = s2 * a00 + c2 * a01;
-        const double b10 = c2 * a10 - s2 * a11, b11 = s2 * a10 + c2 * a11;
-        const double r00 = c1 * b00 - s1 * b10, r10 = s1 * b00 + c1 * b10;
-        const double r01 = c1 * b01 - s1 * b11, r11 = s1 * b01 + c1 * b11;
-        A[p1 * m + p2] = r00;
-        A[q1 * m + q2] = r11;
-        if (kk.x == kk.y) {
-          A[p1 * m + q1] = r01;                     // the annihilated element (rounding level)
-          A[q1 * m + p1] = r01;
-        } else {
-          A[p1 * m + q2] = r01;
-          A[q1 * m + p2] = r10;
-          A[p2 * m + p1] = r00;
-          A[q2 * m + p1] = r01;
-          A[p2 * m + q1] = r10;
-          A[q2 * m + q1] = r11;
         }
       }
       __syncthreads();
@@ -221,7 +216,7 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
     double off = 0.0, tot = 0.0;
     for (int e = tid; e < m * m; e += THREADS) {
       int i = e / m, j = e - i * m;
-      double v = A[e] * A[e];
+      double v = A[i * ld + j] * A[i * ld + j];
       tot += v;
       if (i != j) off += v;
     }
@@ -250,28 +245,28 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
 
   // order by |lambda| descending (ties: lower index first)
   for (int i = tid; i < n; i += THREADS) {
-    double li = fabs(A[i * m + i]);
+    double li = fabs(A[i * ld + i]);
     int rank = 0;
     for (int j = 0; j < n; ++j) {
-      double lj = fabs(A[j * m + j]);
+      double lj = fabs(A[j * ld + j]);
       rank += (lj > li) || (lj == li && j < i);
     }
     s_rank[i] = rank;
     sv[rank] = converged ? li : nan("");
     if (!converged && status) *status = 1;
-    s_inv[i] = li > cut ? 1.0 / A[i * m + i] : 0.0;
+    s_inv[i] = li > cut ? 1.0 / A[i * ld + i] : 0.0;
   }
   __syncthreads();
   for (int e = tid; e < n * n; e += THREADS) {
     int a = e / n, i = e - a * n;
-    U[a * ndir + s_rank[i]] = V[a * m + i];
+    U[a * ndir + s_rank[i]] = V[a * ld + i];
   }
   // pinv(C_S) = sum_{|lambda_i| > cut} v_i v_i^T / lambda_i
   for (int e = tid; e < n * n; e += THREADS) {
     int a = e / n, b = e - a * n;
     if (b < a) continue;
     double acc = 0.0;
-    for (int i = 0; i < n; ++i) acc = fma(V[a * m + i] * V[b * m + i], s_inv[i], acc);
+    for (int i = 0; i < n; ++i) acc = fma(V[a * ld + i] * V[b * ld + i], s_inv[i], acc);
     P[a * ndir + b] = acc;
     P[b * ndir + a] = acc;
   }
@@ -384,7 +379,7 @@ extern "C" int ssf_kl_decompose(const double *pp, int ndir, const uint64_t *mask
   SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR, "ssf_kl_decompose: ndir=%d out of range [1,%d]", ndir, SSF_MAX_DIR);
   if (npat <= 0) return SSF_OK;
   const int mmax = (ndir + 1) & ~1;
-  size_t smem = sizeof(double) * 2 * (size_t)mmax * mmax;
+  size_t smem = sizeof(double) * 2 * (size_t)mmax * (mmax + 1);
   SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
   SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
   if (ndir > 64) {
@@ -425,7 +420,7 @@ extern "C" int ssf_kl_patterns_update(const uint64_t *masks, int64_t nsys, int n
   // decompose the slots handed out by this pass: the grid is an upper bound, CTAs beyond
   // counters[0] return at once
   const int mmax = (ndir + 1) & ~1;
-  size_t smem = sizeof(double) * 2 * (size_t)mmax * mmax;
+  size_t smem = sizeof(double) * 2 * (size_t)mmax * (mmax + 1);
   const int64_t bound = nsys < max_slots ? nsys : max_slots;
   if (ndir > 64) {
     SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
