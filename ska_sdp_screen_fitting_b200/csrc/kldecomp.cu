@@ -13,6 +13,7 @@ namespace {
 // threads per CTA: 256 for up to 64 directions; 512 above, where a pattern's two 100 x 100
 // FP64 matrices leave room for only one CTA per SM and more warps hide the latency
 constexpr int MAX_SWEEPS = 40;
+static_assert(SSF_MAX_DIR <= 128, "warm start: 4 columns per lane of one warp");
 // off-diagonal / total ENERGY below which one more sweep is the last (see the sweep loop)
 #ifndef SSF_JACOBI_LAST
 #define SSF_JACOBI_LAST 1e-24
@@ -32,7 +33,8 @@ __global__ void __launch_bounds__(THREADS)
 decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__restrict__ masks,
                  double r0sq, double half_beta, double cut, double *__restrict__ Cout,
                  double *__restrict__ Pout, double *__restrict__ Uout, double *__restrict__ svout,
-                 const int32_t *__restrict__ range, int32_t *__restrict__ status) {
+                 const int32_t *__restrict__ range, int32_t *__restrict__ status,
+                 const double *U0) {
   SSF_DYN_SMEM(double, sm);
   __shared__ int s_idx[SSF_MAX_DIR];
   __shared__ double s_c[2][SSF_MAX_DIR / 2 + 1], s_s[2][SSF_MAX_DIR / 2 + 1];   // double-buffered rotations
@@ -42,7 +44,7 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
   __shared__ double s_red[THREADS / 32], s_red2[THREADS / 32];
   __shared__ uchar2 s_blk[(SSF_MAX_DIR / 2) * (SSF_MAX_DIR / 2 + 1) / 2];
   __shared__ double s_off, s_tot;
-  __shared__ double s_inv[SSF_MAX_DIR];
+  __shared__ double s_inv[SSF_MAX_DIR + 16], s_gsu[SSF_MAX_DIR + 16], s_gsa[SSF_MAX_DIR + 16];
 
   // range != null: device-resident pattern cache -- this launch covers the slots
   // [range[1], range[0]) that ssf_kl_patterns_update has just handed out (grid = upper bound)
@@ -103,6 +105,201 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
     V[i * ld + j] = (i == j) ? 1.0 : 0.0;
   }
   __syncthreads();
+
+  // ---- warm start (device pattern cache only) -------------------------------------------------
+  // Every flag pattern is a principal submatrix of the SAME full matrix, whose eigenvectors U0
+  // (columns by |lambda| descending) are in slot 0.  Deleting row j from an orthogonal Q and one
+  // column leaves columns w_c with Gram matrix I - u u^T (u = row j); Gram-Schmidt over them IN
+  // |lambda| ORDER has the closed form (s_c = 1 - sum_{c' < c} u_c'^2)
+  //     q_c = (w_c + (u_c / s_c) sum_{c' < c} u_c' w_c') sqrt(s_c / s_{c+1}),
+  // a prefix sum along each row.  The leading eigenvectors stay almost untouched and the
+  // error lands on the small eigenvalues, so C_S is already nearly diagonal in this basis
+  // (off-diagonal energy ~1e-4 of the total) and Jacobi needs half the sweeps of a cold start.
+  if (U0 != nullptr && n < ndir && n > 1) {
+    const int mfull = (ndir + 1) & ~1;
+    const int ldf = mfull + 1;
+    double *F = sm + (size_t)mfull * ldf;         // second half of the allocation: [ndir][ldf]
+    int *s_col = s_rank;                          // reused before the ranking needs it
+    for (int e = tid; e < ndir * ndir; e += THREADS) {
+      const int i = e / ndir, c = e - i * ndir;
+      F[i * ldf + c] = U0[e];
+    }
+    for (int c = tid; c < ndir; c += THREADS) s_col[c] = 1;   // column still active
+    __syncthreads();
+    for (int j = 0; j < ndir; ++j) {
+      if (((j < 64 ? m0 >> j : m1 >> (j - 64)) & 1ull) != 0) continue;   // uniform: kept direction
+      if (warp == 0) {
+        // the dropped column: largest |Q[j][c]| (keeps s_end = u_c^2 >= 1 / n: well conditioned)
+        double best = -1.0;
+        int bc = 0;
+        for (int c = lane; c < ndir; c += 32) {
+          const double v = s_col[c] ? fabs(F[j * ldf + c]) : -1.0;
+          if (v > best) {
+            best = v;
+            bc = c;
+          }
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+          const double ov = __shfl_xor_sync(0xffffffffu, best, o);
+          const int oc = __shfl_xor_sync(0xffffffffu, bc, o);
+          if (ov > best || (ov == best && oc < bc)) {
+            best = ov;
+            bc = oc;
+          }
+        }
+        if (lane == 0) s_col[bc] = 0;
+        __syncwarp();
+        // s_c = 1 - sum_{c' < c} u_c'^2 over the surviving columns: 4 columns per lane + warp scan
+        double x[4], loc = 0.0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int c = 4 * lane + q;
+          const double uc = (c < ndir && s_col[c]) ? F[j * ldf + c] : 0.0;
+          x[q] = uc;
+          loc = fma(uc, uc, loc);
+        }
+        double incl = loc;
+        for (int o = 1; o < 32; o <<= 1) {
+          const double t = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += t;
+        }
+        double sc = 1.0 - (incl - loc);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int c = 4 * lane + q;
+          if (c < ndir) {
+            const double sn = sc - x[q] * x[q];
+            s_gsu[c] = x[q];
+            s_gsa[c] = x[q] / sc;
+            s_inv[c] = s_col[c] ? sqrt(sc / sn) : 0.0;     // 0 marks a dead column
+            sc = sn;
+          }
+        }
+      }
+      __syncthreads();
+      // Gram-Schmidt in closed form, one row per thread, columns in |lambda| order
+      for (int i = tid; i < ndir; i += THREADS) {
+        if (i == j) continue;
+        double *fr = F + i * ldf;
+        double P = 0.0;
+        for (int c = 0; c < ndir; ++c) {
+          const double g = s_inv[c];
+          if (g == 0.0) continue;
+          const double wc = fr[c];
+          fr[c] = fma(s_gsa[c], P, wc) * g;
+          P = fma(s_gsu[c], wc, P);
+        }
+      }
+      __syncthreads();
+    }
+    if (tid == 0) {                               // compact list of the surviving columns
+      int k = 0;
+      for (int c = 0; c < ndir; ++c)
+        if (s_col[c]) s_col[k++] = c;
+      s_n = n;
+    }
+    __syncthreads();
+    // 4 x 4 register tiles with strided rows / columns (element (a, b) of tile (ti, tj) is
+    // (ti + a nt, tj + b nt)): lanes walk consecutive columns, no bank conflicts
+    constexpr int MAXM = THREADS >= 512 ? ((SSF_MAX_DIR + 1) & ~1) : 64;   // the 256-thread variant serves <= 64
+    constexpr int NT = ((MAXM + 3) / 4 * ((MAXM + 3) / 4) + THREADS - 1) / THREADS;
+    const int nt = (m + 3) / 4;
+    double acc[NT][16];
+    // T = C_S Q
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+      const int e = tid + t * THREADS;
+      const int ti = e / nt, tj = e - ti * nt;
+#pragma unroll
+      for (int x = 0; x < 16; ++x) acc[t][x] = 0.0;
+      if (ti >= nt) continue;
+      int fc[4];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) fc[b] = (tj + b * nt < n) ? s_col[tj + b * nt] : -1;
+      for (int l = 0; l < n; ++l) {
+        const double *fr = F + s_idx[l] * ldf;
+        double av[4], fv[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) av[a] = (ti + a * nt < n) ? A[(ti + a * nt) * ld + l] : 0.0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) fv[b] = fc[b] >= 0 ? fr[fc[b]] : 0.0;
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) acc[t][a * 4 + b] = fma(av[a], fv[b], acc[t][a * 4 + b]);
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+      const int e = tid + t * THREADS;
+      const int ti = e / nt, tj = e - ti * nt;
+      if (ti >= nt) continue;
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+          if (ti + a * nt < m && tj + b * nt < m) A[(ti + a * nt) * ld + tj + b * nt] = acc[t][a * 4 + b];
+    }
+    __syncthreads();
+    // A0 = Q^T T
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+      const int e = tid + t * THREADS;
+      const int ti = e / nt, tj = e - ti * nt;
+#pragma unroll
+      for (int x = 0; x < 16; ++x) acc[t][x] = 0.0;
+      if (ti >= nt) continue;
+      int fc[4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a) fc[a] = (ti + a * nt < n) ? s_col[ti + a * nt] : -1;
+      for (int l = 0; l < n; ++l) {
+        const double *fr = F + s_idx[l] * ldf;
+        double qv[4], tv[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) qv[a] = fc[a] >= 0 ? fr[fc[a]] : 0.0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) tv[b] = (tj + b * nt < n) ? A[l * ld + tj + b * nt] : 0.0;
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) acc[t][a * 4 + b] = fma(qv[a], tv[b], acc[t][a * 4 + b]);
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+      const int e = tid + t * THREADS;
+      const int ti = e / nt, tj = e - ti * nt;
+      if (ti >= nt) continue;
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const int i = ti + a * nt, c = tj + b * nt;
+          if (i < m && c < m) {
+            A[i * ld + c] = acc[t][a * 4 + b];
+            // gather the compact Q (V overlaps F: through registers, stored after the barrier)
+            acc[t][a * 4 + b] = (i < n && c < n) ? F[s_idx[i] * ldf + s_col[c]] : (i == c ? 1.0 : 0.0);
+          }
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+      const int e = tid + t * THREADS;
+      const int ti = e / nt, tj = e - ti * nt;
+      if (ti >= nt) continue;
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const int i = ti + a * nt, c = tj + b * nt;
+          if (i < m && c < m) V[i * ld + c] = acc[t][a * 4 + b];
+        }
+    }
+    __syncthreads();
+  }
 
   // Rotation of pair k of round-robin step r (m / 2 disjoint pairs), published in buffer `buf`.
   auto publish = [&](int r, int buf) {
@@ -239,7 +436,7 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
       s_tot = b;
     }
     __syncthreads();
-    if (last) converged = true;
+    if (last || s_off <= 1e-30 * s_tot) converged = true;   // 1e-30: what the extra sweep reaches
     if (s_off <= SSF_JACOBI_LAST * s_tot) last = true;
   }
 
@@ -384,10 +581,10 @@ extern "C" int ssf_kl_decompose(const double *pp, int ndir, const uint64_t *mask
   SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
   if (ndir > 64) {
     SSF_LAUNCH(decompose_kernel<BIG>, npat, BIG, smem, (cudaStream_t)stream, pp, ndir, masks, r0 * r0,
-               beta / 2.0, pinv_cut, C, pinvC, U, sv, (const int32_t *)nullptr, (int32_t *)nullptr);
+               beta / 2.0, pinv_cut, C, pinvC, U, sv, (const int32_t *)nullptr, (int32_t *)nullptr, (const double *)nullptr);
   } else {
     SSF_LAUNCH(decompose_kernel<256>, npat, 256, smem, (cudaStream_t)stream, pp, ndir, masks, r0 * r0,
-               beta / 2.0, pinv_cut, C, pinvC, U, sv, (const int32_t *)nullptr, (int32_t *)nullptr);
+               beta / 2.0, pinv_cut, C, pinvC, U, sv, (const int32_t *)nullptr, (int32_t *)nullptr, (const double *)nullptr);
   }
   SSF_LAUNCHED();
   return SSF_OK;
@@ -421,15 +618,19 @@ extern "C" int ssf_kl_patterns_update(const uint64_t *masks, int64_t nsys, int n
   // counters[0] return at once
   const int mmax = (ndir + 1) & ~1;
   size_t smem = sizeof(double) * 2 * (size_t)mmax * (mmax + 1);
+  static const bool warm = [] {                  // SSF_DECOMP_WARM=0: cold Jacobi start (experiments)
+    const char *e = getenv("SSF_DECOMP_WARM");
+    return !(e && e[0] == '0');
+  }();
   const int64_t bound = nsys < max_slots ? nsys : max_slots;
   if (ndir > 64) {
     SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
     SSF_LAUNCH(decompose_kernel<BIG>, (int)bound, BIG, smem, st, pp, ndir, slot_masks, r0 * r0, beta / 2.0, pinv_cut,
-               C, pinvC, U, sv, (const int32_t *)counters, status);
+               C, pinvC, U, sv, (const int32_t *)counters, status, warm ? (const double *)U : (const double *)nullptr);
   } else {
     SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
     SSF_LAUNCH(decompose_kernel<256>, (int)bound, 256, smem, st, pp, ndir, slot_masks, r0 * r0, beta / 2.0, pinv_cut,
-               C, pinvC, U, sv, (const int32_t *)counters, status);
+               C, pinvC, U, sv, (const int32_t *)counters, status, warm ? (const double *)U : (const double *)nullptr);
   }
   SSF_LAUNCHED();
   SSF_LAUNCH(pc_commit_kernel, 1, 1, 0, st, counters);

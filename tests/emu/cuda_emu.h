@@ -83,6 +83,12 @@ static inline T __shfl_xor_sync(unsigned m, T v, int lanemask) {
   return __shfl_sync(m, v, lane ^ lanemask);
 }
 
+template <typename T>
+static inline T __shfl_up_sync(unsigned m, T v, int delta) {
+  int lane = (threadIdx.x + threadIdx.y * blockDim.x + threadIdx.z * blockDim.x * blockDim.y) & 31;
+  return __shfl_sync(m, v, lane >= delta ? lane - delta : lane);
+}
+
 template <typename T> static inline T __ldg(const T *p) { return *p; }
 template <typename T> static inline void __stcs(T *p, T v) { *p = v; }
 static inline double __dadd_rn(double a, double b) { volatile double r = a + b; return r; }

@@ -50,6 +50,36 @@ def check_decompose(eng, n_d=9, seed=5):
         assert np.all(c[k, n:, :].cpu().numpy() == 0) and np.all(p[k, :, n:].cpu().numpy() == 0)
 
 
+def check_pattern_cache_decompose(eng, n_d=11, seed=6, max_flagged=3, n_sys=6):
+    """Decompositions handed out by the device pattern cache (warm-started from slot 0's
+    eigenvectors) against the reference's SVD / pinv of the same subsets."""
+    from ska_sdp_screen_fitting_b200.engine import PatternCache
+    rng = np.random.default_rng(seed)
+    pp, _, _ = klfit.piercepoints(make_directions(rng, n_d))
+    cache = PatternCache(eng, eng.tensor(pp[:, :2], torch.float64), max_bytes=64 << 20)
+    subsets = [list(range(n_d))]
+    for s in range(n_sys - 1):
+        drop = rng.choice(n_d, size=1 + s % max_flagged, replace=False)
+        subsets.append([i for i in range(n_d) if i not in drop])
+    subsets.append([0, n_d // 2, n_d - 1])                      # heavily flagged
+    masks = torch.tensor([mask_of(s) for s in subsets], dtype=torch.int64, device=eng.device)
+    pat = cache.lookup(masks).cpu().numpy()
+    eng.check_fit_status()
+    assert pat[0] == 0 and len(set(pat.tolist())) == len({tuple(s) for s in subsets})
+    for k, sub in enumerate(subsets):
+        n = len(sub)
+        c_o, p_o, u_o = klfit.calculate_svd(pp[sub])
+        slot = int(pat[k])
+        assert np.allclose(cache.c[slot, :n, :n].cpu().numpy(), c_o, rtol=1e-13, atol=0)
+        sv_o = np.linalg.svd(c_o, compute_uv=False)
+        assert np.allclose(cache.sv[slot, :n].cpu().numpy(), sv_o, rtol=1e-12, atol=1e-10)
+        scale = np.abs(p_o).max()
+        assert np.abs(cache.p[slot, :n, :n].cpu().numpy() - p_o).max() < 1e-10 * max(scale, 1.0)
+        u_k = cache.u[slot, :n, :n].cpu().numpy()
+        signs = np.sign(np.sum(u_k * u_o, axis=0))
+        assert np.abs(u_k * signs - u_o).max() < 1e-9
+
+
 def synthetic_fit_case(seed, n_t, n_f, n_a, n_d, flag_fraction=0.03):
     rng = np.random.default_rng(seed)
     dirs = make_directions(rng, n_d)

@@ -10,6 +10,11 @@ def test_decompose(emu_engine):
     pc.check_decompose(emu_engine)
 
 
+def test_pattern_cache_warm_started_decompositions(emu_engine):
+    pc.check_pattern_cache_decompose(emu_engine)
+    pc.check_pattern_cache_decompose(emu_engine, n_d=14, seed=8, max_flagged=5)
+
+
 def test_fit_with_flags_and_outliers(emu_engine):
     pc.check_fit(emu_engine)
 
