@@ -97,7 +97,9 @@ int ssf_kl_patterns_update(const uint64_t *masks, int64_t nsys, int ndir, const 
  *   mode 1: iteration > 0     -> order-adjust state machine, first order iteration skips
  *                                the fit (reference quirk, :694-705), <= 3 refits (:692-779)
  *   mode + 2: amplitude type  -> `phase` holds amplitudes; log10 fit (:535-548), residual
- *                                amp - 10^fit (:576-590), log-residual chi^2 (:732-744)
+ *                                amp - 10^fit (:576-590), log-residual chi^2 (:732-741)
+ *   mode + 4: tec type        -> `phase` holds dTEC values, fitted as they are (:549-562),
+ *                                residual val - fit, chi^2 = sum w resid^2 (:742-746)
  *   white, resid [nsys, ndir] f64 in/out (mode 1 reads the residual of the previous pass)
  * Systems with no unflagged direction are left untouched (:683-684).
  *   status  [1] i32 in/out     set to 1 if any system had a weight in (0, pinv_cut] (the
@@ -122,7 +124,8 @@ int ssf_kl_flag_outliers(const double *resid, float *weights, int ndir, int64_t 
  * systems are time-major with `ngroups` = freq*station*pol systems per time slot
  * (sys = t*ngroups + g); one weighted rms per group over all directions and times
  * (group_std [ngroups] scratch), weights of |log resid| > nsigma*rms set to 0 in place.
- * nsigma = inf flags nothing and only emits the masks. */
+ * nsigma = inf flags nothing and only emits the masks.
+ * val == NULL: tec type, the residual itself is clipped (:338-346 with :661-663). */
 int ssf_kl_flag_outliers_amp(const double *val, const double *resid, float *weights, int ndir,
                              int64_t nsys, int64_t ngroups, double nsigma, double *group_std,
                              uint64_t *masks_out, void *stream);

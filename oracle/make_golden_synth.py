@@ -94,4 +94,42 @@ def golden_gain(mods):
         fake_h5parm.reset()
 
 
-JOBS = {"gain": golden_gain}
+def tec_case(seed=29, n_d=12, n_t=8, n_st=3):
+    """Seeded dTEC-like values [station, dir, time]: a gradient over the pierce points per
+    station plus noise, a few flagged solutions and gross outliers."""
+    rng = np.random.default_rng(seed)
+    dirs = np.column_stack([np.deg2rad(126.23 + rng.uniform(-2, 2, n_d)),
+                            np.deg2rad(64.5 + rng.uniform(-1.5, 1.5, n_d))]).astype(np.float32)
+    grad = rng.normal(0, 0.04, (n_st, 2))
+    xy = np.rad2deg(dirs.astype(np.float64)) - [126.23, 64.5]
+    val = (grad[:, None, None, 0] * xy[None, :, None, 0] + grad[:, None, None, 1] * xy[None, :, None, 1]
+           + 0.01 * np.sin(np.arange(n_t))[None, None, :])
+    sigma = np.array([0.004, 1.0, 1.6])[:n_st, None, None]     # reduced chi2 << 1, ~1, > 1: orders move
+    val = val + sigma * rng.normal(0, 1.0, (n_st, n_d, n_t))
+    weights = np.ones(val.shape, np.float32)
+    weights[rng.random(val.shape) < 0.05] = 0.0
+    out = rng.random(val.shape) < 0.02
+    val[out] += 12.0 * np.broadcast_to(sigma, val.shape)[out]
+    return dirs, val, weights
+
+
+def golden_tec(mods):
+    """_process_station(screen_type="tec") of the reference (stationscreen.py:549-562, 338-346,
+    742-746) on the seeded case: the tec type is in the fit operator but no API path reaches it,
+    so the operator itself is the pin."""
+    ss = mods["stationscreen"]
+    dirs, val, weights = tec_case()
+    n_st, n_d, n_t = val.shape
+    pp, _, _ = ss._calculate_piercepoints(np.zeros((1, 3)), dirs)
+    full = ss._calculate_svd(pp, 100, 5.0 / 3.0, n_d)
+    ss.FULL_MATRICES = full
+    names = np.array([f"d{i}" for i in range(n_d)])
+    out = dict(dirs=dirs, val=val, weights=weights, station_order=np.array([5.0, 6.0, 8.0]))
+    res = [ss._process_station(val[a].copy(), pp, np.full(n_t, out["station_order"][a]), weights[a].copy(),
+                               "tec", 2, 5.0, True, names, full, 5.0 / 3.0, 100) for a in range(n_st)]
+    out.update(screen=np.stack([r[0] for r in res]), weights_out=np.stack([r[1] for r in res]),
+               resid=np.stack([r[2] for r in res]), order=np.stack([r[3] for r in res]))
+    np.savez_compressed(os.path.join(GOLDEN, "tec_station.npz"), **out)
+
+
+JOBS = {"gain": golden_gain, "tec": golden_tec}

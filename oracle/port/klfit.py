@@ -47,7 +47,7 @@ def piercepoints(source_dirs_rad):
 
 
 def fit_screen(full, pp, phase, weights, order, r_0=R_0, beta=BETA, screen_type="phase"):
-    """stationscreen.py:433-594 (_fit_screen, screen_type "phase" or "amplitude")."""
+    """stationscreen.py:433-594 (_fit_screen, screen_type "phase", "amplitude" or "tec")."""
     n_all = len(phase)
     unfl = np.where(weights > 0.0)[0]
     n = len(unfl)
@@ -63,6 +63,9 @@ def fit_screen(full, pp, phase, weights, order, r_0=R_0, beta=BETA, screen_type=
             rr1 = uk.T @ (w @ np.log10(phase[unfl]))
         amp_fit_log = pinv_c @ (uk @ (inv_u @ rr1))
         screen_fit = c @ amp_fit_log
+    elif screen_type == "tec":                                   # :549-562: linear, one right-hand side
+        rr1 = uk.T @ (w @ phase[unfl])
+        screen_fit = c @ (pinv_c @ (uk @ (inv_u @ rr1)))
     else:
         fits = []
         for r in (np.cos(phase[unfl]), np.sin(phase[unfl])):     # :509-528
@@ -100,11 +103,11 @@ def normalize_phase(phase):
 
 def flag_outliers(weights, residual, nsigma, screen_type="phase"):
     """stationscreen.py:303-350: 5-sigma clip -- phase: circular std over directions per time;
-    amplitude: ONE weighted rms over all directions and times of the station (:341-346).
+    amplitude / tec: ONE weighted rms over all directions and times of the station (:338-346).
     Mutates and returns ``weights`` ([ndir, nt]), as the reference does."""
     if not (weights > 0.0).any():
         return weights
-    if screen_type == "amplitude":
+    if screen_type in ("amplitude", "tec"):
         nonfl = weights > 0.0
         with np.errstate(all="ignore"):
             std = np.sqrt(np.average(residual[nonfl] ** 2, weights=weights[nonfl], axis=0))
@@ -151,7 +154,8 @@ def process_station(phase, pp, screen_order, station_weights, full, niter=2, nsi
     init_w = station_weights.copy()
     for it in range(niter):
         if it > 0:
-            diff = residual.copy() if screen_type == "phase" else log_residual(phase, residual)
+            # :661-668: phase and tec flag on the residual itself, amplitude on the log residual
+            diff = log_residual(phase, residual) if screen_type == "amplitude" else residual.copy()
             station_weights = flag_outliers(init_w, diff, nsigma, screen_type)
         prev_w = init_w
         prev_redchi2 = 0
@@ -182,9 +186,12 @@ def process_station(phase, pp, screen_order, station_weights, full, niter=2, nsi
                     if screen_type == "phase":
                         redchi2 = circ_chi2(residual[:, t], station_weights[:, t]) / (
                             n_unfl - screen_order[t])
-                    else:                                                        # :732-744
+                    elif screen_type == "amplitude":                             # :732-741
                         diff = log_residual(phase[:, t], residual[:, t])
                         redchi2 = np.sum(np.square(diff) * station_weights[:, t]) / (
+                            n_unfl - screen_order[t])
+                    else:                                                        # tec, :742-746
+                        redchi2 = np.sum(np.square(residual[:, t]) * station_weights[:, t]) / (
                             n_unfl - screen_order[t])
                     if oi > 0:
                         if redchi2 > 1.0 and prev_redchi2 < redchi2:

@@ -61,7 +61,8 @@ __host__ __device__ inline size_t smem_doubles(int nall) {
 // (0, cut]) -- not supported by the Cholesky path.
 __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restrict__ pp, int nall,
                          int n, int k, double r0sq, double half_beta, double cut,
-                         double *__restrict__ white_out, double *__restrict__ resid_out, bool amp) {
+                         double *__restrict__ white_out, double *__restrict__ resid_out, int kind) {
+  const bool amp = kind == 1;           // kind: 0 phase, 1 amplitude (log10), 2 tec (linear, :549-562)
   __shared__ int sh_uniform, sh_ok;
   const int tid = threadIdx.x;
   const int ld = pt.ld;
@@ -69,6 +70,7 @@ __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restr
     double phi = s.ph[s.idx[tid]];
     double sn = 0.0, cs;
     if (amp) cs = log10(phi);          // amplitude type fits log10(amp) (:535-541); one right-hand side
+    else if (kind == 2) cs = phi;      // tec type fits the values themselves (:549-556)
     else sincos(phi, &sn, &cs);
     s.rc[tid] = cs;
     s.rs[tid] = sn;
@@ -177,7 +179,7 @@ __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restr
       ac = fma(c, s.gc[e], ac);
       as = fma(c, s.gs_[e], as);
     }
-    s.fit[tid] = amp ? ac : atan2(as, ac);        // amplitude: screen_fit = C amp_fit_log (:547)
+    s.fit[tid] = kind != 0 ? ac : atan2(as, ac);  // amplitude / tec: screen_fit = C fit (:547, :561)
   }
   __syncthreads();
   // white = pinvC fit   (:534)
@@ -268,9 +270,10 @@ fit_pass_kernel(const double *__restrict__ phase, const float *__restrict__ weig
     if (ord > (double)(n - 1)) ord = (double)(n - 1);  // :685-686
     const double st_order = station_order[sys];
 
-    const bool amp = (mode & 2) != 0;
+    const int kind = (mode & 2) ? 1 : ((mode & 4) ? 2 : 0);
+    const bool amp = kind == 1;
     if ((mode & 1) == 0) {
-      bool ok = fit_once(s, pt, pp, nall, n, (int)ord, r0sq, half_beta, cut, w_out, r_out, amp);
+      bool ok = fit_once(s, pt, pp, nall, n, (int)ord, r0sq, half_beta, cut, w_out, r_out, kind);
       if (!ok && tid == 0) atomicExch(status, 1);
       if (tid == 0) order[sys] = ord;
       continue;
@@ -282,7 +285,7 @@ fit_pass_kernel(const double *__restrict__ phase, const float *__restrict__ weig
     double sign = 1.0, prev_redchi2 = 0.0;
     for (int oi = 0; oi < 4; ++oi) {
       if (oi > 0) {
-        bool ok = fit_once(s, pt, pp, nall, n, (int)ord, r0sq, half_beta, cut, w_out, r_out, amp);
+        bool ok = fit_once(s, pt, pp, nall, n, (int)ord, r0sq, half_beta, cut, w_out, r_out, kind);
         if (!ok && tid == 0) atomicExch(status, 1);
       }
       if (hit_lower2 || hit_upper2) break;
@@ -295,6 +298,8 @@ fit_pass_kernel(const double *__restrict__ phase, const float *__restrict__ weig
           const double v = s.ph[tid];
           const double diff = log10(v) - log10(fabs(v - r));
           sh_t1[tid] = diff * diff * s.w[tid];
+        } else if (kind == 2) {
+          sh_t1[tid] = r * r * s.w[tid];                          // tec: plain chi2 (:742-746)
         } else {
           double sn, cs;
           sincos(r, &sn, &cs);
@@ -305,7 +310,7 @@ fit_pass_kernel(const double *__restrict__ phase, const float *__restrict__ weig
       __syncthreads();
       if (tid == 0) {
         double chi2;
-        if (amp) {
+        if (kind != 0) {
           chi2 = 0.0;
           for (int d = 0; d < nall; ++d) chi2 += sh_t1[d];
         } else {
@@ -436,7 +441,12 @@ flag_kernel(const double *__restrict__ resid, float *__restrict__ weights, int n
 // Amplitude type (_flag_outliers, stationscreen.py:341-348, with the log residual of :664-668):
 // ONE weighted rms per (freq, station, pol) group over all directions and times.  Systems are
 // time-major: sys = t * ngroups + g.  One warp per group, fixed summation order.
-__device__ __forceinline__ double amp_log_resid(double v, double r) { return log10(v) - log10(fabs(v - r)); }
+// val == nullptr: tec type, the residual itself is clipped (:661-663).
+__device__ __forceinline__ double amp_log_resid(const double *val, int64_t i, double r) {
+  if (val == nullptr) return r;
+  const double v = val[i];
+  return log10(v) - log10(fabs(v - r));
+}
 
 __global__ void __launch_bounds__(128)
 amp_std_kernel(const double *__restrict__ val, const double *__restrict__ resid,
@@ -453,7 +463,7 @@ amp_std_kernel(const double *__restrict__ val, const double *__restrict__ resid,
     for (int d = lane; d < nall; d += 32) {
       const double w = (double)weights[base + d];
       if (w > 0.0) {
-        const double diff = amp_log_resid(val[base + d], resid[base + d]);
+        const double diff = amp_log_resid(val, base + d, resid[base + d]);
         acc = fma(diff * diff, w, acc);
         sw += w;
         ++cnt;
@@ -483,7 +493,7 @@ amp_flag_kernel(const double *__restrict__ val, const double *__restrict__ resid
     for (int d = lane; d < nall; d += 32) {
       float wd = w[d];
       if (group_std) {
-        const double diff = amp_log_resid(val[sys * nall + d], resid[sys * nall + d]);
+        const double diff = amp_log_resid(val, sys * nall + d, resid[sys * nall + d]);
         if (fabs(diff) > lim) {
           wd = 0.0f;
           w[d] = 0.0f;
@@ -516,7 +526,7 @@ extern "C" int ssf_kl_fit_pass(const double *phase, const float *weights, const 
                   resid && status,
               "ssf_kl_fit_pass: null pointer");
   SSF_REQUIRE(ndir >= 2 && ndir <= SSF_MAX_DIR, "ssf_kl_fit_pass: ndir=%d out of range [2,%d]", ndir, SSF_MAX_DIR);
-  SSF_REQUIRE(mode >= 0 && mode <= 3, "ssf_kl_fit_pass: mode must be in 0..3");
+  SSF_REQUIRE(mode >= 0 && mode <= 5, "ssf_kl_fit_pass: mode must be in 0..5 (bit 1 amplitude and bit 2 tec exclude each other)");
   if (nsys <= 0) return SSF_OK;
   size_t smem = sizeof(double) * smem_doubles(ndir);
   if (smem > 48 * 1024)
@@ -546,7 +556,7 @@ extern "C" int ssf_kl_flag_outliers(const double *resid, float *weights, int ndi
 extern "C" int ssf_kl_flag_outliers_amp(const double *val, const double *resid, float *weights, int ndir,
                                         int64_t nsys, int64_t ngroups, double nsigma, double *group_std,
                                         uint64_t *masks_out, void *stream) {
-  SSF_REQUIRE(val && resid && weights && masks_out, "ssf_kl_flag_outliers_amp: null pointer");
+  SSF_REQUIRE(resid && weights && masks_out, "ssf_kl_flag_outliers_amp: null pointer");   // val may be null (tec)
   SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR, "ssf_kl_flag_outliers_amp: ndir out of range");
   if (nsys <= 0) return SSF_OK;
   SSF_REQUIRE(ngroups >= 1 && nsys % ngroups == 0, "ssf_kl_flag_outliers_amp: nsys must be a multiple of ngroups");

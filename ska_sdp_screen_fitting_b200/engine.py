@@ -149,9 +149,11 @@ class Engine:
 
     def kl_flag_outliers_amp(self, val, resid, weights, ngroups, nsigma):
         """ssf_kl_flag_outliers_amp in place on ``weights`` (amplitude type: one rms per
-        (freq, station, pol) group over all directions and times); returns the masks."""
+        (freq, station, pol) group over all directions and times); returns the masks.
+        ``val=None``: tec type, the residual itself is clipped instead of the log residual."""
         nsys, ndir = resid.shape
-        self._check(val, torch.float64, "val")
+        if val is not None:
+            self._check(val, torch.float64, "val")
         self._check(resid, torch.float64, "resid")
         self._check(weights, torch.float32, "weights")
         masks = self.empty((nsys, 2), torch.int64)
@@ -189,13 +191,16 @@ class Engine:
         ``check_fit_status()`` later.
         ``screen_type="amplitude"``: ``phase`` holds amplitudes, rows are time-major with
         ``ngroups`` = freq * station * pol systems per time slot (the outlier rms is taken per
-        group over all times, stationscreen.py:341-346); ``white`` are log10 screens."""
+        group over all times, stationscreen.py:341-346); ``white`` are log10 screens.
+        ``screen_type="tec"``: the values themselves are fitted (:549-562), clipped like the
+        amplitude type but on the plain residual (:338-346, :661-663), plain chi2 (:742-746)."""
         nsys, ndir = phase.shape
         amp = screen_type == "amplitude"
-        if screen_type not in ("phase", "amplitude"):
-            raise ValueError("screen_type must be 'phase' or 'amplitude'")
-        if amp and (not ngroups or nsys % ngroups):
-            raise ValueError("amplitude fits need ngroups (systems per time slot) dividing nsys")
+        tec = screen_type == "tec"
+        if screen_type not in ("phase", "amplitude", "tec"):
+            raise ValueError("screen_type must be 'phase', 'amplitude' or 'tec'")
+        if (amp or tec) and (not ngroups or nsys % ngroups):
+            raise ValueError("amplitude / tec fits need ngroups (systems per time slot) dividing nsys")
         t0 = time.perf_counter()
         white = self.zeros((nsys, ndir), torch.float64)
         resid = self.zeros((nsys, ndir), torch.float64)
@@ -208,8 +213,9 @@ class Engine:
             self._fit_status = self.zeros((2,), torch.int32)     # [weights out of range, no convergence]
         for it in range(niter):
             t0 = time.perf_counter()
-            if amp:
-                masks = self.kl_flag_outliers_amp(phase, resid, weights, ngroups, nsigma if it > 0 else math.inf)
+            if amp or tec:
+                masks = self.kl_flag_outliers_amp(phase if amp else None, resid, weights, ngroups,
+                                                  nsigma if it > 0 else math.inf)
             else:
                 masks = self.kl_flag_outliers(resid, weights, nsigma if it > 0 else math.inf)
             t0 = self.host_tick("flag_launch", t0)
@@ -219,7 +225,7 @@ class Engine:
                 continue
             pat = cache.lookup(masks)
             t0 = self.host_tick("pattern_lookup", t0)
-            mode = (1 if (it > 0 and adjust_order) else 0) | (2 if amp else 0)
+            mode = (1 if (it > 0 and adjust_order) else 0) | (2 if amp else 0) | (4 if tec else 0)
             self.kl_fit_pass(phase, weights, pat, pp, cache.mats, mode, order, station_order, white,
                              resid, r0, beta, cut, status=self._fit_status[0:1])
             self.host_tick("fit_pass_launch", t0)

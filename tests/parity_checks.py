@@ -8,6 +8,8 @@ Tolerances (stated once, used everywhere):
   * KL screens: 1e-5 absolute on the phase-derived planes cos/sin (north_star: 1e-5 on phase)
   * Gaussian smoothing: 1e-6 absolute (float32 accumulation vs scipy's float64 line buffer)
 """
+import os
+
 import numpy as np
 import torch
 
@@ -164,6 +166,27 @@ def check_fit_amplitude(eng, seed=23, n_t=6, n_f=2, n_a=4, n_d=24):
     # the residuals are amplitudes (not logs) and scale with them: relative above 1
     assert (np.abs(resid.cpu().numpy() - want["resid"]) <= TOL_FIT * np.maximum(1.0, np.abs(want["resid"]))).all()
     return want
+
+
+def check_fit_tec_golden(eng, golden_dir):
+    """tec-type fit (values fitted as they are, rms clip on the plain residual, plain chi2)
+    against the outputs of the reference's own _process_station(screen_type="tec")
+    (tests/golden/tec_station.npz, oracle/make_golden_synth.py::golden_tec)."""
+    g = np.load(os.path.join(golden_dir, "tec_station.npz"))
+    n_st, n_d, n_t = g["val"].shape
+    pp, _, _ = klfit.piercepoints(g["dirs"])
+    val = eng.tensor(np.ascontiguousarray(g["val"].transpose(2, 0, 1)).reshape(n_t * n_st, n_d), torch.float64)
+    wts = eng.tensor(np.ascontiguousarray(g["weights"].transpose(2, 0, 1)).reshape(n_t * n_st, n_d), torch.float32)
+    st_order = eng.tensor(np.tile(g["station_order"], n_t), torch.float64)
+    white, resid, order = eng.kl_fit(val, wts, st_order, eng.tensor(pp[:, :2], torch.float64), niter=2,
+                                     screen_type="tec", ngroups=n_st)
+    back = lambda t, shape: t.cpu().numpy().reshape(shape)
+    assert np.array_equal(back(wts, (n_t, n_st, n_d)).transpose(1, 2, 0), g["weights_out"])
+    assert (g["weights_out"] != g["weights"]).any(), "the case must exercise outlier flagging"
+    assert np.array_equal(back(order, (n_t, n_st)).T, g["order"])
+    assert (g["order"] != g["station_order"][:, None]).any(), "the case must exercise the order state machine"
+    assert np.abs(back(white, (n_t, n_st, n_d)).transpose(1, 2, 0) - g["screen"]).max() < TOL_FIT
+    assert np.abs(back(resid, (n_t, n_st, n_d)).transpose(1, 2, 0) - g["resid"]).max() < TOL_FIT * 20
 
 
 def check_kl_gain_eval(eng, n=24, n_d=9, ncol=7, seed=31, cell=0.1, variant=0):

@@ -43,6 +43,10 @@ def test_fit_amplitude_type(emu_engine):
     pc.check_fit_amplitude(emu_engine)
 
 
+def test_fit_tec_type_against_reference_operator_golden(emu_engine, golden_dir):
+    pc.check_fit_tec_golden(emu_engine, golden_dir)
+
+
 def test_kl_gain_fit_against_reference_golden(emu_engine, golden_dir, repo_solutions):
     pc.check_kl_gain_golden(emu_engine, golden_dir, repo_solutions, full=False)
 

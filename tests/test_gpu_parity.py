@@ -24,6 +24,10 @@ def test_pattern_cache_warm_started_decompositions(gpu_engine):
     pc.check_pattern_cache_decompose(gpu_engine, n_d=99, seed=10, max_flagged=3, n_sys=8)
 
 
+def test_fit_tec_type_against_reference_operator_golden(gpu_engine, golden_dir):
+    pc.check_fit_tec_golden(gpu_engine, golden_dir)
+
+
 def test_fit_with_flags_and_outliers(gpu_engine):
     pc.check_fit(gpu_engine)
     pc.check_fit(gpu_engine, seed=17, n_t=6, n_f=3, n_a=8, n_d=45)

@@ -143,6 +143,19 @@ def test_port_against_the_reference_modules_directly(repo_solutions):
     assert np.array_equal(w_r, w_p) and np.array_equal(ord_r, ord_p)
 
 
+def test_port_tec_type_matches_reference_operator_golden():
+    """_process_station(screen_type="tec") of the reference (golden_tec) against the port."""
+    g = np.load(os.path.join(GOLDEN, "tec_station.npz"))
+    pp, _, _ = klfit.piercepoints(g["dirs"])
+    full = klfit.calculate_svd(pp)
+    n_t = g["val"].shape[2]
+    for a in range(g["val"].shape[0]):
+        scr, w, res, so = klfit.process_station(g["val"][a].copy(), pp, np.full(n_t, g["station_order"][a]),
+                                                g["weights"][a].copy(), full, 2, 5.0, True, screen_type="tec")
+        assert np.abs(scr - g["screen"][a]).max() < 1e-12 and np.abs(res - g["resid"][a]).max() < 1e-11
+        assert np.array_equal(w, g["weights_out"][a]) and np.array_equal(so, g["order"][a])
+
+
 # ------------------------------------------------------------------------------ gain fixture
 @pytest.fixture(scope="module")
 def gain_golden():
