@@ -58,15 +58,22 @@ def header_bytes(cards):
     return (text + " " * pad).encode("ascii")
 
 
-def aterm_cards(shape, rad, dec, cellsize_deg, freqs, times):
-    """Header of a "gain" a-term cube (processing_utils.py:202-289).  ``shape`` is the numpy
-    shape [nt, nf, na, 4, ny, nx]."""
-    nt, nf, _, _, ny, nx = shape
+def aterm_cards(shape, rad, dec, cellsize_deg, freqs, times, aterm_type="gain"):
+    """Header of an a-term cube (processing_utils.py:202-289).  ``shape`` is the numpy shape
+    [nt, nf, na, 4, ny, nx] for ``aterm_type="gain"`` (what Screen.write produces,
+    screen.py:182-190) or [nt, nf, na, ny, nx] for ``"tec"`` (no MATRIX axis, :187-190,
+    :230-238)."""
+    if aterm_type not in ("gain", "tec"):
+        raise ValueError("aterm_type must be 'gain' or 'tec'")
+    if len(shape) != (6 if aterm_type == "gain" else 5):
+        raise ValueError(f"a {aterm_type} cube has {6 if aterm_type == 'gain' else 5} axes, got shape {tuple(shape)}")
+    nt, nf = shape[0], shape[1]
+    ny, nx = shape[-2], shape[-1]
     freqs = np.asarray(freqs, np.float64)
     times = np.asarray(times, np.float64)
     cards = [("SIMPLE", True, "conforms to FITS standard"),
              ("BITPIX", -32, "array data type"),
-             ("NAXIS", 6, "number of array dimensions")]
+             ("NAXIS", len(shape), "number of array dimensions")]
     cards += [(f"NAXIS{i + 1}", int(n)) for i, n in enumerate(reversed(shape))]
     cards.append(("EXTEND", True))
 
@@ -76,17 +83,20 @@ def aterm_cards(shape, rad, dec, cellsize_deg, freqs, times):
 
     cards += axis(1, float(rad), -float(cellsize_deg), nx / 2.0, "deg", "RA---SIN")
     cards += axis(2, float(dec), float(cellsize_deg), ny / 2.0, "deg", "DEC--SIN")
-    cards += axis(3, 0.0, 1.0, 1.0, "", "MATRIX")
-    cards += axis(4, 0.0, 1.0, 1.0, "", "ANTENNA")
+    i = 3
+    if aterm_type == "gain":
+        cards += axis(i, 0.0, 1.0, 1.0, "", "MATRIX")
+        i += 1
+    cards += axis(i, 0.0, 1.0, 1.0, "", "ANTENNA")
     del_freq = float(np.min(freqs[1:] - freqs[:-1])) if nf > 1 else 1e8       # :249-253
     cards.append(("RESTFRQ", float(freqs[0])))
-    cards += axis(5, float(freqs[0]), del_freq, 1.0, "Hz", "FREQ")
+    cards += axis(i + 1, float(freqs[0]), del_freq, 1.0, "Hz", "FREQ")
     if nt > 1:                                                                 # :263-276
         deltas = times[1:] - times[:-1]
         del_time = float(np.min(deltas[:-1])) if nt > 2 else float(deltas[0])
     else:
         del_time = 1.0
-    cards += axis(6, float(times[0]), del_time, 1.0, "s", "TIME")
+    cards += axis(i + 2, float(times[0]), del_time, 1.0, "s", "TIME")
     cards += [("EQUINOX", 2000.0), ("TELESCOP", "LOFAR")]
     return cards
 

@@ -143,6 +143,51 @@ def test_port_against_the_reference_modules_directly(repo_solutions):
     assert np.array_equal(w_r, w_p) and np.array_equal(ord_r, ord_p)
 
 
+def test_fits_header_matches_the_reference_header(repo_solutions, tmp_path):
+    """W1: the product's header cards, key by key and in order, against the header the
+    reference wrote for the same cube (make_template_image, processing_utils.py:202-289;
+    stored in voronoi_c1.npz by oracle/make_golden.py), and read back from a written file."""
+    from ska_sdp_screen_fitting_b200 import fits
+
+    g = np.load(os.path.join(GOLDEN, "voronoi_c1.npz"))
+    sol = repo_solutions
+    shape = (len(sol.time), len(sol.freq), len(sol.ant), 4, 17, 17)
+    cards = fits.aterm_cards(shape, 126.23, 64.50, 0.2, sol.freq, sol.time)
+    assert [c[0] for c in cards] == list(g["header_keys"])
+    for (key, val, *_), want in zip(cards, g["header_vals"]):
+        if isinstance(val, bool) or isinstance(val, str):
+            assert str(val) == str(want), key
+        else:
+            assert float(val) == float(want), key
+    writer = fits.CubeWriter(str(tmp_path / "h.fits"), (2, 1, 1, 4, 3, 3),
+                             fits.aterm_cards((2, 1, 1, 4, 3, 3), 1.0, 2.0, 0.1, [1e8], [0.0, 8.0]))
+    writer.write_times(0, np.arange(72, dtype=np.float32).reshape(2, 1, 1, 4, 3, 3))
+    writer.close()
+    header, data = fits.read(str(tmp_path / "h.fits"))
+    assert header["NAXIS"] == 6 and header["CTYPE3"] == "MATRIX" and header["CDELT6"] == 8.0
+    assert np.array_equal(np.asarray(data).ravel(), np.arange(72, dtype=np.float32))
+    # the dTEC layout of make_template_image (:187-190, :230-238): no MATRIX axis
+    tec = dict((c[0], c[1]) for c in fits.aterm_cards((2, 3, 5, 7, 9), 1.0, 2.0, 0.1, [1e8, 1.1e8, 1.3e8],
+                                                     [0.0, 8.0], aterm_type="tec"))
+    assert tec["NAXIS"] == 5 and [tec[f"NAXIS{i}"] for i in range(1, 6)] == [9, 7, 5, 3, 2]
+    assert [tec[f"CTYPE{i}"] for i in range(1, 6)] == ["RA---SIN", "DEC--SIN", "ANTENNA", "FREQ", "TIME"]
+    assert tec["CRPIX1"] == 4.5 and tec["CRPIX2"] == 3.5 and tec["CDELT4"] == 1e7
+
+
+def test_time_chunks_follow_the_reference_gap_rule():
+    """W1 chunking (screen.py:283-294): a new file wherever dt > 1.2 x the smallest dt; two or
+    fewer time slots are never split."""
+    from ska_sdp_screen_fitting_b200.screen import time_chunks
+
+    t = 8.0 * np.arange(10)
+    assert time_chunks(t) == [10]
+    gapped = np.concatenate([t[:4], t[4:7] + 100.0, t[7:] + 300.0])
+    assert time_chunks(gapped) == [4, 7, 10]
+    assert time_chunks(np.array([0.0, 8.0, 17.5])) == [3]            # 9.5 < 1.2 * 8
+    assert time_chunks(np.array([0.0, 8.0, 17.7])) == [2, 3]         # 9.7 > 9.6
+    assert time_chunks(np.array([0.0, 50.0])) == [2] and time_chunks(np.array([3.0])) == [1]
+
+
 def test_port_tec_type_matches_reference_operator_golden():
     """_process_station(screen_type="tec") of the reference (golden_tec) against the port."""
     g = np.load(os.path.join(GOLDEN, "tec_station.npz"))
