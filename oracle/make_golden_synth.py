@@ -132,4 +132,53 @@ def golden_tec(mods):
     np.savez_compressed(os.path.join(GOLDEN, "tec_station.npz"), **out)
 
 
-JOBS = {"gain": golden_gain, "tec": golden_tec}
+GAP_AFTER = ((8, 200.0), (15, 500.0))       # (first slot after the gap, extra seconds)
+
+
+def gapped_times(times):
+    out = np.array(times, np.float64)
+    for start, extra in GAP_AFTER:
+        out[start:] += extra
+    return out
+
+
+def golden_gaps(mods):
+    """Time gaps -> one FITS file per gap-free chunk (screen.py:283-294, 328-394): the repo's
+    phase000 values on a time axis with two gaps (overlaid as phase001), tessellated screens,
+    unsmoothed.  Stores per file the time-axis header cards and a sub-sampled cube, plus the
+    file list."""
+    from oracle.refshim import fake_astropy, fake_h5parm
+
+    tmp = tempfile.mkdtemp(prefix="ssf_golden_")
+    for f in ("solutions.h5", "skymodel.txt"):
+        shutil.copy(os.path.join(GOLDEN, f), tmp)
+    cwd = os.getcwd()
+    os.chdir(tmp)
+    try:
+        fake_h5parm.reset()
+        h5 = fake_h5parm.H5parm("solutions.h5")
+        ph = h5.get_solset("sol000").get_soltab("phase000")
+        times = gapped_times(ph.time)
+        fake_h5parm.add_soltab("solutions.h5", "sol000", "phase001", "phase", ["time", "freq", "ant", "dir"],
+                               [times, ph.freq, ph.ant, ph.dir], np.array(ph.val), np.array(ph.weight))
+        args = dict(TEST_ARGS, bounds_deg=list(TEST_ARGS["bounds_deg"]))
+        mods["make_aterm_images"].make_aterm_image(
+            "solutions.h5", soltabname="phase001", screen_type="tessellated", outroot="gap", smooth_deg=0.0, **args)
+        with open("gap.txt", encoding="utf8") as fh:
+            names = [os.path.basename(ln.strip()) for ln in fh if ln.strip()]
+        out = dict(times=times, files=np.array(names), sub_f=SUB_F, sub_a=SUB_A)
+        for k, name in enumerate(names):
+            hdu = fake_astropy.open(name)
+            hdr = hdu[0].header
+            out[f"naxis6_{k}"] = hdr["NAXIS6"]
+            out[f"crval6_{k}"] = hdr["CRVAL6"]
+            out[f"cdelt6_{k}"] = hdr["CDELT6"]
+            out[f"cube_{k}"] = hdu[0].data[:, SUB_F][:, :, SUB_A].copy()
+        np.savez_compressed(os.path.join(GOLDEN, "gaps_c1.npz"), **out)
+    finally:
+        os.chdir(cwd)
+        shutil.rmtree(tmp)
+        fake_h5parm.reset()
+
+
+JOBS = {"gain": golden_gain, "tec": golden_tec, "gaps": golden_gaps}

@@ -321,6 +321,37 @@ def check_voronoi_gain_golden(eng, golden_dir, repo_solutions, tmp_path, full=Tr
             assert np.array_equal(one.astype(np.float32), gold[key][:, 1, 2])
 
 
+def check_time_gaps_golden(eng, golden_dir, repo_solutions, tmp_path):
+    """Screen.write on a time axis with two gaps: one FITS file per gap-free chunk, file list,
+    per-file time cards and cube contents against what the reference wrote
+    (tests/golden/gaps_c1.npz, oracle/make_golden_synth.py::golden_gaps)."""
+    import os
+
+    from ska_sdp_screen_fitting_b200 import fits
+    from ska_sdp_screen_fitting_b200.h5parm_io import Solutions
+    from ska_sdp_screen_fitting_b200.voronoi_screen import VoronoiScreen
+
+    gold = np.load(os.path.join(golden_dir, "gaps_c1.npz"))
+    ph = repo_solutions
+    gapped = Solutions("phase", ph.val, ph.weight, gold["times"], ph.freq, list(ph.ant), list(ph.dir), [],
+                       dict(ph.source_dict), dict(ph.station_dict))
+    scr = VoronoiScreen("gap", None, os.path.join(golden_dir, "skymodel.txt"), 126.23, 64.50, 3.33, 3.33,
+                        phase_soltab_name="phase001")
+    scr._engine = eng
+    scr.solutions = {"phase001": gapped}
+    scr.process()
+    outfiles = scr.write(str(tmp_path), 0.2, smooth_pix=0.0)
+    assert [os.path.basename(f) for f in outfiles] == list(gold["files"])
+    with open(os.path.join(str(tmp_path), "gap.txt"), encoding="utf8") as fh:
+        assert [os.path.basename(ln.strip()) for ln in fh if ln.strip()] == list(gold["files"])
+    for k, name in enumerate(outfiles):
+        header, data = fits.read(name)
+        assert header["NAXIS6"] == int(gold[f"naxis6_{k}"])
+        assert header["CRVAL6"] == float(gold[f"crval6_{k}"]) and header["CDELT6"] == float(gold[f"cdelt6_{k}"])
+        sub = np.asarray(data)[:, list(gold["sub_f"])][:, :, list(gold["sub_a"])]
+        assert np.array_equal(sub, gold[f"cube_{k}"]), name
+
+
 def check_kl_gain_golden(eng, golden_dir, repo_solutions, full=True):
     """KLScreen on gain solutions against what the reference's own code produced: the
     amplitude screen soltab (values, residuals, orders, weights) and the a-term cube."""

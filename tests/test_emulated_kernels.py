@@ -82,6 +82,10 @@ def test_voronoi_gain_against_reference_golden(emu_engine, golden_dir, repo_solu
     pc.check_voronoi_gain_golden(emu_engine, golden_dir, repo_solutions, tmp_path, full=False)
 
 
+def test_time_gaps_give_one_file_per_chunk_like_the_reference(emu_engine, golden_dir, repo_solutions, tmp_path):
+    pc.check_time_gaps_golden(emu_engine, golden_dir, repo_solutions, tmp_path)
+
+
 def test_smoothing(emu_engine):
     pc.check_smooth(emu_engine, shape=(3, 13, 21), sigmas=(0.5, 2.0, 3.0))
 

@@ -28,6 +28,10 @@ def test_fit_tec_type_against_reference_operator_golden(gpu_engine, golden_dir):
     pc.check_fit_tec_golden(gpu_engine, golden_dir)
 
 
+def test_time_gaps_give_one_file_per_chunk_like_the_reference(gpu_engine, golden_dir, repo_solutions, tmp_path):
+    pc.check_time_gaps_golden(gpu_engine, golden_dir, repo_solutions, tmp_path)
+
+
 def test_fit_with_flags_and_outliers(gpu_engine):
     pc.check_fit(gpu_engine)
     pc.check_fit(gpu_engine, seed=17, n_t=6, n_f=3, n_a=8, n_d=45)
