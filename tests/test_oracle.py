@@ -259,3 +259,34 @@ def test_product_interpolation_matches_scipy(gain_golden, repo_solutions):
     got = 10 ** _interp_axis(g["amp_freq"], _interp_axis(g["amp_time"], np.log10(g["amp_val"]), 0, sol.time, "nearest"),
                              1, sol.freq, "nearest")
     assert np.array_equal(got, want)
+
+
+def test_cli_with_string_bounds_writes_the_reference_cube(emu_library, vor_golden, tmp_path):
+    """The console entry point (main.py:13-78 of the reference: same flags, defaults, and the
+    "[a;b;c;d]" string form of the bounds, make_aterm_images.py:80-87) run as a subprocess on the
+    repo data; kernels from the CPU emulator build.  Unsmoothed tessellated cube: bit-exact
+    against the reference's, plus the file list and the template file."""
+    import subprocess
+    import sys
+
+    from ska_sdp_screen_fitting_b200 import fits
+
+    root = os.path.dirname(os.path.dirname(GOLDEN))
+    env = dict(os.environ, SSF_B200_LIBRARY=emu_library,
+               PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    cmd = [sys.executable, "-m", "ska_sdp_screen_fitting_b200.main", os.path.join(GOLDEN, "solutions.h5"),
+           "--screen_type", "tessellated", "--outroot", str(tmp_path / "cli"),
+           "--bounds_deg", "[124.565; 66.165; 127.895; 62.835]", "--bounds_mid_deg", "[126.23;64.50]",
+           "--skymodel", os.path.join(GOLDEN, "skymodel.txt"), "--padding_fraction", "0",
+           "--cellsize_deg", "0.2", "--ncpu", "3"]
+    done = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert done.returncode == 0, done.stderr[-2000:]
+    assert sorted(os.listdir(tmp_path)) == ["cli.txt", "cli_0.fits", "cli_template.fits"]
+    with open(tmp_path / "cli.txt", encoding="utf8") as fh:
+        assert [ln.strip() for ln in fh] == [str(tmp_path / "cli_0.fits")]
+    _, data = fits.read(str(tmp_path / "cli_0.fits"))
+    sub = np.asarray(data)[:, list(vor_golden["sub_f"])][:, :, list(vor_golden["sub_a"])]
+    assert np.array_equal(sub, vor_golden["cube_nosmooth"])
+    # unknown flags / a missing positional are argparse errors (exit status 2), like the reference
+    bad = subprocess.run(cmd[:3] + ["--no_such_flag", "1"], env=env, capture_output=True, text=True, timeout=120)
+    assert bad.returncode == 2
