@@ -842,10 +842,12 @@ int launch_tc(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, 
   SSF_CUDA(cudaGetDevice(&device));
   cudaMemPool_t pool = scratch_pool(device);
   SSF_REQUIRE(pool != nullptr, "tcgen05 contraction: could not create the scratch memory pool");
-  if (per_sm == 1) {
-    // more than 56 directions: persistent kernel with basis-tile prefetch (SSF_TC_BIGK=0: experiment hook)
+  {
+    // more than 56 directions: persistent kernel with basis-tile prefetch
+    // (experiment hooks: SSF_TC_BIGK=0 never, SSF_TC_BIGK=2 always)
     const char *e = getenv("SSF_TC_BIGK");
-    if (!(e && e[0] == '0')) return launch_bigk<MODE>(Bt, G, ndir, ldg, npix, ncol, slab, pool, stream);
+    const bool never = e && e[0] == '0', always = e && e[0] == '2';
+    if ((per_sm == 1 && !never) || always) return launch_bigk<MODE>(Bt, G, ndir, ldg, npix, ncol, slab, pool, stream);
   }
   float *Bs = nullptr;
   const size_t bs_bytes = sizeof(float) * (size_t)n_ct * 2 * TC_N * Kp;
