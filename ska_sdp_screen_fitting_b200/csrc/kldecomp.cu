@@ -13,6 +13,7 @@ namespace {
 // threads per CTA: 256 for up to 64 directions; 512 above, where a pattern's two 100 x 100
 // FP64 matrices leave room for only one CTA per SM and more warps hide the latency
 constexpr int MAX_SWEEPS = 40;
+constexpr int WARM_MAX_FLAGGED = 16;   // warm start (see decompose_kernel) up to this many flagged directions
 static_assert(SSF_MAX_DIR <= 128, "warm start: 4 columns per lane of one warp");
 // off-diagonal / total ENERGY below which one more sweep is the last (see the sweep loop)
 #ifndef SSF_JACOBI_LAST
@@ -115,7 +116,10 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
   // a prefix sum along each row.  The leading eigenvectors stay almost untouched and the
   // error lands on the small eigenvalues, so C_S is already nearly diagonal in this basis
   // (off-diagonal energy ~1e-4 of the total) and Jacobi needs half the sweeps of a cold start.
-  if (U0 != nullptr && n < ndir && n > 1) {
+  // Only for up to WARM_MAX_FLAGGED flagged directions: every deflation costs a little
+  // orthogonality (1e-15 per step up to ~16, 1e-13 after 60), which ends up in the eigenvalues;
+  // heavily flagged patterns are small matrices and start cold.
+  if (U0 != nullptr && n < ndir && n > 1 && ndir - n <= WARM_MAX_FLAGGED) {
     const int mfull = (ndir + 1) & ~1;
     const int ldf = mfull + 1;
     double *F = sm + (size_t)mfull * ldf;         // second half of the allocation: [ndir][ldf]

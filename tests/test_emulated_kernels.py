@@ -13,6 +13,9 @@ def test_decompose(emu_engine):
 def test_pattern_cache_warm_started_decompositions(emu_engine):
     pc.check_pattern_cache_decompose(emu_engine)
     pc.check_pattern_cache_decompose(emu_engine, n_d=14, seed=8, max_flagged=5)
+    # 3 of 64 / 65 kept: far beyond the warm-start limit (cold start), both thread-count variants
+    pc.check_pattern_cache_decompose(emu_engine, n_d=64, seed=13, max_flagged=2, n_sys=6)
+    pc.check_pattern_cache_decompose(emu_engine, n_d=65, seed=12, max_flagged=2, n_sys=6)
 
 
 def test_fit_with_flags_and_outliers(emu_engine):

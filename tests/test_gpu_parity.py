@@ -22,6 +22,9 @@ def test_pattern_cache_warm_started_decompositions(gpu_engine):
     pc.check_pattern_cache_decompose(gpu_engine, n_d=45, seed=8, max_flagged=4, n_sys=12)
     pc.check_pattern_cache_decompose(gpu_engine, n_d=100, seed=9, max_flagged=5, n_sys=12)
     pc.check_pattern_cache_decompose(gpu_engine, n_d=99, seed=10, max_flagged=3, n_sys=8)
+    pc.check_pattern_cache_decompose(gpu_engine, n_d=112, seed=11, max_flagged=6, n_sys=8)   # SSF_MAX_DIR
+    pc.check_pattern_cache_decompose(gpu_engine, n_d=65, seed=12, max_flagged=2, n_sys=6)    # first 512-thread size
+    pc.check_pattern_cache_decompose(gpu_engine, n_d=64, seed=13, max_flagged=2, n_sys=6)    # last 256-thread size
 
 
 def test_fit_tec_type_against_reference_operator_golden(gpu_engine, golden_dir):
