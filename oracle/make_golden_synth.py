@@ -181,4 +181,34 @@ def golden_gaps(mods):
         fake_h5parm.reset()
 
 
-JOBS = {"gain": golden_gain, "tec": golden_tec, "gaps": golden_gaps}
+def golden_padding(mods):
+    """Default padding_fraction (1.4) and a cell size that does not divide the width
+    (make_aterm_images.py:88-97, :116-118; screen.py:180-181): image size, header and cube of
+    the reference for the repo data, tessellated, unsmoothed, README-style bounds."""
+    from oracle.refshim import fake_astropy, fake_h5parm
+
+    tmp = tempfile.mkdtemp(prefix="ssf_golden_")
+    for f in ("solutions.h5", "skymodel.txt"):
+        shutil.copy(os.path.join(GOLDEN, f), tmp)
+    cwd = os.getcwd()
+    os.chdir(tmp)
+    try:
+        fake_h5parm.reset()
+        mods["make_aterm_images"].make_aterm_image(
+            "solutions.h5", soltabname="phase000", screen_type="tessellated", outroot="pad",
+            bounds_deg="[127.895;62.835;124.565;66.165]", bounds_mid_deg="[126.23;64.50]",
+            skymodel="skymodel.txt", solsetname="sol000", cellsize_deg=0.13, smooth_deg=0.0, ncpu=0)
+        hdu = fake_astropy.open("pad_0.fits")
+        hdr = hdu[0].header
+        out = dict(sub_f=SUB_F, sub_a=SUB_A, cube=hdu[0].data[:, SUB_F][:, :, SUB_A].copy(),
+                   header_keys=np.array([k for k, _ in hdr.items()]),
+                   header_vals=np.array([str(v) for _, v in hdr.items()]),
+                   template=fake_astropy.open("pad_template.fits")[0].data[0, 0, 0, 0].copy())
+        np.savez_compressed(os.path.join(GOLDEN, "padding_c1.npz"), **out)
+    finally:
+        os.chdir(cwd)
+        shutil.rmtree(tmp)
+        fake_h5parm.reset()
+
+
+JOBS = {"gain": golden_gain, "tec": golden_tec, "gaps": golden_gaps, "padding": golden_padding}

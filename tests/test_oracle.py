@@ -290,3 +290,37 @@ def test_cli_with_string_bounds_writes_the_reference_cube(emu_library, vor_golde
     # unknown flags / a missing positional are argparse errors (exit status 2), like the reference
     bad = subprocess.run(cmd[:3] + ["--no_such_flag", "1"], env=env, capture_output=True, text=True, timeout=120)
     assert bad.returncode == 2
+
+
+def test_cli_default_padding_matches_the_reference(emu_library, tmp_path):
+    """Default padding_fraction = 1.4 and a cell size that does not divide the padded width
+    (make_aterm_images.py:88-97, :116-118): image size, every header card, the template and the
+    unsmoothed cube against the reference's (tests/golden/padding_c1.npz, golden_padding)."""
+    import subprocess
+    import sys
+
+    from ska_sdp_screen_fitting_b200 import fits
+
+    g = np.load(os.path.join(GOLDEN, "padding_c1.npz"))
+    root = os.path.dirname(os.path.dirname(GOLDEN))
+    env = dict(os.environ, SSF_B200_LIBRARY=emu_library,
+               PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    cmd = [sys.executable, "-m", "ska_sdp_screen_fitting_b200.main", os.path.join(GOLDEN, "solutions.h5"),
+           "--outroot", str(tmp_path / "pad"), "--bounds_deg", "[127.895;62.835;124.565;66.165]",
+           "--bounds_mid_deg", "[126.23;64.50]", "--skymodel", os.path.join(GOLDEN, "skymodel.txt"),
+           "--cellsize_deg", "0.13"]
+    done = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=900)
+    assert done.returncode == 0, done.stderr[-2000:]
+    header, data = fits.read(str(tmp_path / "pad_0.fits"))
+    assert list(header.keys()) == list(g["header_keys"])
+    for key, want in zip(g["header_keys"], g["header_vals"]):
+        got = header[key]
+        if isinstance(got, (bool, str)):
+            assert str(got) == str(want), key
+        else:
+            # cards carry 16 significant digits, as astropy's (".16G") do
+            assert abs(float(got) - float(want)) <= 1e-15 * abs(float(want)), key
+    sub = np.asarray(data)[:, list(g["sub_f"])][:, :, list(g["sub_a"])]
+    assert sub.shape == g["cube"].shape and np.array_equal(sub, g["cube"])
+    _, tmpl = fits.read(str(tmp_path / "pad_template.fits"))
+    assert np.array_equal(np.asarray(tmpl)[0, 0, 0, 0], g["template"])
