@@ -41,6 +41,18 @@ extern "C" {
 
 #define SSF_MAX_DIR 112   /* max directions (pierce points) per system (2 n^2 doubles of smem) */
 
+/* Output format of the cube kernels (`out_flags`), fused into their store epilogues:
+ *   SSF_OUT_BIG_ENDIAN  every float32 is stored byte-swapped, i.e. in the big-endian order of
+ *                       a BITPIX -32 FITS cube (what astropy's hdu.writeto does on the host,
+ *                       screen.py:381-382) -- no separate pass over the slab;
+ *   SSF_OUT_PLANES2     only planes 0 (Re XX) and 1 (Im XX) are stored, slab = float32
+ *                       [ncol, 2, ny, nx].  For phase-only solutions planes 2, 3 repeat planes
+ *                       0, 1 (kl_screen.py:368-373, voronoi_screen.py:194-198); the FITS writer
+ *                       places each pair twice, so half the bytes are written to HBM and cross
+ *                       PCIe.  Not valid for the gain entry points (their planes differ). */
+#define SSF_OUT_BIG_ENDIAN 1
+#define SSF_OUT_PLANES2 2
+
 int ssf_version(void);
 const char *ssf_last_error(void);
 /* Number of kernel launches issued through this library by the calling process so far. */
@@ -153,7 +165,14 @@ int ssf_kl_coeffs(const double *white, int64_t ncol, int ndir, const double *C,
                   float *G, int ldg, void *stream);
 /* variant: 0 = FP32 SIMT, 1 = tcgen05 (3xTF32 split, FP32 accumulate in TMEM), -1 = auto */
 int ssf_kl_eval(const float *Bt, const float *G, int ndir, int ldg, int64_t npix,
-                int64_t ncol, float *slab, int variant, void *stream);
+                int64_t ncol, float *slab, int variant, int out_flags, void *stream);
+
+/* dTEC screens (aterm_type="tec", processing_utils.py:187-190: a 5-axis cube [t, f, a, y, x]
+ * with no MATRIX axis): the same contraction without the cos/sin epilogue,
+ *     slab[col, pix] = Phi[pix, col]        (float32 [ncol, ny*nx]; NaN kept)
+ * out_flags: SSF_OUT_BIG_ENDIAN only. */
+int ssf_kl_eval_tec(const float *Bt, const float *G, int ndir, int ldg, int64_t npix,
+                    int64_t ncol, float *slab, int variant, int out_flags, void *stream);
 
 /* Gain solutions (scalar phase + log10 XX/YY amplitude screens, kl_screen.py:319-378):
  * G3 [ncol, 3, ldg] f32 = coefficients (phase, Axx, Ayy) from ssf_kl_coeffs on the stacked
@@ -161,7 +180,7 @@ int ssf_kl_eval(const float *Bt, const float *G, int ndir, int ldg, int64_t npix
  * NaN -> (1, 0, 1, 0) fused into the store.  variant: -1 auto, 0 FP32 SIMT, 1 tcgen05
  * (16 columns x 3 accumulator groups per 64-wide tile; same kernel as ssf_kl_eval). */
 int ssf_kl_eval_gain(const float *Bt, const float *G3, int ndir, int ldg, int64_t npix,
-                     int64_t ncol, float *slab, int variant, void *stream);
+                     int64_t ncol, float *slab, int variant, int out_flags, void *stream);
 
 /* ------------------------------------------------------------------------------------
  * Voronoi.  ssf_voronoi_assign: float64 nearest patch per integer pixel, lowest index
@@ -176,7 +195,7 @@ int ssf_voronoi_assign(const double *px, const double *py, int ndir, int nx, int
 int ssf_voronoi_lut(const double *phase, const double *amp, int64_t ncol, int ndir,
                     float *lut, void *stream);
 int ssf_voronoi_fill(const int32_t *tmpl, const float *lut, int ndir, int64_t npix,
-                     int64_t ncol, float *slab, int fix_nan, void *stream);
+                     int64_t ncol, float *slab, int fix_nan, int out_flags, void *stream);
 
 /* Gain solutions (scalar phase + XX/YY amplitudes, voronoi_screen.py:177-214):
  * amp [ncol, ndir, 2] f64 = (XX, YY) amplitudes; lut4 [ncol, ndir, 4] f32 =
@@ -184,7 +203,7 @@ int ssf_voronoi_fill(const int32_t *tmpl, const float *lut, int ndir, int64_t np
 int ssf_voronoi_lut_gain(const double *phase, const double *amp, int64_t ncol, int ndir,
                          float *lut4, void *stream);
 int ssf_voronoi_fill_gain(const int32_t *tmpl, const float *lut4, int ndir, int64_t npix,
-                          int64_t ncol, float *slab, int fix_nan, void *stream);
+                          int64_t ncol, float *slab, int fix_nan, int out_flags, void *stream);
 
 /* Smoothed Voronoi through linearity: slab[col, p, pix] = sum_d S[d, pix] * lut[col, d, p&1]
  * where S[d, :] is the Gaussian-smoothed indicator image of cell d (built with
@@ -193,7 +212,7 @@ int ssf_voronoi_fill_gain(const int32_t *tmpl, const float *lut4, int ndir, int6
 int ssf_voronoi_indicators(const int32_t *tmpl, int ndir, int64_t npix, float *ind,
                            void *stream);
 int ssf_voronoi_contract(const float *S, const float *lut, int ndir, int64_t npix,
-                         int64_t ncol, float *slab, int variant, void *stream);
+                         int64_t ncol, float *slab, int variant, int out_flags, void *stream);
 
 /* ------------------------------------------------------------------------------------
  * Separable Gaussian smoothing, in place, of nimg images [ny, nx] float32: y pass then x
@@ -210,6 +229,14 @@ int ssf_nan_fix(float *slab, int64_t ncol, int64_t npix, void *stream);
  * storage order of a BITPIX -32 FITS cube (astropy does this inside hdu.writeto,
  * screen.py:381-382).  `data` must be 16-byte aligned. */
 int ssf_bswap32(void *data, int64_t count, void *stream);
+
+/* Strided device -> host copy of `rows` runs of `width_bytes` (cudaMemcpy2DAsync on `stream`):
+ * how a slab of column pairs [ncol, 2, ny, nx] (SSF_OUT_PLANES2) lands at planes 0-1 of each
+ * 4-plane column of the pinned host image of the FITS cube (src_pitch = 2 planes, dst_pitch =
+ * 4 planes), or a slab of whole columns lands contiguously (both pitches = width).  The FITS
+ * write of the reference is hdu.writeto (screen.py:381-382); this is the device half of it. */
+int ssf_copy_rows_d2h(void *dst_host, int64_t dst_pitch, const void *src_dev, int64_t src_pitch,
+                      int64_t width_bytes, int64_t rows, void *stream);
 
 /* ------------------------------------------------------------------------------------
  * Host convenience entry points (what a ctypes/cffi binding of the reference would call):

@@ -25,6 +25,13 @@ def kl_phase_images(kmat, white_td):
     return np.einsum("ijd,td->ijt", kmat, white_td)
 
 
+def kl_screen_values(x_coord, y_coord, pp, white_td):
+    """The screen itself, [t, ny, nx] float64: what calculate_kl_screen returns
+    (kl_screen.py:411-449), before make_matrix takes cos / sin of it.  For dTEC solutions this
+    is the content of an aterm_type="tec" cube (processing_utils.py:187-190: [t, f, a, y, x])."""
+    return kl_phase_images(kl_kernel_matrix(x_coord, y_coord, pp), white_td).T
+
+
 def kl_make_matrix(x_coord, y_coord, pp, white_td, amp_xx_td=None, amp_yy_td=None):
     """kl_screen.py:192-380: data[t, 4, ny, nx] float64.  Gain solutions: ``amp_xx_td`` /
     ``amp_yy_td`` are the log10 amplitude screens (white values), evaluated with the same

@@ -44,22 +44,27 @@ SIGNATURES = {
     "ssf_kl_flag_outliers_amp": (c_int, [_P, _P, _P, c_int, c_int64, c_int64, c_double, _P, _P, _P]),
     "ssf_kl_basis": (c_int, [_P, _P, c_int, c_int, _P, c_int, _P, c_double, c_double, _P, _P]),
     "ssf_kl_coeffs": (c_int, [_P, c_int64, c_int, _P, _P, c_int, _P]),
-    "ssf_kl_eval": (c_int, [_P, _P, c_int, c_int, c_int64, c_int64, _P, c_int, _P]),
-    "ssf_kl_eval_gain": (c_int, [_P, _P, c_int, c_int, c_int64, c_int64, _P, c_int, _P]),
+    "ssf_kl_eval": (c_int, [_P, _P, c_int, c_int, c_int64, c_int64, _P, c_int, c_int, _P]),
+    "ssf_kl_eval_tec": (c_int, [_P, _P, c_int, c_int, c_int64, c_int64, _P, c_int, c_int, _P]),
+    "ssf_kl_eval_gain": (c_int, [_P, _P, c_int, c_int, c_int64, c_int64, _P, c_int, c_int, _P]),
     "ssf_voronoi_assign": (c_int, [_P, _P, c_int, c_int, c_int, _P, _P]),
     "ssf_voronoi_lut": (c_int, [_P, _P, c_int64, c_int, _P, _P]),
-    "ssf_voronoi_fill": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, c_int, _P]),
+    "ssf_voronoi_fill": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, c_int, c_int, _P]),
     "ssf_voronoi_lut_gain": (c_int, [_P, _P, c_int64, c_int, _P, _P]),
-    "ssf_voronoi_fill_gain": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, c_int, _P]),
+    "ssf_voronoi_fill_gain": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, c_int, c_int, _P]),
     "ssf_voronoi_indicators": (c_int, [_P, c_int, c_int64, _P, _P]),
-    "ssf_voronoi_contract": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, c_int, _P]),
+    "ssf_voronoi_contract": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, c_int, c_int, _P]),
     "ssf_gauss_smooth": (c_int, [_P, c_int64, c_int, c_int, c_double, _P, _P]),
     "ssf_nan_fix": (c_int, [_P, c_int64, c_int64, _P]),
     "ssf_bswap32": (c_int, [_P, c_int64, _P]),
+    "ssf_copy_rows_d2h": (c_int, [_P, c_int64, _P, c_int64, c_int64, c_int64, _P]),
     "ssf_voronoi_cube_host": (c_int, [_P, _P, c_int, c_int, c_int, c_int64, c_double, _P]),
     "ssf_kl_cube_host": (c_int, [_P, _P, c_int, c_int, _P, c_int, _P, c_int64, c_double, c_double,
                                  c_double, _P]),
 }
+
+OUT_BIG_ENDIAN = 1      # SSF_OUT_BIG_ENDIAN
+OUT_PLANES2 = 2         # SSF_OUT_PLANES2
 
 _loaded = {}
 

@@ -63,4 +63,27 @@ __device__ __forceinline__ double structure_fn(double d2, double inv_r0sq, doubl
 __device__ __forceinline__ float fix_re(float v) { return v != v ? 1.0f : v; }
 __device__ __forceinline__ float fix_im(float v) { return v != v ? 0.0f : v; }
 
+// Output format of the cube kernels (SSF_OUT_* flags of ssf.h), resolved once on the host:
+//   prmt   = byte-permute selector applied to every stored word: 0x3210 keeps the native
+//            little-endian float32, 0x0123 stores it byte-swapped = the big-endian order of a
+//            BITPIX -32 FITS cube (the swap of hdu.writeto, screen.py:381-382, fused into the
+//            store: one PRMT per value, no second pass over the slab)
+//   planes = 4: slab [ncol, 4, npix]; 2: only planes 0 and 1 are stored, slab [ncol, 2, npix]
+//            (phase-only solutions: planes 2, 3 repeat 0, 1 -- kl_screen.py:368-373,
+//            voronoi_screen.py:194-198 -- and the FITS writer places the pair twice);
+//            1: one plane of raw screen values (tec cube, processing_utils.py:187-190)
+struct OutFmt {
+  uint32_t prmt;
+  int planes;
+};
+inline bool out_fmt(int flags, OutFmt *f) {
+  if (flags & ~(SSF_OUT_BIG_ENDIAN | SSF_OUT_PLANES2)) return false;
+  f->prmt = (flags & SSF_OUT_BIG_ENDIAN) ? 0x0123u : 0x3210u;
+  f->planes = (flags & SSF_OUT_PLANES2) ? 2 : 4;
+  return true;
+}
+__device__ __forceinline__ float out_word(float v, uint32_t prmt) {
+  return __uint_as_float(__byte_perm(__float_as_uint(v), 0u, prmt));
+}
+
 }  // namespace ssf

@@ -20,7 +20,8 @@ constexpr int TC = 8;  // columns per inner tile
 template <bool KL, bool VEC>
 __global__ void __launch_bounds__(THREADS)
 contract_simt_kernel(const float *__restrict__ Bt, const float *__restrict__ G, int ndir, int ldg,
-                     int64_t npix, int64_t ncol, float *__restrict__ slab, int64_t col_tiles_per_cta) {
+                     int64_t npix, int64_t ncol, float *__restrict__ slab, int64_t col_tiles_per_cta,
+                     ssf::OutFmt fmt) {
   // KL: coefficient tile gs[d][TC]; Voronoi: gs[d][2*TC] (re block then im block)
   SSF_DYN_SMEM(float, gs);
   constexpr int W = KL ? TC : 2 * TC;
@@ -84,30 +85,39 @@ contract_simt_kernel(const float *__restrict__ Bt, const float *__restrict__ G, 
       float re[PIX_PER_THREAD], im[PIX_PER_THREAD];
 #pragma unroll
       for (int j = 0; j < PIX_PER_THREAD; ++j) {
+        if (KL && fmt.planes == 1) {             // raw screen values (tec cube): NaN kept
+          re[j] = ssf::out_word(acc[c][j], fmt.prmt);
+          im[j] = 0.0f;
+          continue;
+        }
         if (KL) {
           sincosf(acc[c][j], &im[j], &re[j]);
         } else {
           re[j] = acc[c][j];
           im[j] = acc[TC + c][j];
         }
-        re[j] = ssf::fix_re(re[j]);
-        im[j] = ssf::fix_im(im[j]);
+        re[j] = ssf::out_word(ssf::fix_re(re[j]), fmt.prmt);
+        im[j] = ssf::out_word(ssf::fix_im(im[j]), fmt.prmt);
       }
-      float *out = slab + col * 4 * npix + p0;
+      float *out = slab + col * fmt.planes * npix + p0;
       if (VEC) {
         float4 r4 = make_float4(re[0], re[1], re[2], re[3]), i4 = make_float4(im[0], im[1], im[2], im[3]);
         __stcs(reinterpret_cast<float4 *>(out), r4);
-        __stcs(reinterpret_cast<float4 *>(out + npix), i4);
-        __stcs(reinterpret_cast<float4 *>(out + 2 * npix), r4);
-        __stcs(reinterpret_cast<float4 *>(out + 3 * npix), i4);
+        if (fmt.planes >= 2) __stcs(reinterpret_cast<float4 *>(out + npix), i4);
+        if (fmt.planes == 4) {
+          __stcs(reinterpret_cast<float4 *>(out + 2 * npix), r4);
+          __stcs(reinterpret_cast<float4 *>(out + 3 * npix), i4);
+        }
       } else {
 #pragma unroll
         for (int j = 0; j < PIX_PER_THREAD; ++j) {
           if (p0 + j < npix) {
             out[j] = re[j];
-            out[npix + j] = im[j];
-            out[2 * npix + j] = re[j];
-            out[3 * npix + j] = im[j];
+            if (fmt.planes >= 2) out[npix + j] = im[j];
+            if (fmt.planes == 4) {
+              out[2 * npix + j] = re[j];
+              out[3 * npix + j] = im[j];
+            }
           }
         }
       }
@@ -139,7 +149,8 @@ constexpr int MAX_PRE = (SSF_MAX_DIR * 16 + THREADS - 1) / THREADS;  // coeffici
 template <bool KL, int PPT, int TCOL>
 __global__ void __launch_bounds__(THREADS, 2)
 contract_tile_kernel(const float *__restrict__ Bt, const float *__restrict__ G, int ndir, int ldg,
-                     int64_t npix, int64_t ncol, float *__restrict__ slab, int tiles_per_chunk) {
+                     int64_t npix, int64_t ncol, float *__restrict__ slab, int tiles_per_chunk,
+                     ssf::OutFmt fmt) {
   constexpr int TPIX = THREADS * PPT;
   constexpr int W = KL ? TCOL : 2 * TCOL;       // accumulator columns (Voronoi: re block, im block)
   SSF_DYN_SMEM(float, sm);
@@ -248,30 +259,39 @@ contract_tile_kernel(const float *__restrict__ Bt, const float *__restrict__ G, 
       float re[PPT], im[PPT];
 #pragma unroll
       for (int j = 0; j < PPT; ++j) {
+        if (KL && fmt.planes == 1) {             // raw screen values (tec cube): NaN kept
+          re[j] = ssf::out_word(acc[c][j], fmt.prmt);
+          im[j] = 0.0f;
+          continue;
+        }
         if (KL) {
           sincos_reduced(acc[c][j], &im[j], &re[j]);
         } else {
           re[j] = acc[c][j];
           im[j] = acc[TCOL + c][j];
         }
-        re[j] = ssf::fix_re(re[j]);
-        im[j] = ssf::fix_im(im[j]);
+        re[j] = ssf::out_word(ssf::fix_re(re[j]), fmt.prmt);
+        im[j] = ssf::out_word(ssf::fix_im(im[j]), fmt.prmt);
       }
-      float *out = slab + col * 4 * npix + p0;
+      float *out = slab + col * fmt.planes * npix + p0;
       if (PPT == 4) {
         const float4 r4 = make_float4(re[0], re[1], re[2], re[3]);
         const float4 i4 = make_float4(im[0], im[1], im[2], im[3]);
         __stcs(reinterpret_cast<float4 *>(out), r4);
-        __stcs(reinterpret_cast<float4 *>(out + npix), i4);
-        __stcs(reinterpret_cast<float4 *>(out + 2 * npix), r4);
-        __stcs(reinterpret_cast<float4 *>(out + 3 * npix), i4);
+        if (fmt.planes >= 2) __stcs(reinterpret_cast<float4 *>(out + npix), i4);
+        if (fmt.planes == 4) {
+          __stcs(reinterpret_cast<float4 *>(out + 2 * npix), r4);
+          __stcs(reinterpret_cast<float4 *>(out + 3 * npix), i4);
+        }
       } else {
         const float2 r2 = make_float2(re[0], re[PPT - 1]);
         const float2 i2 = make_float2(im[0], im[PPT - 1]);
         __stcs(reinterpret_cast<float2 *>(out), r2);
-        __stcs(reinterpret_cast<float2 *>(out + npix), i2);
-        __stcs(reinterpret_cast<float2 *>(out + 2 * npix), r2);
-        __stcs(reinterpret_cast<float2 *>(out + 3 * npix), i2);
+        if (fmt.planes >= 2) __stcs(reinterpret_cast<float2 *>(out + npix), i2);
+        if (fmt.planes == 4) {
+          __stcs(reinterpret_cast<float2 *>(out + 2 * npix), r2);
+          __stcs(reinterpret_cast<float2 *>(out + 3 * npix), i2);
+        }
       }
     }
   }
@@ -301,7 +321,7 @@ int pick_chunks(int pix_tiles, int64_t n_ct, int capacity) {
 
 template <bool KL, int PPT, int TCOL>
 int launch_tile(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol,
-                float *slab, cudaStream_t stream) {
+                float *slab, ssf::OutFmt fmt, cudaStream_t stream) {
   constexpr int TPIX = THREADS * PPT;
   constexpr int W = KL ? TCOL : 2 * TCOL;
   const size_t smem = sizeof(float) * ((size_t)ndir * TPIX + (size_t)ndir * W);
@@ -315,24 +335,24 @@ int launch_tile(const float *Bt, const float *G, int ndir, int ldg, int64_t npix
   const int gx = (int)((n_ct + per - 1) / per);
   SSF_REQUIRE(pix_tiles <= 65535, "image too large for the tiled contraction grid");
   dim3 grid(gx, pix_tiles);
-  SSF_LAUNCH(kfn, grid, THREADS, smem, stream, Bt, G, ndir, ldg, npix, ncol, slab, per);
+  SSF_LAUNCH(kfn, grid, THREADS, smem, stream, Bt, G, ndir, ldg, npix, ncol, slab, per, fmt);
   SSF_LAUNCHED();
   return SSF_OK;
 }
 
 template <bool KL>
 int launch(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol,
-           float *slab, cudaStream_t stream) {
+           float *slab, ssf::OutFmt fmt, cudaStream_t stream) {
   const bool vec = (npix % 4 == 0) && ((uintptr_t)slab % 16 == 0) && ((uintptr_t)Bt % 16 == 0);
   const bool g_ok = KL || ((uintptr_t)G % 8 == 0);
   if (vec && g_ok && npix >= 1024 && ncol >= 4) {
     // tiled fast path; 4 pixels per thread while the basis tile leaves room for 2 CTAs per SM
     if (KL) {
-      if (ndir <= 52) return launch_tile<true, 4, 16>(Bt, G, ndir, ldg, npix, ncol, slab, stream);
-      return launch_tile<true, 2, 16>(Bt, G, ndir, ldg, npix, ncol, slab, stream);
+      if (ndir <= 52) return launch_tile<true, 4, 16>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, stream);
+      return launch_tile<true, 2, 16>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, stream);
     }
-    if (ndir <= 52) return launch_tile<false, 4, 8>(Bt, G, ndir, ldg, npix, ncol, slab, stream);
-    return launch_tile<false, 2, 8>(Bt, G, ndir, ldg, npix, ncol, slab, stream);
+    if (ndir <= 52) return launch_tile<false, 4, 8>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, stream);
+    return launch_tile<false, 2, 8>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, stream);
   }
   const int pix_tiles = ssf::div_up(npix, TILE_PIX);
   const int64_t n_ct = (ncol + TC - 1) / TC;
@@ -346,7 +366,7 @@ int launch(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int
   dim3 grid(pix_tiles, gy);
   size_t smem = sizeof(float) * ndir * (KL ? TC : 2 * TC);
   auto kfn = vec ? contract_simt_kernel<KL, true> : contract_simt_kernel<KL, false>;
-  SSF_LAUNCH(kfn, grid, THREADS, smem, stream, Bt, G, ndir, ldg, npix, ncol, slab, per);
+  SSF_LAUNCH(kfn, grid, THREADS, smem, stream, Bt, G, ndir, ldg, npix, ncol, slab, per, fmt);
   SSF_LAUNCHED();
   return SSF_OK;
 }
@@ -355,11 +375,11 @@ int launch(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int
 
 namespace ssf {
 int kl_eval_simt(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol,
-                 float *slab, cudaStream_t stream) {
-  return launch<true>(Bt, G, ndir, ldg, npix, ncol, slab, stream);
+                 float *slab, OutFmt fmt, cudaStream_t stream) {
+  return launch<true>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, stream);
 }
 int voronoi_contract_simt(const float *St, const float *lut, int ndir, int64_t npix, int64_t ncol,
-                          float *slab, cudaStream_t stream) {
-  return launch<false>(St, lut, ndir, ndir, npix, ncol, slab, stream);
+                          float *slab, OutFmt fmt, cudaStream_t stream) {
+  return launch<false>(St, lut, ndir, ndir, npix, ncol, slab, fmt, stream);
 }
 }  // namespace ssf

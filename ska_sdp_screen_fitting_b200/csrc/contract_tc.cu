@@ -40,11 +40,11 @@
 // The tensor-core variant has no CPU emulation: the emulator library reports "not supported".
 namespace ssf {
 bool contract_tc_supported(bool, int, int64_t, int64_t, const void *, const void *) { return false; }
-int contract_tc(bool, const float *, const float *, int, int, int64_t, int64_t, float *, cudaStream_t) {
+int contract_tc(bool, const float *, const float *, int, int, int64_t, int64_t, float *, OutFmt, cudaStream_t) {
   set_error("tcgen05 contraction variant is not available in the CPU emulator");
   return SSF_ENOTSUP;
 }
-int contract_tc_gain(const float *, const float *, int, int, int64_t, int64_t, float *, cudaStream_t) {
+int contract_tc_gain(const float *, const float *, int, int, int64_t, int64_t, float *, OutFmt, cudaStream_t) {
   set_error("tcgen05 contraction variant is not available in the CPU emulator");
   return SSF_ENOTSUP;
 }
@@ -200,38 +200,52 @@ __device__ __forceinline__ void sincos_reduced(float x, float *s, float *c) {
 // Epilogue stores of one thread's 32 accumulator columns (its pixel, 32 slab columns): the 32
 // lanes of the warp write 128 contiguous bytes per plane.  CHECK = ragged last tile.
 template <bool CHECK>
-__device__ __forceinline__ void store_kl(const float (&v)[32], float *out, int64_t npix, int nvalid) {
-  const int64_t p2 = 2 * npix, p3 = 3 * npix, p4 = 4 * npix;
+__device__ __forceinline__ void store_kl(const float (&v)[32], float *out, int64_t npix, int nvalid, ssf::OutFmt fmt) {
+  const int64_t p2 = 2 * npix, p3 = 3 * npix, pc = fmt.planes * npix;
+  const bool four = fmt.planes == 4;                         // uniform: predicated stores, no divergence
 #pragma unroll
   for (int j = 0; j < 32; ++j) {                             // fully unrolled: v[j] stays in registers
     if (CHECK && j >= nvalid) break;
     float sn, cs;
     sincos_reduced(v[j], &sn, &cs);
-    cs = ssf::fix_re(cs);
-    sn = ssf::fix_im(sn);
+    cs = ssf::out_word(ssf::fix_re(cs), fmt.prmt);
+    sn = ssf::out_word(ssf::fix_im(sn), fmt.prmt);
     __stcs(out, cs);
     __stcs(out + npix, sn);
-    __stcs(out + p2, cs);
-    __stcs(out + p3, sn);
-    out += p4;
+    if (four) {
+      __stcs(out + p2, cs);
+      __stcs(out + p3, sn);
+    }
+    out += pc;
+  }
+}
+// dTEC cube (ssf_kl_eval_tec): the raw screen value, one plane per column, NaN kept.
+__device__ __forceinline__ void store_raw(const float (&v)[32], float *out, int64_t npix, int nvalid, ssf::OutFmt fmt) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    if (j >= nvalid) break;
+    __stcs(out, ssf::out_word(v[j], fmt.prmt));
+    out += npix;
   }
 }
 template <bool CHECK>
-__device__ __forceinline__ void store_vo(const float (&v)[32], float *out, int64_t npix, int nvalid, int h) {
-  const int64_t p2 = 2 * npix, p4 = 4 * npix;
+__device__ __forceinline__ void store_vo(const float (&v)[32], float *out, int64_t npix, int nvalid, int h,
+                                         ssf::OutFmt fmt) {
+  const int64_t p2 = 2 * npix, pc = fmt.planes * npix;
+  const bool four = fmt.planes == 4;
 #pragma unroll
   for (int j = 0; j < 32; ++j) {
     if (CHECK && j >= nvalid) break;
-    const float x = h == 0 ? ssf::fix_re(v[j]) : ssf::fix_im(v[j]);
+    const float x = ssf::out_word(h == 0 ? ssf::fix_re(v[j]) : ssf::fix_im(v[j]), fmt.prmt);
     __stcs(out, x);
-    __stcs(out + p2, x);
-    out += p4;
+    if (four) __stcs(out + p2, x);
+    out += pc;
   }
 }
 
 // Gain tiles: 8 slab columns per epilogue warp; phase, log10 Axx and log10 Ayy accumulators.
 __device__ __forceinline__ void store_gain(const float (&ph)[8], const float (&ax)[8], const float (&ay)[8],
-                                           float *out, int64_t npix, int nvalid) {
+                                           float *out, int64_t npix, int nvalid, uint32_t prmt) {
   const int64_t p2 = 2 * npix, p3 = 3 * npix, p4 = 4 * npix;
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -239,10 +253,10 @@ __device__ __forceinline__ void store_gain(const float (&ph)[8], const float (&a
     float sn, cs;
     sincos_reduced(ph[j], &sn, &cs);
     const float axx = exp10f(ax[j]), ayy = exp10f(ay[j]);
-    __stcs(out, ssf::fix_re(axx * cs));
-    __stcs(out + npix, ssf::fix_im(axx * sn));
-    __stcs(out + p2, ssf::fix_re(ayy * cs));
-    __stcs(out + p3, ssf::fix_im(ayy * sn));
+    __stcs(out, ssf::out_word(ssf::fix_re(axx * cs), prmt));
+    __stcs(out + npix, ssf::out_word(ssf::fix_im(axx * sn), prmt));
+    __stcs(out + p2, ssf::out_word(ssf::fix_re(ayy * cs), prmt));
+    __stcs(out + p3, ssf::out_word(ssf::fix_im(ayy * sn), prmt));
     out += p4;
   }
 }
@@ -294,7 +308,7 @@ __global__ void split_b_kernel(const float *__restrict__ G, int ndir, int ldg, i
 template <int MODE, int NEPI>
 __global__ void __maxnreg__(NEPI == 8 ? SSF_TC_MAXREG : 96)
 contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, int ndir, int64_t npix,
-                   int64_t ncol, float *__restrict__ slab, int tiles_per_chunk, int Kp) {
+                   int64_t ncol, float *__restrict__ slab, int tiles_per_chunk, int Kp, ssf::OutFmt fmt) {
   constexpr bool KL = MODE == 1;
   constexpr int CT = tile_columns(MODE);         // slab columns per tile
   constexpr int THREADS = (NEPI + 2) * 32;
@@ -434,7 +448,8 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, i
         __syncwarp();
         if (lane == 0) mbar_arrive(t_empty + 8 * t);
         const int64_t left = ncol - (c0 + 8 * h);
-        if (left > 0) store_gain(ph, ax, ay, slab + (c0 + 8 * h) * 4 * npix + pix, npix, left >= 8 ? 8 : (int)left);
+        if (left > 0)
+          store_gain(ph, ax, ay, slab + (c0 + 8 * h) * 4 * npix + pix, npix, left >= 8 ? 8 : (int)left, fmt.prmt);
         continue;
       }
       float v[32];
@@ -443,16 +458,17 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, i
       __syncwarp();
       if (lane == 0) mbar_arrive(t_empty + 8 * t);
       if (KL) {
-        float *out = slab + (c0 + 32 * h) * 4 * npix + pix;
+        float *out = slab + (c0 + 32 * h) * fmt.planes * npix + pix;
         const int64_t left = ncol - (c0 + 32 * h);
-        if (left >= 32) store_kl<false>(v, out, npix, 32);    // branch-free common case
-        else store_kl<true>(v, out, npix, (int)left);
+        if (fmt.planes == 1) store_raw(v, out, npix, left >= 32 ? 32 : (int)left, fmt);
+        else if (left >= 32) store_kl<false>(v, out, npix, 32, fmt);    // branch-free common case
+        else store_kl<true>(v, out, npix, (int)left, fmt);
       } else {
         // h = 0: Re rows -> planes 0, 2; h = 1: Im rows -> planes 1, 3
-        float *out = slab + c0 * 4 * npix + (int64_t)h * npix + pix;
+        float *out = slab + c0 * fmt.planes * npix + (int64_t)h * npix + pix;
         const int64_t left = ncol - c0;
-        if (left >= 32) store_vo<false>(v, out, npix, 32, h);
-        else store_vo<true>(v, out, npix, (int)left, h);
+        if (left >= 32) store_vo<false>(v, out, npix, 32, h, fmt);
+        else store_vo<true>(v, out, npix, (int)left, h, fmt);
       }
     }
   }
@@ -507,7 +523,7 @@ template <int MODE>
 __global__ void __launch_bounds__(BK_THREADS, 1)
 contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float *__restrict__ Bs, int ndir,
                         int64_t npix, int64_t ncol, float *__restrict__ slab, int tiles_per_chunk, int chunks,
-                        int Kp, int nb, int64_t n_items) {
+                        int Kp, int nb, int64_t n_items, ssf::OutFmt fmt) {
   SSF_DYN_SMEM(float, sm);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int kc4 = Kp >> 2;
@@ -672,7 +688,8 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
           __syncwarp();
           if (lane == 0) mbar_arrive(t_empty + 8 * t);
           const int64_t left = ncol - (c0 + 8 * h);
-          if (left > 0) store_gain(ph, ax, ay, slab + (c0 + 8 * h) * 4 * npix + pix, npix, left >= 8 ? 8 : (int)left);
+          if (left > 0)
+            store_gain(ph, ax, ay, slab + (c0 + 8 * h) * 4 * npix + pix, npix, left >= 8 ? 8 : (int)left, fmt.prmt);
           continue;
         }
         float v[32];
@@ -681,16 +698,17 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
         __syncwarp();
         if (lane == 0) mbar_arrive(t_empty + 8 * t);
         if (MODE == 1) {
-          float *out = slab + (c0 + 32 * h) * 4 * npix + pix;
+          float *out = slab + (c0 + 32 * h) * fmt.planes * npix + pix;
           const int64_t left = ncol - (c0 + 32 * h);
-          if (left >= 32) store_kl<false>(v, out, npix, 32);
-          else if (left > 0) store_kl<true>(v, out, npix, (int)left);
+          if (fmt.planes == 1) store_raw(v, out, npix, left >= 32 ? 32 : (int)left, fmt);
+          else if (left >= 32) store_kl<false>(v, out, npix, 32, fmt);
+          else if (left > 0) store_kl<true>(v, out, npix, (int)left, fmt);
         } else {
           // Voronoi: h = 0: Re rows -> planes 0, 2; h = 1: Im rows -> planes 1, 3
-          float *out = slab + c0 * 4 * npix + (int64_t)h * npix + pix;
+          float *out = slab + c0 * fmt.planes * npix + (int64_t)h * npix + pix;
           const int64_t left = ncol - c0;
-          if (left >= 32) store_vo<false>(v, out, npix, 32, h);
-          else store_vo<true>(v, out, npix, (int)left, h);
+          if (left >= 32) store_vo<false>(v, out, npix, 32, h, fmt);
+          else store_vo<true>(v, out, npix, (int)left, h, fmt);
         }
       }
     }
@@ -707,7 +725,7 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
 
 template <int MODE>
 int launch_bigk(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
-                cudaMemPool_t pool, cudaStream_t stream);
+                ssf::OutFmt fmt, cudaMemPool_t pool, cudaStream_t stream);
 
 // Column tiles per CTA.  Measured on B200 (profiles/r01c chunk sweeps): with the coefficient
 // tiles arriving by TMA the launch is fastest when a CTA covers about 256 slab columns (4 KL
@@ -727,7 +745,7 @@ int pick_tiles_per_cta(int ct, int Kp, int64_t n_ct) {
 
 template <int MODE>
 int launch_bigk(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
-                cudaMemPool_t pool, cudaStream_t stream) {
+                ssf::OutFmt fmt, cudaMemPool_t pool, cudaStream_t stream) {
   constexpr int CT = tile_columns(MODE);
   const int Kp = (ndir + 7) / 8 * 8;
   const int64_t n_ct = (ncol + CT - 1) / CT;
@@ -779,7 +797,7 @@ int launch_bigk(const float *Bt, const float *G, int ndir, int ldg, int64_t npix
   SSF_CUDA(cudaFuncSetAttribute(contract_tc_bigk_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int grid = (int)(n_items < 148 ? n_items : 148);
   SSF_LAUNCH(contract_tc_bigk_kernel<MODE>, grid, BK_THREADS, smem, stream, bt_map, Bs, ndir, npix, ncol, slab, per,
-             (int)chunks, Kp, nb, n_items);
+             (int)chunks, Kp, nb, n_items, fmt);
   SSF_LAUNCHED();
   cudaError_t fe = cudaFreeAsync(Bs, stream);
   SSF_CUDA(fe);
@@ -810,7 +828,7 @@ cudaMemPool_t scratch_pool(int device) {
 
 template <int MODE, int NEPI>
 int launch_kernel(const float *Bt, const float *Bs, int ndir, int64_t npix, int64_t ncol, float *slab, int Kp,
-                  size_t smem, int per_sm, cudaStream_t stream) {
+                  size_t smem, int per_sm, ssf::OutFmt fmt, cudaStream_t stream) {
   constexpr int CT = tile_columns(MODE);
   auto kfn = contract_tc_kernel<MODE, NEPI>;
   SSF_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -825,14 +843,14 @@ int launch_kernel(const float *Bt, const float *Bs, int ndir, int64_t npix, int6
   }
   const int gx = (int)((n_ct + per - 1) / per);
   dim3 grid(gx, pix_tiles);
-  SSF_LAUNCH(kfn, grid, (NEPI + 2) * 32, smem, stream, Bt, Bs, ndir, npix, ncol, slab, per, Kp);
+  SSF_LAUNCH(kfn, grid, (NEPI + 2) * 32, smem, stream, Bt, Bs, ndir, npix, ncol, slab, per, Kp, fmt);
   SSF_LAUNCHED();
   return SSF_OK;
 }
 
 template <int MODE>
 int launch_tc(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
-              cudaStream_t stream) {
+              ssf::OutFmt fmt, cudaStream_t stream) {
   constexpr int CT = tile_columns(MODE);
   const int Kp = (ndir + 7) / 8 * 8;
   const int64_t n_ct = (ncol + CT - 1) / CT;
@@ -849,7 +867,7 @@ int launch_tc(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, 
     // (experiment hooks: SSF_TC_BIGK=0 never, SSF_TC_BIGK=2 always)
     const char *e = getenv("SSF_TC_BIGK");
     const bool never = e && e[0] == '0', always = e && e[0] == '2';
-    if ((per_sm == 1 && !never) || always) return launch_bigk<MODE>(Bt, G, ndir, ldg, npix, ncol, slab, pool, stream);
+    if ((per_sm == 1 && !never) || always) return launch_bigk<MODE>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, pool, stream);
   }
   float *Bs = nullptr;
   const size_t bs_bytes = sizeof(float) * (size_t)n_ct * 2 * TC_N * Kp;
@@ -857,8 +875,8 @@ int launch_tc(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, 
   const int64_t n_thr = n_ct * TC_N * (Kp >> 2);
   SSF_LAUNCH(split_b_kernel<MODE>, ssf::div_up(n_thr, 256), 256, 0, stream, G, ndir, ldg, ncol, Kp, n_ct, Bs);
   SSF_LAUNCHED();
-  int rc = per_sm == 2 ? launch_kernel<MODE, 8>(Bt, Bs, ndir, npix, ncol, slab, Kp, smem, per_sm, stream)
-                       : launch_kernel<MODE, 16>(Bt, Bs, ndir, npix, ncol, slab, Kp, smem, per_sm, stream);
+  int rc = per_sm == 2 ? launch_kernel<MODE, 8>(Bt, Bs, ndir, npix, ncol, slab, Kp, smem, per_sm, fmt, stream)
+                       : launch_kernel<MODE, 16>(Bt, Bs, ndir, npix, ncol, slab, Kp, smem, per_sm, fmt, stream);
   cudaError_t fe = cudaFreeAsync(Bs, stream);
   if (rc == SSF_OK) SSF_CUDA(fe);
   return rc;
@@ -874,17 +892,17 @@ bool contract_tc_supported(bool kl, int ndir, int64_t npix, int64_t ncol, const 
          ((uintptr_t)bt % 16 == 0) && ((uintptr_t)slab % 16 == 0);
 }
 int contract_tc(bool kl, const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol,
-                float *slab, cudaStream_t stream) {
+                float *slab, OutFmt fmt, cudaStream_t stream) {
   if (kl) {
     SSF_REQUIRE(ldg % 4 == 0 && (uintptr_t)G % 16 == 0, "tcgen05 KL contraction: G must be 16 B aligned, ldg %% 4 == 0");
-    return launch_tc<1>(Bt, G, ndir, ldg, npix, ncol, slab, stream);
+    return launch_tc<1>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, stream);
   }
   SSF_REQUIRE((uintptr_t)G % 8 == 0, "tcgen05 Voronoi contraction: lut must be 8 B aligned");
-  return launch_tc<0>(Bt, G, ndir, ldg, npix, ncol, slab, stream);
+  return launch_tc<0>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, stream);
 }
 int contract_tc_gain(const float *Bt, const float *G3, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
-                     cudaStream_t stream) {
-  return launch_tc<2>(Bt, G3, ndir, ldg, npix, ncol, slab, stream);
+                     OutFmt fmt, cudaStream_t stream) {
+  return launch_tc<2>(Bt, G3, ndir, ldg, npix, ncol, slab, fmt, stream);
 }
 }  // namespace ssf
 #endif  // SSF_CPU_EMU

@@ -51,6 +51,22 @@ struct DeviceArena {
 
 }  // namespace
 
+extern "C" int ssf_copy_rows_d2h(void *dst_host, int64_t dst_pitch, const void *src_dev, int64_t src_pitch,
+                                 int64_t width_bytes, int64_t rows, void *stream) {
+  SSF_REQUIRE(dst_host && src_dev, "ssf_copy_rows_d2h: null pointer");
+  SSF_REQUIRE(width_bytes >= 0 && rows >= 0 && dst_pitch >= width_bytes && src_pitch >= width_bytes,
+              "ssf_copy_rows_d2h: pitches must be >= width");
+  if (rows == 0 || width_bytes == 0) return SSF_OK;
+  if (dst_pitch == width_bytes && src_pitch == width_bytes) {
+    SSF_CUDA(cudaMemcpyAsync(dst_host, src_dev, (size_t)(width_bytes * rows), cudaMemcpyDeviceToHost,
+                             (cudaStream_t)stream));
+  } else {
+    SSF_CUDA(cudaMemcpy2DAsync(dst_host, (size_t)dst_pitch, src_dev, (size_t)src_pitch, (size_t)width_bytes,
+                               (size_t)rows, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  }
+  return SSF_OK;
+}
+
 extern "C" int ssf_voronoi_cube_host(const int32_t *tmpl_host, const double *phase_host, int ndir,
                                      int ny, int nx, int64_t ncol, double smooth_pix,
                                      float *slab_host) {
@@ -75,11 +91,11 @@ extern "C" int ssf_voronoi_cube_host(const int32_t *tmpl_host, const double *pha
     // beyond the filter radius.  The host entry point always takes the direct form.
     float *d_scratch;
     SSF_TRY(arena.alloc(&d_scratch, ncol * 4 * npix));
-    SSF_TRY(ssf_voronoi_fill(d_tmpl, d_lut, ndir, npix, ncol, d_slab, 0, nullptr));
+    SSF_TRY(ssf_voronoi_fill(d_tmpl, d_lut, ndir, npix, ncol, d_slab, 0, 0, nullptr));
     SSF_TRY(ssf_gauss_smooth(d_slab, ncol * 4, ny, nx, smooth_pix, d_scratch, nullptr));
     SSF_TRY(ssf_nan_fix(d_slab, ncol, npix, nullptr));
   } else {
-    SSF_TRY(ssf_voronoi_fill(d_tmpl, d_lut, ndir, npix, ncol, d_slab, 1, nullptr));
+    SSF_TRY(ssf_voronoi_fill(d_tmpl, d_lut, ndir, npix, ncol, d_slab, 1, 0, nullptr));
   }
   SSF_CUDA(cudaMemcpy(slab_host, d_slab, sizeof(float) * ncol * 4 * npix, cudaMemcpyDeviceToHost));
   return SSF_OK;
@@ -121,7 +137,7 @@ extern "C" int ssf_kl_cube_host(const double *x_host, const double *y_host, int 
   SSF_TRY(ssf_kl_decompose(d_pp, ndir, d_mask, 1, r0, beta, pinv_cut, d_C, d_pinv, d_U, d_sv, nullptr));
   SSF_TRY(ssf_kl_basis(d_x, d_y, nx, ny, d_pp, ndir, d_pinv, r0, beta, d_Bt, nullptr));
   SSF_TRY(ssf_kl_coeffs(d_white, ncol, ndir, d_C, d_G, ldg, nullptr));
-  SSF_TRY(ssf_kl_eval(d_Bt, d_G, ndir, ldg, npix, ncol, d_slab, -1, nullptr));
+  SSF_TRY(ssf_kl_eval(d_Bt, d_G, ndir, ldg, npix, ncol, d_slab, -1, 0, nullptr));
   SSF_CUDA(cudaMemcpy(slab_host, d_slab, sizeof(float) * ncol * 4 * npix, cudaMemcpyDeviceToHost));
   return SSF_OK;
 }

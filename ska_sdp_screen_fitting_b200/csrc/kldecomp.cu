@@ -481,7 +481,7 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
 //   counters[0] = slots in use (slot 0 = the full pattern, decomposed by the caller)
 //   counters[1] = slots already decomposed
 //   counters[2] = 1 after an unrecoverable overflow (one pass has more patterns than slots)
-//   counters[3] = flagged systems of the current pass (scratch)
+//   counters[3] = systems of the current pass whose pattern is not cached yet (scratch)
 constexpr int PC_EMPTY = -1, PC_BUSY = -2;
 
 __device__ __forceinline__ bool pc_is_full(uint64_t lo, uint64_t hi, int ndir) {
@@ -490,16 +490,41 @@ __device__ __forceinline__ bool pc_is_full(uint64_t lo, uint64_t hi, int ndir) {
   return lo == f0 && hi == f1;
 }
 
+__device__ __forceinline__ int pc_hash(uint64_t lo, uint64_t hi, int hash_cap) {
+  uint64_t h = (lo ^ (hi * 0x9E3779B97F4A7C15ull)) * 0xD6E8FEB86659FD93ull;
+  h ^= h >> 32;
+  return (int)(h & (uint64_t)(hash_cap - 1));
+}
+
+// Read-only probe: counts the flagged systems of this pass whose pattern is NOT in the table yet
+// (an upper bound on the slots the pass can take: systems that share a new pattern count once
+// each).  Nobody writes the table during this kernel.
 __global__ void pc_count_kernel(const uint64_t *__restrict__ masks, int64_t nsys, int ndir,
-                                int32_t *__restrict__ counters) {
+                                const uint64_t *__restrict__ table_keys, const int32_t *__restrict__ table_slots,
+                                int hash_cap, int32_t *__restrict__ counters) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int flagged = 0;
-  if (i < nsys) flagged = pc_is_full(masks[2 * i], masks[2 * i + 1], ndir) ? 0 : 1;
+  int miss = 0;
+  if (i < nsys) {
+    const uint64_t lo = masks[2 * i], hi = masks[2 * i + 1];
+    if (!pc_is_full(lo, hi, ndir)) {
+      miss = 1;
+      int pos = pc_hash(lo, hi, hash_cap);
+      for (int probes = 0; probes < hash_cap; ++probes) {
+        const int32_t s = table_slots[pos];
+        if (s < 0) break;                          // empty: not cached
+        if (table_keys[2 * pos] == lo && table_keys[2 * pos + 1] == hi) {
+          miss = 0;
+          break;
+        }
+        pos = (pos + 1) & (hash_cap - 1);
+      }
+    }
+  }
 #ifndef SSF_CPU_EMU
-  flagged = __reduce_add_sync(0xffffffffu, flagged);
-  if ((threadIdx.x & 31) == 0 && flagged) atomicAdd(&counters[3], flagged);
+  miss = __reduce_add_sync(0xffffffffu, miss);
+  if ((threadIdx.x & 31) == 0 && miss) atomicAdd(&counters[3], miss);
 #else
-  if (flagged) atomicAdd(&counters[3], flagged);
+  if (miss) atomicAdd(&counters[3], miss);
 #endif
 }
 
@@ -515,7 +540,6 @@ __global__ void pc_reset_commit_kernel(int max_slots, int32_t *__restrict__ coun
   if (counters[0] + counters[3] > max_slots) {
     counters[0] = 1;
     counters[1] = 1;
-    if (1 + counters[3] > max_slots) counters[2] = 1;
   }
   counters[3] = 0;
 }
@@ -531,19 +555,21 @@ __global__ void pc_lookup_kernel(const uint64_t *__restrict__ masks, int64_t nsy
     pat[i] = 0;
     return;
   }
-  uint64_t h = (lo ^ (hi * 0x9E3779B97F4A7C15ull)) * 0xD6E8FEB86659FD93ull;
-  h ^= h >> 32;
-  int pos = (int)(h & (uint64_t)(hash_cap - 1));
+  int pos = pc_hash(lo, hi, hash_cap);
   volatile int32_t *vslots = table_slots;
   volatile uint64_t *vkeys = table_keys;
-  int result = 0;
+  // -1 = no slot: the pass holds more distinct patterns than the cache has slots (counters[2] is
+  // set; ssf_kl_fit_pass skips such systems and raises its status) -- callers keep a pass to at
+  // most max_slots - 1 systems, which cannot overflow
+  int result = -1;
   for (int probes = 0; probes < hash_cap;) {
     const int32_t s = vslots[pos];
     if (s == PC_EMPTY) {
       if (atomicCAS(&table_slots[pos], PC_EMPTY, PC_BUSY) == PC_EMPTY) {
         const int slot = atomicAdd(&counters[0], 1);
-        if (slot >= max_slots) {                 // cannot happen after pc_reset unless one pass overflows
+        if (slot >= max_slots) {                 // a genuine overflow: more distinct patterns than slots
           counters[2] = 1;
+          atomicSub(&counters[0], 1);
           atomicExch(&table_slots[pos], PC_EMPTY);
           break;
         }
@@ -609,7 +635,8 @@ extern "C" int ssf_kl_patterns_update(const uint64_t *masks, int64_t nsys, int n
   if (nsys <= 0) return SSF_OK;
   cudaStream_t st = (cudaStream_t)stream;
   const int nb = ssf::div_up(nsys, 256);
-  SSF_LAUNCH(pc_count_kernel, nb, 256, 0, st, masks, nsys, ndir, counters);
+  SSF_LAUNCH(pc_count_kernel, nb, 256, 0, st, masks, nsys, ndir, (const uint64_t *)table_keys,
+             (const int32_t *)table_slots, hash_cap, counters);
   SSF_LAUNCHED();
   SSF_LAUNCH(pc_reset_kernel, ssf::div_up(hash_cap, 256), 256, 0, st, table_slots, hash_cap, max_slots, counters);
   SSF_LAUNCHED();

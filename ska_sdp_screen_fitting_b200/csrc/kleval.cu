@@ -4,11 +4,11 @@
 #include "common.cuh"
 
 namespace ssf {
-int kl_eval_simt(const float *, const float *, int, int, int64_t, int64_t, float *, cudaStream_t);
-int voronoi_contract_simt(const float *, const float *, int, int64_t, int64_t, float *, cudaStream_t);
-int contract_tc(bool kl, const float *, const float *, int, int, int64_t, int64_t, float *, cudaStream_t);
+int kl_eval_simt(const float *, const float *, int, int, int64_t, int64_t, float *, OutFmt, cudaStream_t);
+int voronoi_contract_simt(const float *, const float *, int, int64_t, int64_t, float *, OutFmt, cudaStream_t);
+int contract_tc(bool kl, const float *, const float *, int, int, int64_t, int64_t, float *, OutFmt, cudaStream_t);
 bool contract_tc_supported(bool kl, int ndir, int64_t npix, int64_t ncol, const void *bt, const void *slab);
-int contract_tc_gain(const float *, const float *, int, int, int64_t, int64_t, float *, cudaStream_t);
+int contract_tc_gain(const float *, const float *, int, int, int64_t, int64_t, float *, OutFmt, cudaStream_t);
 }  // namespace ssf
 
 namespace {
@@ -87,7 +87,7 @@ constexpr int GAIN_THREADS = 128;
 template <bool VEC>
 __global__ void __launch_bounds__(GAIN_THREADS)
 kl_gain_kernel(const float *__restrict__ Bt, const float *__restrict__ G3, int ndir, int ldg, int64_t npix,
-               int64_t ncol, float *__restrict__ slab, int64_t cols_per_cta) {
+               int64_t ncol, float *__restrict__ slab, int64_t cols_per_cta, uint32_t prmt) {
   SSF_DYN_SMEM(float, gs);                       // [3][ndir] of the current column
   const int64_t p0 = ((int64_t)blockIdx.x * GAIN_THREADS + threadIdx.x) * 4;
   const int64_t c_begin = (int64_t)blockIdx.y * cols_per_cta;
@@ -129,10 +129,10 @@ kl_gain_kernel(const float *__restrict__ Bt, const float *__restrict__ G3, int n
       float sn, cs;
       sincosf(acc[0][j], &sn, &cs);
       const float ax = exp10f(acc[1][j]), ay = exp10f(acc[2][j]);
-      pl[0][j] = ssf::fix_re(ax * cs);
-      pl[1][j] = ssf::fix_im(ax * sn);
-      pl[2][j] = ssf::fix_re(ay * cs);
-      pl[3][j] = ssf::fix_im(ay * sn);
+      pl[0][j] = ssf::out_word(ssf::fix_re(ax * cs), prmt);
+      pl[1][j] = ssf::out_word(ssf::fix_im(ax * sn), prmt);
+      pl[2][j] = ssf::out_word(ssf::fix_re(ay * cs), prmt);
+      pl[3][j] = ssf::out_word(ssf::fix_im(ay * sn), prmt);
     }
     float *out = slab + col * 4 * npix + p0;
 #pragma unroll
@@ -182,24 +182,42 @@ extern "C" int ssf_kl_coeffs(const double *white, int64_t ncol, int ndir, const 
   return SSF_OK;
 }
 
-extern "C" int ssf_kl_eval(const float *Bt, const float *G, int ndir, int ldg, int64_t npix,
-                           int64_t ncol, float *slab, int variant, void *stream) {
-  SSF_REQUIRE(Bt && G && slab, "ssf_kl_eval: null pointer");
-  SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR && ldg >= ndir && npix >= 1, "ssf_kl_eval: bad sizes");
+namespace {
+int kl_eval_any(const char *who, const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol,
+                float *slab, int variant, ssf::OutFmt fmt, cudaStream_t stream) {
+  SSF_REQUIRE(Bt && G && slab, "%s: null pointer", who);
+  SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR && ldg >= ndir && npix >= 1, "%s: bad sizes", who);
   if (ncol <= 0) return SSF_OK;
   bool tc_ok = ssf::contract_tc_supported(true, ndir, npix, ncol, Bt, slab) && (ldg % 4 == 0);
   if (variant == 1 && !tc_ok) {
-    ssf::set_error("ssf_kl_eval: tcgen05 variant needs npix %% 128 == 0, 16 B aligned buffers, ldg %% 4 == 0");
+    ssf::set_error("%s: tcgen05 variant needs npix %% 128 == 0, 16 B aligned buffers, ldg %% 4 == 0", who);
     return SSF_ENOTSUP;
   }
-  if (variant == 1 || (variant < 0 && tc_ok))
-    return ssf::contract_tc(true, Bt, G, ndir, ldg, npix, ncol, slab, (cudaStream_t)stream);
-  return ssf::kl_eval_simt(Bt, G, ndir, ldg, npix, ncol, slab, (cudaStream_t)stream);
+  if (variant == 1 || (variant < 0 && tc_ok)) return ssf::contract_tc(true, Bt, G, ndir, ldg, npix, ncol, slab, fmt, stream);
+  return ssf::kl_eval_simt(Bt, G, ndir, ldg, npix, ncol, slab, fmt, stream);
+}
+}  // namespace
+
+extern "C" int ssf_kl_eval(const float *Bt, const float *G, int ndir, int ldg, int64_t npix,
+                           int64_t ncol, float *slab, int variant, int out_flags, void *stream) {
+  ssf::OutFmt fmt;
+  SSF_REQUIRE(ssf::out_fmt(out_flags, &fmt), "ssf_kl_eval: unknown out_flags %d", out_flags);
+  return kl_eval_any("ssf_kl_eval", Bt, G, ndir, ldg, npix, ncol, slab, variant, fmt, (cudaStream_t)stream);
+}
+
+extern "C" int ssf_kl_eval_tec(const float *Bt, const float *G, int ndir, int ldg, int64_t npix,
+                               int64_t ncol, float *slab, int variant, int out_flags, void *stream) {
+  ssf::OutFmt fmt;
+  SSF_REQUIRE(ssf::out_fmt(out_flags, &fmt) && fmt.planes == 4, "ssf_kl_eval_tec: out_flags may only hold SSF_OUT_BIG_ENDIAN");
+  fmt.planes = 1;
+  return kl_eval_any("ssf_kl_eval_tec", Bt, G, ndir, ldg, npix, ncol, slab, variant, fmt, (cudaStream_t)stream);
 }
 
 extern "C" int ssf_voronoi_contract(const float *S, const float *lut, int ndir, int64_t npix,
-                                    int64_t ncol, float *slab, int variant, void *stream) {
+                                    int64_t ncol, float *slab, int variant, int out_flags, void *stream) {
   SSF_REQUIRE(S && lut && slab, "ssf_voronoi_contract: null pointer");
+  ssf::OutFmt fmt;
+  SSF_REQUIRE(ssf::out_fmt(out_flags, &fmt), "ssf_voronoi_contract: unknown out_flags %d", out_flags);
   SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR && npix >= 1, "ssf_voronoi_contract: bad sizes");
   if (ncol <= 0) return SSF_OK;
   bool tc_ok = ssf::contract_tc_supported(false, ndir, npix, ncol, S, slab);
@@ -208,14 +226,17 @@ extern "C" int ssf_voronoi_contract(const float *S, const float *lut, int ndir, 
     return SSF_ENOTSUP;
   }
   if (variant == 1 || (variant < 0 && tc_ok))
-    return ssf::contract_tc(false, S, lut, ndir, ndir, npix, ncol, slab, (cudaStream_t)stream);
-  return ssf::voronoi_contract_simt(S, lut, ndir, npix, ncol, slab, (cudaStream_t)stream);
+    return ssf::contract_tc(false, S, lut, ndir, ndir, npix, ncol, slab, fmt, (cudaStream_t)stream);
+  return ssf::voronoi_contract_simt(S, lut, ndir, npix, ncol, slab, fmt, (cudaStream_t)stream);
 }
 
 
 extern "C" int ssf_kl_eval_gain(const float *Bt, const float *G3, int ndir, int ldg, int64_t npix,
-                                int64_t ncol, float *slab, int variant, void *stream) {
+                                int64_t ncol, float *slab, int variant, int out_flags, void *stream) {
   SSF_REQUIRE(Bt && G3 && slab, "ssf_kl_eval_gain: null pointer");
+  ssf::OutFmt fmt;
+  SSF_REQUIRE(ssf::out_fmt(out_flags, &fmt) && fmt.planes == 4,
+              "ssf_kl_eval_gain: out_flags may only hold SSF_OUT_BIG_ENDIAN (the four planes differ)");
   SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR && ldg >= ndir && npix >= 1, "ssf_kl_eval_gain: bad sizes");
   if (ncol <= 0) return SSF_OK;
   const bool tc_ok = ssf::contract_tc_supported(true, ndir, npix, ncol, Bt, slab);
@@ -224,7 +245,7 @@ extern "C" int ssf_kl_eval_gain(const float *Bt, const float *G3, int ndir, int 
     return SSF_ENOTSUP;
   }
   if (variant == 1 || (variant < 0 && tc_ok))
-    return ssf::contract_tc_gain(Bt, G3, ndir, ldg, npix, ncol, slab, (cudaStream_t)stream);
+    return ssf::contract_tc_gain(Bt, G3, ndir, ldg, npix, ncol, slab, fmt, (cudaStream_t)stream);
   const int64_t pix_tiles = (npix + 4 * GAIN_THREADS - 1) / (4 * GAIN_THREADS);
   // enough column chunks for ~8 CTAs per SM; a chunk keeps its basis tile in L1 across columns
   int64_t chunks = (148 * 8 + pix_tiles - 1) / pix_tiles;
@@ -236,10 +257,10 @@ extern "C" int ssf_kl_eval_gain(const float *Bt, const float *G3, int ndir, int 
   const bool vec = npix % 4 == 0 && (uintptr_t)Bt % 16 == 0 && (uintptr_t)slab % 16 == 0;
   if (vec)
     SSF_LAUNCH(kl_gain_kernel<true>, grid, GAIN_THREADS, smem, (cudaStream_t)stream, Bt, G3, ndir, ldg, npix, ncol,
-               slab, per);
+               slab, per, fmt.prmt);
   else
     SSF_LAUNCH(kl_gain_kernel<false>, grid, GAIN_THREADS, smem, (cudaStream_t)stream, Bt, G3, ndir, ldg, npix, ncol,
-               slab, per);
+               slab, per, fmt.prmt);
   SSF_LAUNCHED();
   return SSF_OK;
 }

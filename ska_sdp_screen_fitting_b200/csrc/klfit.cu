@@ -256,6 +256,9 @@ fit_pass_kernel(const double *__restrict__ phase, const float *__restrict__ weig
     __syncthreads();
     const int n = sh_n;
     if (n == 0) continue;  // :683-684
+    // no slot: the pattern cache overflowed in this pass (ssf_kl_patterns_update sets its
+    // overflow counter, which the caller checks); never fit against another pattern's matrices
+    if (pat[sys] < 0) continue;
     Pattern pt;
     const size_t off = (size_t)pat[sys] * nall * nall;
     pt.C = C + off;

@@ -54,15 +54,16 @@ __global__ void lut_kernel(const double *__restrict__ phase, const double *__res
 template <bool VEC4>
 __global__ void fill_kernel(const int32_t *__restrict__ tmpl, const float2 *__restrict__ lut,
                             int ndir, int64_t npix, int64_t ncol, float *__restrict__ slab,
-                            int fix_nan) {
+                            int fix_nan, ssf::OutFmt fmt) {
   const int64_t per_col = VEC4 ? npix / 4 : npix;
   const int64_t total = per_col * ncol;
+  const bool four = fmt.planes == 4;
   for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < total;
        w += (int64_t)gridDim.x * blockDim.x) {
     int64_t col = w / per_col;
     int64_t q = w - col * per_col;
     const float2 *row = lut + col * ndir;
-    float *out = slab + col * 4 * npix;
+    float *out = slab + col * fmt.planes * npix;
     if (VEC4) {
       int4 t = __ldg(reinterpret_cast<const int4 *>(tmpl) + q);
       float2 a = __ldg(row + (t.x - 1)), b = __ldg(row + (t.y - 1));
@@ -72,19 +73,29 @@ __global__ void fill_kernel(const int32_t *__restrict__ tmpl, const float2 *__re
         re = make_float4(ssf::fix_re(re.x), ssf::fix_re(re.y), ssf::fix_re(re.z), ssf::fix_re(re.w));
         im = make_float4(ssf::fix_im(im.x), ssf::fix_im(im.y), ssf::fix_im(im.z), ssf::fix_im(im.w));
       }
+      re = make_float4(ssf::out_word(re.x, fmt.prmt), ssf::out_word(re.y, fmt.prmt), ssf::out_word(re.z, fmt.prmt),
+                       ssf::out_word(re.w, fmt.prmt));
+      im = make_float4(ssf::out_word(im.x, fmt.prmt), ssf::out_word(im.y, fmt.prmt), ssf::out_word(im.z, fmt.prmt),
+                       ssf::out_word(im.w, fmt.prmt));
       float4 *o = reinterpret_cast<float4 *>(out) + q;
       const int64_t ps = npix / 4;
       __stcs(o, re);
       __stcs(o + ps, im);
-      __stcs(o + 2 * ps, re);
-      __stcs(o + 3 * ps, im);
+      if (four) {
+        __stcs(o + 2 * ps, re);
+        __stcs(o + 3 * ps, im);
+      }
     } else {
       float2 a = __ldg(row + (__ldg(tmpl + q) - 1));
       float re = fix_nan ? ssf::fix_re(a.x) : a.x, im = fix_nan ? ssf::fix_im(a.y) : a.y;
+      re = ssf::out_word(re, fmt.prmt);
+      im = ssf::out_word(im, fmt.prmt);
       out[q] = re;
       out[npix + q] = im;
-      out[2 * npix + q] = re;
-      out[3 * npix + q] = im;
+      if (four) {
+        out[2 * npix + q] = re;
+        out[3 * npix + q] = im;
+      }
     }
   }
 }
@@ -106,7 +117,7 @@ __global__ void lut_gain_kernel(const double *__restrict__ phase, const double *
 template <bool VEC4>
 __global__ void fill_gain_kernel(const int32_t *__restrict__ tmpl, const float4 *__restrict__ lut,
                                  int ndir, int64_t npix, int64_t ncol, float *__restrict__ slab,
-                                 int fix_nan) {
+                                 int fix_nan, uint32_t prmt) {
   const int64_t per_col = VEC4 ? npix / 4 : npix;
   const int64_t total = per_col * ncol;
   for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < total;
@@ -129,16 +140,17 @@ __global__ void fill_gain_kernel(const int32_t *__restrict__ tmpl, const float4 
       }
       float4 *o = reinterpret_cast<float4 *>(out) + q;
       const int64_t ps = npix / 4;
-      __stcs(o, p0);
-      __stcs(o + ps, p1);
-      __stcs(o + 2 * ps, p2);
-      __stcs(o + 3 * ps, p3);
+      float4 pl[4] = {p0, p1, p2, p3};
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        __stcs(o + k * ps, make_float4(ssf::out_word(pl[k].x, prmt), ssf::out_word(pl[k].y, prmt),
+                                       ssf::out_word(pl[k].z, prmt), ssf::out_word(pl[k].w, prmt)));
     } else {
       float4 a = __ldg(row + (__ldg(tmpl + q) - 1));
-      out[q] = fix_nan ? ssf::fix_re(a.x) : a.x;
-      out[npix + q] = fix_nan ? ssf::fix_im(a.y) : a.y;
-      out[2 * npix + q] = fix_nan ? ssf::fix_re(a.z) : a.z;
-      out[3 * npix + q] = fix_nan ? ssf::fix_im(a.w) : a.w;
+      out[q] = ssf::out_word(fix_nan ? ssf::fix_re(a.x) : a.x, prmt);
+      out[npix + q] = ssf::out_word(fix_nan ? ssf::fix_im(a.y) : a.y, prmt);
+      out[2 * npix + q] = ssf::out_word(fix_nan ? ssf::fix_re(a.z) : a.z, prmt);
+      out[3 * npix + q] = ssf::out_word(fix_nan ? ssf::fix_im(a.w) : a.w, prmt);
     }
   }
 }
@@ -213,17 +225,19 @@ extern "C" int ssf_voronoi_lut(const double *phase, const double *amp, int64_t n
 }
 
 extern "C" int ssf_voronoi_fill(const int32_t *tmpl, const float *lut, int ndir, int64_t npix,
-                                int64_t ncol, float *slab, int fix_nan, void *stream) {
+                                int64_t ncol, float *slab, int fix_nan, int out_flags, void *stream) {
   SSF_REQUIRE(tmpl && lut && slab, "ssf_voronoi_fill: null pointer");
+  ssf::OutFmt fmt;
+  SSF_REQUIRE(ssf::out_fmt(out_flags, &fmt), "ssf_voronoi_fill: unknown out_flags %d", out_flags);
   SSF_REQUIRE(ndir >= 1 && npix >= 1 && ncol >= 0, "ssf_voronoi_fill: bad sizes");
   if (ncol == 0) return SSF_OK;
   bool vec = (npix % 4 == 0) && ((uintptr_t)slab % 16 == 0) && ((uintptr_t)tmpl % 16 == 0);
   if (vec) {
     SSF_LAUNCH(fill_kernel<true>, grid_for(npix / 4 * ncol, 256, 8), 256, 0, (cudaStream_t)stream,
-               tmpl, (const float2 *)lut, ndir, npix, ncol, slab, fix_nan);
+               tmpl, (const float2 *)lut, ndir, npix, ncol, slab, fix_nan, fmt);
   } else {
     SSF_LAUNCH(fill_kernel<false>, grid_for(npix * ncol, 256, 8), 256, 0, (cudaStream_t)stream,
-               tmpl, (const float2 *)lut, ndir, npix, ncol, slab, fix_nan);
+               tmpl, (const float2 *)lut, ndir, npix, ncol, slab, fix_nan, fmt);
   }
   SSF_LAUNCHED();
   return SSF_OK;
@@ -242,18 +256,21 @@ extern "C" int ssf_voronoi_lut_gain(const double *phase, const double *amp, int6
 }
 
 extern "C" int ssf_voronoi_fill_gain(const int32_t *tmpl, const float *lut4, int ndir, int64_t npix,
-                                     int64_t ncol, float *slab, int fix_nan, void *stream) {
+                                     int64_t ncol, float *slab, int fix_nan, int out_flags, void *stream) {
   SSF_REQUIRE(tmpl && lut4 && slab, "ssf_voronoi_fill_gain: null pointer");
+  ssf::OutFmt fmt;
+  SSF_REQUIRE(ssf::out_fmt(out_flags, &fmt) && fmt.planes == 4,
+              "ssf_voronoi_fill_gain: out_flags may only hold SSF_OUT_BIG_ENDIAN (the four planes differ)");
   SSF_REQUIRE(ndir >= 1 && npix >= 1 && ncol >= 0, "ssf_voronoi_fill_gain: bad sizes");
   SSF_REQUIRE((uintptr_t)lut4 % 16 == 0, "ssf_voronoi_fill_gain: lut4 must be 16-byte aligned");
   if (ncol == 0) return SSF_OK;
   bool vec = (npix % 4 == 0) && ((uintptr_t)slab % 16 == 0) && ((uintptr_t)tmpl % 16 == 0);
   if (vec) {
     SSF_LAUNCH(fill_gain_kernel<true>, grid_for(npix / 4 * ncol, 256, 8), 256, 0, (cudaStream_t)stream,
-               tmpl, (const float4 *)lut4, ndir, npix, ncol, slab, fix_nan);
+               tmpl, (const float4 *)lut4, ndir, npix, ncol, slab, fix_nan, fmt.prmt);
   } else {
     SSF_LAUNCH(fill_gain_kernel<false>, grid_for(npix * ncol, 256, 8), 256, 0, (cudaStream_t)stream,
-               tmpl, (const float4 *)lut4, ndir, npix, ncol, slab, fix_nan);
+               tmpl, (const float4 *)lut4, ndir, npix, ncol, slab, fix_nan, fmt.prmt);
   }
   SSF_LAUNCHED();
   return SSF_OK;

@@ -223,12 +223,19 @@ class Engine:
                 # the flagged weights alias the "previous" weights in the reference, so
                 # without order adjustment nothing is refitted (stationscreen.py:694-701)
                 continue
-            pat = cache.lookup(masks)
-            t0 = self.host_tick("pattern_lookup", t0)
             mode = (1 if (it > 0 and adjust_order) else 0) | (2 if amp else 0) | (4 if tec else 0)
-            self.kl_fit_pass(phase, weights, pat, pp, cache.mats, mode, order, station_order, white,
-                             resid, r0, beta, cut, status=self._fit_status[0:1])
-            self.host_tick("fit_pass_launch", t0)
+            # one lookup + fit pass per run of at most max_slots - 1 systems: even if every one
+            # of them had a flag pattern of its own the cache cannot run out of slots inside a
+            # pass (between passes it forgets all patterns but the full one when it has to)
+            step = cache.max_slots - 1
+            for s0 in range(0, nsys, step):
+                s1 = min(nsys, s0 + step)
+                pat = cache.lookup(masks[s0:s1])
+                t0 = self.host_tick("pattern_lookup", t0)
+                self.kl_fit_pass(phase[s0:s1], weights[s0:s1], pat, pp, cache.mats, mode, order[s0:s1],
+                                 station_order[s0:s1], white[s0:s1], resid[s0:s1], r0, beta, cut,
+                                 status=self._fit_status[0:1])
+                t0 = self.host_tick("fit_pass_launch", t0)
         if check:
             self.check_fit_status()
         return white, resid, order
@@ -240,8 +247,10 @@ class Engine:
         self._fit_status.zero_()
         for cache in list(self._caches):
             if cache.counters[2].item():
-                raise _lib.SsfError("ssf_kl_patterns_update", -5, "one fit pass has more distinct flag patterns "
-                                    "than the pattern cache has slots: raise PatternCache(max_bytes=...)")
+                cache.counters[2:3].zero_()
+                raise _lib.SsfError("ssf_kl_patterns_update", -5, "one lookup held more distinct flag patterns "
+                                    "than the pattern cache has slots (systems without a slot were not "
+                                    "fitted): pass at most max_slots - 1 systems per lookup")
         if no_conv:
             raise _lib.SsfError("ssf_kl_decompose", -3, "Jacobi eigen-solver did not converge")
         if bad_w:
@@ -264,17 +273,34 @@ class Engine:
         self._call("ssf_kl_coeffs", _ptr(white), ncol, ndir, _ptr(c), _ptr(g), ldg, self.stream())
         return g
 
-    def kl_eval(self, bt, g, ndir, slab, variant=-1):
+    @staticmethod
+    def out_planes(out_flags):
+        """Planes per column a cube kernel stores for these SSF_OUT_* flags."""
+        return 2 if out_flags & _lib.OUT_PLANES2 else 4
+
+    def kl_eval(self, bt, g, ndir, slab, variant=-1, out_flags=0):
+        """slab: float32 [ncol, 4, npix], or [ncol, 2, npix] with OUT_PLANES2."""
         ncol, ldg = g.shape
         npix = bt.shape[1]
         self._check(slab, torch.float32, "slab")
-        if slab.numel() != ncol * 4 * npix:
+        if slab.numel() != ncol * self.out_planes(out_flags) * npix:
             raise ValueError("slab has the wrong size")
         self._timed_call("kl_eval", "ssf_kl_eval", _ptr(bt), _ptr(g), ndir, ldg, npix, ncol, _ptr(slab), variant,
-                  self.stream())
+                         out_flags, self.stream())
         return slab
 
-    def kl_eval_gain(self, bt, g3, ndir, slab, variant=-1):
+    def kl_eval_tec(self, bt, g, ndir, slab, variant=-1, out_flags=0):
+        """dTEC screens: slab float32 [ncol, npix] = the screen values themselves."""
+        ncol, ldg = g.shape
+        npix = bt.shape[1]
+        self._check(slab, torch.float32, "slab")
+        if slab.numel() != ncol * npix:
+            raise ValueError("slab has the wrong size")
+        self._timed_call("kl_eval", "ssf_kl_eval_tec", _ptr(bt), _ptr(g), ndir, ldg, npix, ncol, _ptr(slab), variant,
+                         out_flags, self.stream())
+        return slab
+
+    def kl_eval_gain(self, bt, g3, ndir, slab, variant=-1, out_flags=0):
         """g3 [ncol, 3, ldg] f32 (phase, Axx, Ayy coefficients) -> gain cube slab."""
         ncol, _, ldg = g3.shape
         npix = bt.shape[1]
@@ -283,7 +309,7 @@ class Engine:
         if slab.numel() != ncol * 4 * npix:
             raise ValueError("slab has the wrong size")
         self._timed_call("kl_eval", "ssf_kl_eval_gain", _ptr(bt), _ptr(g3), ndir, ldg, npix, ncol, _ptr(slab),
-                         variant, self.stream())
+                         variant, out_flags, self.stream())
         return slab
 
     # ------------------------------------------------------------------ Voronoi
@@ -300,15 +326,15 @@ class Engine:
         self._call("ssf_voronoi_lut", _ptr(phase), _ptr(amp), ncol, ndir, _ptr(lut), self.stream())
         return lut
 
-    def voronoi_fill(self, tmpl, lut, slab, fix_nan=True):
+    def voronoi_fill(self, tmpl, lut, slab, fix_nan=True, out_flags=0):
         ncol, ndir, _ = lut.shape
         npix = tmpl.numel()
         self._check(tmpl, torch.int32, "tmpl")
         self._check(slab, torch.float32, "slab")
-        if slab.numel() != ncol * 4 * npix:
+        if slab.numel() != ncol * self.out_planes(out_flags) * npix:
             raise ValueError("slab has the wrong size")
         self._timed_call("voronoi_fill", "ssf_voronoi_fill", _ptr(tmpl), _ptr(lut), ndir, npix, ncol, _ptr(slab),
-                  1 if fix_nan else 0, self.stream())
+                         1 if fix_nan else 0, out_flags, self.stream())
         return slab
 
     def voronoi_lut_gain(self, phase, amp):
@@ -322,7 +348,7 @@ class Engine:
         self._call("ssf_voronoi_lut_gain", _ptr(phase), _ptr(amp), ncol, ndir, _ptr(lut), self.stream())
         return lut
 
-    def voronoi_fill_gain(self, tmpl, lut4, slab, fix_nan=True):
+    def voronoi_fill_gain(self, tmpl, lut4, slab, fix_nan=True, out_flags=0):
         ncol, ndir, _ = lut4.shape
         npix = tmpl.numel()
         self._check(tmpl, torch.int32, "tmpl")
@@ -330,7 +356,7 @@ class Engine:
         if slab.numel() != ncol * 4 * npix:
             raise ValueError("slab has the wrong size")
         self._timed_call("voronoi_fill", "ssf_voronoi_fill_gain", _ptr(tmpl), _ptr(lut4), ndir, npix, ncol,
-                         _ptr(slab), 1 if fix_nan else 0, self.stream())
+                         _ptr(slab), 1 if fix_nan else 0, out_flags, self.stream())
         return slab
 
     def voronoi_indicators(self, tmpl, ndir):
@@ -339,11 +365,13 @@ class Engine:
         self._call("ssf_voronoi_indicators", _ptr(tmpl), ndir, npix, _ptr(ind), self.stream())
         return ind
 
-    def voronoi_contract(self, smoothed_ind, lut, slab, variant=-1):
+    def voronoi_contract(self, smoothed_ind, lut, slab, variant=-1, out_flags=0):
         ncol, ndir, _ = lut.shape
         npix = smoothed_ind.numel() // ndir
+        if slab.numel() != ncol * self.out_planes(out_flags) * npix:
+            raise ValueError("slab has the wrong size")
         self._timed_call("voronoi_contract", "ssf_voronoi_contract", _ptr(smoothed_ind), _ptr(lut), ndir, npix, ncol,
-                  _ptr(slab), variant, self.stream())
+                         _ptr(slab), variant, out_flags, self.stream())
         return slab
 
     def gauss_smooth(self, images, sigma, scratch=None):
@@ -367,7 +395,11 @@ class Engine:
         self._call("ssf_bswap32", _ptr(t), t.numel(), self.stream())
         return t
 
-
+    def copy_rows_d2h(self, dst_host, dst_pitch, src, src_pitch, width_bytes, rows):
+        """ssf_copy_rows_d2h on the current stream: ``rows`` runs of ``width_bytes`` from the
+        device tensor ``src`` to the (pinned) host tensor / address ``dst_host``."""
+        dst = dst_host if isinstance(dst_host, int) else dst_host.data_ptr()
+        self._call("ssf_copy_rows_d2h", dst, dst_pitch, _ptr(src), src_pitch, width_bytes, rows, self.stream())
 
 
 class PatternCache:
@@ -404,6 +436,7 @@ class PatternCache:
         if engine._fit_status is None:
             engine._fit_status = engine.zeros((2,), torch.int32)
         engine._fit_status[1:2] += torch.isnan(self.sv[0]).any().to(torch.int32)
+        engine._caches.add(self)                      # check_fit_status reports this cache's overflow flag
 
     @property
     def mats(self):

@@ -20,6 +20,19 @@ TOL_KL = 1e-5
 TOL_SMOOTH = 1e-6
 
 
+def expect_formats(native, run, planes2=True):
+    """The fused output formats of a cube kernel (SSF_OUT_BIG_ENDIAN, SSF_OUT_PLANES2) against
+    its native 4-plane little-endian output: same values, bit for bit, only stored differently.
+    ``run(out_flags, planes)`` returns the slab as a numpy float32 array [ncol, planes, ...]."""
+    for flags in (1, 2, 3) if planes2 else (1,):
+        planes = 2 if flags & 2 else 4
+        got = run(flags, planes)
+        want = native[:, :planes]
+        if flags & 1:
+            got = got.view(np.uint32).byteswap().view(np.float32)
+        assert np.array_equal(got.view(np.uint32), np.ascontiguousarray(want).view(np.uint32)), flags
+
+
 def make_directions(rng, n_d, spread=2.0):
     return np.column_stack([np.deg2rad(126.23 + rng.uniform(-spread, spread, n_d) / np.cos(np.deg2rad(64.5))),
                             np.deg2rad(64.5 + rng.uniform(-spread, spread, n_d))]).astype(np.float32)
@@ -80,6 +93,49 @@ def check_pattern_cache_decompose(eng, n_d=11, seed=6, max_flagged=3, n_sys=6):
         u_k = cache.u[slot, :n, :n].cpu().numpy()
         signs = np.sign(np.sum(u_k * u_o, axis=0))
         assert np.abs(u_k * signs - u_o).max() < 1e-9
+
+
+def check_pattern_cache_pressure(eng, n_d=8, seed=41):
+    """A pass with far more flagged systems than cache slots: 50 systems that share
+    ONE flag pattern fit in a 4-slot cache, and 12 distinct patterns go through it in runs of
+    max_slots - 1 systems (the cache forgets between runs) -- both equal a roomy cache."""
+    from ska_sdp_screen_fitting_b200.engine import PatternCache
+    rng = np.random.default_rng(seed)
+    pp, _, _ = klfit.piercepoints(make_directions(rng, n_d))
+    ppt = eng.tensor(pp[:, :2], torch.float64)
+    per = (3 * n_d * n_d + n_d) * 8 + 16
+    for n_sys, distinct in ((50, 1), (36, 12)):
+        val = rng.normal(0, 0.3, (n_sys, n_d))
+        weight = np.ones((n_sys, n_d), np.float32)
+        for i in range(n_sys):
+            k = i % distinct
+            weight[i, k % n_d] = 0.0
+            if k >= n_d:
+                weight[i, (k + 3) % n_d] = 0.0
+        so = np.full(n_sys, 4.0)
+        outs = []
+        for max_bytes in (4 * per, 64 << 20):
+            cache = PatternCache(eng, ppt, max_bytes=max_bytes)
+            assert (cache.max_slots == 4) == (max_bytes == 4 * per)
+            w = eng.tensor(weight, torch.float32)
+            white, resid, order = eng.kl_fit(eng.tensor(val, torch.float64), w, eng.tensor(so, torch.float64),
+                                             ppt, cache=cache)
+            outs.append((white.cpu().numpy(), resid.cpu().numpy(), order.cpu().numpy()))
+            assert cache.stats()[1] == 0
+        for a, b in zip(*outs):
+            assert np.array_equal(a, b)
+        assert np.abs(outs[0][0]).max() > 0
+    # a lookup that really holds more patterns than slots: reported, systems without a slot get -1
+    cache = PatternCache(eng, ppt, max_bytes=4 * per)
+    masks = torch.tensor([mask_of([d for d in range(n_d) if d != k]) for k in range(6)], dtype=torch.int64,
+                         device=eng.device)
+    pat = cache.lookup(masks).cpu().numpy()
+    assert cache.stats()[1] == 1 and (pat == -1).sum() == 3 and sorted(pat[pat > 0]) == [1, 2, 3]
+    import pytest
+    from ska_sdp_screen_fitting_b200._lib import SsfError
+    with pytest.raises(SsfError):
+        eng.check_fit_status()
+    eng.check_fit_status()                                   # the flag is cleared by the report
 
 
 def synthetic_fit_case(seed, n_t, n_f, n_a, n_d, flag_fraction=0.03):
@@ -208,6 +264,8 @@ def check_kl_gain_eval(eng, n=24, n_d=9, ncol=7, seed=31, cell=0.1, variant=0):
     want = screens.kl_make_matrix(x, y, pp, white[0], white[1], white[2])
     got = slab.cpu().numpy()
     assert (np.abs(got - want) <= TOL_KL * np.maximum(1.0, np.abs(want))).all()
+    expect_formats(got, lambda flags, planes: eng.kl_eval_gain(
+        bt, g3, n_d, eng.empty((ncol, planes, n, n), torch.float32), variant, flags).cpu().numpy(), planes2=False)
 
 
 def check_kl_eval(eng, n=24, n_d=9, ncol=11, seed=3, variant=0, cell=0.1):
@@ -232,6 +290,15 @@ def check_kl_eval(eng, n=24, n_d=9, ncol=11, seed=3, variant=0, cell=0.1):
     got = slab.cpu().numpy()
     assert np.abs(got - want).max() < TOL_KL
     assert np.array_equal(got[:, 0], got[:, 2]) and np.array_equal(got[:, 1], got[:, 3])
+    expect_formats(got, lambda flags, planes: eng.kl_eval(
+        bt, g, n_d, eng.empty((ncol, planes, n, n), torch.float32), variant, flags).cpu().numpy())
+    # dTEC cube: the screen values themselves (no cos/sin), one plane per column
+    phi = screens.kl_screen_values(x, y, pp, white)
+    for flags in (0, 1):
+        tec = eng.kl_eval_tec(bt, g, n_d, eng.empty((ncol, n, n), torch.float32), variant, flags).cpu().numpy()
+        if flags:
+            tec = tec.view(np.uint32).byteswap().view(np.float32)
+        assert np.abs(tec - phi).max() < TOL_KL * max(1.0, np.abs(phi).max())
     return float(np.abs(got - want).max())
 
 
@@ -254,6 +321,8 @@ def check_voronoi(eng, n=20, n_d=7, ncol=13, seed=9):
         if fix:
             want = screens.nan_fix(want)
         assert np.array_equal(slab.cpu().numpy(), want, equal_nan=True)
+        expect_formats(slab.cpu().numpy(), lambda flags, planes: eng.voronoi_fill(
+            tmpl, lut, eng.empty((ncol, planes, n, n), torch.float32), fix, flags).cpu().numpy())
     return tmpl, lut, want_t, phases
 
 
@@ -274,6 +343,8 @@ def check_voronoi_gain(eng, n=20, n_d=7, ncol=13, seed=19):
         if fix:
             want = screens.nan_fix(want)
         assert np.array_equal(slab.cpu().numpy(), want, equal_nan=True)
+        expect_formats(slab.cpu().numpy(), lambda flags, planes: eng.voronoi_fill_gain(
+            tmpl, lut4, eng.empty((ncol, planes, n, n), torch.float32), fix, flags).cpu().numpy(), planes2=False)
 
 
 def gain_solutions(golden_dir, repo_solutions):
@@ -419,6 +490,8 @@ def check_smoothed_voronoi(eng, n=24, n_d=6, ncol=5, sigma=1.5, seed=4, variant=
     slab2 = eng.empty((ncol, 4, n, n), torch.float32)
     eng.voronoi_contract(ind, lut, slab2, variant)
     assert np.abs(slab2.cpu().numpy() - want).max() < 2 * TOL_SMOOTH
+    expect_formats(slab2.cpu().numpy(), lambda flags, planes: eng.voronoi_contract(
+        ind, lut, eng.empty((ncol, planes, n, n), torch.float32), variant, flags).cpu().numpy())
 
 
 def check_bswap_nanfix(eng, seed=1):

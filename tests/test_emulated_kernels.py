@@ -18,6 +18,10 @@ def test_pattern_cache_warm_started_decompositions(emu_engine):
     pc.check_pattern_cache_decompose(emu_engine, n_d=65, seed=12, max_flagged=2, n_sys=6)
 
 
+def test_pattern_cache_under_pressure(emu_engine):
+    pc.check_pattern_cache_pressure(emu_engine)
+
+
 def test_fit_with_flags_and_outliers(emu_engine):
     pc.check_fit(emu_engine)
 

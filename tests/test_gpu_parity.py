@@ -27,6 +27,10 @@ def test_pattern_cache_warm_started_decompositions(gpu_engine):
     pc.check_pattern_cache_decompose(gpu_engine, n_d=64, seed=13, max_flagged=2, n_sys=6)    # last 256-thread size
 
 
+def test_pattern_cache_under_pressure(gpu_engine):
+    pc.check_pattern_cache_pressure(gpu_engine)
+
+
 def test_fit_tec_type_against_reference_operator_golden(gpu_engine, golden_dir):
     pc.check_fit_tec_golden(gpu_engine, golden_dir)
 
