@@ -29,6 +29,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+sys.path.insert(1, os.path.join(ROOT, "tests"))        # synthetic_cases: the seeded input generator
 
 FIT_AHEAD = 2
 FIT_GROUP = 4      # slabs per fit call of the streaming KL path
@@ -203,7 +204,7 @@ def auto_slots(workload):
 
 
 def build_case(args, rank, total_slots):
-    from ska_sdp_screen_fitting_b200 import synthetic
+    import synthetic_cases as synthetic
 
     kw = {}
     if args.workload == "skalow":
@@ -559,7 +560,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return None
-    from ska_sdp_screen_fitting_b200 import synthetic
+    import synthetic_cases as synthetic
 
     ncpu = os.cpu_count() or 1
     use_kl = args.workload != "voronoi1k"
@@ -649,7 +650,7 @@ def main():
             restore_affinity()
             ncpu = os.cpu_count() or 1
             use_kl = head == "kl"
-            from ska_sdp_screen_fitting_b200 import synthetic
+            import synthetic_cases as synthetic
             n_slots = cpu_slots_for(use_kl, ncpu)
             case = synthetic.make_case(args.workload, seed=3, n_times=n_slots, n_freqs=1,
                                        n_stations=min(4, synthetic.SHAPES[args.workload][0]))

@@ -17,7 +17,8 @@ import torch.distributed as dist
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-from ska_sdp_screen_fitting_b200 import synthetic  # noqa: E402
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import synthetic_cases as synthetic  # noqa: E402
 from ska_sdp_screen_fitting_b200.engine import Engine  # noqa: E402
 from ska_sdp_screen_fitting_b200.kl_screen import KLScreen  # noqa: E402
 from ska_sdp_screen_fitting_b200.voronoi_screen import VoronoiScreen  # noqa: E402

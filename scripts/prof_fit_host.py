@@ -7,9 +7,10 @@ import time
 
 import torch
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-
-from ska_sdp_screen_fitting_b200 import synthetic
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import synthetic_cases as synthetic
 from ska_sdp_screen_fitting_b200.engine import Engine
 from ska_sdp_screen_fitting_b200.kl_screen import KLScreen
 

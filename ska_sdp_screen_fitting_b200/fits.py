@@ -11,10 +11,15 @@ memory and every byte is written once (the reference writes the cube twice,
 screen.py:331-334 then :381-382).
 """
 import os
+import time
 
 import numpy as np
 
 BLOCK = 2880
+try:
+    _IOV_MAX = min(1024, os.sysconf("SC_IOV_MAX"))
+except (ValueError, OSError, AttributeError):        # pragma: no cover
+    _IOV_MAX = 1024
 
 
 def _fmt_float(value):
@@ -135,24 +140,67 @@ class CubeWriter:
         while done < nbytes:                         # pwrite caps at ~2 GiB per call
             done += os.pwrite(self._fd, view[done:done + (1 << 30)], off + done)
 
-    def write_columns(self, c0, slab, already_big_endian=False):
+    def write_columns(self, c0, slab, already_big_endian=False, pairs=False, pool=None):
         """slab: whole (time, freq, antenna) columns -- [ncol, 4, ny, nx] -- starting at the flat
         column index ``c0`` = (t * n_freq + f) * n_ant + a.  The cube is column-major in exactly
-        that order (processing_utils.py:190-194), so any run of columns is one byte range."""
+        that order (processing_utils.py:190-194), so any run of columns is one byte range.
+
+        ``pairs=True``: slab holds only the first half of every column ([ncol, 2, ny, nx]: planes
+        0, 1 of a phase-only cube, whose planes 2, 3 repeat them -- kl_screen.py:368-373); each
+        half is placed twice with one gathered write (``pwritev``), so the copy that crossed
+        PCIe is half the file.  ``pool``: a ThreadPoolExecutor; the columns are split among its
+        workers (``pwrite`` releases the GIL; one thread fills a tmpfs / page cache at only a few
+        GB/s).  Returns the seconds spent writing."""
         arr = np.ascontiguousarray(slab)
         if arr.dtype.itemsize != 4:
             raise TypeError("slab must be a 4-byte type")
         if not already_big_endian:
             arr = arr.astype(">f4", copy=False)
         col_bytes = int(np.prod(self.shape[3:])) * 4
+        src_bytes = col_bytes // 2 if pairs else col_bytes
         nbytes = arr.nbytes
-        if nbytes % col_bytes or c0 * col_bytes + nbytes > self.shape[0] * self._row_bytes:
+        if pairs and col_bytes % 2:
+            raise ValueError("pairs need an even number of planes")
+        if nbytes % src_bytes or (c0 + nbytes // src_bytes) * col_bytes > self.shape[0] * self._row_bytes:
             raise ValueError("slab does not fit the cube")
+        ncol = nbytes // src_bytes
         view = memoryview(arr).cast("B")
-        off = len(self._head) + c0 * col_bytes
-        done = 0
-        while done < nbytes:
-            done += os.pwrite(self._fd, view[done:done + (1 << 30)], off + done)
+        base = len(self._head)
+        fd = self._fd
+
+        def run(lo, hi):
+            if not pairs:
+                off, pos, end = base + (c0 + lo) * col_bytes, lo * col_bytes, hi * col_bytes
+                while pos < end:                         # pwrite caps at ~2 GiB per call
+                    done = os.pwrite(fd, view[pos:min(end, pos + (1 << 30))], off)
+                    pos += done
+                    off += done
+                return
+            per_call = max(1, min(_IOV_MAX // 2, (1 << 30) // col_bytes))
+            for b0 in range(lo, hi, per_call):
+                b1 = min(hi, b0 + per_call)
+                iov = []
+                for c in range(b0, b1):
+                    half = view[c * src_bytes:(c + 1) * src_bytes]
+                    iov += [half, half]
+                off, want = base + (c0 + b0) * col_bytes, (b1 - b0) * col_bytes
+                done = os.pwritev(fd, iov, off)
+                while done < want:                       # short write: finish byte by byte range
+                    c, within = divmod(done, col_bytes)
+                    src = (b0 + c) * src_bytes + within % src_bytes
+                    left = src_bytes - within % src_bytes
+                    done += os.pwrite(fd, view[src:src + left], off + done)
+
+        t_begin = time.perf_counter()
+        workers = getattr(pool, "_max_workers", 1) if pool is not None else 1
+        parts = max(1, min(workers, ncol))
+        if parts == 1:
+            run(0, ncol)
+        else:
+            bounds = [ncol * i // parts for i in range(parts + 1)]
+            for fut in [pool.submit(run, bounds[i], bounds[i + 1]) for i in range(parts)]:
+                fut.result()
+        return time.perf_counter() - t_begin
 
     def close(self):
         if self._fd is not None:

@@ -46,6 +46,18 @@ class Solutions:
     def station_positions(self):
         return [self.station_dict[name] for name in self.ant]
 
+    def rows(self, time_ranges):
+        """The same soltab restricted to the given (start, stop) time-index ranges (views when
+        there is one range)."""
+        if len(time_ranges) == 1:
+            a, b = time_ranges[0]
+            val, weight, time = self.val[a:b], self.weight[a:b], self.time[a:b]
+        else:
+            idx = np.concatenate([np.arange(a, b) for a, b in time_ranges]) if time_ranges else np.arange(0)
+            val, weight, time = self.val[idx], self.weight[idx], self.time[idx]
+        return Solutions(self.soltype, val, weight, time, self.freq, self.ant, self.dir, self.pol,
+                         self.source_dict, self.station_dict)
+
     @classmethod
     def from_arrays(cls, val, weight, time, freq, ant, dirs, source_rad, station_xyz,
                     soltype="phase"):
@@ -62,7 +74,17 @@ def count_directions(filename, solset_name, soltab_name):
         return len(np.asarray(handle[f"{solset_name}/{soltab_name}/dir"]))
 
 
-def read_solutions(filename, solset_name="sol000", soltab_name="phase000"):
+def read_time_axis(filename, solset_name="sol000", soltab_name="phase000"):
+    """The (small) time axis alone: every rank of a time-sharded run reads it in full to agree on
+    the output-file boundaries (screen.py:283-294) before reading its own rows of val/weight."""
+    with h5min.File(filename) as handle:
+        return np.asarray(handle[f"{solset_name}/{soltab_name}/time"].read(), np.float64)
+
+
+def read_solutions(filename, solset_name="sol000", soltab_name="phase000", time_ranges=None):
+    """``time_ranges``: optional list of (start, stop) time-index ranges; only those rows of
+    val / weight are read (each rank reads only its time rows) and ``time`` is
+    restricted to match."""
     with h5min.File(filename) as handle:
         if solset_name not in handle:
             raise KeyError(f"Solution set {solset_name} not found in {filename}")
@@ -80,8 +102,20 @@ def read_solutions(filename, solset_name="sol000", soltab_name="phase000"):
         if missing:
             raise ValueError(f"{soltab_name}: axes {missing} missing (have {axes})")
         perm = [axes.index(a) for a in want]
-        val = np.asarray(val_ds.read()).transpose(perm)
-        weight = np.asarray(wt_ds.read()).transpose(perm)
+        times = np.asarray(tab["time"].read(), np.float64)
+        if time_ranges is None:
+            val = np.asarray(val_ds.read()).transpose(perm)
+            weight = np.asarray(wt_ds.read()).transpose(perm)
+        elif axes[0] == "time":
+            # time-major on disk (what DP3 and LoSoTo write): read just the rows
+            val = np.concatenate([val_ds.read_rows(a, b) for a, b in time_ranges]).transpose(perm)
+            weight = np.concatenate([wt_ds.read_rows(a, b) for a, b in time_ranges]).transpose(perm)
+        else:
+            rows = np.concatenate([np.arange(a, b) for a, b in time_ranges])
+            val = np.asarray(val_ds.read()).transpose(perm)[rows]
+            weight = np.asarray(wt_ds.read()).transpose(perm)[rows]
+        if time_ranges is not None:
+            times = np.concatenate([times[a:b] for a, b in time_ranges]) if time_ranges else times[:0]
         title = tab.attrs.get("TITLE", "phase")
         if isinstance(title, bytes):
             title = title.decode()
@@ -91,7 +125,7 @@ def read_solutions(filename, solset_name="sol000", soltab_name="phase000"):
             soltype=str(title),
             val=np.ascontiguousarray(val),
             weight=np.ascontiguousarray(weight),
-            time=np.asarray(tab["time"].read(), np.float64),
+            time=times,
             freq=np.asarray(tab["freq"].read(), np.float64),
             ant=_text(tab["ant"].read()),
             dir=_text(tab["dir"].read()),

@@ -17,7 +17,7 @@ import time
 import numpy as np
 import torch
 
-from . import wcs
+from . import _lib, wcs
 from .engine import BETA, PINV_CUT, R_0, PatternCache
 from .screen import Screen
 
@@ -79,9 +79,14 @@ class KLScreen(Screen):
         self._pinv_full = None
         self._fit_stream = None
         self._patterns = None
-        self.fit_ahead = 2                # fit groups the streaming fit runs ahead of the evaluation
-        self.fit_group = 4                # slabs fitted per fit call (amortises the per-call host work)
+        self.fit_ahead = 2                # fit blocks the streaming fit runs ahead of the evaluation
+        self.fit_group = 4                # stream_slabs: slabs fitted per fit call (amortises the per-call host work)
+        self.keep_fit_results = True      # streamed write(): bring white / resid / order / weights back to the host
         self._settle = None
+        self._host_sol = None             # (val, weight) host arrays of this rank's time rows
+        self._skip_dev = None
+        self._fitted = None               # results of fit_now()
+        self._streamed = None             # pinned host copies of the results of a streamed write()
 
     # ------------------------------------------------------------------ fit
     def setup(self, sol, antenna_weight_sums=None):
@@ -121,19 +126,23 @@ class KLScreen(Screen):
         self.station_dict = sol.station_dict
         self.station_positions = sol.station_positions
 
-    def fit_device(self, val, weight, check=True):
+    def fit_device(self, val, weight, check=True, skip=None):
         """The per-system part of stationscreen.run for a device slab val [t, f, a, d] f64 /
         weight [t, f, a, d] f32 (any number of time slots).  Returns device tensors
-        (white [t,f,a,d], resid [t,f,a,d], order [t,f,a], weights_out [t,f,a,d])."""
+        (white [t,f,a,d], resid [t,f,a,d], order [t,f,a], weights_out [t,f,a,d]).
+        ``skip`` [f, a] bool: the (freq, station) pairs _process_single_freq leaves out
+        (all-NaN values or all-zero weights over ALL times, stationscreen.py:818-825); when the
+        slab is only part of the time axis the caller passes the global answer."""
         eng = self.engine
         t_host = time.perf_counter()
         n_t, n_f, n_a, n_d = val.shape
         ref_ind = self.ref_ind
         if ref_ind != -1:                                                 # stationscreen.py:994-997
             val = val - val[:, :, ref_ind:ref_ind + 1, :]
-        # stations skipped by _process_single_freq (stationscreen.py:818-825)
-        skip = torch.isnan(val).all(dim=3).all(dim=0) | (weight == 0).all(dim=3).all(dim=0)  # [f, a]
-        skip[:, ref_ind] = True
+        if skip is None:
+            # stations skipped by _process_single_freq (stationscreen.py:818-825)
+            skip = torch.isnan(val).all(dim=3).all(dim=0) | (weight == 0).all(dim=3).all(dim=0)  # [f, a]
+            skip[:, ref_ind] = True
         work_w = torch.where(skip[None, :, :, None], torch.zeros_like(weight), weight).contiguous()
         so = self._so_dev[None, None, :].expand(n_t, n_f, n_a).reshape(-1).contiguous()
         eng.host_tick("fit_prelude", t_host)
@@ -176,53 +185,50 @@ class KLScreen(Screen):
         return (white.view(shape).permute(back).contiguous(), resid.view(shape).permute(back).contiguous(),
                 order, weights_out.permute(back).contiguous())
 
-    def stream_slabs(self, val_dev, wt_dev, slots, ring, cellsize_deg, first=0, count=None):
-        """Streaming form of fit + evaluation for slab-at-a-time processing: yields
-        ``(k, slab)`` for k = first, first+1, ... where slab = ring[k % len(ring)] holds the
-        cube of time slots [k*slots, (k+1)*slots).  The FP64 fit of slab k+1 runs on a side
-        stream while the evaluation kernel of slab k writes the cube (the fit is latency-
-        bound and uses a fraction of the SMs; the evaluation is HBM-bound)."""
+    # ------------------------------------------------------------------ streamed fit
+    def _fit_blocks(self, fetch, bounds, skip=None):
+        """Generator over fitted blocks of time slots, with the fits running ahead of the consumer.
+
+        ``bounds`` = [(r0, r1), ...] row ranges in consumption order; ``fetch(r0, r1)`` returns the
+        device tensors (val [rows, f, a, d] f64, weight f32) of a block and is called on the fit
+        stream by a helper thread (host staging + H2D copy for host-resident solutions, a slice
+        for device-resident ones).  Yields ``(r0, r1, fit)`` with fit = the tuple ``fit_device``
+        returns, after ordering the consumer's current stream behind that block's fit.
+
+        The FP64 fit of the next blocks runs on a high-priority side stream while the consumer's
+        evaluation kernels write the cube (the fit is latency-bound and uses a fraction of the
+        SMs; the evaluation is HBM-bound), up to ``fit_ahead`` blocks in front of it."""
         eng = self.engine
-        n_d = val_dev.shape[-1]
-        total = val_dev.shape[0] // slots
-        last = total if count is None else min(total, first + count)
         if eng.device.type != "cuda":
-            for k in range(first, last):
-                white = self.fit_device(val_dev[k * slots:(k + 1) * slots],
-                                        wt_dev[k * slots:(k + 1) * slots], check=False)[0]
-                slab = ring[k % len(ring)]
-                self._fill_columns(white.view(-1, n_d), slab, cellsize_deg, None, 0.0, True)
-                yield k, slab
+            for r0, r1 in bounds:
+                val, wt = fetch(r0, r1)
+                yield r0, r1, self.fit_device(val, wt, check=False, skip=skip)
             return
         main = torch.cuda.current_stream(eng.device)
         if self._fit_stream is None:
             self._fit_stream = torch.cuda.Stream(eng.device, priority=-1)   # the fit fills freed SM slots first
         side = self._fit_stream
-
         side.wait_stream(main)                           # inputs / setup are ready
-
-        group = max(1, int(self.fit_group))
         state = {"last_done": None, "blocked": False}
 
-        def launch_fit(k0, k1):
-            """One fit call over the time slots of slabs [k0, k1)."""
+        def launch_fit(r0, r1):
             t_host = time.perf_counter()
             with torch.cuda.stream(side):
-                white = self.fit_device(val_dev[k0 * slots:k1 * slots],
-                                        wt_dev[k0 * slots:k1 * slots], check=False)[0]
+                val, wt = fetch(r0, r1)
+                fit = self.fit_device(val, wt, check=False, skip=skip)
                 done = torch.cuda.Event()
                 done.record(side)
             state["last_done"] = done
-            white.record_stream(main)
+            for t in fit:
+                t.record_stream(main)
             self.timings["fit_host_s"] = self.timings.get("fit_host_s", 0.0) + time.perf_counter() - t_host
             self.timings["fit_calls"] = self.timings.get("fit_calls", 0) + 1
-            self.timings["fit_slabs"] = self.timings.get("fit_slabs", 0) + (k1 - k0)
-            return k0, k1, white, done
+            self.timings["fit_rows"] = self.timings.get("fit_rows", 0) + (r1 - r0)
+            return r0, r1, fit, done
 
-        # The fits are issued by a helper thread that runs up to `ahead` groups of `group` slabs
-        # in front of the evaluation: the host-side part of a fit (pattern lookup: one small
-        # blocking D2H per pass, a fixed cost per call whatever the number of systems) is paid
-        # once per group and never keeps the evaluation stream waiting for its next launch.
+        # The fits are issued by a helper thread that runs up to `ahead` blocks in front of the
+        # evaluation: the host side of a fit call (a few dozen launches) never keeps the
+        # evaluation stream waiting for its next launch.
         ahead = max(1, int(self.fit_ahead))
         ready = queue.Queue(maxsize=ahead)
         stop = threading.Event()
@@ -230,8 +236,8 @@ class KLScreen(Screen):
         def issue_fits():
             try:
                 torch.cuda.set_device(eng.device)
-                for k0 in range(first, last, group):
-                    item = launch_fit(k0, min(last, k0 + group))
+                for r0, r1 in bounds:
+                    item = launch_fit(r0, r1)
                     while not stop.is_set():
                         try:
                             ready.put_nowait(item)
@@ -242,13 +248,13 @@ class KLScreen(Screen):
                     state["blocked"] = False
                     if stop.is_set():
                         return
-            except BaseException as exc:  # surfaced in the consumer
+            except BaseException as exc:  # noqa: BLE001 - surfaced in the consumer
                 ready.put(exc)
 
         def settle():
             """Blocks until the helper has issued every fit it may run ahead (or all of them) and
             orders the main stream after the last one: benchmarks call this on both sides of a
-            timed region so that the region contains as many slab fits as slab evaluations."""
+            timed region so that the region contains as many block fits as block evaluations."""
             time.sleep(0.001)            # let the helper notice a slot the consumer just freed
             while helper.is_alive() and not state["blocked"]:
                 time.sleep(0.0002)
@@ -256,52 +262,87 @@ class KLScreen(Screen):
                 main.wait_event(state["last_done"])
 
         self._settle = settle
-
         helper = threading.Thread(target=issue_fits, name="ssf-fit", daemon=True)
         helper.start()
         try:
-            k = first
-            while k < last:
+            for _ in bounds:
                 item = ready.get()
                 if isinstance(item, BaseException):
                     raise item
-                k0, k1, white, done = item
+                r0, r1, fit, done = item
                 main.wait_event(done)
-                white = white.view(k1 - k0, -1, n_d)
-                for k in range(k0, k1):
-                    slab = ring[k % len(ring)]
-                    self._fill_columns(white[k - k0], slab, cellsize_deg, None, 0.0, True)
-                    yield k, slab
-                k = k1
+                yield r0, r1, fit
         finally:
             stop.set()
             helper.join(timeout=30)
             self._settle = None
 
+    def stream_slabs(self, val_dev, wt_dev, slots, ring, cellsize_deg, first=0, count=None, out_flags=0):
+        """Fit + evaluation of device-resident solutions slab by slab: yields ``(k, slab)`` for
+        k = first, first+1, ... where slab = ring[k % len(ring)] holds the cube of time slots
+        [k*slots, (k+1)*slots).  Fits are issued ``fit_group`` slabs at a time (``_fit_blocks``)."""
+        n_d = val_dev.shape[-1]
+        total = val_dev.shape[0] // slots
+        last = total if count is None else min(total, first + count)
+        group = max(1, int(self.fit_group))
+        bounds = [(k0 * slots, min(last, k0 + group) * slots) for k0 in range(first, last, group)]
+
+        def fetch(r0, r1):
+            return val_dev[r0:r1], wt_dev[r0:r1]
+
+        for r0, r1, fit in self._fit_blocks(fetch, bounds):
+            white = fit[0].view((r1 - r0) // slots, -1, n_d)
+            for j in range(white.shape[0]):
+                k = r0 // slots + j
+                slab = ring[k % len(ring)]
+                self._fill_columns(white[j], slab, cellsize_deg, None, 0.0, True, out_flags=out_flags)
+                yield k, slab
+
     def settle_fit_lead(self):
-        """See ``stream_slabs``: no-op unless a streamed run is active."""
+        """See ``_fit_blocks``: no-op unless a streamed run is active."""
         if self._settle is not None:
             self._settle()
 
     def fit(self):
-        """kl_screen.py:61-155 + stationscreen.run (phase type)."""
-        sol = self._load_solutions(self.input_phase_soltab_name)
+        """kl_screen.py:61-155 + stationscreen.run (phase type).
+
+        The per-system fits are DEFERRED: this reads the rank's time rows, fixes everything that is
+        global over time (reference station, stations to skip, per-station orders, pierce points,
+        the decomposition of the full structure matrix) and returns.  ``write()`` then fits block
+        by block on a side stream underneath the evaluation of the previous block; asking for a
+        result first (``vals_ph``, ``residuals``, ``screen_order``, ``weights_out``,
+        ``make_matrix``) runs the whole fit at once (``fit_now``)."""
+        sol, times = self._load_rows(self.input_phase_soltab_name)
         if sol.val.ndim != 4:
             raise NotImplementedError("phase soltabs with a pol axis are not supported (scalarphase only, "
                                       "as the reference's make_matrix assumes: kl_screen.py:263-271)")
         eng = self.engine
-        self.setup(sol)
-        white, resid, order, weights_out = self.fit_device(eng.tensor(sol.val, torch.float64),
-                                                           eng.tensor(sol.weight, torch.float32))
-        self._dev_vals = white
-        self.vals_ph = white.cpu().numpy()
-        self.residuals = resid.cpu().numpy()
-        self.screen_order = order.cpu().numpy()
-        self.weights_out = weights_out.cpu().numpy()
+        val, weight = np.asarray(sol.val), np.asarray(sol.weight)
+        # global over time: per-antenna weight sums (processing_utils.py:560-572) and the
+        # (freq, station) pairs _process_single_freq skips (stationscreen.py:818-825)
+        sums = np.zeros(val.shape[2])
+        all_nan = np.ones(val.shape[1:3], bool)
+        all_zero = np.ones(val.shape[1:3], bool)
+        for t0 in range(0, val.shape[0], 64):
+            sums += np.sum(weight[t0:t0 + 64], axis=(0, 1, 3), dtype=float)
+            all_nan &= np.isnan(val[t0:t0 + 64]).all(axis=(0, 3))
+            all_zero &= (weight[t0:t0 + 64] == 0).all(axis=(0, 3))
+        sums = self._all_reduce(sums, "sum")
+        flags = self._all_reduce(np.stack([all_nan, all_zero]).astype(np.int32), "min").astype(bool)
+        self.setup(sol, antenna_weight_sums=sums)
+        self.times_ph = times
+        skip = flags[0] | flags[1]
+        skip[:, self.ref_ind] = True
+        self._skip_dev = torch.as_tensor(skip).to(eng.device)
+        self._host_sol = (val, weight)
+        self._fitted = None
+        self._streamed = None
         if not self.phase_only:                                           # kl_screen.py:113-126, :135-139
             amp = self._load_solutions(self.input_amplitude_soltab_name)
             if amp.val.ndim != 5 or amp.val.shape[-1] < 2:
                 raise ValueError("amplitude soltab must be [time, freq, ant, dir, pol] with XX and YY")
+            # the slow amplitude table is small and its outlier rms spans all times of a (freq,
+            # station, pol): every rank fits all of it (replicated, deterministic)
             a_white, a_resid, a_order, a_w = self.fit_amplitude_device(eng.tensor(amp.val, torch.float64),
                                                                        eng.tensor(amp.weight, torch.float32))
             self.log_amps = True
@@ -311,6 +352,126 @@ class KLScreen(Screen):
             self.amp_residuals = a_resid.cpu().numpy()
             self.amp_screen_order = a_order.cpu().numpy()
             self.amp_weights_out = a_w.cpu().numpy()
+
+    def _fetch_host(self, r0, r1):
+        """Rows [r0, r1) of the host-resident solutions -> device (pinned staging, async copy on
+        the current stream)."""
+        eng = self.engine
+        val, weight = self._host_sol
+        v = torch.from_numpy(np.ascontiguousarray(val[r0:r1], dtype=np.float64))
+        w = torch.from_numpy(np.ascontiguousarray(weight[r0:r1], dtype=np.float32))
+        if eng.device.type == "cuda":
+            v, w = v.pin_memory(), w.pin_memory()
+        self.timings["h2d_bytes"] = self.timings.get("h2d_bytes", 0) + v.numel() * 8 + w.numel() * 4
+        return v.to(eng.device, non_blocking=True), w.to(eng.device, non_blocking=True)
+
+    def fit_now(self):
+        """Fits all of this rank's time rows at once and keeps the results on the device
+        (``_dev_vals``) and as the reference's host attributes."""
+        if self._fitted is not None:
+            return self._fitted
+        if self._streamed is not None:                       # a streamed write() already fitted everything
+            self._fitted = {k: v.numpy() for k, v in self._streamed.items()}
+            self._fitted["dev"] = None
+            return self._fitted
+        if self._host_sol is None:
+            raise RuntimeError("KLScreen.fit() has not been called")
+        eng = self.engine
+        n_rows = self._host_sol[0].shape[0]
+        parts = []
+        rows = max(1, int(self.block_columns * 4 // max(1, len(self.freqs_ph) * len(self.station_names))))
+        for r0 in range(0, n_rows, rows):
+            v, w = self._fetch_host(r0, min(n_rows, r0 + rows))
+            parts.append(self.fit_device(v, w, check=False, skip=self._skip_dev))
+        eng.check_fit_status()
+        white, resid, order, weights_out = (torch.cat([p[i] for p in parts]) for i in range(4))
+        self._fitted = {"dev": white, "white": white.cpu().numpy(), "resid": resid.cpu().numpy(),
+                        "order": order.cpu().numpy(), "weights": weights_out.cpu().numpy()}
+        return self._fitted
+
+    # the reference's result attributes (kl_screen.py:131-154), computed on first use
+    @property
+    def vals_ph(self):
+        return None if self._host_sol is None else self.fit_now()["white"]
+
+    @vals_ph.setter
+    def vals_ph(self, value):
+        if value is not None:
+            self._fitted = dict(self._fitted or {}, white=value)
+
+    @property
+    def residuals(self):
+        return None if self._host_sol is None else self.fit_now()["resid"]
+
+    @residuals.setter
+    def residuals(self, value):
+        if value is not None:
+            self._fitted = dict(self._fitted or {}, resid=value)
+
+    @property
+    def screen_order(self):
+        return None if self._host_sol is None else self.fit_now()["order"]
+
+    @screen_order.setter
+    def screen_order(self, value):
+        if value is not None:
+            self._fitted = dict(self._fitted or {}, order=value)
+
+    @property
+    def weights_out(self):
+        return None if self._host_sol is None else self.fit_now()["weights"]
+
+    @weights_out.setter
+    def weights_out(self, value):
+        if value is not None:
+            self._fitted = dict(self._fitted or {}, weights=value)
+
+    @property
+    def _dev_vals(self):
+        if self._host_sol is None:
+            return None
+        fitted = self.fit_now()
+        if fitted.get("dev") is None:
+            fitted["dev"] = self.engine.tensor(fitted["white"], torch.float64)
+        return fitted["dev"]
+
+    @_dev_vals.setter
+    def _dev_vals(self, value):
+        pass
+
+    def _blocks(self, local0, local1):
+        """write()'s source of column blocks.  After an eager fit the base class serves the
+        device-resident results; otherwise the blocks are fitted here as they are consumed
+        (``_fit_blocks``), the solutions of each block going host -> device right before its fit,
+        and -- unless ``keep_fit_results`` is off -- the results coming back to pinned host arrays
+        so the reference's attributes exist after the run without a second fit."""
+        if self._fitted is not None and self._fitted.get("white") is not None:
+            yield from super()._blocks(local0, local1)
+            return
+        eng = self.engine
+        n_f, n_a = len(self.freqs_ph), len(self.station_names)
+        per_t = n_f * n_a
+        n_d = self._host_sol[0].shape[-1]
+        n_rows = self._host_sol[0].shape[0]
+        rows = max(1, int(self.block_columns // per_t))
+        bounds = [(r0, min(local1, r0 + rows)) for r0 in range(local0, local1, rows)]
+        keep = None
+        if self.keep_fit_results:
+            if self._streamed is None:
+                pin = eng.device.type == "cuda"
+                self._streamed = {
+                    "white": torch.empty((n_rows, n_f, n_a, n_d), dtype=torch.float64, pin_memory=pin),
+                    "resid": torch.empty((n_rows, n_f, n_a, n_d), dtype=torch.float64, pin_memory=pin),
+                    "order": torch.empty((n_rows, n_f, n_a), dtype=torch.float64, pin_memory=pin),
+                    "weights": torch.empty((n_rows, n_f, n_a, n_d), dtype=torch.float32, pin_memory=pin)}
+            keep = self._streamed
+        for r0, r1, fit in self._fit_blocks(self._fetch_host, bounds, skip=self._skip_dev):
+            white = fit[0]
+            if keep is not None:
+                for name, t in zip(("white", "resid", "order", "weights"), fit):
+                    keep[name][r0:r1].copy_(t, non_blocking=True)
+            amp = None if self.phase_only else self._dev_amp[r0:r1].reshape(-1, n_d, 2)
+            yield r0, r1, white.view(-1, n_d), amp
 
     # ------------------------------------------------------------------ evaluation
     def _prepare(self, cellsize_deg, out_dir):
@@ -324,7 +485,15 @@ class KLScreen(Screen):
                                    self._pp_dev, self._pinv_full, self.r_0, self.beta_val)
         self._basis_key = key
 
-    def _fill_columns(self, cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan, amp=None):
+    def _out_format(self, smooth_pix):
+        # KL screens are never smoothed (make_aterm_images.py:101-103), so the evaluation kernel's
+        # store is the last touch of every value: FITS byte order always, plane pairs when the
+        # solutions are phase-only (planes 2, 3 = planes 0, 1, kl_screen.py:368-373)
+        if self.phase_only:
+            return _lib.OUT_BIG_ENDIAN | _lib.OUT_PLANES2, 2
+        return _lib.OUT_BIG_ENDIAN, 4
+
+    def _fill_columns(self, cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan, amp=None, out_flags=0):
         # smooth_pix is forced to 0 for KL screens by make_aterm_image (make_aterm_images.py:101-103);
         # NaN -> (1, 0) is fused into the store of ssf_kl_eval either way.
         self._prepare(cellsize_deg, out_dir)
@@ -334,9 +503,23 @@ class KLScreen(Screen):
             n_col, n_d = cols.shape
             stacked = torch.stack([cols, amp[..., 0], amp[..., 1]], dim=1).reshape(-1, n_d).contiguous()
             g3 = eng.kl_coeffs(stacked, self._c_full)
-            eng.kl_eval_gain(self._basis, g3.view(n_col, 3, -1), n_d, slab, self.eval_variant)
+            eng.kl_eval_gain(self._basis, g3.view(n_col, 3, -1), n_d, slab, self.eval_variant, out_flags)
             return
-        coeffs = eng.kl_coeffs(cols, self._c_full)
-        eng.kl_eval(self._basis, coeffs, cols.shape[1], slab, self.eval_variant)
+        coeffs = eng.kl_coeffs(cols.contiguous(), self._c_full)
+        eng.kl_eval(self._basis, coeffs, cols.shape[1], slab, self.eval_variant, out_flags)
         if smooth_pix and smooth_pix > 0:
+            if out_flags:
+                raise ValueError("smoothing needs native 4-plane slabs")
             eng.gauss_smooth(slab, smooth_pix)
+
+    def make_tec_matrix(self, t_start_index, t_stop_index, freq_ind, stat_ind, cellsize_deg):
+        """dTEC screens of one (freq, station): float64 [t, ny, nx] -- the screen itself without
+        the cos / sin of make_matrix, i.e. the content of an ``aterm_type="tec"`` cube
+        (processing_utils.py:187-190) for solutions fitted with the tec screen type."""
+        self._prepare(cellsize_deg, None)
+        eng = self.engine
+        n_y, n_x = self.image_shape(cellsize_deg)
+        cols = self._dev_vals[t_start_index:t_stop_index, freq_ind, stat_ind, :].contiguous()
+        out = eng.empty((cols.shape[0], n_y, n_x), torch.float32)
+        eng.kl_eval_tec(self._basis, eng.kl_coeffs(cols, self._c_full), cols.shape[1], out, self.eval_variant)
+        return out.double().cpu().numpy()

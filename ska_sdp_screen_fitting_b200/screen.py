@@ -18,11 +18,15 @@ exchanged.
 """
 import logging
 import os
+import queue
+import threading
+import time
+from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 import torch
 
-from . import fits, wcs
+from . import _lib, fits, wcs
 from .engine import Engine
 
 
@@ -117,8 +121,14 @@ class Screen:
         self.ncpu = None
         # --- engine-side state (not part of the reference's attribute set)
         self.solutions = None            # optional in-memory h5parm_io.Solutions (bypasses file)
-        self.slab_bytes = 2 << 30        # device slab budget for write()
+        self.slab_bytes = 1 << 30        # device slab budget for write() (two slabs are in flight)
+        self.block_columns = 24576       # columns handed to write() at a time by _blocks
+        self.host_buffers = 3            # pinned staging buffers between the copy stream and the file
+        self.write_threads = min(16, os.cpu_count() or 1)   # parallel pwrite calls per staged slab
+        self.sink = "file"               # "null": stop at the pinned host buffer (benchmarks: link vs file system)
         self.timings = {}
+        self._chunks = None              # [(g_start, g_stop, my0, my1, local0)] from _plan_rows
+        self._copy_stream = None
         self._engine = None
         self._dev_vals = None            # device [t, f, a, d] float64: what make_matrix consumes
         self._dev_amp = None             # device [t, f, a, d, 2] float64 (gain solutions only)
@@ -155,7 +165,7 @@ class Screen:
         if self.phase_only:
             return
         vals_amp = np.asarray(self.vals_amp)
-        n_t, n_f = self.vals_ph.shape[0], self.vals_ph.shape[1]
+        n_t, n_f = len(self.times_ph), len(self.freqs_ph)
         if len(self.times_amp) == 1:
             # a single time: the values are repeated as needed (numpy.resize semantics, :121-126)
             new_shape = list(vals_amp.shape)
@@ -169,7 +179,9 @@ class Screen:
                 logvals = _interp_axis(self.freqs_amp, logvals, 1, self.freqs_ph, interp_kind)
             vals_amp = logvals if self.log_amps else 10 ** logvals
         self.vals_amp = vals_amp
-        self._dev_amp = self.engine.tensor(np.ascontiguousarray(vals_amp[..., :2]), torch.float64)
+        # the cube kernels read this rank's time rows only
+        local = vals_amp if self._chunks is None or _dist_info()[1] == 1 else vals_amp[self._local_rows()]
+        self._dev_amp = self.engine.tensor(np.ascontiguousarray(local[..., :2]), torch.float64)
 
     def get_memory_usage(self, cellsize_deg):
         """GB of HOST memory per time slot.  The reference's estimates (kl_screen.py:157-190,
@@ -190,9 +202,10 @@ class Screen:
         self._fill_columns(cols, slab, cellsize_deg, out_dir, smooth_pix=0.0, fix_nan=False, amp=amp)
         return slab.double().cpu().numpy()
 
-    def _fill_columns(self, cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan, amp=None):
+    def _fill_columns(self, cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan, amp=None, out_flags=0):
         """cols: device [ncol, ndir] float64; amp: device [ncol, ndir, 2] float64 (XX, YY) for
-        gain solutions; slab: device float32 [ncol, 4, ny, nx]."""
+        gain solutions; slab: device float32 [ncol, 4, ny, nx] ([ncol, 2, ny, nx] with
+        OUT_PLANES2 in ``out_flags``, one of the formats ``_out_format`` offered)."""
         raise NotImplementedError
 
     def _prepare(self, cellsize_deg, out_dir):
@@ -204,82 +217,231 @@ class Screen:
         self.fit()
         self.interpolate()
 
+    # ------------------------------------------------------------------ time rows of this rank
+    def _plan_rows(self, times):
+        """Output-file chunks (screen.py:283-294) and this rank's share of each: with
+        ``torch.distributed`` initialised every rank owns a contiguous run of the time slots of
+        every file.  Sets ``_chunks`` = [(g_start, g_stop, my0, my1, local0)] and
+        returns the rank's (start, stop) global time ranges; the rank's LOCAL time index runs
+        over the concatenation of those ranges."""
+        rank, world, _ = _dist_info()
+        chunks, ranges, g_start, local = [], [], 0, 0
+        for g_stop in time_chunks(times):
+            my0, my1 = split_range(g_start, g_stop, world, rank)
+            chunks.append((g_start, g_stop, my0, my1, local))
+            ranges.append((my0, my1))
+            local += my1 - my0
+            g_start = g_stop
+        self._chunks = chunks
+        return ranges
+
+    def _load_rows(self, soltab_name):
+        """(Solutions restricted to this rank's time rows, full time axis)."""
+        if self.solutions is not None:
+            sol = self.solutions[soltab_name] if isinstance(self.solutions, dict) else self.solutions
+            times = np.asarray(sol.time, np.float64)
+            ranges = self._plan_rows(times)
+            return (sol if _dist_info()[1] == 1 else sol.rows(ranges)), times
+        from .h5parm_io import read_solutions, read_time_axis
+        times = read_time_axis(self.input_h5parm_filename, self.input_solset_name, soltab_name)
+        ranges = self._plan_rows(times)
+        if _dist_info()[1] == 1:
+            ranges = None
+        return read_solutions(self.input_h5parm_filename, self.input_solset_name, soltab_name,
+                              time_ranges=ranges), times
+
+    def _local_rows(self):
+        """Global time index of every local row."""
+        return np.concatenate([np.arange(c[2], c[3]) for c in self._chunks]) if self._chunks else np.arange(0)
+
+    @staticmethod
+    def _all_reduce(array, op="sum"):
+        """Element-wise reduction of a small host array over the ranks (metadata only)."""
+        _, world, dist = _dist_info()
+        if world == 1:
+            return array
+        t = torch.as_tensor(np.ascontiguousarray(array))
+        if dist.get_backend() == "nccl":
+            t = t.cuda()
+        dist.all_reduce(t, op={"sum": dist.ReduceOp.SUM, "min": dist.ReduceOp.MIN}[op])
+        return t.cpu().numpy()
+
     # ------------------------------------------------------------------ write
-    def slab_columns(self, cellsize_deg):
+    def slab_columns(self, cellsize_deg, planes=4):
         """(time, freq, antenna) columns per device slab.  A slab is a run of whole columns, not
         of whole time slots: one SKA-Low time slot (32 freqs x 512 stations x 2048^2) is 1.1 TB."""
         n_y, n_x = self.image_shape(cellsize_deg)
-        return max(1, int(self.slab_bytes // (16 * n_y * n_x)))
+        return max(1, int(self.slab_bytes // (4 * planes * n_y * n_x)))
+
+    def _out_format(self, smooth_pix):
+        """(out_flags the slab kernels of this run fuse into their stores, planes stored per
+        column).  Subclasses widen this; the base asks for native 4-plane slabs and a separate
+        byte-swap pass."""
+        return 0, 4
+
+    def _blocks(self, local0, local1):
+        """Yields ``(r0, r1, cols, amp)`` for runs of this rank's local time rows [r0, r1) in
+        [local0, local1): cols = device float64 [(r1 - r0) * n_freq * n_ant, n_dir] of the values
+        the cube kernels consume (whitened screens / referenced phases), amp = the matching
+        [.., n_dir, 2] amplitudes of gain solutions or None.  The base serves them from the
+        device-resident result of an eager fit(); KLScreen overrides it with the streamed fit."""
+        per_t = len(self.freqs_ph) * len(self.station_names)
+        n_d = self._dev_vals.shape[-1]
+        rows = max(1, int(self.block_columns // per_t))
+        for r0 in range(local0, local1, rows):
+            r1 = min(local1, r0 + rows)
+            cols = self._dev_vals[r0:r1].reshape(-1, n_d)
+            amp = None if self.phase_only else self._dev_amp[r0:r1].reshape(-1, n_d, 2)
+            yield r0, r1, cols, amp
 
     def write(self, out_dir, cellsize_deg, smooth_pix=0, ncpu=0):
         """Writes ``{name}_{g}.fits`` per gap-free time chunk and ``{name}.txt``
-        (screen.py:260-394)."""
+        (screen.py:260-394).
+
+        Pipeline per device slab (a run of (time, freq, antenna) columns): the cube kernels write
+        it in FITS byte order (and, for phase-only solutions, as plane pairs) on the main stream;
+        a copy stream moves it to one of ``host_buffers`` pinned staging buffers as soon as it is
+        complete, while the next slab is computed into the other device buffer; a flusher thread
+        places each staged slab at its byte offset of the output file with ``write_threads``
+        parallel gathered writes.  KL screens fit the next block of time slots on a third stream
+        meanwhile (KLScreen._blocks)."""
         self.ncpu = ncpu
+        t_write = time.perf_counter()
         rank, world, dist = _dist_info()
         eng = self.engine
+        cuda = eng.device.type == "cuda"
         n_y, n_x = self.image_shape(cellsize_deg)
+        npix = n_y * n_x
         n_f, n_a = len(self.freqs_ph), len(self.station_names)
-        times = np.asarray(self.times_ph, np.float64)
-        self._prepare(cellsize_deg, out_dir)
-        step = self.slab_columns(cellsize_deg)
         per_t = n_f * n_a
-        n_d = self._dev_vals.shape[-1]
-        flat_vals = self._dev_vals.reshape(-1, n_d)
-        flat_amp = None if self.phase_only else self._dev_amp.reshape(-1, n_d, 2)
-        pinned = [None, None]
+        times = np.asarray(self.times_ph, np.float64)
+        if self._chunks is None:
+            self._plan_rows(times)
+        t0 = time.perf_counter()
+        self._prepare(cellsize_deg, out_dir)
+        if cuda:
+            torch.cuda.synchronize(eng.device)
+        self.timings["prepare_s"] = time.perf_counter() - t0
+        out_flags, planes = self._out_format(smooth_pix)
+        fused_swap = bool(out_flags & _lib.OUT_BIG_ENDIAN)
+        step = self.slab_columns(cellsize_deg, planes)
+        # never allocate more than the rank's largest chunk needs
+        most = max([(c[3] - c[2]) * per_t for c in self._chunks] + [1])
+        step = min(step, most)
+        slab_elems = step * planes * npix
+        dev_ring = [eng.empty((slab_elems,), torch.float32) for _ in range(2)]
+        n_host = max(2, int(self.host_buffers))
+        host_ring = [torch.empty(slab_elems, dtype=torch.float32, pin_memory=cuda) for _ in range(n_host)]
+        host_free = queue.Queue()
+        for i in range(n_host):
+            host_free.put(i)
+        main = torch.cuda.current_stream(eng.device) if cuda else None
+        if cuda and self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(eng.device)
+        copied = [None, None]
+        stats = {"pwrite_s": 0.0, "file_bytes": 0, "d2h_bytes": 0, "slabs": 0, "flush_wait_s": 0.0}
+        flush_q = queue.Queue()
+        failure = []
+        pool = ThreadPoolExecutor(max(1, int(self.write_threads))) if self.sink == "file" else None
+
+        def flusher():
+            while True:
+                item = flush_q.get()
+                try:
+                    if item is None:
+                        return
+                    writer, col_rel, hb, ncol, event = item
+                    try:
+                        if event is not None:
+                            event.synchronize()
+                        if writer is not None and not failure:
+                            data = host_ring[hb][:ncol * planes * npix].numpy().view(">f4")
+                            stats["pwrite_s"] += writer.write_columns(col_rel, data, already_big_endian=True,
+                                                                      pairs=planes == 2, pool=pool)
+                            stats["file_bytes"] += ncol * 16 * npix
+                    except BaseException as exc:  # noqa: BLE001 - surfaced by the caller
+                        failure.append(exc)
+                    finally:
+                        host_free.put(hb)
+                finally:
+                    flush_q.task_done()
+
+        thread = threading.Thread(target=flusher, name="ssf-flush", daemon=True)
+        thread.start()
         outfiles = []
-        g_start = 0
         voxels = 0
-        for gnum, g_stop in enumerate(time_chunks(times)):
-            outfile = os.path.join(out_dir, f"{self.name}_{gnum}.fits")
-            shape = (g_stop - g_start, n_f, n_a, 4, n_y, n_x)
-            cards = fits.aterm_cards(shape, self.rad, self.dec, cellsize_deg, self.freqs_ph,
-                                     times[g_start:g_stop])
-            if rank == 0:
-                writer = fits.CubeWriter(outfile, shape, cards)
-            if dist is not None:
-                dist.barrier()
-            if rank != 0:
-                writer = fits.CubeWriter(outfile, shape, cards, create=False)
-            my0, my1 = split_range(g_start, g_stop, world, rank)
-            pending = None
-            buf = 0
-            for c0 in range(my0 * per_t, my1 * per_t, step):
-                c1 = min(my1 * per_t, c0 + step)
-                cols = flat_vals[c0:c1]
-                amp = None if flat_amp is None else flat_amp[c0:c1]
-                slab = eng.empty((cols.shape[0], 4, n_y, n_x), torch.float32)
-                self._fill_columns(cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan=True, amp=amp)
-                eng.bswap32(slab)
-                if pinned[buf] is None or pinned[buf].numel() < slab.numel():
-                    pinned[buf] = torch.empty(slab.numel(), dtype=torch.float32,
-                                              pin_memory=eng.device.type == "cuda")
-                host = pinned[buf][:slab.numel()]
-                host.copy_(slab.view(-1), non_blocking=True)
-                event = None
-                if eng.device.type == "cuda":
-                    event = torch.cuda.Event()
-                    event.record()
-                if pending is not None:
-                    self._flush(writer, *pending)
-                pending = (c0 - g_start * per_t, host, event)
-                buf ^= 1
-                voxels += cols.shape[0] * n_y * n_x
-            if pending is not None:
-                self._flush(writer, *pending)
-            writer.close()
-            outfiles.append(outfile)
-            g_start = g_stop
+        k = 0
+        try:
+            for gnum, (g_start, g_stop, my0, my1, local0) in enumerate(self._chunks):
+                outfile = os.path.join(out_dir, f"{self.name}_{gnum}.fits")
+                outfiles.append(outfile)
+                writer = None
+                if self.sink == "file":
+                    shape = (g_stop - g_start, n_f, n_a, 4, n_y, n_x)
+                    cards = fits.aterm_cards(shape, self.rad, self.dec, cellsize_deg, self.freqs_ph,
+                                             times[g_start:g_stop])
+                    if rank == 0:
+                        writer = fits.CubeWriter(outfile, shape, cards)
+                    if dist is not None:
+                        dist.barrier()
+                    if rank != 0:
+                        writer = fits.CubeWriter(outfile, shape, cards, create=False)
+                for r0, _r1, cols_all, amp_all in self._blocks(local0, local0 + (my1 - my0)):
+                    col_base = (my0 - g_start + (r0 - local0)) * per_t     # first column of the block in the file
+                    for c0 in range(0, cols_all.shape[0], step):
+                        if failure:
+                            raise failure[0]
+                        c1 = min(cols_all.shape[0], c0 + step)
+                        ncol = c1 - c0
+                        b = k & 1
+                        if copied[b] is not None:
+                            main.wait_event(copied[b])           # slab b has left the device
+                        slab = dev_ring[b][:ncol * planes * npix].view(ncol, planes, n_y, n_x)
+                        self._fill_columns(cols_all[c0:c1], slab, cellsize_deg, out_dir, smooth_pix, fix_nan=True,
+                                           amp=None if amp_all is None else amp_all[c0:c1], out_flags=out_flags)
+                        if not fused_swap:
+                            eng.bswap32(slab)
+                        t_wait = time.perf_counter()
+                        hb = host_free.get()                     # a staging buffer the flusher is done with
+                        stats["flush_wait_s"] += time.perf_counter() - t_wait
+                        nbytes = ncol * planes * npix * 4
+                        event = None
+                        if cuda:
+                            done = torch.cuda.Event()
+                            done.record(main)
+                            with torch.cuda.stream(self._copy_stream):
+                                self._copy_stream.wait_event(done)
+                                eng.copy_rows_d2h(host_ring[hb], nbytes, slab, nbytes, nbytes, 1)
+                                event = torch.cuda.Event()
+                                event.record(self._copy_stream)
+                            copied[b] = event
+                        else:
+                            host_ring[hb][:ncol * planes * npix].copy_(slab.view(-1))
+                        flush_q.put((writer, col_base + c0, hb, ncol, event))
+                        stats["d2h_bytes"] += nbytes
+                        stats["slabs"] += 1
+                        voxels += ncol * npix
+                        k += 1
+                flush_q.join()
+                if writer is not None:
+                    writer.close()
+                if failure:
+                    raise failure[0]
+        finally:
+            flush_q.put(None)
+            thread.join(timeout=60)
+            if pool is not None:
+                pool.shutdown(wait=True)
+        if cuda:
+            torch.cuda.synchronize(eng.device)
+        eng.check_fit_status()                                   # deferred checks of the streamed fit
         if dist is not None:
             dist.barrier()
-        self.timings["voxels_written"] = voxels
-        if rank == 0:
+        if rank == 0 and self.sink == "file":
             with open(os.path.join(out_dir, f"{self.name}.txt"), "w", encoding="utf8") as handle:
                 handle.writelines([o + "\n" for o in outfiles])
+        stats.update(voxels_written=voxels, write_s=time.perf_counter() - t_write, planes_copied=planes,
+                     out_flags=out_flags, columns_per_slab=step, host_buffers=n_host,
+                     write_threads=int(self.write_threads) if pool is not None else 0, sink=self.sink)
+        self.timings.update(stats)
         return outfiles
-
-    @staticmethod
-    def _flush(writer, col_rel, host, event):
-        if event is not None:
-            event.synchronize()
-        writer.write_columns(col_rel, host.numpy().view(">f4"), already_big_endian=True)

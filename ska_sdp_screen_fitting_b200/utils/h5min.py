@@ -16,6 +16,7 @@ parser of the on-disk format:
 
 Anything else raises ``H5FormatError`` -- loudly, never a silent wrong read.
 """
+import mmap
 import struct
 import zlib
 
@@ -122,6 +123,27 @@ class Dataset(_Node):
             out = self._f._read_chunked(self)
         return out.reshape(self.shape)
 
+    def read_rows(self, start, stop):
+        """Rows [start, stop) of the leading axis only: a rank of a time-sharded run reads just
+        its own time slots (the file is memory-mapped, so nothing else is touched; chunked
+        datasets decode only the chunks that overlap the range)."""
+        if not self.shape:
+            raise IndexError("scalar dataset has no rows")
+        start, stop = max(0, int(start)), min(int(stop), self.shape[0])
+        stop = max(start, stop)
+        row = int(np.prod(self.shape[1:], dtype=np.int64))
+        shape = (stop - start,) + tuple(self.shape[1:])
+        kind = self._layout[0]
+        if kind == "contiguous":
+            _, addr, _size = self._layout
+            if addr == _UNDEF:
+                return np.zeros(shape, dtype=self.dtype)
+            return np.frombuffer(self._f._buf, dtype=self.dtype, count=(stop - start) * row,
+                                 offset=addr + start * row * self.dtype.itemsize).copy().reshape(shape)
+        if kind == "compact":
+            return self.read()[start:stop]
+        return self._f._read_chunked(self, rows=(start, stop))
+
     def __getitem__(self, key):
         return self.read()[key]
 
@@ -137,8 +159,13 @@ class File(Group):
     """``File(path)`` -> root group; ``f["sol000/phase000/val"].read()``."""
 
     def __init__(self, path):
+        # memory-mapped, read-only: opening costs nothing and a reader touches only the pages
+        # of the datasets (or rows, Dataset.read_rows) it asks for
         with open(path, "rb") as fh:
-            self._buf = fh.read()
+            try:
+                self._buf = mmap.mmap(fh.fileno(), 0, access=mmap.ACCESS_READ)
+            except (ValueError, OSError):            # empty file / no mmap on this file system
+                self._buf = fh.read()
         self.filename = path
         base = 0
         while base < len(self._buf) and self._buf[base:base + 8] != _SIG:
@@ -160,12 +187,20 @@ class File(Group):
         Group.__init__(self, self, "/", root_addr)
 
     def close(self):
-        pass
+        # arrays handed out are copies, so the mapping can go (numpy views of it would keep it alive)
+        self._cache = {}
+        if isinstance(self._buf, mmap.mmap):
+            try:
+                self._buf.close()
+            except BufferError:                      # an exported view is still alive
+                pass
+        self._buf = b""
 
     def __enter__(self):
         return self
 
     def __exit__(self, *exc):
+        self.close()
         return False
 
     # ------------------------------------------------------------------ primitives
@@ -220,7 +255,7 @@ class File(Group):
             raise H5FormatError("bad local heap")
         data_addr = self._uint(buf, heap_addr + 8 + 2 * self._sl, self._so)
         start = data_addr + off
-        end = buf.index(b"\0", start)
+        end = buf.find(b"\0", start)
         return buf[start:end].decode("utf8")
 
     def _read_symbol_table(self, btree, heap):
@@ -413,17 +448,20 @@ class File(Group):
         return name, (val[0] if not shape else val.copy().reshape(shape))
 
     # -------------------------------------------------------------- chunked read
-    def _read_chunked(self, ds):
+    def _read_chunked(self, ds, rows=None):
         _, btree, cdims = ds._layout
         rank = len(ds.shape)
         chunk_shape = cdims[:rank]
-        out = np.zeros(ds.shape, dtype=ds.dtype)
+        r0, r1 = (0, ds.shape[0]) if rows is None else rows
+        out = np.zeros((r1 - r0,) + tuple(ds.shape[1:]), dtype=ds.dtype)
         if btree == _UNDEF:
             return out
         chunks = []
         self._walk_chunk_btree(btree, rank, chunks)
         itemsize = ds.dtype.itemsize
         for size, mask, offs, addr in chunks:
+            if offs[0] >= r1 or offs[0] + chunk_shape[0] <= r0:
+                continue                             # no row of the requested range in this chunk
             raw = self._buf[addr:addr + size]
             for idx, (fid, cd) in reversed(list(enumerate(ds._filters))):
                 if mask & (1 << idx):
@@ -442,10 +480,14 @@ class File(Group):
             block = np.frombuffer(raw, dtype=ds.dtype,
                                   count=int(np.prod(chunk_shape))).reshape(chunk_shape)
             sl_out, sl_in = [], []
-            for o, c, n in zip(offs, chunk_shape, ds.shape):
-                hi = min(o + c, n)
-                sl_out.append(slice(o, hi))
-                sl_in.append(slice(0, hi - o))
+            for axis, (o, c, n) in enumerate(zip(offs, chunk_shape, ds.shape)):
+                lo, hi = o, min(o + c, n)
+                if axis == 0:
+                    lo, hi = max(lo, r0), min(hi, r1)
+                    sl_out.append(slice(lo - r0, hi - r0))
+                else:
+                    sl_out.append(slice(lo, hi))
+                sl_in.append(slice(lo - o, hi - o))
             out[tuple(sl_out)] = block[tuple(sl_in)]
         return out
 

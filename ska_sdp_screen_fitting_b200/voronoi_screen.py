@@ -13,9 +13,9 @@ import os
 import numpy as np
 import torch
 
-from . import fits, skymodel, template, wcs
+from . import _lib, fits, skymodel, template, wcs
 from .kl_screen import reference_station
-from .screen import Screen
+from .screen import Screen, _dist_info
 
 
 class VoronoiScreen(Screen):
@@ -43,17 +43,21 @@ class VoronoiScreen(Screen):
 
     def fit(self):
         """voronoi_screen.py:57-102: no fitting, the phases are referenced to one station."""
-        sol = self._load_solutions(self.input_phase_soltab_name)
+        sol, times = self._load_rows(self.input_phase_soltab_name)
         if sol.val.ndim != 4:
             raise NotImplementedError("phase soltabs with a pol axis are not supported (scalarphase only, "
                                       "as in the reference: voronoi_screen.py:69-70)")
         eng = self.engine
-        ref_ind = reference_station(sol.weight, 10)
+        # the reference station is global over time (processing_utils.py:560-572): per-antenna
+        # weight sums of this rank's rows, summed over the ranks
+        sums = self._all_reduce(np.sum(np.asarray(sol.weight), axis=(0, 1, 3), dtype=float), "sum")[:10]
+        ref_ind = int(np.nonzero(sums == sums.max())[0][0])
         val = eng.tensor(sol.val, torch.float64)
         self._dev_vals = (val - val[:, :, ref_ind:ref_ind + 1, :]).contiguous()
-        self._has_nan = bool(np.isnan(np.asarray(sol.val)).any())
+        has_nan = np.array([int(np.isnan(np.asarray(sol.val)).any())], np.int32)
+        self._has_nan = bool(-self._all_reduce(-has_nan, "min")[0])          # max over the ranks
         self.vals_ph = self._dev_vals.cpu().numpy()
-        self.times_ph = sol.time
+        self.times_ph = times
         self.freqs_ph = sol.freq
         if self.phase_only:
             self.vals_amp = np.ones_like(self.vals_ph)
@@ -90,7 +94,7 @@ class VoronoiScreen(Screen):
         eng = self.engine
         n_y, n_x = self.image_shape(cellsize_deg)
         ra_deg, dec_deg = self._patch_radec()
-        if out_dir is not None:
+        if out_dir is not None and _dist_info()[0] == 0:     # one writer: rank 0
             shape = (1, len(self.freqs_ph), len(self.station_names), 4, n_y, n_x)
             cards = fits.aterm_cards(shape, self.rad, self.dec, cellsize_deg, self.freqs_ph,
                                      np.asarray(self.times_ph)[0:1])
@@ -126,7 +130,31 @@ class VoronoiScreen(Screen):
         return self._ind_dev
 
     # ------------------------------------------------------------------ fill
-    def _fill_columns(self, cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan, amp=None):
+    def _use_linear(self, smooth_pix, cols=None):
+        """Whether a smoothed slab takes the linear (contraction) form."""
+        if not (bool(smooth_pix) and smooth_pix > 0) or not self.phase_only:
+            return False
+        if self.smooth_mode != "auto":
+            return self.smooth_mode == "linear"
+        has_nan = self._has_nan
+        if has_nan is None:
+            has_nan = cols is None or bool(torch.isnan(cols).any().item())
+        # tiny images (the repo's 17 x 17 test geometry) stay on the reference's own order of
+        # operations: nothing to gain there, and it is the tighter parity
+        return (not has_nan) and self._tmpl_dev.numel() >= 128 * 128
+
+    def _out_format(self, smooth_pix):
+        # the fill and the linear smoothed form store final values: FITS byte order, and plane
+        # pairs for phase-only solutions (planes 2, 3 = planes 0, 1, voronoi_screen.py:194-198).
+        # The direct smoothing path filters native 4-plane slabs in place and swaps afterwards.
+        smooth = bool(smooth_pix) and smooth_pix > 0
+        if smooth and not self._use_linear(smooth_pix):
+            return 0, 4
+        if self.phase_only:
+            return _lib.OUT_BIG_ENDIAN | _lib.OUT_PLANES2, 2
+        return _lib.OUT_BIG_ENDIAN, 4
+
+    def _fill_columns(self, cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan, amp=None, out_flags=0):
         self._prepare(cellsize_deg, out_dir)
         eng = self.engine
         npix = self._tmpl_dev.numel()
@@ -135,25 +163,23 @@ class VoronoiScreen(Screen):
             # gain solutions: XX / YY amplitudes on planes 0-1 / 2-3 (voronoi_screen.py:177-214);
             # smoothing in the reference's own order of operations (screen.py:353-378)
             lut4 = eng.voronoi_lut_gain(cols.contiguous(), amp.contiguous())
-            eng.voronoi_fill_gain(self._tmpl_dev, lut4, slab, fix_nan=fix_nan and not smooth)
+            if smooth and out_flags:
+                raise ValueError("the direct smoothing path needs native 4-plane slabs")
+            eng.voronoi_fill_gain(self._tmpl_dev, lut4, slab, fix_nan=fix_nan and not smooth, out_flags=out_flags)
             if smooth:
                 eng.gauss_smooth(slab, smooth_pix)
                 if fix_nan:
                     eng.nan_fix(slab, cols.shape[0], npix)
             return
-        lut = eng.voronoi_lut(cols)
-        linear = self.smooth_mode == "linear"
-        if smooth and self.smooth_mode == "auto":
-            has_nan = self._has_nan if self._has_nan is not None else bool(torch.isnan(cols).any().item())
-            # tiny images (the repo's 17 x 17 test geometry) stay on the reference's own order
-            # of operations: nothing to gain there, and it is the tighter parity
-            linear = (not has_nan) and npix >= 128 * 128
-        if smooth and linear:
-            eng.voronoi_contract(self._smoothed_indicators(smooth_pix), lut, slab)
+        lut = eng.voronoi_lut(cols.contiguous())
+        if smooth and self._use_linear(smooth_pix, cols):
+            eng.voronoi_contract(self._smoothed_indicators(smooth_pix), lut, slab, out_flags=out_flags)
         elif smooth:
+            if out_flags:
+                raise ValueError("the direct smoothing path needs native 4-plane slabs")
             eng.voronoi_fill(self._tmpl_dev, lut, slab, fix_nan=False)
             eng.gauss_smooth(slab, smooth_pix)
             if fix_nan:
                 eng.nan_fix(slab, cols.shape[0], npix)
         else:
-            eng.voronoi_fill(self._tmpl_dev, lut, slab, fix_nan=fix_nan)
+            eng.voronoi_fill(self._tmpl_dev, lut, slab, fix_nan=fix_nan, out_flags=out_flags)

@@ -532,3 +532,73 @@ def check_raw_contraction(eng, npix=1024, n_d=45, ncol=70, seed=11, variant=1):
     assert np.all(got[-1, 0] == 1.0)                          # NaN column -> NaN fix (1, .)
     assert np.array_equal(got[:, 0], got[:, 2]) and np.array_equal(got[:, 1], got[:, 3])
     return float(err_re.max())
+
+
+def check_streamed_write(eng, tmp_path, n_pix=16, shape="tiny", n_times=None, smooth=1.5, cellsize=None):
+    """The API path: ``process()`` + ``write()`` streams (KL: the fit of the next block of time
+    slots runs beside the evaluation; all screens: fused big-endian / plane-pair stores, D2H on a
+    copy stream, parallel gathered file writes).  The cube must equal, byte for byte, the one
+    written after an eager fit through native 4-plane slabs and the separate swap pass -- and the
+    fit results kept from the streamed run must equal the eager ones."""
+    import synthetic_cases
+    from ska_sdp_screen_fitting_b200 import _lib, fits
+    from ska_sdp_screen_fitting_b200.kl_screen import KLScreen
+    from ska_sdp_screen_fitting_b200.voronoi_screen import VoronoiScreen
+
+    case = synthetic_cases.make_case(shape, seed=11, n_pix=n_pix, n_times=n_times, cellsize_deg=cellsize)
+    case.solutions.time[-2:] += 300.0                       # a gap: two output files
+    n_f, n_a = len(case.solutions.freq), len(case.solutions.ant)
+
+    def build(cls, name):
+        scr = cls(name, None, None, case.rad, case.dec, case.width_deg, case.width_deg)
+        scr._engine = eng
+        scr.solutions = case.solutions
+        if cls is VoronoiScreen:
+            scr.patch_radec = case.patch_radec
+            scr.template_mode = "nearest"
+        scr.process()
+        return scr
+
+    def same_files(a, b):
+        for fa, fb in zip(a, b):
+            with open(fa, "rb") as ha, open(fb, "rb") as hb:
+                assert ha.read() == hb.read(), (fa, fb)
+
+    out = str(tmp_path)
+    os.makedirs(out, exist_ok=True)
+    # --- KL: streamed (blocks of 2 time slots, slabs of 5 columns) against eager + native slabs
+    kl = build(KLScreen, "kl_streamed")
+    kl.block_columns = 2 * n_f * n_a
+    kl.slab_bytes = 5 * 8 * n_pix * n_pix
+    assert kl._fitted is None
+    files = kl.write(out, case.cellsize_deg)
+    assert kl.timings["planes_copied"] == 2 and kl.timings["out_flags"] == 3
+    assert kl.timings["d2h_bytes"] * 2 == kl.timings["file_bytes"] == kl.timings["voxels_written"] * 16
+    eager = build(KLScreen, "kl_eager")
+    eager.fit_now()
+    eager._out_format = lambda smooth_pix: (0, 4)
+    files_e = eager.write(out, case.cellsize_deg)
+    assert eager.timings["planes_copied"] == 4 and len(files) == 2
+    same_files(files, files_e)
+    for name in ("vals_ph", "residuals", "screen_order", "weights_out"):
+        assert np.array_equal(getattr(kl, name), getattr(eager, name)), name
+    header, data = fits.read(files[0])
+    one = eager.make_matrix(0, 2, 1, 2, case.cellsize_deg, None, 0)
+    assert np.array_equal(np.asarray(data)[0:2, 1, 2], one.astype(np.float32))
+    # --- Voronoi: unsmoothed fill and both smoothing forms against native slabs
+    for tag, sm, mode in (("fill", 0.0, "auto"), ("linear", smooth, "linear"), ("direct", smooth, "direct")):
+        vo = build(VoronoiScreen, f"vo_{tag}")
+        vo.smooth_mode = mode
+        vo.slab_bytes = 5 * 8 * n_pix * n_pix
+        files = vo.write(out, case.cellsize_deg, smooth_pix=sm)
+        assert vo.timings["planes_copied"] == (4 if tag == "direct" else 2)
+        ref = build(VoronoiScreen, f"vo_{tag}_native")
+        ref.smooth_mode = mode
+        ref._out_format = lambda smooth_pix: (0, 4)
+        same_files(files, ref.write(out, case.cellsize_deg, smooth_pix=sm))
+    # --- "null" sink: the same pipeline up to the pinned host buffer, no file
+    kl2 = build(KLScreen, "kl_null")
+    kl2.sink = "null"
+    kl2.write(out, case.cellsize_deg)
+    assert kl2.timings["file_bytes"] == 0 and kl2.timings["voxels_written"] == kl.timings["voxels_written"]
+    assert not os.path.exists(os.path.join(out, "kl_null_0.fits"))

@@ -1,4 +1,6 @@
 """
+TEST / BENCHMARK INFRASTRUCTURE (not part of the product package).
+
 Seeded synthetic solution sets in the shapes BASELINE.json names: LOFAR-HBA
 (62 stations, 45 directions), SKA-Low (512 stations, 100 directions) and small test shapes.
 Everything is generated from ``numpy.random.default_rng(seed)`` and recorded in the result.
@@ -7,7 +9,7 @@ from dataclasses import dataclass
 
 import numpy as np
 
-from .h5parm_io import Solutions
+from ska_sdp_screen_fitting_b200.h5parm_io import Solutions
 
 FIELD_RA, FIELD_DEC = 126.23, 64.50
 T0, DT = 4.98795843e9, 8.0111208

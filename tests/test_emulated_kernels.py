@@ -93,6 +93,10 @@ def test_time_gaps_give_one_file_per_chunk_like_the_reference(emu_engine, golden
     pc.check_time_gaps_golden(emu_engine, golden_dir, repo_solutions, tmp_path)
 
 
+def test_streamed_write_equals_eager_write(emu_engine, tmp_path):
+    pc.check_streamed_write(emu_engine, tmp_path)
+
+
 def test_smoothing(emu_engine):
     pc.check_smooth(emu_engine, shape=(3, 13, 21), sigmas=(0.5, 2.0, 3.0))
 

@@ -39,6 +39,14 @@ def test_time_gaps_give_one_file_per_chunk_like_the_reference(gpu_engine, golden
     pc.check_time_gaps_golden(gpu_engine, golden_dir, repo_solutions, tmp_path)
 
 
+def test_streamed_write_equals_eager_write(gpu_engine, tmp_path):
+    """The API path on the real device: side-stream fits, copy-stream D2H, tcgen05 evaluation with
+    fused big-endian plane-pair stores -- byte-identical files to the eager / native path."""
+    pc.check_streamed_write(gpu_engine, tmp_path)
+    pc.check_streamed_write(gpu_engine, tmp_path / "b", n_pix=128, shape="small", n_times=9, cellsize=0.025,
+                            smooth=2.0)
+
+
 def test_fit_with_flags_and_outliers(gpu_engine):
     pc.check_fit(gpu_engine)
     pc.check_fit(gpu_engine, seed=17, n_t=6, n_f=3, n_a=8, n_d=45)
