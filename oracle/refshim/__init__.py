@@ -1,11 +1,11 @@
 """
-TEST INFRASTRUCTURE (oracle): run the reference's OWN modules, unmodified, from
-``/root/reference/src`` under a compatibility shim.
+TEST INFRASTRUCTURE (oracle): run the reference's OWN modules, unmodified, under a
+compatibility shim -- from ``/root/reference/src`` in the build container, or from the copy
+``oracle/build_ref.py`` leaves in ``oracle/_ref`` (git-ignored, ships to the GPU box) elsewhere.
 
-Only usable in the build container (``/root/reference`` does not exist on the GPU box).
-Used by ``oracle/make_golden.py`` to generate ``tests/golden/*.npz`` and by the
-``not gpu`` tests that pin ``oracle.port`` against the reference (skipped when the
-reference tree is absent).
+Used by ``oracle/make_golden*.py`` to generate ``tests/golden/*.npz``, by the ``not gpu`` tests
+that pin ``oracle.port`` against the reference (skipped when no reference tree is available),
+and by ``bench.py``'s CPU arm (``oracle/refrun.py``).
 
 What is shimmed and why:
   astropy.wcs / astropy.io.fits / astropy.coordinates  -> fake_astropy  (not installed)
@@ -21,12 +21,14 @@ import os
 import sys
 import types
 
-REFERENCE_SRC = "/root/reference/src"
+_MOUNT = "/root/reference/src"
+_COPY = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "_ref")
+REFERENCE_SRC = _MOUNT if os.path.isdir(os.path.join(_MOUNT, "ska_sdp_screen_fitting")) else _COPY
 _LOADED = {}
 
 
 def available():
-    return os.path.isdir(os.path.join(REFERENCE_SRC, "ska_sdp_screen_fitting"))
+    return os.path.isfile(os.path.join(REFERENCE_SRC, "ska_sdp_screen_fitting", "stationscreen.py"))
 
 
 def _module(name, **attrs):

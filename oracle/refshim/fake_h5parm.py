@@ -11,9 +11,17 @@ import numpy as np
 
 from ska_sdp_screen_fitting_b200.utils import h5min
 
+_VIRTUAL = {}  # filename -> {solset: dict(ant={name: xyz}, source={name: radec})}: h5parms that
+               # exist only in memory (synthetic inputs; their soltabs are added with add_soltab)
 _CREATED = {}  # filename -> {solset: {soltab_name: _Obj}}
 _EXTRA = {}    # filename -> {solset: {soltab_name: dict(type, axes, axes_vals, val, weight)}}:
                # in-memory soltabs overlaid on a real file (synthetic amplitude tables)
+
+
+def add_virtual(filename, solset, ant, source):
+    """Declare an in-memory h5parm ``filename`` with one solset: ``ant`` = {name: float32 xyz},
+    ``source`` = {name: float32 [ra, dec] rad} (the antenna / source tables, h5parm.py:731-767)."""
+    _VIRTUAL.setdefault(filename, {})[solset] = dict(ant=dict(ant), source=dict(source))
 
 
 def add_soltab(filename, solset, name, soltype, axes, axes_vals, val, weight):
@@ -103,6 +111,8 @@ class Solset:
             obj = _Obj(name, e["type"], self._h5._store)
             return Soltab(self, name, e["type"], e["axes"], e["axes_vals"], e["val"].copy(),
                           e["weight"].copy(), obj)
+        if self._h5._file is None:
+            raise Exception(f"Solution-table {name}  not found in solset {self.name}.")
         grp = self._file_group()
         if name not in grp:
             raise Exception(f"Solution-table {name}  not found in solset {self.name}.")
@@ -119,16 +129,23 @@ class Solset:
                       tab["val"].read(), tab["weight"].read(), obj)
 
     def get_soltab_names(self):
-        names = [k for k in self._file_group().keys() if k not in ("antenna", "source")]
+        if self._h5._file is None:
+            names = list(_EXTRA.get(self._h5.filename, {}).get(self.name, {}).keys())
+        else:
+            names = [k for k in self._file_group().keys() if k not in ("antenna", "source")]
         return names + list(self._h5._store.get(self.name, {}).keys())
 
     def get_ant(self):
+        if self._h5._file is None:
+            return dict(_VIRTUAL[self._h5.filename][self.name]["ant"])
         out = {}
         for row in self._file_group()["antenna"].read():
             out[row["name"].split(b"\0")[0].decode()] = row["position"]
         return out
 
     def get_source(self):
+        if self._h5._file is None:
+            return dict(_VIRTUAL[self._h5.filename][self.name]["source"])
         out = {}
         for row in self._file_group()["source"].read():
             out[row["name"].split(b"\0")[0].decode()] = row["dir"]
@@ -148,11 +165,11 @@ class H5parm:
     def __init__(self, h5parm_file, readonly=True, complevel=0, complib="zlib"):
         del readonly, complevel, complib
         self.filename = h5parm_file
-        self._file = h5min.File(h5parm_file)
+        self._file = None if h5parm_file in _VIRTUAL else h5min.File(h5parm_file)
         self._store = _CREATED.setdefault(h5parm_file, {})
 
     def get_solset(self, name):
-        if name not in self._file:
+        if name not in (self._file if self._file is not None else _VIRTUAL[self.filename]):
             raise Exception(f"Solution set {name} not found.")
         return Solset(self, name)
 
@@ -163,3 +180,4 @@ class H5parm:
 def reset():
     _CREATED.clear()
     _EXTRA.clear()
+    _VIRTUAL.clear()

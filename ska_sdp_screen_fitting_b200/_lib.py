@@ -11,9 +11,6 @@ from ctypes import c_char_p, c_double, c_int, c_int64, c_uint64, c_void_p
 
 PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(PKG, "libssf_b200.so")
-# When set (tests only), load this library instead: tests/emu builds the same kernel sources
-# with g++ against a CUDA emulator so kernel logic can be checked in a GPU-less container.
-_OVERRIDE_ENV = "SSF_B200_LIBRARY"
 
 
 class SsfLibraryError(RuntimeError):
@@ -69,13 +66,10 @@ OUT_PLANES2 = 2         # SSF_OUT_PLANES2
 _loaded = {}
 
 
-def library_path():
-    return os.environ.get(_OVERRIDE_ENV) or LIB_PATH
-
-
 def load(path=None):
-    """Loads a shared library once per path and declares every signature."""
-    path = path or library_path()
+    """Loads ``libssf_b200.so`` (once) and declares every signature.  ``path``: another build of
+    the same ABI -- the product never passes one."""
+    path = path or LIB_PATH
     if path in _loaded:
         return _loaded[path]
     if not os.path.exists(path):

@@ -2,8 +2,8 @@
 Device-side orchestration of the hot path: torch tensors supply device memory and the
 current CUDA stream; every computation is a call into ``libssf_b200.so`` (include/ssf.h).
 
-torch is plumbing only (allocation, views, ``unique`` over flag masks); nothing here
-computes a screen in Python or falls back to the CPU.
+torch is plumbing only (allocation, views, streams); nothing here computes a screen in Python
+or falls back to the CPU.
 """
 import math
 import threading
@@ -26,25 +26,26 @@ def _ptr(t):
 
 
 class Engine:
-    """Thin, stateless-per-call wrapper; ``device`` is a CUDA device (or "cpu" only when the
-    test emulator library is loaded through SSF_B200_LIBRARY)."""
+    """Thin, stateless-per-call wrapper of ``libssf_b200.so`` on one CUDA device.  There is no
+    other device: without the library or without CUDA the constructor raises."""
 
-    def __init__(self, device=None, library=None):
-        path = library or _lib.library_path()
-        self._lib = _lib.load(path)
+    def __init__(self, device=None):
+        lib = _lib.load()
+        device = torch.device("cuda" if device is None else device)
+        if device.type != "cuda":
+            raise _lib.SsfLibraryError("libssf_b200.so needs a CUDA device; there is no CPU path")
+        if device.index is None:
+            device = torch.device("cuda", torch.cuda.current_device())
+        self._init_state(lib, device)
+
+    def _init_state(self, lib, device):
+        self._lib = lib
+        self.device = device
         self._fit_status = None
         self.timers = None
         self.host_times = {}
         self._cpu_mark = {}
         self._caches = weakref.WeakSet()
-        emulated = path != _lib.LIB_PATH
-        if device is None:
-            device = "cpu" if emulated else "cuda"
-        self.device = torch.device(device)
-        if not emulated and self.device.type != "cuda":
-            raise _lib.SsfLibraryError("libssf_b200.so needs a CUDA device; there is no CPU path")
-        if self.device.type == "cuda" and self.device.index is None:
-            self.device = torch.device("cuda", torch.cuda.current_device())
 
     # ------------------------------------------------------------------ helpers
     def _call(self, name, *args):

@@ -129,6 +129,7 @@ class Screen:
         self.timings = {}
         self._chunks = None              # [(g_start, g_stop, my0, my1, local0)] from _plan_rows
         self._copy_stream = None
+        self._rings = None
         self._engine = None
         self._dev_vals = None            # device [t, f, a, d] float64: what make_matrix consumes
         self._dev_amp = None             # device [t, f, a, d, 2] float64 (gain solutions only)
@@ -329,9 +330,14 @@ class Screen:
         most = max([(c[3] - c[2]) * per_t for c in self._chunks] + [1])
         step = min(step, most)
         slab_elems = step * planes * npix
-        dev_ring = [eng.empty((slab_elems,), torch.float32) for _ in range(2)]
         n_host = max(2, int(self.host_buffers))
-        host_ring = [torch.empty(slab_elems, dtype=torch.float32, pin_memory=cuda) for _ in range(n_host)]
+        if self._rings is None or self._rings[0] != (slab_elems, n_host):
+            # two device slabs and the pinned staging buffers, kept across write() calls (pinning
+            # a GiB of host memory costs more than filling it)
+            self._rings = None
+            self._rings = ((slab_elems, n_host), [eng.empty((slab_elems,), torch.float32) for _ in range(2)],
+                           [torch.empty(slab_elems, dtype=torch.float32, pin_memory=cuda) for _ in range(n_host)])
+        _, dev_ring, host_ring = self._rings
         host_free = queue.Queue()
         for i in range(n_host):
             host_free.put(i)

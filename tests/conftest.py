@@ -30,9 +30,10 @@ def emu_library():
 
 @pytest.fixture(scope="session")
 def emu_engine(emu_library):
-    from ska_sdp_screen_fitting_b200.engine import Engine
+    sys.path.insert(0, os.path.join(ROOT, "tests", "emu"))
+    from emu_engine import EmuEngine
 
-    return Engine(device="cpu", library=emu_library)
+    return EmuEngine(emu_library)
 
 
 @pytest.fixture(scope="session")

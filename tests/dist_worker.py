@@ -17,7 +17,9 @@ def main():
     emu_lib, golden, out_dir = sys.argv[4], sys.argv[5], sys.argv[6]
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     sys.path.insert(0, root)
-    os.environ["SSF_B200_LIBRARY"] = emu_lib
+    sys.path.insert(0, os.path.join(root, "tests", "emu"))
+    import emu_engine
+    emu_engine.install(emu_lib)
     import torch
     import torch.distributed as dist
 

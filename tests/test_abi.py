@@ -44,21 +44,32 @@ def test_emulator_library_exports_every_symbol(emu_library):
 def test_missing_library_fails_loudly(tmp_path, monkeypatch):
     from ska_sdp_screen_fitting_b200 import _lib
 
-    monkeypatch.setenv("SSF_B200_LIBRARY", str(tmp_path / "nope.so"))
+    monkeypatch.setattr(_lib, "LIB_PATH", str(tmp_path / "nope.so"))
     with pytest.raises(_lib.SsfLibraryError):
         _lib.load()
 
 
-def test_no_cpu_path_for_the_product_library():
-    import torch
+def test_no_cpu_path_in_the_product_package(monkeypatch):
+    """Engine() takes CUDA devices only, no environment variable or argument selects another
+    library, and the product package never imports the oracle."""
+    import inspect
 
-    from ska_sdp_screen_fitting_b200 import _lib
+    from ska_sdp_screen_fitting_b200 import _lib, engine
     from ska_sdp_screen_fitting_b200.engine import Engine
 
-    if torch.cuda.is_available():
-        pytest.skip("GPU present")
     with pytest.raises(_lib.SsfLibraryError):
-        Engine(device="cpu", library=_lib.LIB_PATH)
+        Engine(device="cpu")
+    assert list(inspect.signature(Engine.__init__).parameters) == ["self", "device"]
+    monkeypatch.setenv("SSF_B200_LIBRARY", "/nonexistent/libssf_emu.so")
+    assert _lib.load() is _lib.load(_lib.LIB_PATH)
+    pkg = os.path.dirname(engine.__file__)
+    for base, _, names in os.walk(pkg):
+        for name in names:
+            if name.endswith(".py"):
+                with open(os.path.join(base, name), encoding="utf8") as fh:
+                    text = fh.read()
+                assert "SSF_B200_LIBRARY" not in text, name
+                assert not re.search(r"^\s*(from|import)\s+oracle", text, flags=re.M), name
 
 
 def test_bad_arguments_return_status_not_crash(emu_engine):

@@ -272,9 +272,9 @@ def test_cli_with_string_bounds_writes_the_reference_cube(emu_library, vor_golde
     from ska_sdp_screen_fitting_b200 import fits
 
     root = os.path.dirname(os.path.dirname(GOLDEN))
-    env = dict(os.environ, SSF_B200_LIBRARY=emu_library,
-               PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
-    cmd = [sys.executable, "-m", "ska_sdp_screen_fitting_b200.main", os.path.join(GOLDEN, "solutions.h5"),
+    env = dict(os.environ, PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    cmd = [sys.executable, os.path.join(root, "tests", "emu", "emu_engine.py"), emu_library,
+           "ska_sdp_screen_fitting_b200.main", os.path.join(GOLDEN, "solutions.h5"),
            "--screen_type", "tessellated", "--outroot", str(tmp_path / "cli"),
            "--bounds_deg", "[124.565; 66.165; 127.895; 62.835]", "--bounds_mid_deg", "[126.23;64.50]",
            "--skymodel", os.path.join(GOLDEN, "skymodel.txt"), "--padding_fraction", "0",
@@ -288,8 +288,33 @@ def test_cli_with_string_bounds_writes_the_reference_cube(emu_library, vor_golde
     sub = np.asarray(data)[:, list(vor_golden["sub_f"])][:, :, list(vor_golden["sub_a"])]
     assert np.array_equal(sub, vor_golden["cube_nosmooth"])
     # unknown flags / a missing positional are argparse errors (exit status 2), like the reference
-    bad = subprocess.run(cmd[:3] + ["--no_such_flag", "1"], env=env, capture_output=True, text=True, timeout=120)
+    bad = subprocess.run(cmd[:5] + ["--no_such_flag", "1"], env=env, capture_output=True, text=True, timeout=120)
     assert bad.returncode == 2
+
+
+def test_console_script_is_registered_like_the_reference(tmp_path):
+    """pyproject.toml registers the reference's console command
+    (/root/reference/pyproject.toml:35-36) and the entry point it names resolves to ``start``;
+    ``--help`` runs through it and lists the reference's flags."""
+    import subprocess
+    import sys
+    import tomllib
+
+    root = os.path.dirname(os.path.dirname(GOLDEN))
+    with open(os.path.join(root, "pyproject.toml"), "rb") as fh:
+        meta = tomllib.load(fh)
+    target = meta["project"]["scripts"]["ska-sdp-screen-fitting"]
+    module, func = target.split(":")
+    assert (module, func) == ("ska_sdp_screen_fitting_b200.main", "start")
+    # what the generated console script does: import the module, call the function
+    script = tmp_path / "ska-sdp-screen-fitting"
+    script.write_text(f"import sys\nfrom {module} import {func}\nsys.exit({func}())\n")
+    env = dict(os.environ, PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    done = subprocess.run([sys.executable, str(script), "--help"], env=env, capture_output=True, text=True, timeout=300)
+    assert done.returncode == 0, done.stderr[-2000:]
+    for flag in ("h5parmfile", "--soltabname", "--screen_type", "--outroot", "--bounds_deg", "--bounds_mid_deg",
+                 "--skymodel", "--solsetname", "--padding_fraction", "--cellsize_deg", "--smooth_deg", "--ncpu"):
+        assert flag in done.stdout, flag
 
 
 def test_cli_default_padding_matches_the_reference(emu_library, tmp_path):
@@ -303,9 +328,9 @@ def test_cli_default_padding_matches_the_reference(emu_library, tmp_path):
 
     g = np.load(os.path.join(GOLDEN, "padding_c1.npz"))
     root = os.path.dirname(os.path.dirname(GOLDEN))
-    env = dict(os.environ, SSF_B200_LIBRARY=emu_library,
-               PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
-    cmd = [sys.executable, "-m", "ska_sdp_screen_fitting_b200.main", os.path.join(GOLDEN, "solutions.h5"),
+    env = dict(os.environ, PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    cmd = [sys.executable, os.path.join(root, "tests", "emu", "emu_engine.py"), emu_library,
+           "ska_sdp_screen_fitting_b200.main", os.path.join(GOLDEN, "solutions.h5"),
            "--outroot", str(tmp_path / "pad"), "--bounds_deg", "[127.895;62.835;124.565;66.165]",
            "--bounds_mid_deg", "[126.23;64.50]", "--skymodel", os.path.join(GOLDEN, "skymodel.txt"),
            "--cellsize_deg", "0.13"]
