@@ -212,3 +212,86 @@ def golden_padding(mods):
 
 
 JOBS = {"gain": golden_gain, "tec": golden_tec, "gaps": golden_gaps, "padding": golden_padding}
+
+
+# ------------------------------------------------------------------ phase fit at real direction counts
+PHASE_SHAPES = {"phase45": dict(n_dirs=45, seed=45), "phase100": dict(n_dirs=100, seed=100)}
+PIX_SAMPLE = tuple(range(5, 512, 67))        # 8 rows x 8 columns of the 512 x 512 grid
+
+
+def phase_case(n_dirs, seed, n_times=4, n_freqs=2, n_stations=6):
+    """Seeded LOFAR-like case at the direction counts of BASELINE.json's configs (45 / 100) on the
+    512 x 512 grid of configs[2]: 3 % of the solutions flagged (weight 0), 1 % gross phase
+    outliers (+2.5 rad) for the 5-sigma circular clip -- which can only fire above ~30 directions
+    -- and station noise levels from far below to far above the level at which the reduced
+    chi-square crosses 1, so the screen orders move in both directions."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import synthetic_cases
+
+    case = synthetic_cases.make_case("lofar", seed=seed, n_times=n_times, n_freqs=n_freqs,
+                                     n_stations=n_stations, n_dirs=n_dirs, flag_fraction=0.03)
+    rng = np.random.default_rng(seed + 1)
+    sol = case.solutions
+    noise = np.array([0.0, 0.004, 0.05, 0.3, 1.0, 1.6])[:n_stations]
+    sol.val = sol.val + noise[None, None, :, None] * rng.normal(0, 1.0, sol.val.shape)
+    sol.val[rng.random(sol.val.shape) < 0.01] += 2.5
+    sol.weight[:, :, 0, :] = 1.0                  # station 0 stays the reference station
+    sol.weight[:, 1, 3, :] = 0.0                  # a fully flagged (freq, station): skipped by the fit
+    # The circular chi-square of the phase type is (1 - hypot(<sin^2>, <cos^2>)) * sum(w)
+    # (stationscreen.py:353-387): at most 0.29 per unit of weight, so with unit weights the
+    # reduced chi-square (:729-731) stays below 1 and the order never leaves its starting value.
+    # It scales with the weights, though, and h5parm weights need not be 1: station 3 carries
+    # inverse-variance-like weights of 25, station 4 weights drawn from {1, 4, 9} (non-uniform:
+    # the general normal-equation path), and the two noisy stations keep only 23 / 24 directions
+    # in two time slots (the order is capped at n_unflagged - 1 there).
+    if n_stations > 4:
+        sol.weight[:, :, 0, :] = 30.0             # ... and station 0 still has the largest weight sum
+        sol.weight[:, :, 3, :] *= 25.0
+        sol.weight[:, :, 4, :] *= rng.choice([1.0, 4.0, 9.0], size=sol.weight[:, :, 4, :].shape).astype(np.float32)
+    for a in range(max(0, n_stations - 2), n_stations):
+        for t, keep in ((1, 23), (2, 24)):
+            drop = rng.permutation(n_dirs)[keep:]
+            sol.weight[t, :, a, drop] = 0.0
+    return case
+
+
+def golden_phase(mods, tag):
+    """The reference's make_aterm_image(screen_type="kl") on ``phase_case``: fit soltabs
+    (screen, weights after flagging, residuals, orders) and the cube at an 8 x 8 pixel sample."""
+    from oracle import refrun
+    from oracle.refshim import fake_astropy, fake_h5parm
+
+    case = phase_case(**PHASE_SHAPES[tag])
+    sol = case.solutions
+    tmp = tempfile.mkdtemp(prefix="ssf_golden_")
+    try:
+        fake_h5parm.reset()
+        files, tabs = refrun.run_case(case, "kl", tmp, ncpu=0, name=tag)
+        cube = fake_astropy.open(files[0])[0].data
+        scr, res = tabs["phase_screen000"], tabs["phase_screen000resid"]
+        assert cube.shape[-1] == 512 and len(files) == 1
+        ix = np.array(PIX_SAMPLE)
+        out = dict(val=np.asarray(sol.val), weight=np.asarray(sol.weight), time=sol.time, freq=sol.freq,
+                   ant=np.array(sol.ant), dir=np.array(sol.dir),
+                   source_rad=np.array(sol.source_positions), station_xyz=np.array(sol.station_positions),
+                   patch_radec=case.patch_radec, rad=case.rad, dec=case.dec, width_deg=case.width_deg,
+                   cellsize_deg=case.cellsize_deg, pix=ix,
+                   screen=scr._val, screen_weights=scr._weight, resid=res._val, order=res._weight[..., 0],
+                   piercepoints=np.array(scr.obj.piercepoint),
+                   midra=scr.obj._v_attrs["midra"], middec=scr.obj._v_attrs["middec"],
+                   cube_sample=cube[..., ix[:, None], ix[None, :]].copy())
+        flagged = (out["screen_weights"] != out["weight"]).sum()
+        moved = (out["order"] != out["order"][0:1]).sum()
+        print(f"  {tag}: {flagged} solutions flagged by the clip, {moved} systems with a moved order, "
+              f"orders seen: {np.unique(out['order'])}")
+        assert flagged > 0, "the case must trigger the 5-sigma clip"
+        assert moved > 0, "the case must move the screen orders"
+        np.savez_compressed(os.path.join(GOLDEN, f"{tag}.npz"), **out)
+    finally:
+        shutil.rmtree(tmp)
+        fake_h5parm.reset()
+
+
+JOBS.update({"phase45": lambda mods: golden_phase(mods, "phase45"),
+             "phase100": lambda mods: golden_phase(mods, "phase100")})

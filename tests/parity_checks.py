@@ -602,3 +602,45 @@ def check_streamed_write(eng, tmp_path, n_pix=16, shape="tiny", n_times=None, sm
     kl2.write(out, case.cellsize_deg)
     assert kl2.timings["file_bytes"] == 0 and kl2.timings["voxels_written"] == kl.timings["voxels_written"]
     assert not os.path.exists(os.path.join(out, "kl_null_0.fits"))
+
+
+def phase_golden_solutions(golden_dir, tag):
+    """(Solutions, golden arrays) of tests/golden/phase45.npz / phase100.npz: the reference's own
+    make_aterm_image(screen_type="kl") on a seeded 45- / 100-direction case with flags, outliers
+    the 5-sigma circular clip fires on and orders that move (oracle/make_golden_synth.py::golden_phase)."""
+    from ska_sdp_screen_fitting_b200.h5parm_io import Solutions
+
+    g = np.load(os.path.join(golden_dir, f"{tag}.npz"))
+    sol = Solutions.from_arrays(g["val"], g["weight"], g["time"], g["freq"], [str(a) for a in g["ant"]],
+                                [str(d) for d in g["dir"]], g["source_rad"], g["station_xyz"])
+    assert (g["screen_weights"] != g["weight"]).any(), "the fixture must hold clipped solutions"
+    return sol, g
+
+
+def check_phase_golden(eng, golden_dir, tag, cube=True):
+    """The CUDA path at real direction counts against the reference itself: fit (white screens,
+    residuals, weights after the 5-sigma clip, final orders) and, with ``cube``, the evaluated
+    a-term planes of every (time, freq, station) at the fixture's 8 x 8 pixel sample of the
+    512 x 512 grid."""
+    from ska_sdp_screen_fitting_b200.kl_screen import KLScreen
+
+    sol, g = phase_golden_solutions(golden_dir, tag)
+    scr = KLScreen("g", None, None, float(g["rad"]), float(g["dec"]), float(g["width_deg"]), float(g["width_deg"]))
+    scr._engine = eng
+    scr.solutions = sol
+    scr.process()
+    assert np.abs(scr.piercepoints - g["piercepoints"]).max() < 1e-9
+    assert np.array_equal(scr.weights_out, g["screen_weights"])
+    assert np.array_equal(scr.screen_order, g["order"])
+    assert np.abs(scr.vals_ph - g["screen"]).max() < TOL_FIT
+    assert np.abs(scr.residuals - g["resid"]).max() < TOL_FIT
+    if not cube:
+        return
+    ix = g["pix"]
+    n_t, n_f, n_a = g["order"].shape
+    for f in range(n_f):
+        for a in range(n_a):
+            got = scr.make_matrix(0, n_t, f, a, float(g["cellsize_deg"]), None, 0)
+            assert got.shape[-1] == 512
+            want = g["cube_sample"][:, f, a].astype(np.float64)
+            assert np.abs(got[..., ix[:, None], ix[None, :]] - want).max() < TOL_KL, (f, a)

@@ -46,6 +46,12 @@ def test_fit_repo_data_subset_against_reference_golden(emu_engine, repo_solution
         assert np.abs(scr.vals_ph[:, :, i] - want[:, :, i]).max() < pc.TOL_FIT
 
 
+def test_fit_at_45_directions_against_the_reference_golden(emu_engine, golden_dir):
+    """Triggered 5-sigma clip, flagged-subset decompositions, moving orders, non-unit weights:
+    the kernels' fit against the reference's own outputs (the cube part runs on the GPU)."""
+    pc.check_phase_golden(emu_engine, golden_dir, "phase45", cube=False)
+
+
 def test_fit_amplitude_type(emu_engine):
     pc.check_fit_amplitude(emu_engine)
 

@@ -65,6 +65,14 @@ def test_fit_repo_data_against_reference_golden(gpu_engine, repo_solutions, gold
     assert np.array_equal(scr.weights_out, gold["screen_weights"])
 
 
+@pytest.mark.parametrize("tag", ["phase45", "phase100"])
+def test_fit_and_screens_at_real_direction_counts_against_the_reference(gpu_engine, golden_dir, tag):
+    """BASELINE.json configs[2] / configs[4] direction counts: triggered 5-sigma clip,
+    re-decomposition of the flagged subsets, order adjustment and the 512 x 512 evaluation, CUDA
+    against outputs of the reference's own code."""
+    pc.check_phase_golden(gpu_engine, golden_dir, tag)
+
+
 def test_kl_eval(gpu_engine):
     pc.check_kl_eval(gpu_engine, n=12, ncol=9)
     pc.check_kl_eval(gpu_engine, n=11, n_d=5, ncol=3, seed=8)       # ragged: npix % 4 != 0

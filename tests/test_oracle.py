@@ -396,3 +396,33 @@ def test_h5_reader_chunked_deflate_shuffle_layout():
     ds._filters = [(32001, [])]                                    # e.g. blosc: must fail loudly
     with pytest.raises(h5min.H5FormatError):
         f._read_chunked(ds)
+
+
+@pytest.mark.parametrize("tag", ["phase45", "phase100"])
+def test_port_fit_at_real_direction_counts_against_the_reference(tag):
+    """oracle.port pinned where the phase-type 5-sigma clip actually fires (> ~30 directions):
+    the reference's make_aterm_image(screen_type="kl") on seeded 45- / 100-direction cases
+    (tests/golden/phase45.npz, phase100.npz): flags, re-decomposed subsets, orders, residuals,
+    and the evaluated cube at the fixture's pixel sample."""
+    import parity_checks as pc
+
+    sol, g = pc.phase_golden_solutions(GOLDEN, tag)
+    ref = klfit.get_reference_station(sol.weight, 10)
+    out = klfit.run_phase(np.asarray(sol.val), np.asarray(sol.weight).copy(), np.asarray(sol.source_positions),
+                          np.asarray(sol.station_positions), ref, min(20, len(sol.dir) - 1))
+    assert np.abs(out["pp"] - g["piercepoints"]).max() < 1e-9
+    assert np.array_equal(out["weights"], g["screen_weights"])
+    assert np.array_equal(out["order"], g["order"])
+    assert np.abs(out["screen"] - g["screen"]).max() < 1e-10
+    assert np.abs(out["resid"] - g["resid"]).max() < 1e-10
+    # orders moved away from the per-station starting order somewhere
+    from ska_sdp_screen_fitting_b200.kl_screen import station_orders
+    start = np.array(station_orders(np.asarray(sol.station_positions), ref, min(20, len(sol.dir) - 1)), float)
+    fitted = g["order"] != 0
+    assert (g["order"] != start[None, None, :])[fitted].any()
+    x, y = wcs.kl_grid_coords(float(g["rad"]), float(g["dec"]), float(g["width_deg"]), float(g["cellsize_deg"]),
+                               out["midra"], out["middec"])
+    ix = g["pix"]
+    for f, a in ((0, 1), (1, 5)):
+        data = screens.kl_make_matrix(x[ix], y[ix], out["pp"], out["screen"][:, f, a, :])
+        assert np.abs(data.astype(np.float32) - g["cube_sample"][:, f, a]).max() < 1e-6
