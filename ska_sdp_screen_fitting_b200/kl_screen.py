@@ -82,6 +82,7 @@ class KLScreen(Screen):
         self.fit_ahead = 2                # fit blocks the streaming fit runs ahead of the evaluation
         self.fit_group = 4                # stream_slabs: slabs fitted per fit call (amortises the per-call host work)
         self.keep_fit_results = True      # streamed write(): bring white / resid / order / weights back to the host
+        self.write_soltabs = False        # append the screen soltabs to the input h5parm after the fit (write_back)
         self._settle = None
         self._host_sol = None             # (val, weight) host arrays of this rank's time rows
         self._skip_dev = None
@@ -349,6 +350,8 @@ class KLScreen(Screen):
             self.vals_amp = a_white.cpu().numpy()
             self.times_amp = amp.time
             self.freqs_amp = amp.freq
+            self._amp_fit = {"white": self.vals_amp}                       # on the slow grid (interpolate() resamples vals_amp)
+            self._amp_axes = (np.asarray(amp.time), np.asarray(amp.freq))
             self.amp_residuals = a_resid.cpu().numpy()
             self.amp_screen_order = a_order.cpu().numpy()
             self.amp_weights_out = a_w.cpu().numpy()
@@ -388,6 +391,59 @@ class KLScreen(Screen):
         self._fitted = {"dev": white, "white": white.cpu().numpy(), "resid": resid.cpu().numpy(),
                         "order": order.cpu().numpy(), "weights": weights_out.cpu().numpy()}
         return self._fitted
+
+    # ------------------------------------------------------------------ soltab write-back
+    def write_back(self, filename=None):
+        """The side effect of the reference's fit (stationscreen.py:1087-1159): appends the soltabs
+        ``phase_screen000`` (whitened screens, weights after flagging) and ``phase_screen000resid``
+        (residuals; the final screen ORDER stored as the weights) to the solset of the h5parm, with
+        the attributes ``beta / r_0 / height / midra / middec`` and the ``piercepoint`` table on the
+        former -- and ``amplitude_screen000`` / ``...resid`` (pol axis, log10 screens) for gain
+        solutions.  Opt-in (``write_soltabs``): the reference always does this, but here the file
+        is modified by this package's own HDF5 appender (utils/h5write.py; no HDF5 library on the
+        image).  With ``torch.distributed`` the ranks' time rows are gathered on rank 0."""
+        from .screen import _dist_info
+        from .utils import h5write
+
+        filename = filename or self.input_h5parm_filename
+        if filename is None:
+            raise ValueError("no h5parm file to write to")
+        res = self.fit_now()
+        parts = {k: res[k] for k in ("white", "resid", "order", "weights")}
+        rank, world, dist = _dist_info()
+        if world > 1:
+            boxes = [None] * world if rank == 0 else None
+            dist.gather_object((self._local_rows(), parts), boxes, dst=0)
+            if rank != 0:
+                return
+            n_t = len(self.times_ph)
+            full = {k: np.zeros((n_t,) + v.shape[1:], v.dtype) for k, v in parts.items()}
+            for rows, part in boxes:
+                for k in full:
+                    full[k][rows] = part[k]
+            parts = full
+        ant = np.array([str(a).encode() for a in self.station_names])
+        dirs = np.array([str(d).encode() for d in self.source_names])
+        axes = ["time", "freq", "ant", "dir"]
+        vals = [np.asarray(self.times_ph, np.float64), np.asarray(self.freqs_ph, np.float64), ant, dirs]
+        attrs = {"beta": float(self.beta_val), "r_0": float(self.r_0), "height": 0.0,
+                 "midra": float(self.mid_ra), "middec": float(self.mid_dec)}
+        solset = self.input_solset_name
+        h5write.append_soltab(filename, solset, "phase_screen000", "phasescreen", axes, vals, parts["white"],
+                              parts["weights"], attrs=attrs, extra={"piercepoint": self.piercepoints})
+        order = np.broadcast_to(parts["order"][..., None], parts["resid"].shape)
+        h5write.append_soltab(filename, solset, "phase_screen000resid", "phasescreenresid", axes, vals,
+                              parts["resid"], order)
+        if not self.phase_only:
+            axes_p = axes + ["pol"]
+            vals_p = [np.asarray(self._amp_axes[0], np.float64), np.asarray(self._amp_axes[1], np.float64), ant, dirs,
+                      np.array([b"XX", b"YY"])]
+            h5write.append_soltab(filename, solset, "amplitude_screen000", "amplitudescreen", axes_p, vals_p,
+                                  self._amp_fit["white"], self.amp_weights_out, attrs=attrs,
+                                  extra={"piercepoint": self.piercepoints})
+            a_order = np.broadcast_to(self.amp_screen_order[:, :, :, None, :], self.amp_residuals.shape)
+            h5write.append_soltab(filename, solset, "amplitude_screen000resid", "amplitudescreenresid", axes_p,
+                                  vals_p, self.amp_residuals, a_order)
 
     # the reference's result attributes (kl_screen.py:131-154), computed on first use
     @property

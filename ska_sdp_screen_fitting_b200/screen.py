@@ -441,6 +441,8 @@ class Screen:
         if cuda:
             torch.cuda.synchronize(eng.device)
         eng.check_fit_status()                                   # deferred checks of the streamed fit
+        if getattr(self, "write_soltabs", False):
+            self.write_back()
         if dist is not None:
             dist.barrier()
         if rank == 0 and self.sink == "file":

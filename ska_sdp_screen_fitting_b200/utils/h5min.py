@@ -286,6 +286,74 @@ class File(Group):
                     out[self._heap_string(heap, name_off)] = ohdr
                     epos += 2 * self._so + 24
 
+    # ---------------------------------------------- locations (used by utils/h5write.Appender)
+    def _walk_entries(self, group):
+        """Yields (name, file offset of the symbol-table entry) for every child of ``group``."""
+        for mtype, body in group._msgs:
+            if mtype == 0x11:
+                btree, heap = self._unpack_oo(body, 0)
+                break
+        else:
+            raise H5FormatError(f"{group.name}: not an old-style group")
+        stack = [btree]
+        buf = self._buf
+        while stack:
+            addr = stack.pop()
+            level = buf[addr + 5]
+            used = self._uint(buf, addr + 6, 2)
+            pos = addr + 8 + 2 * self._so
+            for _ in range(used):
+                pos += self._sl
+                child = self._uint(buf, pos, self._so)
+                pos += self._so
+                if level > 0:
+                    stack.append(child)
+                    continue
+                nsym = self._uint(buf, child + 6, 2)
+                for i in range(nsym):
+                    epos = child + 8 + i * (2 * self._so + 24)
+                    yield self._heap_string(heap, self._uint(buf, epos, self._so)), epos
+
+    def _symbol_entries(self, group):
+        """{child name: (object header address, (btree, heap) cached for groups or None)}."""
+        out = {}
+        for name, epos in self._walk_entries(group):
+            ohdr = self._uint(self._buf, epos + self._so, self._so)
+            cache = self._uint(self._buf, epos + 2 * self._so, 4)
+            stab = self._unpack_oo(self._buf, epos + 2 * self._so + 8) if cache == 1 else None
+            if stab is None:
+                # a group whose entry carries no cached addresses: take them from its header
+                for mtype, body in self._read_object_header(ohdr):
+                    if mtype == 0x11:
+                        stab = self._unpack_oo(body, 0)
+            out[name] = (ohdr, stab)
+        return out
+
+    def _entry_offset(self, group, name):
+        for child, epos in self._walk_entries(group):
+            if child == name:
+                return epos
+        raise KeyError(name)
+
+    def _message_offset(self, addr, want):
+        """File offset of the BODY of the first message of type ``want`` in the object header."""
+        buf = self._buf
+        nmsg = self._uint(buf, addr + 2, 2)
+        blocks = [(addr + 16, self._uint(buf, addr + 8, 4))]
+        seen = 0
+        while blocks and seen < nmsg:
+            pos, size = blocks.pop(0)
+            end = pos + size
+            while pos + 8 <= end and seen < nmsg:
+                mtype, msize, _flags = struct.unpack_from("<HHB", buf, pos)
+                if mtype == want:
+                    return pos + 8
+                if mtype == 0x10:
+                    blocks.append((self._uint(buf, pos + 8, self._so), self._uint(buf, pos + 8 + self._so, self._sl)))
+                pos += 8 + msize
+                seen += 1
+        raise KeyError(f"message type {want:#x} not found")
+
     # ------------------------------------------------------------------ messages
     def _parse_dataspace(self, body):
         ver, rank, flags = body[0], body[1], body[2]

@@ -644,3 +644,66 @@ def check_phase_golden(eng, golden_dir, tag, cube=True):
             assert got.shape[-1] == 512
             want = g["cube_sample"][:, f, a].astype(np.float64)
             assert np.abs(got[..., ix[:, None], ix[None, :]] - want).max() < TOL_KL, (f, a)
+
+
+def check_soltab_write_back(eng, golden_dir, tmp_path, sel_f=(0, 11), sel_a=(0, 1, 30, 61), full=False):
+    """``write_soltabs``: after process() + write() the h5parm holds ``phase_screen000`` /
+    ``phase_screen000resid`` as the reference leaves them (stationscreen.py:1087-1159): values,
+    float16 weights (flags / orders), AXES, attributes, pierce points -- read back with the h5
+    reader and compared with the in-memory results and, where the station orders agree with the
+    full array's, with what the reference wrote (tests/golden/kl_c2.npz).  The input soltab is a
+    sub-cube appended to a copy of the repo file with the package's own appender, unless ``full``."""
+    import shutil
+
+    from ska_sdp_screen_fitting_b200.h5parm_io import read_solutions
+    from ska_sdp_screen_fitting_b200.kl_screen import KLScreen, station_orders
+    from ska_sdp_screen_fitting_b200.utils import h5min, h5write
+
+    gold = np.load(os.path.join(golden_dir, "kl_c2.npz"))
+    path = os.path.join(str(tmp_path), "solutions_wb.h5")
+    os.makedirs(str(tmp_path), exist_ok=True)
+    shutil.copy(os.path.join(golden_dir, "solutions.h5"), path)
+    whole = read_solutions(path, "sol000", "phase000")
+    soltab = "phase000"
+    sel_f, sel_a = (list(range(len(whole.freq))), list(range(len(whole.ant)))) if full else (list(sel_f), list(sel_a))
+    if not full:
+        soltab = "phase001"
+        h5write.append_soltab(path, "sol000", soltab, "phase", ["time", "freq", "ant", "dir"],
+                              [whole.time, whole.freq[sel_f], np.array([whole.ant[a].encode() for a in sel_a]),
+                               np.array([d.encode() for d in whole.dir])],
+                              whole.val[:, sel_f][:, :, sel_a], whole.weight[:, sel_f][:, :, sel_a])
+    scr = KLScreen("wb", path, os.path.join(golden_dir, "skymodel.txt"), 126.23, 64.50, 3.33, 3.33,
+                   phase_soltab_name=soltab)
+    scr._engine = eng
+    scr.write_soltabs = True
+    scr.process()
+    scr.write(str(tmp_path), 0.2)
+    with h5min.File(path) as handle:
+        assert np.array_equal(handle["sol000/phase000/val"].read().reshape(whole.val.shape), whole.val)   # untouched
+        tab, res = handle["sol000/phase_screen000"], handle["sol000/phase_screen000resid"]
+        assert tab.attrs["TITLE"] == "phasescreen" and res.attrs["TITLE"] == "phasescreenresid"
+        assert tab["val"].attrs["AXES"] == "time,freq,ant,dir" == res["weight"].attrs["AXES"]
+        assert tab["weight"].dtype == np.float16
+        for key, want in (("beta", 5.0 / 3.0), ("r_0", 100.0), ("height", 0.0), ("midra", float(gold["midra"])),
+                          ("middec", float(gold["middec"]))):
+            assert abs(float(tab.attrs[key]) - want) < 1e-9, key
+        assert np.abs(tab["piercepoint"].read() - gold["piercepoints"]).max() < 1e-9
+        white, w_out = tab["val"].read(), tab["weight"].read()
+        resid, order = res["val"].read(), res["weight"].read()
+        assert [a.decode() for a in tab["ant"].read()] == [whole.ant[a] for a in sel_a]
+    assert np.array_equal(white, scr.vals_ph) and np.array_equal(resid, scr.residuals)
+    assert np.array_equal(w_out, scr.weights_out.astype(np.float16))
+    assert np.array_equal(order, np.broadcast_to(scr.screen_order[..., None], order.shape).astype(np.float16))
+    pos = np.asarray(whole.station_positions)
+    orders_full = station_orders(pos, 0, 6)
+    same = [i for i, a in enumerate(sel_a) if station_orders(pos[sel_a], 0, 6)[i] == orders_full[a]]
+    assert len(same) >= 2
+    for i in same:
+        f_ix, a = np.array(sel_f), sel_a[i]
+        assert np.abs(white[:, :, i] - gold["screen"][:, f_ix, a]).max() < TOL_FIT
+        assert np.abs(resid[:, :, i] - gold["resid"][:, f_ix, a]).max() < TOL_FIT
+        assert np.array_equal(order[:, :, i, 0], gold["order"][:, f_ix, a])
+        assert np.array_equal(w_out[:, :, i], gold["screen_weights"][:, f_ix, a])
+    # the table just written is a valid INPUT: the reader serves it back as a soltab
+    back = read_solutions(path, "sol000", "phase_screen000")
+    assert back.val.shape == white.shape and back.ant == [whole.ant[a] for a in sel_a]

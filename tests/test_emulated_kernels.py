@@ -103,6 +103,10 @@ def test_streamed_write_equals_eager_write(emu_engine, tmp_path):
     pc.check_streamed_write(emu_engine, tmp_path)
 
 
+def test_soltab_write_back(emu_engine, golden_dir, tmp_path):
+    pc.check_soltab_write_back(emu_engine, golden_dir, tmp_path)
+
+
 def test_smoothing(emu_engine):
     pc.check_smooth(emu_engine, shape=(3, 13, 21), sigmas=(0.5, 2.0, 3.0))
 

@@ -47,6 +47,11 @@ def test_streamed_write_equals_eager_write(gpu_engine, tmp_path):
                             smooth=2.0)
 
 
+def test_soltab_write_back(gpu_engine, golden_dir, tmp_path):
+    """The whole repo data set: the soltabs appended to the h5parm against the ones the reference wrote."""
+    pc.check_soltab_write_back(gpu_engine, golden_dir, tmp_path, full=True)
+
+
 def test_fit_with_flags_and_outliers(gpu_engine):
     pc.check_fit(gpu_engine)
     pc.check_fit(gpu_engine, seed=17, n_t=6, n_f=3, n_a=8, n_d=45)
