@@ -295,3 +295,73 @@ def golden_phase(mods, tag):
 
 JOBS.update({"phase45": lambda mods: golden_phase(mods, "phase45"),
              "phase100": lambda mods: golden_phase(mods, "phase100")})
+
+
+def tec_run_case(seed=31, n_t=8, n_f=2, n_a=4, n_d=12):
+    """A dTEC soltab [time, freq, ant, dir]: ``tec_case`` per frequency (station 0 is the quiet
+    reference), stations a few km apart."""
+    rng = np.random.default_rng(seed)
+    dirs, val, weights = tec_case(seed=seed, n_d=n_d, n_t=n_t, n_st=n_a - 1)
+    val_t = np.zeros((n_t, n_f, n_a, n_d))
+    wt = np.ones((n_t, n_f, n_a, n_d), np.float32)
+    for f in range(n_f):
+        val_t[:, f, 1:, :] = val.transpose(2, 0, 1) * (1.0 + 0.1 * f)
+        wt[:, f, 1:, :] = weights.transpose(2, 0, 1)
+    val_t[:, :, 0, :] = rng.normal(0, 0.001, (n_t, n_f, n_d))
+    pos = (np.array([3826896.2, 460979.5, 5064658.0]) + rng.normal(0, 5e3, (n_a, 3))).astype(np.float32)
+    return dirs, val_t, wt, pos
+
+
+def golden_tec_run(mods):
+    """stationscreen.run on a soltab of TYPE "tec" (the whole operation: referencing, per-station
+    orders, _process_single_freq, result soltabs) and the screen images K . white of
+    calculate_kl_screen (kl_screen.py:411-449) on a 16 x 16 grid: what an aterm_type="tec" cube
+    (processing_utils.py:187-190) of those screens holds.  No API path of the reference reaches
+    either with a tec soltab, so the operators themselves are the pin."""
+    from types import SimpleNamespace
+
+    from oracle import refrun
+    from oracle.port import wcs as owcs
+    from oracle.refshim import fake_h5parm
+
+    ss, kls, misc = mods["stationscreen"], mods["kl_screen"], mods["processing_utils"]
+    dirs, val, wt, pos = tec_run_case()
+    n_t, n_f, n_a, n_d = val.shape
+    ants, names = [f"ST{i:03d}" for i in range(n_a)], [f"[Patch_{i}]" for i in range(n_d)]
+    sol = SimpleNamespace(val=val, weight=wt, time=4.9e9 + 8.0 * np.arange(n_t), freq=1.2e8 + 4e6 * np.arange(n_f),
+                          ant=ants, dir=names, station_dict=dict(zip(ants, pos)), source_dict=dict(zip(names, dirs)))
+    fake_h5parm.reset()
+    try:
+        refrun.register(sol, "tec.h5", soltab_name="tec000", soltype="tec")
+        solset = fake_h5parm.H5parm("tec.h5").get_solset("sol000")
+        soltab = solset.get_soltab("tec000")
+        ref_ind = misc.get_reference_station(soltab, 10)
+        ss.run(soltab, "tec_screen000", order=min(20, n_d - 1), ref_ant=ref_ind, scale_order=True,
+               adjust_order=True, ncpu=1)
+        store = fake_h5parm._CREATED["tec.h5"]["sol000"]
+        scr, res = store["tec_screen000"]._soltab, store["tec_screen000resid"]._soltab
+        pp = np.array(scr.obj.piercepoint)
+        rad, dec, n_pix, cell = 126.23, 64.5, 16, 0.25
+        x, y = owcs.kl_grid_coords(rad, dec, (n_pix - 0.5) * cell, cell, scr.obj._v_attrs["midra"],
+                                   scr.obj._v_attrs["middec"])
+        images = np.zeros((n_t, n_f, n_a, n_pix, n_pix))
+        kls.PIERCEPOINTS, kls.X_COORD, kls.Y_COORD = pp, x, y
+        for f in range(n_f):
+            for a in range(n_a):
+                kls.SCREEN_PH = scr._val[:, f, a, :].T.copy()                    # [dir, time], kl_screen.py:263-271
+                shared = np.zeros((n_pix, n_pix, n_t))
+                kls.VAR_DICT = {"shared_val": shared, "val_shape": shared.shape}     # as make_matrix sets it (:293)
+                for k in range(n_t):
+                    kls.calculate_kl_screen(k, n_d, 5.0 / 3.0, 100, "ph")
+                images[:, f, a] = shared.transpose(2, 1, 0)                     # [t, y, x] (the .T of :368-373)
+        out = dict(dirs=dirs, val=val, weight=wt, station_xyz=pos, time=sol.time, freq=sol.freq,
+                   ref_ind=ref_ind, screen=scr._val, screen_weights=scr._weight, resid=res._val,
+                   order=res._weight[..., 0], piercepoints=pp, rad=rad, dec=dec, n_pix=n_pix, cellsize_deg=cell,
+                   images=images)
+        assert (out["screen_weights"] != wt).any() and len(np.unique(out["order"])) > 2
+        np.savez_compressed(os.path.join(GOLDEN, "tec_run.npz"), **out)
+    finally:
+        fake_h5parm.reset()
+
+
+JOBS["tec_run"] = golden_tec_run

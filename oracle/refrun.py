@@ -42,14 +42,15 @@ def write_skymodel(path, names, radec_deg):
             fh.write(f" , , {name.strip('[]')}, {_hms(float(ra))}, {_dms(float(dec))}\n")
 
 
-def register(sol, h5name, soltab_name="phase000", solset="sol000", amp=None, amp_name="amplitude000"):
+def register(sol, h5name, soltab_name="phase000", solset="sol000", amp=None, amp_name="amplitude000",
+             soltype="phase"):
     """Makes ``sol`` (a product ``Solutions`` record, or anything with the same fields) readable
     by the reference as soltab ``soltab_name`` of the in-memory h5parm ``h5name``."""
     from oracle.refshim import fake_h5parm
 
     fake_h5parm.add_virtual(h5name, solset, {n: np.asarray(p, np.float32) for n, p in sol.station_dict.items()},
                             {n: np.asarray(p, np.float32) for n, p in sol.source_dict.items()})
-    fake_h5parm.add_soltab(h5name, solset, soltab_name, "phase", ["time", "freq", "ant", "dir"],
+    fake_h5parm.add_soltab(h5name, solset, soltab_name, soltype, ["time", "freq", "ant", "dir"],
                            [np.asarray(sol.time, float), np.asarray(sol.freq, float), np.array(list(sol.ant)),
                             np.array(list(sol.dir))], np.asarray(sol.val), np.asarray(sol.weight))
     if amp is not None:

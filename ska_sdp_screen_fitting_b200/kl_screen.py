@@ -158,6 +158,27 @@ class KLScreen(Screen):
         eng.host_tick("fit_post", t_host)
         return white.view(n_t, n_f, n_a, n_d), resid.view(n_t, n_f, n_a, n_d), order, weights_out
 
+    def fit_tec_device(self, val, weight, check=True):
+        """stationscreen.run on a soltab of type "tec" (val [t, f, a, d] f64 / weight f32): the
+        flow of the phase type -- referencing, per-station orders, niter = 2 -- with the tec
+        branches of the operators (values fitted as they are :549-562, rms clip over all times of
+        a (freq, station) on the plain residual :338-346, plain chi-square :742-746)."""
+        eng = self.engine
+        n_t, n_f, n_a, n_d = val.shape
+        if self.ref_ind != -1:
+            val = val - val[:, :, self.ref_ind:self.ref_ind + 1, :]
+        skip = torch.isnan(val).all(dim=3).all(dim=0) | (weight == 0).all(dim=3).all(dim=0)
+        skip[:, self.ref_ind] = True
+        work_w = torch.where(skip[None, :, :, None], torch.zeros_like(weight), weight).contiguous()
+        so = self._so_dev[None, None, :].expand(n_t, n_f, n_a).reshape(-1).contiguous()
+        white, resid, order = eng.kl_fit(val.reshape(-1, n_d).contiguous(), work_w.view(-1, n_d), so, self._pp_dev,
+                                         niter=2, nsigma=5.0, adjust_order=True, r0=self.r_0, beta=self.beta_val,
+                                         cut=PINV_CUT, cache=self._patterns, check=check, screen_type="tec",
+                                         ngroups=n_f * n_a)
+        order = torch.where(skip[None], torch.zeros_like(order.view(n_t, n_f, n_a)), order.view(n_t, n_f, n_a))
+        weights_out = torch.where(skip[None, :, :, None], weight, work_w)
+        return white.view(n_t, n_f, n_a, n_d), resid.view(n_t, n_f, n_a, n_d), order, weights_out
+
     def fit_amplitude_device(self, val, weight, check=True):
         """stationscreen.run on an amplitude soltab as KLScreen.fit calls it (kl_screen.py:114-126:
         niter=3, scale_order=False, no reference station) for device tensors val
@@ -338,6 +359,19 @@ class KLScreen(Screen):
         self._host_sol = (val, weight)
         self._fitted = None
         self._streamed = None
+        if str(sol.soltype).lower().startswith("tec"):
+            # dTEC solutions: the values themselves are fitted (stationscreen.py:549-562) and the
+            # outlier rms spans all time slots of a (freq, station) (:338-346), so the fit takes
+            # the whole table at once; write() then makes the 5-axis cube of the screens
+            if self._all_reduce(np.ones(1), "sum")[0] > 1:
+                raise NotImplementedError("tec screens are fitted on one rank (their outlier rms spans all times)")
+            if not self.phase_only:
+                raise ValueError("a tec soltab cannot be combined with an amplitude soltab")
+            self.aterm_type = "tec"
+            white, resid, order, w_out = self.fit_tec_device(eng.tensor(val, torch.float64),
+                                                             eng.tensor(weight, torch.float32))
+            self._fitted = {"dev": white, "white": white.cpu().numpy(), "resid": resid.cpu().numpy(),
+                            "order": order.cpu().numpy(), "weights": w_out.cpu().numpy()}
         if not self.phase_only:                                           # kl_screen.py:113-126, :135-139
             amp = self._load_solutions(self.input_amplitude_soltab_name)
             if amp.val.ndim != 5 or amp.val.shape[-1] < 2:
@@ -429,10 +463,11 @@ class KLScreen(Screen):
         attrs = {"beta": float(self.beta_val), "r_0": float(self.r_0), "height": 0.0,
                  "midra": float(self.mid_ra), "middec": float(self.mid_dec)}
         solset = self.input_solset_name
-        h5write.append_soltab(filename, solset, "phase_screen000", "phasescreen", axes, vals, parts["white"],
+        kind = "tec" if self.aterm_type == "tec" else "phase"          # f"{screen_type}screen", stationscreen.py:1097
+        h5write.append_soltab(filename, solset, f"{kind}_screen000", f"{kind}screen", axes, vals, parts["white"],
                               parts["weights"], attrs=attrs, extra={"piercepoint": self.piercepoints})
         order = np.broadcast_to(parts["order"][..., None], parts["resid"].shape)
-        h5write.append_soltab(filename, solset, "phase_screen000resid", "phasescreenresid", axes, vals,
+        h5write.append_soltab(filename, solset, f"{kind}_screen000resid", f"{kind}screenresid", axes, vals,
                               parts["resid"], order)
         if not self.phase_only:
             axes_p = axes + ["pol"]
@@ -545,6 +580,8 @@ class KLScreen(Screen):
         # KL screens are never smoothed (make_aterm_images.py:101-103), so the evaluation kernel's
         # store is the last touch of every value: FITS byte order always, plane pairs when the
         # solutions are phase-only (planes 2, 3 = planes 0, 1, kl_screen.py:368-373)
+        if self.aterm_type == "tec":
+            return _lib.OUT_BIG_ENDIAN, 1
         if self.phase_only:
             return _lib.OUT_BIG_ENDIAN | _lib.OUT_PLANES2, 2
         return _lib.OUT_BIG_ENDIAN, 4
@@ -554,6 +591,11 @@ class KLScreen(Screen):
         # NaN -> (1, 0) is fused into the store of ssf_kl_eval either way.
         self._prepare(cellsize_deg, out_dir)
         eng = self.engine
+        if self.aterm_type == "tec" and slab.shape[1] == 1:
+            # dTEC cube: the screen values themselves, one plane per column
+            eng.kl_eval_tec(self._basis, eng.kl_coeffs(cols.contiguous(), self._c_full), cols.shape[1], slab,
+                            self.eval_variant, out_flags & _lib.OUT_BIG_ENDIAN)
+            return
         if amp is not None:
             # gain solutions: phase, log10 XX and log10 YY amplitude screens share the basis
             n_col, n_d = cols.shape

@@ -126,6 +126,7 @@ class Screen:
         self.host_buffers = 3            # pinned staging buffers between the copy stream and the file
         self.write_threads = min(16, os.cpu_count() or 1)   # parallel pwrite calls per staged slab
         self.sink = "file"               # "null": stop at the pinned host buffer (benchmarks: link vs file system)
+        self.aterm_type = "gain"         # "tec": 5-axis dTEC cube (KLScreen on a soltab of type tec)
         self.timings = {}
         self._chunks = None              # [(g_start, g_stop, my0, my1, local0)] from _plan_rows
         self._copy_stream = None
@@ -325,6 +326,9 @@ class Screen:
         self.timings["prepare_s"] = time.perf_counter() - t0
         out_flags, planes = self._out_format(smooth_pix)
         fused_swap = bool(out_flags & _lib.OUT_BIG_ENDIAN)
+        # planes per column in the FILE: 4 for a-term ("gain") cubes, 1 for dTEC cubes, which have
+        # no MATRIX axis (processing_utils.py:187-190)
+        file_planes = 1 if self.aterm_type == "tec" else 4
         step = self.slab_columns(cellsize_deg, planes)
         # never allocate more than the rank's largest chunk needs
         most = max([(c[3] - c[2]) * per_t for c in self._chunks] + [1])
@@ -364,7 +368,7 @@ class Screen:
                             data = host_ring[hb][:ncol * planes * npix].numpy().view(">f4")
                             stats["pwrite_s"] += writer.write_columns(col_rel, data, already_big_endian=True,
                                                                       pairs=planes == 2, pool=pool)
-                            stats["file_bytes"] += ncol * 16 * npix
+                            stats["file_bytes"] += ncol * 4 * file_planes * npix
                     except BaseException as exc:  # noqa: BLE001 - surfaced by the caller
                         failure.append(exc)
                     finally:
@@ -383,9 +387,9 @@ class Screen:
                 outfiles.append(outfile)
                 writer = None
                 if self.sink == "file":
-                    shape = (g_stop - g_start, n_f, n_a, 4, n_y, n_x)
+                    shape = (g_stop - g_start, n_f, n_a) + ((4,) if file_planes == 4 else ()) + (n_y, n_x)
                     cards = fits.aterm_cards(shape, self.rad, self.dec, cellsize_deg, self.freqs_ph,
-                                             times[g_start:g_stop])
+                                             times[g_start:g_stop], aterm_type=self.aterm_type)
                     if rank == 0:
                         writer = fits.CubeWriter(outfile, shape, cards)
                     if dist is not None:

@@ -707,3 +707,38 @@ def check_soltab_write_back(eng, golden_dir, tmp_path, sel_f=(0, 11), sel_a=(0, 
     # the table just written is a valid INPUT: the reader serves it back as a soltab
     back = read_solutions(path, "sol000", "phase_screen000")
     assert back.val.shape == white.shape and back.ant == [whole.ant[a] for a in sel_a]
+
+
+def check_tec_run_golden(eng, golden_dir, tmp_path):
+    """A soltab of type "tec" through the public classes: KLScreen.process() fits it with the tec
+    branches of the operators (against the reference's own stationscreen.run on that soltab) and
+    write() makes the 5-axis dTEC cube [t, f, a, y, x] of processing_utils.py:187-190 (against the
+    screen images of the reference's calculate_kl_screen) -- tests/golden/tec_run.npz."""
+    from ska_sdp_screen_fitting_b200 import fits
+    from ska_sdp_screen_fitting_b200.h5parm_io import Solutions
+    from ska_sdp_screen_fitting_b200.kl_screen import KLScreen
+
+    g = np.load(os.path.join(golden_dir, "tec_run.npz"))
+    n_t, n_f, n_a, n_d = g["val"].shape
+    sol = Solutions.from_arrays(g["val"], g["weight"], g["time"], g["freq"], [f"ST{i:03d}" for i in range(n_a)],
+                                [f"[Patch_{i}]" for i in range(n_d)], g["dirs"], g["station_xyz"], soltype="tec")
+    n_pix, cell = int(g["n_pix"]), float(g["cellsize_deg"])
+    scr = KLScreen("tec", None, None, float(g["rad"]), float(g["dec"]), (n_pix - 0.5) * cell, (n_pix - 0.5) * cell)
+    scr._engine = eng
+    scr.solutions = sol
+    scr.process()
+    assert scr.aterm_type == "tec" and scr.ref_ind == int(g["ref_ind"])
+    assert np.array_equal(scr.weights_out, g["screen_weights"])
+    assert (g["screen_weights"] != g["weight"]).any(), "the fixture must hold clipped solutions"
+    assert np.array_equal(scr.screen_order, g["order"])
+    assert np.abs(scr.vals_ph - g["screen"]).max() < TOL_FIT
+    assert np.abs(scr.residuals - g["resid"]).max() < TOL_FIT * 20
+    os.makedirs(str(tmp_path), exist_ok=True)
+    files = scr.write(str(tmp_path), cell)
+    header, data = fits.read(files[0])
+    assert header["NAXIS"] == 5 and data.shape == (n_t, n_f, n_a, n_pix, n_pix)
+    assert [header[f"CTYPE{i}"] for i in range(1, 6)] == ["RA---SIN", "DEC--SIN", "ANTENNA", "FREQ", "TIME"]
+    scale = max(1.0, float(np.abs(g["images"]).max()))
+    assert np.abs(np.asarray(data, np.float64) - g["images"]).max() < TOL_KL * scale
+    one = scr.make_tec_matrix(0, n_t, 1, 2, cell)
+    assert np.array_equal(one.astype(np.float32), np.asarray(data)[:, 1, 2])

@@ -60,6 +60,10 @@ def test_fit_tec_type_against_reference_operator_golden(emu_engine, golden_dir):
     pc.check_fit_tec_golden(emu_engine, golden_dir)
 
 
+def test_tec_soltab_fit_and_dtec_cube_against_reference_golden(emu_engine, golden_dir, tmp_path):
+    pc.check_tec_run_golden(emu_engine, golden_dir, tmp_path)
+
+
 def test_kl_gain_fit_against_reference_golden(emu_engine, golden_dir, repo_solutions):
     pc.check_kl_gain_golden(emu_engine, golden_dir, repo_solutions, full=False)
 

@@ -35,6 +35,10 @@ def test_fit_tec_type_against_reference_operator_golden(gpu_engine, golden_dir):
     pc.check_fit_tec_golden(gpu_engine, golden_dir)
 
 
+def test_tec_soltab_fit_and_dtec_cube_against_reference_golden(gpu_engine, golden_dir, tmp_path):
+    pc.check_tec_run_golden(gpu_engine, golden_dir, tmp_path)
+
+
 def test_time_gaps_give_one_file_per_chunk_like_the_reference(gpu_engine, golden_dir, repo_solutions, tmp_path):
     pc.check_time_gaps_golden(gpu_engine, golden_dir, repo_solutions, tmp_path)
 
