@@ -238,6 +238,15 @@ int ssf_bswap32(void *data, int64_t count, void *stream);
 int ssf_copy_rows_d2h(void *dst_host, int64_t dst_pitch, const void *src_dev, int64_t src_pitch,
                       int64_t width_bytes, int64_t rows, void *stream);
 
+/* Host only: places a staged slab (pinned host memory, FITS byte order) into the memory-mapped
+ * FITS cube.  Column c of `src` (`src_bytes` bytes) is copied to dst + c * copies * src_bytes,
+ * `copies` times back to back: copies = 1 for whole columns, 2 for the plane pairs of a
+ * phase-only cube (SSF_OUT_PLANES2), whose planes 2, 3 repeat planes 0, 1.  `threads` worker
+ * threads share the bytes.  This is the host half of the reference's hdu.writeto
+ * (screen.py:381-382); pwrite calls on one file serialise on the inode lock, copies into a
+ * shared mapping do not. */
+int ssf_host_place(void *dst, const void *src, int64_t ncol, int64_t src_bytes, int copies, int threads);
+
 /* ------------------------------------------------------------------------------------
  * Host convenience entry points (what a ctypes/cffi binding of the reference would call):
  * HOST buffers in, HOST slab out; allocation, H2D, kernels, D2H inside.

@@ -55,6 +55,7 @@ SIGNATURES = {
     "ssf_nan_fix": (c_int, [_P, c_int64, c_int64, _P]),
     "ssf_bswap32": (c_int, [_P, c_int64, _P]),
     "ssf_copy_rows_d2h": (c_int, [_P, c_int64, _P, c_int64, c_int64, c_int64, _P]),
+    "ssf_host_place": (c_int, [_P, _P, c_int64, c_int64, c_int, c_int]),
     "ssf_voronoi_cube_host": (c_int, [_P, _P, c_int, c_int, c_int, c_int64, c_double, _P]),
     "ssf_kl_cube_host": (c_int, [_P, _P, c_int, c_int, _P, c_int, _P, c_int64, c_double, c_double,
                                  c_double, _P]),

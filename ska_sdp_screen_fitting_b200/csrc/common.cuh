@@ -20,6 +20,9 @@ namespace ssf {
 
 void set_error(const char *fmt, ...);
 void count_launch(int n = 1);
+// Streaming multiprocessors of the current device (queried once per device; grids of the
+// persistent / capped kernels are sized from it).
+int sm_count();
 
 inline int div_up(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 

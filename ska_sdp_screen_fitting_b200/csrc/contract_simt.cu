@@ -330,7 +330,7 @@ int launch_tile(const float *Bt, const float *G, int ndir, int ldg, int64_t npix
   const int pix_tiles = ssf::div_up(npix, TPIX);
   const int64_t n_ct = (ncol + TCOL - 1) / TCOL;
   const int per_sm = smem <= 113 * 1024 ? 2 : 1;
-  const int chunks = pick_chunks(pix_tiles, n_ct, 148 * per_sm);
+  const int chunks = pick_chunks(pix_tiles, n_ct, ssf::sm_count() * per_sm);
   const int per = (int)((n_ct + chunks - 1) / chunks);
   const int gx = (int)((n_ct + per - 1) / per);
   SSF_REQUIRE(pix_tiles <= 65535, "image too large for the tiled contraction grid");
@@ -357,7 +357,7 @@ int launch(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int
   const int pix_tiles = ssf::div_up(npix, TILE_PIX);
   const int64_t n_ct = (ncol + TC - 1) / TC;
   // enough CTAs for ~8 per SM, but keep each CTA on one pixel tile for many column tiles
-  int64_t want_y = (148 * 8 + pix_tiles - 1) / pix_tiles;
+  int64_t want_y = (ssf::sm_count() * 8 + pix_tiles - 1) / pix_tiles;
   if (want_y > n_ct) want_y = n_ct;
   if (want_y > 65535) want_y = 65535;
   if (want_y < 1) want_y = 1;

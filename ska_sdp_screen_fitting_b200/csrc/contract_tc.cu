@@ -64,13 +64,16 @@ constexpr int TC_N = 64;                        // accumulator columns per tile
 #ifndef SSF_TC_MAXREG
 #define SSF_TC_MAXREG 72
 #endif
-constexpr int B_STAGES = 2;                     // shared-memory ring of coefficient tiles
+constexpr int B_MAX = 4;                        // most shared-memory stages of coefficient tiles (ring depth nb <= B_MAX)
 constexpr int T_STAGES = 4;                     // TMEM accumulator ring
 constexpr int TMEM_COLS = T_STAGES * TC_N;      // 256 columns (two resident CTAs use all 512)
-constexpr int N_BARS = 2 * B_STAGES + 2 * T_STAGES;
-// Slab columns per 64-row coefficient tile.  MODE 0 = Voronoi (Re + Im rows per column),
+constexpr int N_BARS = 2 * B_MAX + 2 * T_STAGES;
+// Slab columns per coefficient tile.  MODE 0 = Voronoi (Re + Im rows per column),
 // 1 = KL phase screens (one row per column), 2 = KL gain (phase + log10 Axx + log10 Ayy rows).
 __host__ __device__ constexpr int tile_columns(int mode) { return mode == 1 ? TC_N : mode == 0 ? TC_N / 2 : 16; }
+// Rows (the MMA's N) of a coefficient tile: gain tiles are 3 x 16 rows -- a 64-row tile would
+// carry 16 zero rows, a quarter of the tensor-pipe time and of the operand traffic for nothing.
+__host__ __device__ constexpr int tile_rows(int mode) { return mode == 2 ? 48 : TC_N; }
 
 // ------------------------------------------------------------------------------------ PTX
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -155,6 +158,23 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float *v) {
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// Accumulator chains.  Consecutive tcgen05.mma instructions that accumulate into the SAME tensor-
+// memory columns execute one after the other, each waiting out the pipeline latency of the one
+// before: ~90 cycles per instruction measured, whatever N is, where a 128 x 48 x 8 / 128 x 64 x 8
+// TF32 product is only 24 / 32 cycles of tensor-pipe work (a GEMM never sees this: its N = 256
+// instructions are longer than the latency).  At 100 directions the 52 instructions of a tile
+// then take ~5000 cycles -- 3.5 x the time its 32 KB gain tile needs to leave the SM.  So a tile's
+// K steps are dealt round-robin onto C accumulators (chain c = K steps with ks % C == c, still
+// corrections first within each chain), consecutive instructions alternate between them, and
+// the epilogue adds the C partial sums.
+__host__ __device__ constexpr int chains_for(int mode, bool bigk) {
+#ifdef SSF_TC_CHAINS
+  return SSF_TC_CHAINS;
+#else
+  return mode == 2 ? 1 : (bigk ? 2 : 1);
+#endif
+}
+
 // 32 lanes x 8 consecutive accumulator columns -> 8 registers per thread.
 __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float *v) {
   uint32_t r[8];
@@ -165,6 +185,14 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float *v) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
   for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// v[0..8) += 32 lanes x 8 consecutive accumulator columns (the partial sum of another chain).
+__device__ __forceinline__ void tmem_add8(uint32_t taddr, float *v) {
+  float w[8];
+  tmem_ld8(taddr, w);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] += w[i];
 }
 
 // Shared-memory matrix descriptor, K-major, no swizzle (cute::UMMA::SmemDescriptor):
@@ -178,8 +206,9 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
 
 // Instruction descriptor (cute::UMMA::InstrDescriptor): D = F32 (bit 4), A = B = TF32 (2 at
 // bits 7 and 10), both K-major, N >> 3 at bit 17, M >> 4 at bit 24.
-constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_N >> 3) << 17) |
-                           ((uint32_t)(TC_M >> 4) << 24);
+__host__ __device__ constexpr uint32_t idesc_for(int n) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
+}
 
 // Float offset of element (row r, k) in the canonical layout with kc4 = Kp / 4 core matrices
 // per 8-row group: core matrix = 8 rows x 4 floats (128 B), K-adjacent matrices contiguous.
@@ -263,20 +292,21 @@ __device__ __forceinline__ void store_gain(const float (&ph)[8], const float (&a
 
 // ------------------------------------------------------------------------------------ pre-pass
 // Coefficient tiles, split and laid out as the MMA wants them:
-//   Bs[tile][hi | lo][canon(row, k)]   (64 rows x Kp, zero padded)
+//   Bs[tile][hi | lo][canon(row, k)]   (tile_rows(MODE) rows x Kp, zero padded)
 // KL:      row r of tile t = slab column 64 t + r               (G[col, d], leading dimension ldg)
 // Voronoi: rows r < 32 = Re, r >= 32 = Im of column 32 t + (r & 31)   (lut[col, d, 0/1])
-// Gain:    rows 16 g + r, g = 0 (phase), 1 (log10 Axx), 2 (log10 Ayy) of column 16 t + r;
-//          rows 48.. are zero                                   (G3[col, g, d], leading dimension ldg)
+// Gain:    48 rows: 16 g + r, g = 0 (phase), 1 (log10 Axx), 2 (log10 Ayy) of column 16 t + r
+//                                                               (G3[col, g, d], leading dimension ldg)
 template <int MODE>
 __global__ void split_b_kernel(const float *__restrict__ G, int ndir, int ldg, int64_t ncol, int Kp,
                                int64_t n_ct, float *__restrict__ Bs) {
+  constexpr int NR = tile_rows(MODE);
   const int kc4 = Kp >> 2;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= n_ct * TC_N * kc4) return;
+  if (idx >= n_ct * NR * kc4) return;
   const int kc = (int)(idx % kc4);
-  const int r = (int)((idx / kc4) % TC_N);
-  const int64_t tile = idx / ((int64_t)kc4 * TC_N);
+  const int r = (int)((idx / kc4) % NR);
+  const int64_t tile = idx / ((int64_t)kc4 * NR);
   float x[4];
 #pragma unroll
   for (int u = 0; u < 4; ++u) {
@@ -284,7 +314,7 @@ __global__ void split_b_kernel(const float *__restrict__ G, int ndir, int ldg, i
     float v = 0.0f;
     if (MODE == 2) {
       const int64_t col = tile * 16 + (r & 15);
-      if (r < 48 && col < ncol && k < ndir) v = G[(col * 3 + (r >> 4)) * ldg + k];
+      if (col < ncol && k < ndir) v = G[(col * 3 + (r >> 4)) * ldg + k];
     } else if (MODE == 1) {
       const int64_t col = tile * TC_N + r;
       if (col < ncol && k < ndir) v = G[col * ldg + k];
@@ -297,20 +327,25 @@ __global__ void split_b_kernel(const float *__restrict__ G, int ndir, int ldg, i
   const float4 hv = make_float4(to_tf32(x[0]), to_tf32(x[1]), to_tf32(x[2]), to_tf32(x[3]));
   const float4 lv = make_float4(to_tf32(x[0] - hv.x), to_tf32(x[1] - hv.y), to_tf32(x[2] - hv.z),
                                 to_tf32(x[3] - hv.w));
-  float *dst = Bs + tile * (2 * TC_N * Kp) + canon(r, 4 * kc, kc4);
+  float *dst = Bs + tile * (2 * NR * Kp) + canon(r, 4 * kc, kc4);
   *reinterpret_cast<float4 *>(dst) = hv;
-  *reinterpret_cast<float4 *>(dst + TC_N * Kp) = lv;
+  *reinterpret_cast<float4 *>(dst + NR * Kp) = lv;
 }
 
 // ------------------------------------------------------------------------------------ kernel
-// Shared memory (floats): A_hi[128 Kp] A_lo[128 Kp] B[2 stages][hi, lo][64 Kp], then the
-// mbarriers b_full[2] b_empty[2] t_full[4] t_empty[4] and the TMEM base address.
+// Shared memory (floats): A_hi[128 Kp] A_lo[128 Kp] B[nb stages][hi, lo][NR Kp], then the
+// mbarriers b_full[4] b_empty[4] t_full[4] t_empty[4] and the TMEM base address.
 template <int MODE, int NEPI>
 __global__ void __maxnreg__(NEPI == 8 ? SSF_TC_MAXREG : 96)
 contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, int ndir, int64_t npix,
-                   int64_t ncol, float *__restrict__ slab, int tiles_per_chunk, int Kp, ssf::OutFmt fmt) {
+                   int64_t ncol, float *__restrict__ slab, int tiles_per_chunk, int Kp, int nb, ssf::OutFmt fmt) {
   constexpr bool KL = MODE == 1;
+  constexpr int NR = tile_rows(MODE);            // rows of a coefficient tile = N of the MMA
+  constexpr uint32_t IDESC = idesc_for(NR);
   constexpr int CT = tile_columns(MODE);         // slab columns per tile
+  constexpr int C = chains_for(MODE, false);     // accumulator chains per tile
+  constexpr int TSTRIDE = C * NR;                // TMEM columns of one tile stage
+  constexpr int TS = TMEM_COLS / TSTRIDE < T_STAGES ? TMEM_COLS / TSTRIDE : T_STAGES;   // tile stages
   constexpr int THREADS = (NEPI + 2) * 32;
   constexpr int GROUPS = NEPI / 8;               // epilogue groups taking alternate tiles
   SSF_DYN_SMEM(float, sm);
@@ -318,11 +353,11 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, i
   const int kc4 = Kp >> 2;
   float *a_hi = sm, *a_lo = sm + TC_M * Kp;
   float *b_base = sm + 2 * TC_M * Kp;            // stage s: hi at s*2*64*Kp, lo right after
-  uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (2 * TC_M + 2 * B_STAGES * TC_N) * Kp);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (2 * TC_M + 2 * nb * NR) * Kp);
   uint32_t *tmem_holder = reinterpret_cast<uint32_t *>(bars + N_BARS);
-  const uint32_t b_full = smem_u32(bars), b_empty = smem_u32(bars + B_STAGES);
-  const uint32_t t_full = smem_u32(bars + 2 * B_STAGES), t_empty = smem_u32(bars + 2 * B_STAGES + T_STAGES);
-  const uint32_t stage_bytes = (uint32_t)(2 * TC_N * Kp * sizeof(float));
+  const uint32_t b_full = smem_u32(bars), b_empty = smem_u32(bars + B_MAX);
+  const uint32_t t_full = smem_u32(bars + 2 * B_MAX), t_empty = smem_u32(bars + 2 * B_MAX + T_STAGES);
+  const uint32_t stage_bytes = (uint32_t)(2 * NR * Kp * sizeof(float));
 
   const int64_t pix0 = (int64_t)blockIdx.y * TC_M;
   const int64_t n_ct = (ncol + CT - 1) / CT;
@@ -331,12 +366,12 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, i
   if (ct_end > n_ct) ct_end = n_ct;
   if (ct_begin >= ct_end) return;                // whole CTA, before any barrier / allocation
   const int n_tiles = (int)(ct_end - ct_begin);
-  const float *b_src = Bs + ct_begin * (2 * TC_N * Kp);
+  const float *b_src = Bs + ct_begin * (2 * NR * Kp);
 
   if (tid == NEPI * 32) {
     // the TMA lane initialises the barriers and starts the first coefficient tiles at once, so
     // their latency runs under the staging of the basis tile below
-    for (int i = 0; i < B_STAGES; ++i) {
+    for (int i = 0; i < B_MAX; ++i) {
       mbar_init(b_full + 8 * i, 1);
       mbar_init(b_empty + 8 * i, 1);
     }
@@ -345,9 +380,9 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, i
       mbar_init(t_empty + 8 * i, 8);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    for (int it = 0; it < B_STAGES && it < n_tiles; ++it) {
+    for (int it = 0; it < nb && it < n_tiles; ++it) {
       mbar_expect_tx(b_full + 8 * it, stage_bytes);
-      bulk_g2s(smem_u32(b_base + (size_t)it * 2 * TC_N * Kp), b_src + (size_t)it * 2 * TC_N * Kp, stage_bytes,
+      bulk_g2s(smem_u32(b_base + (size_t)it * 2 * NR * Kp), b_src + (size_t)it * 2 * NR * Kp, stage_bytes,
                b_full + 8 * it);
     }
   }
@@ -387,11 +422,11 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, i
   if (warp == NEPI) {
     // ===== TMA lane: refill stage s once the MMAs of the tile that used it have retired =====
     if (lane == 0) {
-      for (int it = B_STAGES; it < n_tiles; ++it) {
-        const int s = it % B_STAGES, use = it / B_STAGES;
+      for (int it = nb; it < n_tiles; ++it) {
+        const int s = it % nb, use = it / nb;
         mbar_wait(b_empty + 8 * s, (use - 1) & 1);
         mbar_expect_tx(b_full + 8 * s, stage_bytes);
-        bulk_g2s(smem_u32(b_base + (size_t)s * 2 * TC_N * Kp), b_src + (size_t)it * 2 * TC_N * Kp, stage_bytes,
+        bulk_g2s(smem_u32(b_base + (size_t)s * 2 * NR * Kp), b_src + (size_t)it * 2 * NR * Kp, stage_bytes,
                  b_full + 8 * s);
       }
     }
@@ -402,27 +437,35 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, i
       const uint64_t da_hi = make_desc(smem_u32(a_hi), lbo, sbo), da_lo = make_desc(smem_u32(a_lo), lbo, sbo);
       const int ksteps = Kp >> 3;
       for (int it = 0; it < n_tiles; ++it) {
-        const int s = it % B_STAGES, t = it % T_STAGES;
-        mbar_wait(b_full + 8 * s, (it / B_STAGES) & 1);                  // coefficient tile landed
-        if (it >= T_STAGES) mbar_wait(t_empty + 8 * t, (it / T_STAGES - 1) & 1);   // accumulator drained
+        const int s = it % nb, t = it % TS;
+        mbar_wait(b_full + 8 * s, (it / nb) & 1);                  // coefficient tile landed
+        if (it >= TS) mbar_wait(t_empty + 8 * t, (it / TS - 1) & 1);   // accumulator drained
         tc_fence_after();
-        const float *bh = b_base + (size_t)s * 2 * TC_N * Kp;
-        const uint64_t db_hi = make_desc(smem_u32(bh), lbo, sbo), db_lo = make_desc(smem_u32(bh + TC_N * Kp), lbo, sbo);
-        const uint32_t d_tmem = tmem_base + (uint32_t)(t * TC_N);
+        const float *bh = b_base + (size_t)s * 2 * NR * Kp;
+        const uint64_t db_hi = make_desc(smem_u32(bh), lbo, sbo), db_lo = make_desc(smem_u32(bh + NR * Kp), lbo, sbo);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(t * TSTRIDE);
         // The tensor core truncates (round toward zero) once per accumulating instruction
         // (measured: -0.4 ulp of |D| per tcgen05.mma).  So the small correction products go
         // first, while |D| is ~2^-11 of its final size and the truncation is harmless, and
         // only the K/8 main products A_hi B_hi round at full magnitude.
         // One K step = 8 TF32 = 2 core matrices = 256 B -> start-address field + 16.
+        // Chain c = K steps with ks % C == c accumulates into columns d_tmem + c NR (see
+        // chains_for): consecutive instructions alternate between the chains.
         for (int ks = 0; ks < ksteps; ++ks) {
           const uint64_t adv = (uint64_t)(ks * 16);
-          tc_mma_tf32(d_tmem, da_lo + adv, db_lo + adv, IDESC, ks > 0);
-          tc_mma_tf32(d_tmem, da_lo + adv, db_hi + adv, IDESC, 1);
-          tc_mma_tf32(d_tmem, da_hi + adv, db_lo + adv, IDESC, 1);
+          tc_mma_tf32(d_tmem + (uint32_t)((ks % C) * NR), da_lo + adv, db_lo + adv, IDESC, ks >= C);
         }
         for (int ks = 0; ks < ksteps; ++ks) {
           const uint64_t adv = (uint64_t)(ks * 16);
-          tc_mma_tf32(d_tmem, da_hi + adv, db_hi + adv, IDESC, 1);
+          tc_mma_tf32(d_tmem + (uint32_t)((ks % C) * NR), da_lo + adv, db_hi + adv, IDESC, 1);
+        }
+        for (int ks = 0; ks < ksteps; ++ks) {
+          const uint64_t adv = (uint64_t)(ks * 16);
+          tc_mma_tf32(d_tmem + (uint32_t)((ks % C) * NR), da_hi + adv, db_lo + adv, IDESC, 1);
+        }
+        for (int ks = 0; ks < ksteps; ++ks) {
+          const uint64_t adv = (uint64_t)(ks * 16);
+          tc_mma_tf32(d_tmem + (uint32_t)((ks % C) * NR), da_hi + adv, db_hi + adv, IDESC, 1);
         }
         tc_commit(b_empty + 8 * s);                  // shared-memory stage free for the next copy
         tc_commit(t_full + 8 * t);                   // accumulator ready for the epilogue
@@ -433,17 +476,23 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, i
     const int g = warp >> 3, q = warp & 3, h = (warp >> 2) & 1;
     const int64_t pix = pix0 + 32 * q + lane;
     for (int it = g; it < n_tiles; it += GROUPS) {
-      const int t = it % T_STAGES;
+      const int t = it % TS;
       const int64_t c0 = (ct_begin + it) * CT;
-      mbar_wait(t_full + 8 * t, (it / T_STAGES) & 1);
+      mbar_wait(t_full + 8 * t, (it / TS) & 1);
       tc_fence_after();
       if (MODE == 2) {
         // this warp: its 32 pixels x slab columns c0 + 8 h .. + 7, three accumulator groups
         float ph[8], ax[8], ay[8];
-        const uint32_t ta = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TC_N + 8 * h);
+        const uint32_t ta = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TSTRIDE + 8 * h);
         tmem_ld8(ta, ph);
         tmem_ld8(ta + 16, ax);
         tmem_ld8(ta + 32, ay);
+        const int chains = (Kp >> 3) < C ? (Kp >> 3) : C;        // chains that hold a partial sum
+        for (int c = 1; c < chains; ++c) {
+          tmem_add8(ta + (uint32_t)(c * NR), ph);
+          tmem_add8(ta + (uint32_t)(c * NR) + 16, ax);
+          tmem_add8(ta + (uint32_t)(c * NR) + 32, ay);
+        }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(t_empty + 8 * t);
@@ -453,7 +502,14 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, i
         continue;
       }
       float v[32];
-      tmem_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TC_N + 32 * h), v);
+      tmem_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TSTRIDE + 32 * h), v);
+      if (C > 1) {
+        const int chains = (Kp >> 3) < C ? (Kp >> 3) : C;
+        for (int c = 1; c < chains; ++c)
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            tmem_add8(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TSTRIDE + c * NR + 32 * h + 8 * u), &v[8 * u]);
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(t_empty + 8 * t);
@@ -485,21 +541,30 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, i
 // ------------------------------------------------------------------------------------ big-K kernel
 // More than 56 directions: the split basis tile alone is > 57 KB x 2, so only one CTA fits an SM
 // and the kernel above cannot hide the staging of its basis tile behind a second CTA (0.68-0.72 of
-// the measured HBM peak at 100 directions).  This variant is PERSISTENT (one CTA per SM walks a list
-// of (pixel tile, column chunk) items) and keeps the split basis operand in TENSOR MEMORY
-// (tcgen05.mma with A from TMEM: lane = pixel row, one TF32 per 32-bit column, 2 Kp columns next to
-// the 4 x 64 accumulator columns).  Shared memory then only holds the coefficient ring (3 stages)
+// the measured HBM peak at 100 directions).  This variant is PERSISTENT (one CTA per SM works
+// through a list of (pixel tile, column chunk) items) and keeps the split basis operand in TENSOR
+// MEMORY (tcgen05.mma with A from TMEM: lane = pixel row, one TF32 per 32-bit column, 2 Kp columns
+// next to the 4 x 64 accumulator columns).  Shared memory then only holds the coefficient ring
 // and the RAW basis tile of the NEXT item, which the TMA lane prefetches with one tensor-map copy
 // while the current item is being contracted; four converter warps split it into TMEM
 // (tcgen05.st) as soon as the last MMA of the current item has retired, while the 16 epilogue warps
 // still have accumulator stages to drain.
-//   shared memory (floats): raw[Kp][128]  B[nb stages][hi, lo][64 Kp]
-//   tensor memory (columns): D[4][64] | A_hi[Kp] | A_lo[Kp]
+//
+// Items are handed out DYNAMICALLY: a CTA's first item is its block index, every further one
+// comes from an atomic counter.  SMs differ in their distance to the L2 slices / HBM stacks they
+// write to (two dies; the map differs from GPU to GPU), so with a static round-robin list the
+// slowest SM set the launch time: 0.67 of the measured HBM peak on one box, 0.82 on another.
+// The TMA lane is the scheduler: it fetches the next item one item ahead and publishes it to the
+// other roles through a small shared-memory ring (sched_full / sched_empty mbarriers); item -1
+// ends the walk.
+//   shared memory (floats): raw[Kp][128]  B[nb stages][hi, lo][NR Kp]
+//   tensor memory (columns): D[TS tile stages][C chains][NR] ... | A_hi[Kp] | A_lo[Kp] at the top
 constexpr int BK_EPI = 16, BK_CONV = 4;
 constexpr int BK_THREADS = (BK_EPI + 2 + BK_CONV) * 32;
-constexpr int BK_MAXB = 3;
-constexpr int BK_NBARS = 2 * BK_MAXB + 2 * T_STAGES + 4;
-constexpr int BK_ACOL = T_STAGES * TC_N;         // first TMEM column of A_hi
+constexpr int BK_MAXB = 6;                       // most coefficient stages
+constexpr int BK_SR = 8;                         // scheduler ring slots
+constexpr int BK_NBARS = 2 * BK_MAXB + 2 * T_STAGES + 4 + 2 * BK_SR;
+constexpr int BK_CONSUMERS = 1 + BK_CONV + BK_EPI;   // warps that read every scheduler slot
 
 // D[tmem] (+)= A[tmem] * B[smem desc], kind::tf32, issued by ONE thread.
 __device__ __forceinline__ void tc_mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
@@ -518,25 +583,44 @@ __device__ __forceinline__ void tmem_st8(uint32_t taddr, const float *v) {
                "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7]))
                : "memory");
 }
+// Non-blocking probe of an mbarrier phase.
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{ .reg .pred p; mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+      : "=r"(done)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return done != 0;
+}
 
 template <int MODE>
 __global__ void __launch_bounds__(BK_THREADS, 1)
 contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float *__restrict__ Bs, int ndir,
                         int64_t npix, int64_t ncol, float *__restrict__ slab, int tiles_per_chunk, int chunks,
-                        int Kp, int nb, int64_t n_items, ssf::OutFmt fmt) {
+                        int Kp, int nb, int n_items, int *__restrict__ next_item, ssf::OutFmt fmt) {
+  constexpr int NR = tile_rows(MODE);            // rows of a coefficient tile = N of the MMA
+  constexpr uint32_t IDESC = idesc_for(NR);
+  constexpr int C = chains_for(MODE, true);      // accumulator chains per tile
+  constexpr int TSTRIDE = C * NR;                // TMEM columns of one tile stage
+  const int acol = 512 - 2 * Kp;                 // first TMEM column of A_hi; tile stages below it
+  const int TS = acol / TSTRIDE < T_STAGES ? acol / TSTRIDE : T_STAGES;
+  const int chains = (Kp >> 3) < C ? (Kp >> 3) : C;      // chains that hold a partial sum
   SSF_DYN_SMEM(float, sm);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int kc4 = Kp >> 2;
   float *raw = sm;
-  float *b_base = sm + TC_M * Kp;                // stage s: hi at s*2*64*Kp, lo right after
-  uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (TC_M + 2 * nb * TC_N) * Kp);
+  float *b_base = sm + TC_M * Kp;                // stage s: hi at s*2*NR*Kp, lo right after
+  uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (TC_M + 2 * nb * NR) * Kp);
   uint32_t *tmem_holder = reinterpret_cast<uint32_t *>(bars + BK_NBARS);
+  volatile int *sched = reinterpret_cast<volatile int *>(tmem_holder + 1);     // [BK_SR] published items
   const uint32_t b_full = smem_u32(bars), b_empty = smem_u32(bars + BK_MAXB);
   const uint32_t t_full = smem_u32(bars + 2 * BK_MAXB), t_empty = smem_u32(bars + 2 * BK_MAXB + T_STAGES);
   const uint32_t raw_full = smem_u32(bars + 2 * BK_MAXB + 2 * T_STAGES), raw_free = raw_full + 8;
   const uint32_t a_ready = raw_full + 16, a_free = raw_full + 24;
-  const uint32_t stage_bytes = (uint32_t)(2 * TC_N * Kp * sizeof(float));
-  constexpr int CT = tile_columns(MODE);         // slab columns per 64-row coefficient tile
+  const uint32_t sched_full = raw_full + 32, sched_empty = sched_full + 8 * BK_SR;
+  const uint32_t stage_bytes = (uint32_t)(2 * NR * Kp * sizeof(float));
+  constexpr int CT = tile_columns(MODE);         // slab columns per coefficient tile
   const int64_t n_ct = (ncol + CT - 1) / CT;
 
   if (tid == BK_EPI * 32) {
@@ -552,6 +636,10 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
     mbar_init(raw_free, BK_CONV * 32);
     mbar_init(a_ready, BK_CONV * 32);
     mbar_init(a_free, 1);
+    for (int i = 0; i < BK_SR; ++i) {
+      mbar_init(sched_full + 8 * i, 1);
+      mbar_init(sched_empty + 8 * i, BK_CONSUMERS);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == BK_EPI + 1) {
@@ -566,85 +654,119 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
 
-  // every role walks the same list of items: item -> (pixel tile, first column tile, tile count)
+  // item -> (pixel tile, first column tile, tile count)
 #define BK_ITEM(item, pix0, ct0, nt)                                                   \
-  const int64_t pix0 = ((item) / chunks) * TC_M;                                       \
-  const int64_t ct0 = ((item) % chunks) * (int64_t)tiles_per_chunk;                    \
+  const int64_t pix0 = (int64_t)((item) / chunks) * TC_M;                              \
+  const int64_t ct0 = (int64_t)((item) % chunks) * tiles_per_chunk;                    \
   const int nt = (int)((ct0 + tiles_per_chunk <= n_ct ? ct0 + tiles_per_chunk : n_ct) - ct0)
+  // consumers: the j-th item of this CTA (every lane of the warp reads it, lane 0 frees the slot)
+#define BK_NEXT_ITEM(j, item)                                                          \
+  mbar_wait(sched_full + 8 * ((j) % BK_SR), ((j) / BK_SR) & 1);                        \
+  const int item = sched[(j) % BK_SR];                                                 \
+  __syncwarp();                                                                        \
+  if (lane == 0) mbar_arrive(sched_empty + 8 * ((j) % BK_SR))
 
   if (warp == BK_EPI) {
-    // ===== TMA lane: raw basis tile of the NEXT item, then the coefficient tiles of this one =====
+    // ===== TMA lane = scheduler: next item, its raw basis tile, the coefficient tiles of this one =====
     if (lane == 0) {
-      auto load_raw = [&](int64_t item) {
+      auto load_raw = [&](int item) {
         // one tensor-map copy: box = Kp direction rows x 128 pixels of Bt[ndir][npix]; rows beyond
         // ndir are out of bounds and arrive as zeros
-        const int64_t p0 = (item / chunks) * TC_M;
         mbar_expect_tx(raw_full, (uint32_t)Kp * TC_M * (uint32_t)sizeof(float));
-        tma_load_2d(smem_u32(raw), &bt_map, (int)p0, 0, raw_full);
+        tma_load_2d(smem_u32(raw), &bt_map, (item / chunks) * TC_M, 0, raw_full);
       };
-      load_raw(blockIdx.x);
+      auto publish = [&](int j, int item) {
+        const int slot = j % BK_SR;
+        if (j >= BK_SR) mbar_wait(sched_empty + 8 * slot, (j / BK_SR - 1) & 1);
+        sched[slot] = item;
+        mbar_arrive(sched_full + 8 * slot);        // release: the store above is visible to the waiters
+      };
+      // the item after the next is fetched while this item's tiles are issued: the atomic's
+      // round trip (a microsecond under a saturated store stream) is never waited for
+      int item = blockIdx.x;
+      int next = (int)gridDim.x + atomicAdd(next_item, 1);
+      if (next >= n_items) next = -1;
+      publish(0, item);
+      load_raw(item);
       uint32_t T = 0;
-      int j = 0;
-      for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++j) {
+      for (int j = 0; item >= 0; ++j) {
+        int next2 = -1;
+        if (next >= 0) next2 = (int)gridDim.x + atomicAdd(next_item, 1);
+        publish(j + 1, next);
+        bool raw_sent = next < 0;
         BK_ITEM(item, pix0, ct0, nt);
         (void)pix0;
-        if (item + gridDim.x < n_items) {
-          mbar_wait(raw_free, j & 1);                 // the converters have read this item's raw tile
-          load_raw(item + gridDim.x);
-        }
         for (int it = 0; it < nt; ++it, ++T) {
+          // the raw tile of the next item goes out as soon as the converters have read this one's
+          if (!raw_sent && mbar_test(raw_free, j & 1)) {
+            load_raw(next);
+            raw_sent = true;
+          }
           const int s = T % nb;
           if (T >= (uint32_t)nb) mbar_wait(b_empty + 8 * s, (T / nb - 1) & 1);
           mbar_expect_tx(b_full + 8 * s, stage_bytes);
-          bulk_g2s(smem_u32(b_base + (size_t)s * 2 * TC_N * Kp), Bs + (ct0 + it) * (2 * TC_N * Kp), stage_bytes,
+          bulk_g2s(smem_u32(b_base + (size_t)s * 2 * NR * Kp), Bs + (ct0 + it) * (2 * NR * Kp), stage_bytes,
                    b_full + 8 * s);
         }
+        if (!raw_sent) {
+          mbar_wait(raw_free, j & 1);
+          load_raw(next);
+        }
+        item = next;
+        next = next2 >= n_items ? -1 : next2;
       }
     }
-  } else if (warp == BK_EPI + 1) {
+  }
+  else if (warp == BK_EPI + 1) {
     // ===== MMA lane: A from tensor memory =====
-    if (lane == 0) {
-      const uint32_t lbo = 128, sbo = (uint32_t)kc4 * 128;
-      const uint32_t ta_hi = tmem_base + BK_ACOL, ta_lo = ta_hi + (uint32_t)Kp;
-      const int ksteps = Kp >> 3;
-      uint32_t T = 0;
-      int j = 0;
-      for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++j) {
-        BK_ITEM(item, pix0, ct0, nt);
-        (void)pix0;
-        (void)ct0;
-        mbar_wait(a_ready, j & 1);                    // split basis tile of this item is in TMEM
+    const uint32_t lbo = 128, sbo = (uint32_t)kc4 * 128;
+    const uint32_t ta_hi = tmem_base + (uint32_t)acol, ta_lo = ta_hi + (uint32_t)Kp;
+    const int ksteps = Kp >> 3;
+    uint32_t T = 0;
+    for (int j = 0;; ++j) {
+      BK_NEXT_ITEM(j, item);
+      if (item < 0) break;
+      if (lane != 0) continue;                      // the warp reads the scheduler slot, one lane issues
+      BK_ITEM(item, pix0, ct0, nt);
+      (void)pix0;
+      (void)ct0;
+      mbar_wait(a_ready, j & 1);                    // split basis tile of this item is in TMEM
+      tc_fence_after();
+      for (int it = 0; it < nt; ++it, ++T) {
+        const int s = T % nb, t = T % TS;
+        mbar_wait(b_full + 8 * s, (T / nb) & 1);
+        if (T >= (uint32_t)TS) mbar_wait(t_empty + 8 * t, (T / TS - 1) & 1);
         tc_fence_after();
-        for (int it = 0; it < nt; ++it, ++T) {
-          const int s = T % nb, t = T % T_STAGES;
-          mbar_wait(b_full + 8 * s, (T / nb) & 1);
-          if (T >= T_STAGES) mbar_wait(t_empty + 8 * t, (T / T_STAGES - 1) & 1);
-          tc_fence_after();
-          const float *bh = b_base + (size_t)s * 2 * TC_N * Kp;
-          const uint64_t db_hi = make_desc(smem_u32(bh), lbo, sbo), db_lo = make_desc(smem_u32(bh + TC_N * Kp), lbo, sbo);
-          const uint32_t d_tmem = tmem_base + (uint32_t)(t * TC_N);
-          for (int ks = 0; ks < ksteps; ++ks) {       // corrections first (see the kernel above)
-            const uint64_t adv = (uint64_t)(ks * 16);
-            const uint32_t ac = (uint32_t)(ks * 8);   // one K step = 8 TF32 = 8 TMEM columns of A
-            tc_mma_tf32_ts(d_tmem, ta_lo + ac, db_lo + adv, IDESC, ks > 0);
-            tc_mma_tf32_ts(d_tmem, ta_lo + ac, db_hi + adv, IDESC, 1);
-            tc_mma_tf32_ts(d_tmem, ta_hi + ac, db_lo + adv, IDESC, 1);
-          }
-          for (int ks = 0; ks < ksteps; ++ks)
-            tc_mma_tf32_ts(d_tmem, ta_hi + (uint32_t)(ks * 8), db_hi + (uint64_t)(ks * 16), IDESC, 1);
-          tc_commit(b_empty + 8 * s);
-          tc_commit(t_full + 8 * t);
-        }
-        tc_commit(a_free);                            // the basis operand may be overwritten
+        const float *bh = b_base + (size_t)s * 2 * NR * Kp;
+        const uint64_t db_hi = make_desc(smem_u32(bh), lbo, sbo), db_lo = make_desc(smem_u32(bh + NR * Kp), lbo, sbo);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(t * TSTRIDE);
+        // corrections first, K steps dealt onto the C accumulator chains (see chains_for);
+        // one K step = 8 TF32 = 8 TMEM columns of A = 16 in the descriptor's start-address field
+        for (int ks = 0; ks < ksteps; ++ks)
+          tc_mma_tf32_ts(d_tmem + (uint32_t)((ks % C) * NR), ta_lo + (uint32_t)(ks * 8), db_lo + (uint64_t)(ks * 16),
+                         IDESC, ks >= C);
+        for (int ks = 0; ks < ksteps; ++ks)
+          tc_mma_tf32_ts(d_tmem + (uint32_t)((ks % C) * NR), ta_lo + (uint32_t)(ks * 8), db_hi + (uint64_t)(ks * 16),
+                         IDESC, 1);
+        for (int ks = 0; ks < ksteps; ++ks)
+          tc_mma_tf32_ts(d_tmem + (uint32_t)((ks % C) * NR), ta_hi + (uint32_t)(ks * 8), db_lo + (uint64_t)(ks * 16),
+                         IDESC, 1);
+        for (int ks = 0; ks < ksteps; ++ks)
+          tc_mma_tf32_ts(d_tmem + (uint32_t)((ks % C) * NR), ta_hi + (uint32_t)(ks * 8), db_hi + (uint64_t)(ks * 16),
+                         IDESC, 1);
+        tc_commit(b_empty + 8 * s);
+        tc_commit(t_full + 8 * t);
       }
+      tc_commit(a_free);                            // the basis operand may be overwritten
     }
   } else if (warp >= BK_EPI + 2) {
     // ===== converter warps: raw[k][row] -> split operand in TMEM, thread = pixel row = TMEM lane =====
     const int cw = warp & 3;                          // the TMEM lane quadrant this warp may touch
     const int r = 32 * cw + lane;
-    const uint32_t ta_hi = tmem_base + ((uint32_t)(32 * cw) << 16) + BK_ACOL, ta_lo = ta_hi + (uint32_t)Kp;
-    int j = 0;
-    for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++j) {
+    const uint32_t ta_hi = tmem_base + ((uint32_t)(32 * cw) << 16) + (uint32_t)acol, ta_lo = ta_hi + (uint32_t)Kp;
+    for (int j = 0;; ++j) {
+      BK_NEXT_ITEM(j, item);
+      if (item < 0) break;
       mbar_wait(raw_full, j & 1);
       if (j > 0) mbar_wait(a_free, (j - 1) & 1);
       tc_fence_after();
@@ -668,22 +790,29 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
     // ===== epilogue warps: group g = warp / 8 takes the tiles T with T % 2 == g =====
     const int g = warp >> 3, q = warp & 3, h = (warp >> 2) & 1;
     uint32_t T = 0;
-    for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x) {
+    for (int j = 0;; ++j) {
+      BK_NEXT_ITEM(j, item);
+      if (item < 0) break;
       BK_ITEM(item, pix0, ct0, nt);
       const int64_t pix = pix0 + 32 * q + lane;
       for (int it = 0; it < nt; ++it, ++T) {
         if ((int)(T & 1) != g) continue;
-        const int t = T % T_STAGES;
-        mbar_wait(t_full + 8 * t, (T / T_STAGES) & 1);
+        const int t = T % TS;
+        mbar_wait(t_full + 8 * t, (T / TS) & 1);
         tc_fence_after();
         const int64_t c0 = (ct0 + it) * CT;
         if (MODE == 2) {
           // gain: this warp's 32 pixels x slab columns c0 + 8 h .. + 7, three accumulator groups
           float ph[8], ax[8], ay[8];
-          const uint32_t ta = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TC_N + 8 * h);
+          const uint32_t ta = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TSTRIDE + 8 * h);
           tmem_ld8(ta, ph);
           tmem_ld8(ta + 16, ax);
           tmem_ld8(ta + 32, ay);
+          for (int c = 1; c < chains; ++c) {
+            tmem_add8(ta + (uint32_t)(c * NR), ph);
+            tmem_add8(ta + (uint32_t)(c * NR) + 16, ax);
+            tmem_add8(ta + (uint32_t)(c * NR) + 32, ay);
+          }
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(t_empty + 8 * t);
@@ -693,7 +822,11 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
           continue;
         }
         float v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TC_N + 32 * h), v);
+        tmem_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TSTRIDE + 32 * h), v);
+        for (int c = 1; c < chains; ++c)
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            tmem_add8(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * TSTRIDE + c * NR + 32 * h + 8 * u), &v[8 * u]);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(t_empty + 8 * t);
@@ -714,6 +847,7 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
     }
   }
 #undef BK_ITEM
+#undef BK_NEXT_ITEM
 
   tc_fence_before();
   __syncthreads();
@@ -723,9 +857,20 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
   }
 }
 
-template <int MODE>
-int launch_bigk(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
-                ssf::OutFmt fmt, cudaMemPool_t pool, cudaStream_t stream);
+// Returns pool scratch to the stream-ordered pool on every exit path of a launcher.
+struct ScratchGuard {
+  void *ptr;
+  cudaStream_t stream;
+  ~ScratchGuard() {
+    if (ptr) cudaFreeAsync(ptr, stream);
+  }
+  int release() {
+    void *p = ptr;
+    ptr = nullptr;
+    SSF_CUDA(cudaFreeAsync(p, stream));
+    return SSF_OK;
+  }
+};
 
 // Column tiles per CTA.  Measured on B200 (profiles/r01c chunk sweeps): with the coefficient
 // tiles arriving by TMA the launch is fastest when a CTA covers about 256 slab columns (4 KL
@@ -743,48 +888,71 @@ int pick_tiles_per_cta(int ct, int Kp, int64_t n_ct) {
   return (int)(per < 1 ? 1 : per);
 }
 
+typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                             const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                             CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda), resolved once.
+EncodeFn tensor_map_encoder() {
+  static std::once_flag once;
+  static EncodeFn encode = nullptr;
+  std::call_once(once, [] {
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      encode = reinterpret_cast<EncodeFn>(fn);
+  });
+  return encode;
+}
+
 template <int MODE>
 int launch_bigk(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
                 ssf::OutFmt fmt, cudaMemPool_t pool, cudaStream_t stream) {
   constexpr int CT = tile_columns(MODE);
+  constexpr int NR = tile_rows(MODE);
   const int Kp = (ndir + 7) / 8 * 8;
   const int64_t n_ct = (ncol + CT - 1) / CT;
-  // 3 coefficient stages when they fit next to the raw basis tile (Kp <= 104), else 2
-  int nb = BK_MAXB;
-  size_t smem = sizeof(float) * (size_t)(TC_M + 2 * nb * TC_N) * Kp + 256;
-  if (smem > 227 * 1024) {
-    nb = 2;
-    smem = sizeof(float) * (size_t)(TC_M + 2 * nb * TC_N) * Kp + 256;
+  // as many coefficient stages as fit next to the raw basis tile (KL at Kp = 104: 3, gain: 4)
+  auto smem_for = [&](int stages) { return sizeof(float) * (size_t)(TC_M + 2 * stages * NR) * Kp + 512; };
+  int nb = 2;
+  while (nb < BK_MAXB && smem_for(nb + 1) <= 227 * 1024) ++nb;
+  if (const char *e = getenv("SSF_TC_NB")) {         // experiment hook: ring depth
+    const int want = atoi(e);
+    if (want >= 2 && want <= BK_MAXB && smem_for(want) <= 227 * 1024) nb = want;
   }
+  const size_t smem = smem_for(nb);
+  SSF_REQUIRE(smem <= 227 * 1024, "tcgen05 contraction: %d directions do not fit the persistent kernel", ndir);
+  // scratch: the split coefficient tiles, then the item counter of the dynamic schedule
+  const size_t bs_bytes = (sizeof(float) * (size_t)n_ct * 2 * NR * Kp + 255) / 256 * 256;
   float *Bs = nullptr;
-  SSF_CUDA(cudaMallocFromPoolAsync(reinterpret_cast<void **>(&Bs), sizeof(float) * (size_t)n_ct * 2 * TC_N * Kp, pool,
-                                   stream));
-  SSF_LAUNCH(split_b_kernel<MODE>, ssf::div_up(n_ct * TC_N * (Kp >> 2), 256), 256, 0, stream, G, ndir, ldg, ncol, Kp,
+  SSF_CUDA(cudaMallocFromPoolAsync(reinterpret_cast<void **>(&Bs), bs_bytes + 256, pool, stream));
+  ScratchGuard guard{Bs, stream};
+  int *next_item = reinterpret_cast<int *>(reinterpret_cast<char *>(Bs) + bs_bytes);
+  SSF_CUDA(cudaMemsetAsync(next_item, 0, sizeof(int), stream));
+  SSF_LAUNCH(split_b_kernel<MODE>, ssf::div_up(n_ct * NR * (Kp >> 2), 256), 256, 0, stream, G, ndir, ldg, ncol, Kp,
              n_ct, Bs);
   SSF_LAUNCHED();
+  const int sms = ssf::sm_count();
   // items: one per pixel tile, or column chunks of >= 4 tiles when there are few pixel tiles
+  // (about 8 items per SM at least, so that the dynamic schedule has something to balance)
   const int64_t pix_tiles = npix / TC_M;
   int64_t chunks = 1;
-  if (pix_tiles < 4 * 148) {
-    chunks = (4 * 148 + pix_tiles - 1) / pix_tiles;
+  if (pix_tiles < 8 * sms) {
+    chunks = (8 * sms + pix_tiles - 1) / pix_tiles;
     if (chunks > (n_ct + 3) / 4) chunks = (n_ct + 3) / 4;
     if (chunks < 1) chunks = 1;
+  }
+  if (const char *e = getenv("SSF_TC_PER")) {        // experiment hook: column tiles per item
+    const int64_t want = atoi(e);
+    if (want >= 1) chunks = (n_ct + want - 1) / want;
   }
   const int per = (int)((n_ct + chunks - 1) / chunks);
   chunks = (n_ct + per - 1) / per;
   const int64_t n_items = pix_tiles * chunks;
+  SSF_REQUIRE(n_items < (int64_t)1 << 30, "tcgen05 contraction: too many work items");
   // tensor map of the basis: [ndir rows][npix] float32, box = Kp rows x 128 pixels, no swizzle
-  typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
-                               const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
-                               CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-  static EncodeFn encode = nullptr;
-  if (!encode) {
-    void *fn = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    SSF_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
-    SSF_REQUIRE(fn != nullptr && qres == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled is not available");
-    encode = reinterpret_cast<EncodeFn>(fn);
-  }
+  const EncodeFn encode = tensor_map_encoder();
+  SSF_REQUIRE(encode != nullptr, "cuTensorMapEncodeTiled is not available");
   CUtensorMap bt_map;
   const cuuint64_t gdim[2] = {(cuuint64_t)npix, (cuuint64_t)ndir};
   const cuuint64_t gstride[1] = {(cuuint64_t)npix * sizeof(float)};
@@ -795,13 +963,11 @@ int launch_bigk(const float *Bt, const float *G, int ndir, int ldg, int64_t npix
                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   SSF_REQUIRE(cr == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d)", (int)cr);
   SSF_CUDA(cudaFuncSetAttribute(contract_tc_bigk_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int grid = (int)(n_items < 148 ? n_items : 148);
+  const int grid = (int)(n_items < sms ? n_items : sms);
   SSF_LAUNCH(contract_tc_bigk_kernel<MODE>, grid, BK_THREADS, smem, stream, bt_map, Bs, ndir, npix, ncol, slab, per,
-             (int)chunks, Kp, nb, n_items, fmt);
+             (int)chunks, Kp, nb, (int)n_items, next_item, fmt);
   SSF_LAUNCHED();
-  cudaError_t fe = cudaFreeAsync(Bs, stream);
-  SSF_CUDA(fe);
-  return SSF_OK;
+  return guard.release();
 }
 
 // Stream-ordered scratch for the split coefficient tiles, from a library-private memory pool
@@ -828,13 +994,12 @@ cudaMemPool_t scratch_pool(int device) {
 
 template <int MODE, int NEPI>
 int launch_kernel(const float *Bt, const float *Bs, int ndir, int64_t npix, int64_t ncol, float *slab, int Kp,
-                  size_t smem, int per_sm, ssf::OutFmt fmt, cudaStream_t stream) {
+                  size_t smem, int nb, ssf::OutFmt fmt, cudaStream_t stream) {
   constexpr int CT = tile_columns(MODE);
   auto kfn = contract_tc_kernel<MODE, NEPI>;
   SSF_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int pix_tiles = (int)(npix / TC_M);
   const int64_t n_ct = (ncol + CT - 1) / CT;
-  (void)per_sm;
   int per = pick_tiles_per_cta(CT, Kp, n_ct);
   if (const char *e = getenv("SSF_TC_PER")) {      // experiment hook: column tiles per CTA
     per = atoi(e);
@@ -843,7 +1008,7 @@ int launch_kernel(const float *Bt, const float *Bs, int ndir, int64_t npix, int6
   }
   const int gx = (int)((n_ct + per - 1) / per);
   dim3 grid(gx, pix_tiles);
-  SSF_LAUNCH(kfn, grid, (NEPI + 2) * 32, smem, stream, Bt, Bs, ndir, npix, ncol, slab, per, Kp, fmt);
+  SSF_LAUNCH(kfn, grid, (NEPI + 2) * 32, smem, stream, Bt, Bs, ndir, npix, ncol, slab, per, Kp, nb, fmt);
   SSF_LAUNCHED();
   return SSF_OK;
 }
@@ -852,11 +1017,25 @@ template <int MODE>
 int launch_tc(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
               ssf::OutFmt fmt, cudaStream_t stream) {
   constexpr int CT = tile_columns(MODE);
+  constexpr int NR = tile_rows(MODE);
   const int Kp = (ndir + 7) / 8 * 8;
   const int64_t n_ct = (ncol + CT - 1) / CT;
   if (n_ct == 0) return SSF_OK;
-  const size_t smem = sizeof(float) * (size_t)(2 * TC_M + 2 * B_STAGES * TC_N) * Kp + 128;
-  const int per_sm = 2 * (smem + 1024) <= 227 * 1024 ? 2 : 1;
+  // + the mbarriers (N_BARS x 8 B), the TMEM base address and slack
+  auto smem_for = [&](int stages) { return sizeof(float) * (size_t)(2 * TC_M + 2 * stages * NR) * Kp + 8 * N_BARS + 64; };
+  const int per_sm = 2 * (smem_for(2) + 1024) <= 227 * 1024 ? 2 : 1;
+  // Ring depth of the coefficient tiles: as deep as two resident CTAs allow.  A stage is only
+  // re-armed when the MMAs that read it have retired, and its refill then has to come from L2
+  // through a memory system saturated with stores (microseconds); the small gain tiles (32 KB of
+  // cube per tile) need 3 stages to ride that out, the 128 KB KL tiles are fine with 2.
+  int nb = 2;
+  if (per_sm == 2)
+    while (nb < B_MAX && 2 * (smem_for(nb + 1) + 1024) <= 227 * 1024) ++nb;
+  if (const char *e = getenv("SSF_TC_NB")) {         // experiment hook: ring depth
+    const int want = atoi(e);
+    if (want >= 2 && want <= B_MAX && smem_for(want) + 1024 <= 227 * 1024) nb = want;
+  }
+  const size_t smem = smem_for(nb);
 
   int device = 0;
   SSF_CUDA(cudaGetDevice(&device));
@@ -870,16 +1049,17 @@ int launch_tc(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, 
     if ((per_sm == 1 && !never) || always) return launch_bigk<MODE>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, pool, stream);
   }
   float *Bs = nullptr;
-  const size_t bs_bytes = sizeof(float) * (size_t)n_ct * 2 * TC_N * Kp;
+  const size_t bs_bytes = sizeof(float) * (size_t)n_ct * 2 * NR * Kp;
   SSF_CUDA(cudaMallocFromPoolAsync(reinterpret_cast<void **>(&Bs), bs_bytes, pool, stream));
-  const int64_t n_thr = n_ct * TC_N * (Kp >> 2);
+  ScratchGuard guard{Bs, stream};
+  const int64_t n_thr = n_ct * NR * (Kp >> 2);
   SSF_LAUNCH(split_b_kernel<MODE>, ssf::div_up(n_thr, 256), 256, 0, stream, G, ndir, ldg, ncol, Kp, n_ct, Bs);
   SSF_LAUNCHED();
-  int rc = per_sm == 2 ? launch_kernel<MODE, 8>(Bt, Bs, ndir, npix, ncol, slab, Kp, smem, per_sm, fmt, stream)
-                       : launch_kernel<MODE, 16>(Bt, Bs, ndir, npix, ncol, slab, Kp, smem, per_sm, fmt, stream);
-  cudaError_t fe = cudaFreeAsync(Bs, stream);
-  if (rc == SSF_OK) SSF_CUDA(fe);
-  return rc;
+  const int rc = 2 * (smem + 1024) <= 227 * 1024
+                     ? launch_kernel<MODE, 8>(Bt, Bs, ndir, npix, ncol, slab, Kp, smem, nb, fmt, stream)
+                     : launch_kernel<MODE, 16>(Bt, Bs, ndir, npix, ncol, slab, Kp, smem, nb, fmt, stream);
+  if (rc != SSF_OK) return rc;
+  return guard.release();
 }
 
 }  // namespace

@@ -4,6 +4,8 @@
 #include <string.h>
 
 #include <atomic>
+#include <thread>
+#include <vector>
 
 #include "common.cuh"
 
@@ -20,6 +22,20 @@ void set_error(const char *fmt, ...) {
   va_end(ap);
 }
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+int sm_count() {
+#ifdef SSF_CPU_EMU
+  return 148;
+#else
+  static std::atomic<int> cached[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  int n = cached[dev].load(std::memory_order_relaxed);
+  if (n > 0) return n;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n < 1) n = 148;
+  cached[dev].store(n, std::memory_order_relaxed);
+  return n;
+#endif
+}
 }  // namespace ssf
 
 extern "C" int ssf_version(void) { return 100; }
@@ -64,6 +80,55 @@ extern "C" int ssf_copy_rows_d2h(void *dst_host, int64_t dst_pitch, const void *
     SSF_CUDA(cudaMemcpy2DAsync(dst_host, (size_t)dst_pitch, src_dev, (size_t)src_pitch, (size_t)width_bytes,
                                (size_t)rows, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
   }
+  return SSF_OK;
+}
+
+// Host-side placement of a staged slab into the (memory-mapped) FITS cube: column c of `src`
+// (src_bytes) goes to dst + c * copies * src_bytes, `copies` times back to back.  Threads take
+// contiguous runs of columns; memcpy switches to streaming stores for copies of this size, and
+// the first touch of the pages of a fresh tmpfs / page-cache mapping (the dominant cost) runs in
+// parallel -- unlike pwrite calls on one file, which serialise on the inode lock.
+extern "C" int ssf_host_place(void *dst, const void *src, int64_t ncol, int64_t src_bytes, int copies,
+                              int threads) {
+  SSF_REQUIRE(dst && src, "ssf_host_place: null pointer");
+  SSF_REQUIRE(ncol >= 0 && src_bytes >= 0 && copies >= 1 && copies <= 4, "ssf_host_place: bad sizes");
+  if (ncol == 0 || src_bytes == 0) return SSF_OK;
+  const int64_t total = ncol * src_bytes;
+  int nt = threads < 1 ? 1 : threads > 64 ? 64 : threads;
+  // at least ~4 MiB per thread
+  if ((int64_t)nt > (total >> 22) + 1) nt = (int)((total >> 22) + 1);
+  char *d = static_cast<char *>(dst);
+  const char *s = static_cast<const char *>(src);
+  // a thread's share is a byte range of the SOURCE (so that few very large columns, e.g. 2048^2
+  // SKA-Low planes, still spread over all threads), mapped piecewise onto the destination
+  auto work = [=](int64_t lo, int64_t hi) {
+    const int64_t piece = 1 << 21;
+    for (int64_t p = lo; p < hi;) {
+      const int64_t c = p / src_bytes, within = p - c * src_bytes;
+      int64_t n = src_bytes - within;
+      if (n > hi - p) n = hi - p;
+      if (n > piece) n = piece;
+      for (int k = 0; k < copies; ++k) memcpy(d + (c * copies + k) * src_bytes + within, s + p, (size_t)n);
+      p += n;
+    }
+  };
+  if (nt == 1) {
+    work(0, total);
+    return SSF_OK;
+  }
+  std::vector<std::thread> pool;
+  pool.reserve(nt);
+  try {
+    for (int i = 0; i < nt; ++i) {
+      const int64_t lo = total * i / nt / 64 * 64, hi = i + 1 == nt ? total : total * (i + 1) / nt / 64 * 64;
+      pool.emplace_back(work, lo, hi);
+    }
+  } catch (...) {
+    for (auto &t : pool) t.join();
+    ssf::set_error("ssf_host_place: could not start a worker thread");
+    return SSF_EINVAL;
+  }
+  for (auto &t : pool) t.join();
   return SSF_OK;
 }
 

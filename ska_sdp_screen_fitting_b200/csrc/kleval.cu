@@ -176,7 +176,7 @@ extern "C" int ssf_kl_coeffs(const double *white, int64_t ncol, int ndir, const 
   if (smem > 48 * 1024)
     SSF_CUDA(cudaFuncSetAttribute(coeffs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int64_t blocks = (ncol + cpb - 1) / cpb;
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks > ssf::sm_count() * 8) blocks = ssf::sm_count() * 8;
   SSF_LAUNCH(coeffs_kernel, (int)blocks, 128, smem, (cudaStream_t)stream, white, ncol, ndir, C, G, ldg, cpb);
   SSF_LAUNCHED();
   return SSF_OK;
@@ -248,7 +248,7 @@ extern "C" int ssf_kl_eval_gain(const float *Bt, const float *G3, int ndir, int 
     return ssf::contract_tc_gain(Bt, G3, ndir, ldg, npix, ncol, slab, fmt, (cudaStream_t)stream);
   const int64_t pix_tiles = (npix + 4 * GAIN_THREADS - 1) / (4 * GAIN_THREADS);
   // enough column chunks for ~8 CTAs per SM; a chunk keeps its basis tile in L1 across columns
-  int64_t chunks = (148 * 8 + pix_tiles - 1) / pix_tiles;
+  int64_t chunks = (ssf::sm_count() * 8 + pix_tiles - 1) / pix_tiles;
   if (chunks > ncol) chunks = ncol;
   if (chunks > 65535) chunks = 65535;
   const int64_t per = (ncol + chunks - 1) / chunks;

@@ -57,8 +57,8 @@ __host__ __device__ inline size_t smem_doubles(int nall) {
 
 // One screen fit at `order` (stationscreen.py:501-590, phase type).  Whole CTA participates.
 // On return s.wh/s.fall hold the results: white_out/resid_out are written to global.
-// Returns false (for all threads) if the weights need the general pinv (some weight in
-// (0, cut]) -- not supported by the Cholesky path.
+// Weights all equal: closed form; all > cut: Cholesky solve; some weight in (0, cut]: the general
+// pinv by one-sided Jacobi (below).  Always returns true (kept for the callers' status plumbing).
 __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restrict__ pp, int nall,
                          int n, int k, double r0sq, double half_beta, double cut,
                          double *__restrict__ white_out, double *__restrict__ resid_out, int kind) {
@@ -99,8 +99,90 @@ __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restr
     s.zs[tid] = as;
   }
   __syncthreads();
-  if (!sh_ok) return false;
-  if (sh_uniform) {
+  const bool general = !sh_ok;          // uniform over the CTA
+  if (general) {
+    // Some weight lies in (0, cut]: A = U_k^T W U_k may have eigenvalues <= cut, which
+    // pinv(A, rcond=1e-3) drops (:501-504; absolute cutoff).  One-sided (Hestenes) Jacobi on
+    // B = W^(1/2) U_k  (A = B^T B = V S^2 V^T): rotating column pairs until they are orthogonal
+    // gives B' = B V with |b'_j|^2 = lambda_j, and with g = W^(1/2) r
+    //     U_k pinv(A) U_k^T W r = W^(-1/2) B' diag(lambda_j > cut ? 1 / lambda_j : 0) B'^T g,
+    // so V never has to be formed: B lives in s.A (n k <= nall^2 doubles), y is produced here.
+    for (int e = tid; e < n * k; e += FT) {
+      const int i = e / k, j = e - i * k;
+      s.A[e] = sqrt(s.wc[i]) * pt.U[i * ld + j];
+    }
+    __shared__ int sh_rotated;
+    const int warp = tid >> 5, lane = tid & 31, m = k + (k & 1);
+    for (int sweep = 0; sweep < 40; ++sweep) {
+      __syncthreads();
+      if (tid == 0) sh_rotated = 0;
+      __syncthreads();
+      for (int step = 0; step < m - 1; ++step) {
+        // round-robin tournament: m / 2 disjoint column pairs per step, one warp per pair
+        for (int pr = warp; pr < m / 2; pr += FT / 32) {
+          int p = pr == 0 ? m - 1 : (step + pr) % (m - 1);
+          int q = pr == 0 ? step : (step - pr + m - 1) % (m - 1);
+          if (p >= k || q >= k) continue;
+          if (p > q) {
+            const int t = p;
+            p = q;
+            q = t;
+          }
+          double al = 0.0, be = 0.0, ga = 0.0;
+          for (int i = lane; i < n; i += 32) {
+            const double bp = s.A[i * k + p], bq = s.A[i * k + q];
+            al = fma(bp, bp, al);
+            be = fma(bq, bq, be);
+            ga = fma(bp, bq, ga);
+          }
+          for (int o = 16; o; o >>= 1) {
+            al += __shfl_xor_sync(0xffffffffu, al, o);
+            be += __shfl_xor_sync(0xffffffffu, be, o);
+            ga += __shfl_xor_sync(0xffffffffu, ga, o);
+          }
+          if (fabs(ga) <= 1e-13 * sqrt(al * be)) continue;      // uniform over the warp (lambda errs by ~ga^2)
+          if (lane == 0) sh_rotated = 1;
+          const double zeta = (be - al) / (2.0 * ga);
+          const double t = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+          const double c = 1.0 / sqrt(1.0 + t * t), sn = c * t;
+          for (int i = lane; i < n; i += 32) {
+            const double bp = s.A[i * k + p], bq = s.A[i * k + q];
+            s.A[i * k + p] = c * bp - sn * bq;
+            s.A[i * k + q] = sn * bp + c * bq;
+          }
+        }
+        __syncthreads();
+      }
+      if (!sh_rotated) break;
+    }
+    __syncthreads();
+    // coefficients a_j = (b'_j . g) / lambda_j for lambda_j > cut, else 0 (both right-hand sides)
+    if (tid < k) {
+      double lam = 0.0, yc = 0.0, ys = 0.0;
+      for (int i = 0; i < n; ++i) {
+        const double b = s.A[i * k + tid], sw = sqrt(s.wc[i]);
+        lam = fma(b, b, lam);
+        yc = fma(b, sw * s.rc[i], yc);
+        ys = fma(b, sw * s.rs[i], ys);
+      }
+      const double inv = lam > cut ? 1.0 / lam : 0.0;
+      s.zc[tid] = yc * inv;
+      s.zs[tid] = ys * inv;
+    }
+    __syncthreads();
+    // y = U_k pinv(A) z = W^(-1/2) B' a
+    if (tid < n) {
+      double ac = 0.0, as = 0.0;
+      for (int j = 0; j < k; ++j) {
+        const double b = s.A[tid * k + j];
+        ac = fma(b, s.zc[j], ac);
+        as = fma(b, s.zs[j], as);
+      }
+      const double isw = 1.0 / sqrt(s.wc[tid]);
+      s.yc[tid] = ac * isw;
+      s.ys[tid] = as * isw;
+    }
+  } else if (sh_uniform) {
     // A = w0 U_k^T U_k = w0 I  ->  pinv(A) = I / w0 when w0 > cut, else 0   (:501-504)
     if (tid < k) {
       double w0 = s.wc[0];
@@ -148,7 +230,7 @@ __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restr
   }
   __syncthreads();
   // y = U_k z
-  if (tid < n) {
+  if (!general && tid < n) {
     double ac = 0.0, as = 0.0;
     for (int j = 0; j < k; ++j) {
       double u = pt.U[tid * ld + j];
@@ -534,7 +616,7 @@ extern "C" int ssf_kl_fit_pass(const double *phase, const float *weights, const 
   size_t smem = sizeof(double) * smem_doubles(ndir);
   if (smem > 48 * 1024)
     SSF_CUDA(cudaFuncSetAttribute(fit_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int64_t blocks = nsys < 148 * 16 ? nsys : 148 * 16;
+  int64_t blocks = nsys < ssf::sm_count() * 16 ? nsys : ssf::sm_count() * 16;
   SSF_LAUNCH(fit_pass_kernel, (int)blocks, FT, smem, (cudaStream_t)stream, phase, weights, pat, pp, ndir,
              nsys, C, pinvC, U, r0 * r0, beta / 2.0, pinv_cut, mode, order, station_order, white, resid,
              status);
@@ -548,7 +630,7 @@ extern "C" int ssf_kl_flag_outliers(const double *resid, float *weights, int ndi
   SSF_REQUIRE(ndir >= 1 && ndir <= SSF_MAX_DIR, "ssf_kl_flag_outliers: ndir out of range");
   if (nsys <= 0) return SSF_OK;
   int64_t blocks = (nsys + 3) / 4;
-  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (blocks > ssf::sm_count() * 16) blocks = ssf::sm_count() * 16;
   SSF_LAUNCH(flag_kernel, (int)blocks, 128, 0, (cudaStream_t)stream, resid, weights, ndir, nsys, nsigma,
              masks_out);
   SSF_LAUNCHED();
@@ -571,7 +653,7 @@ extern "C" int ssf_kl_flag_outliers_amp(const double *val, const double *resid, 
     SSF_LAUNCHED();
   }
   int64_t blocks = (nsys + 3) / 4;
-  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (blocks > ssf::sm_count() * 16) blocks = ssf::sm_count() * 16;
   SSF_LAUNCH(amp_flag_kernel, (int)blocks, 128, 0, (cudaStream_t)stream, val, resid, weights, ndir, nsys, ngroups,
              nsigma, flag ? (const double *)group_std : (const double *)nullptr, masks_out);
   SSF_LAUNCHED();

@@ -8,7 +8,9 @@
 namespace {
 
 constexpr int MAX_RADIUS = 1024;
-__constant__ float c_w[2 * MAX_RADIUS + 1];
+// The taps travel as a per-call device buffer (stream-ordered allocation), not a __constant__
+// symbol: two calls with different sigma on different streams or threads must not share state.
+// Every block copies them to shared memory first; all lanes then read the same word (broadcast).
 
 // scipy 'reflect': (d c b a | a b c d | d c b a), any distance outside the line.
 __device__ __forceinline__ int reflect(int i, int n) {
@@ -22,8 +24,10 @@ __device__ __forceinline__ int reflect(int i, int n) {
 // Block 32 (x) by TY (y) threads; smem [(TY + 2r)][32].
 template <int TY>
 __global__ void ypass_kernel(const float *__restrict__ in, float *__restrict__ out, int ny, int nx,
-                             int r) {
-  SSF_DYN_SMEM(float, tile);
+                             int r, const float *__restrict__ taps) {
+  SSF_DYN_SMEM(float, c_w);                          // [2r + 1] taps, then the tile
+  float *tile = c_w + 2 * r + 1;
+  for (int k = threadIdx.y * 32 + threadIdx.x; k <= 2 * r; k += 32 * TY) c_w[k] = taps[k];
   const int64_t img = blockIdx.z;
   const float *src = in + img * (int64_t)ny * nx;
   float *dst = out + img * (int64_t)ny * nx;
@@ -46,8 +50,10 @@ __global__ void ypass_kernel(const float *__restrict__ in, float *__restrict__ o
 // x pass, shared-memory variant: block = one row segment of TX outputs.
 template <int TX>
 __global__ void xpass_smem_kernel(const float *__restrict__ in, float *__restrict__ out, int ny,
-                                  int nx, int r) {
-  SSF_DYN_SMEM(float, row);
+                                  int nx, int r, const float *__restrict__ taps) {
+  SSF_DYN_SMEM(float, c_w);                          // [2r + 1] taps, then the row segment
+  float *row = c_w + 2 * r + 1;
+  for (int k = threadIdx.x; k <= 2 * r; k += TX) c_w[k] = taps[k];
   const int64_t img = blockIdx.z;
   const int y = blockIdx.y;
   const float *src = in + (img * ny + y) * (int64_t)nx;
@@ -66,7 +72,10 @@ __global__ void xpass_smem_kernel(const float *__restrict__ in, float *__restric
 // x pass, warp-shuffle halo exchange (r <= 8): a warp owns 32 - 2r outputs of one row; it
 // loads 32 consecutive (reflected) pixels, one per lane, and every tap is a shuffle.
 __global__ void xpass_shfl_kernel(const float *__restrict__ in, float *__restrict__ out, int ny,
-                                  int nx, int r) {
+                                  int nx, int r, const float *__restrict__ taps) {
+  __shared__ float c_w[17];                          // r <= 8
+  if (threadIdx.x <= 2 * r) c_w[threadIdx.x] = taps[threadIdx.x];
+  __syncthreads();
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int span = 32 - 2 * r;
@@ -107,8 +116,15 @@ extern "C" int ssf_gauss_smooth(float *images, int64_t nimg, int ny, int nx, dou
     sum += dw[k + r];
   }
   for (int k = 0; k <= 2 * r; ++k) hw[k] = (float)(dw[k] / sum);
-  SSF_CUDA(cudaMemcpyToSymbolAsync(c_w, hw, sizeof(float) * (2 * r + 1), 0,
-                                   cudaMemcpyHostToDevice, stream));
+  float *taps = nullptr;
+  SSF_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&taps), sizeof(float) * (2 * r + 1), stream));
+  struct Free {
+    float *p;
+    cudaStream_t s;
+    ~Free() { cudaFreeAsync(p, s); }
+  } free_taps{taps, stream};
+  // pageable source: the runtime stages it before the call returns, so hw may be reused at once
+  SSF_CUDA(cudaMemcpyAsync(taps, hw, sizeof(float) * (2 * r + 1), cudaMemcpyHostToDevice, stream));
   // gridDim.z is limited to 65535 images per launch
   for (int64_t i0 = 0; i0 < nimg; i0 += 65535) {
     int nz = (int)((nimg - i0) < 65535 ? (nimg - i0) : 65535);
@@ -117,24 +133,24 @@ extern "C" int ssf_gauss_smooth(float *images, int64_t nimg, int ny, int nx, dou
     {
       constexpr int TY = 16;
       dim3 grid(ssf::div_up(nx, 32), ssf::div_up(ny, TY), nz), block(32, TY);
-      size_t smem = sizeof(float) * 32 * (TY + 2 * r);
+      size_t smem = sizeof(float) * (32 * (TY + 2 * r) + 2 * r + 1);
       SSF_REQUIRE(smem <= 200 * 1024, "ssf_gauss_smooth: radius too large for the y tile");
       if (smem > 48 * 1024)
         SSF_CUDA(cudaFuncSetAttribute(ypass_kernel<TY>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)smem));
-      SSF_LAUNCH(ypass_kernel<TY>, grid, block, smem, stream, img, tmp, ny, nx, r);
+      SSF_LAUNCH(ypass_kernel<TY>, grid, block, smem, stream, img, tmp, ny, nx, r, taps);
       SSF_LAUNCHED();
     }
     if (r <= 8) {
       const int span = 32 - 2 * r, warps = 8;
       dim3 grid(ssf::div_up(ssf::div_up(nx, span), warps), ny, nz);
-      SSF_LAUNCH(xpass_shfl_kernel, grid, warps * 32, 0, stream, tmp, img, ny, nx, r);
+      SSF_LAUNCH(xpass_shfl_kernel, grid, warps * 32, 0, stream, tmp, img, ny, nx, r, taps);
       SSF_LAUNCHED();
     } else {
       constexpr int TX = 256;
       dim3 grid(ssf::div_up(nx, TX), ny, nz);
-      size_t smem = sizeof(float) * (TX + 2 * r);
-      SSF_LAUNCH(xpass_smem_kernel<TX>, grid, TX, smem, stream, tmp, img, ny, nx, r);
+      size_t smem = sizeof(float) * (TX + 2 * r + 2 * r + 1);
+      SSF_LAUNCH(xpass_smem_kernel<TX>, grid, TX, smem, stream, tmp, img, ny, nx, r, taps);
       SSF_LAUNCHED();
     }
   }

@@ -196,7 +196,7 @@ __global__ void bswap32_kernel(uint32_t *__restrict__ data, int64_t n) {
 
 int grid_for(int64_t work, int threads, int ctas_per_sm) {
   int64_t blocks = (work + threads - 1) / threads;
-  int64_t cap = (int64_t)148 * ctas_per_sm;
+  int64_t cap = (int64_t)ssf::sm_count() * ctas_per_sm;
   return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
 }
 

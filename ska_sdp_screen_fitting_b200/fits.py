@@ -10,7 +10,10 @@ written at their byte offset as they come off the GPU, so a cube never has to ex
 memory and every byte is written once (the reference writes the cube twice,
 screen.py:331-334 then :381-382).
 """
+import ctypes
+import mmap
 import os
+import threading
 import time
 
 import numpy as np
@@ -117,12 +120,80 @@ class CubeWriter:
         self._row_bytes = int(np.prod(self.shape[1:])) * 4
         data_bytes = self.shape[0] * self._row_bytes
         self._total = len(self._head) + data_bytes + (-data_bytes) % BLOCK
+        self._map = None
+        self._map_view = None
+        self._alloc_thread = None
+        self._alloc_front = 0                        # bytes [_alloc_lo, _alloc_front) have their pages
+        self._alloc_lo = 0
+        self._alloc_stop = False
+        self._alloc_cv = threading.Condition()
         if create:
-            self._fd = os.open(path, os.O_WRONLY | os.O_CREAT | os.O_TRUNC, 0o644)
+            self._fd = os.open(path, os.O_RDWR | os.O_CREAT | os.O_TRUNC, 0o644)
             os.pwrite(self._fd, self._head, 0)
             os.ftruncate(self._fd, self._total)      # zero padding to a whole block
         else:
-            self._fd = os.open(path, os.O_WRONLY)
+            self._fd = os.open(path, os.O_RDWR)
+
+    def mapped_address(self):
+        """Address of a shared read-write mapping of the whole file (made on first use), or None
+        where the file system cannot map it.  Copies into the mapping from several threads fault
+        the pages of a fresh tmpfs / page-cache file in parallel; ``pwrite`` calls on one file
+        take turns on the inode lock (measured: profiles/r02_file_sink.txt)."""
+        if self._map is None:
+            try:
+                self._map = mmap.mmap(self._fd, self._total, mmap.MAP_SHARED, mmap.PROT_READ | mmap.PROT_WRITE)
+            except (OSError, ValueError):
+                self._map = False
+                return None
+            self._map_view = np.frombuffer(self._map, np.uint8)
+        return int(self._map_view.ctypes.data) if self._map else None
+
+    def preallocate(self, c0, ncol, chunk=64 << 20):
+        """Starts a background thread that allocates the pages of columns [c0, c0 + ncol) ahead of
+        the writers, ``fallocate`` call by call.  On a tmpfs / page-cache file the first touch of
+        a page is the expensive part of placing a slab: measured on the GPU boxes
+        (profiles/r02_file_sink.txt), threads faulting pages in through a mapping top out at
+        ~8 GB/s however many they are, one fallocate stream allocates 15 GB/s, and copies into
+        pages that exist run at 30-40 GB/s.  Silently does nothing where the file system has no
+        fallocate (the raw system call: glibc's posix_fallocate emulation would race with the
+        writers)."""
+        col_bytes = int(np.prod(self.shape[3:])) * 4
+        lo = len(self._head) + c0 * col_bytes
+        hi = lo + ncol * col_bytes
+        try:
+            libc = ctypes.CDLL(None, use_errno=True)
+            fallocate = libc.fallocate
+            fallocate.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int64, ctypes.c_int64]
+            fallocate.restype = ctypes.c_int
+        except (OSError, AttributeError):
+            return
+        self._alloc_lo = self._alloc_front = lo
+        fd = self._fd
+
+        def run():
+            pos = lo
+            while pos < hi and not self._alloc_stop:
+                n = min(chunk, hi - pos)
+                if fallocate(fd, 0, pos, n) != 0:       # not supported / no space: the writers will fault
+                    pos = hi
+                else:
+                    pos += n
+                with self._alloc_cv:
+                    self._alloc_front = pos
+                    self._alloc_cv.notify_all()
+            with self._alloc_cv:
+                self._alloc_front = hi
+                self._alloc_cv.notify_all()
+
+        self._alloc_thread = threading.Thread(target=run, name="ssf-fallocate", daemon=True)
+        self._alloc_thread.start()
+
+    def _wait_allocated(self, end):
+        if self._alloc_thread is None:
+            return
+        with self._alloc_cv:
+            while self._alloc_front < end and self._alloc_thread.is_alive():
+                self._alloc_cv.wait(0.05)
 
     def write_times(self, t0, slab, already_big_endian=False):
         """slab: array whose leading axis is time, starting at time index ``t0``."""
@@ -140,7 +211,7 @@ class CubeWriter:
         while done < nbytes:                         # pwrite caps at ~2 GiB per call
             done += os.pwrite(self._fd, view[done:done + (1 << 30)], off + done)
 
-    def write_columns(self, c0, slab, already_big_endian=False, pairs=False, pool=None):
+    def write_columns(self, c0, slab, already_big_endian=False, pairs=False, pool=None, place=None):
         """slab: whole (time, freq, antenna) columns -- [ncol, 4, ny, nx] -- starting at the flat
         column index ``c0`` = (t * n_freq + f) * n_ant + a.  The cube is column-major in exactly
         that order (processing_utils.py:190-194), so any run of columns is one byte range.
@@ -150,7 +221,10 @@ class CubeWriter:
         half is placed twice with one gathered write (``pwritev``), so the copy that crossed
         PCIe is half the file.  ``pool``: a ThreadPoolExecutor; the columns are split among its
         workers (``pwrite`` releases the GIL; one thread fills a tmpfs / page cache at only a few
-        GB/s).  Returns the seconds spent writing."""
+        GB/s).  ``place``: ``callable(dst_address, src_address, ncol, src_bytes, copies)`` -- the
+        library's multi-threaded ``ssf_host_place``; used with a shared mapping of the file
+        instead of the write calls wherever the file can be mapped.  Returns the seconds spent
+        writing."""
         arr = np.ascontiguousarray(slab)
         if arr.dtype.itemsize != 4:
             raise TypeError("slab must be a 4-byte type")
@@ -167,6 +241,13 @@ class CubeWriter:
         view = memoryview(arr).cast("B")
         base = len(self._head)
         fd = self._fd
+        if place is not None:
+            address = self.mapped_address()
+            if address is not None:
+                t_begin = time.perf_counter()
+                self._wait_allocated(base + (c0 + ncol) * col_bytes)
+                place(address + base + c0 * col_bytes, int(arr.ctypes.data), ncol, src_bytes, 2 if pairs else 1)
+                return time.perf_counter() - t_begin
 
         def run(lo, hi):
             if not pairs:
@@ -203,6 +284,14 @@ class CubeWriter:
         return time.perf_counter() - t_begin
 
     def close(self):
+        if self._alloc_thread is not None:
+            self._alloc_stop = True
+            self._alloc_thread.join()
+            self._alloc_thread = None
+        if self._map:
+            self._map_view = None
+            self._map.close()
+        self._map = None
         if self._fd is not None:
             os.close(self._fd)
             self._fd = None

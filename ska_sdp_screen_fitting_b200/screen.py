@@ -125,6 +125,7 @@ class Screen:
         self.block_columns = 24576       # columns handed to write() at a time by _blocks
         self.host_buffers = 3            # pinned staging buffers between the copy stream and the file
         self.write_threads = min(16, os.cpu_count() or 1)   # parallel pwrite calls per staged slab
+        self.file_mapping = True         # place slabs by threaded copies into a mapping of the file (else pwritev)
         self.sink = "file"               # "null": stop at the pinned host buffer (benchmarks: link vs file system)
         self.aterm_type = "gain"         # "tec": 5-axis dTEC cube (KLScreen on a soltab of type tec)
         self.timings = {}
@@ -353,6 +354,12 @@ class Screen:
         flush_q = queue.Queue()
         failure = []
         pool = ThreadPoolExecutor(max(1, int(self.write_threads))) if self.sink == "file" else None
+        n_place = max(1, int(self.write_threads))
+
+        def place(dst, src, n_columns, src_bytes, copies):
+            # multi-threaded copies into the shared mapping of the file (ssf_host_place; the call
+            # releases the GIL, so the main thread keeps issuing slabs meanwhile)
+            eng._call("ssf_host_place", dst, src, n_columns, src_bytes, copies, n_place)
 
         def flusher():
             while True:
@@ -367,7 +374,8 @@ class Screen:
                         if writer is not None and not failure:
                             data = host_ring[hb][:ncol * planes * npix].numpy().view(">f4")
                             stats["pwrite_s"] += writer.write_columns(col_rel, data, already_big_endian=True,
-                                                                      pairs=planes == 2, pool=pool)
+                                                                      pairs=planes == 2, pool=pool,
+                                                                      place=place if self.file_mapping else None)
                             stats["file_bytes"] += ncol * 4 * file_planes * npix
                     except BaseException as exc:  # noqa: BLE001 - surfaced by the caller
                         failure.append(exc)
@@ -396,6 +404,8 @@ class Screen:
                         dist.barrier()
                     if rank != 0:
                         writer = fits.CubeWriter(outfile, shape, cards, create=False)
+                    if self.file_mapping and my1 > my0:
+                        writer.preallocate((my0 - g_start) * per_t, (my1 - my0) * per_t)
                 for r0, _r1, cols_all, amp_all in self._blocks(local0, local0 + (my1 - my0)):
                     col_base = (my0 - g_start + (r0 - local0)) * per_t     # first column of the block in the file
                     for c0 in range(0, cols_all.shape[0], step):

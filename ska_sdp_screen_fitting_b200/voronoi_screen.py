@@ -35,6 +35,7 @@ class VoronoiScreen(Screen):
         # (0 * NaN would carry a NaN beyond the filter radius in the linear form)
         self.smooth_mode = "auto"
         self._has_nan = None                  # set by fit(); None = look at every slab
+        self._amp_finite = None               # gain solutions: all amplitudes finite (looked at once)
         self.patch_radec = None               # optional [ndir, 2] deg override of the sky model
         self._tmpl_dev = None
         self._tmpl_key = None
@@ -132,13 +133,19 @@ class VoronoiScreen(Screen):
     # ------------------------------------------------------------------ fill
     def _use_linear(self, smooth_pix, cols=None):
         """Whether a smoothed slab takes the linear (contraction) form."""
-        if not (bool(smooth_pix) and smooth_pix > 0) or not self.phase_only:
+        if not (bool(smooth_pix) and smooth_pix > 0):
             return False
         if self.smooth_mode != "auto":
             return self.smooth_mode == "linear"
         has_nan = self._has_nan
         if has_nan is None:
             has_nan = cols is None or bool(torch.isnan(cols).any().item())
+        if not self.phase_only and not has_nan:
+            # gain solutions: a non-finite amplitude (NaN, or inf from a zero in log space)
+            # would spread through the linear form just like a NaN phase; looked at once per run
+            if self._amp_finite is None:
+                self._amp_finite = self._dev_amp is not None and bool(torch.isfinite(self._dev_amp).all().item())
+            has_nan = not self._amp_finite
         # tiny images (the repo's 17 x 17 test geometry) stay on the reference's own order of
         # operations: nothing to gain there, and it is the tighter parity
         return (not has_nan) and self._tmpl_dev.numel() >= 128 * 128
@@ -154,6 +161,10 @@ class VoronoiScreen(Screen):
             return _lib.OUT_BIG_ENDIAN | _lib.OUT_PLANES2, 2
         return _lib.OUT_BIG_ENDIAN, 4
 
+    def interpolate(self, interp_kind="nearest"):
+        super().interpolate(interp_kind)
+        self._amp_finite = None
+
     def _fill_columns(self, cols, slab, cellsize_deg, out_dir, smooth_pix, fix_nan, amp=None, out_flags=0):
         self._prepare(cellsize_deg, out_dir)
         eng = self.engine
@@ -163,6 +174,19 @@ class VoronoiScreen(Screen):
             # gain solutions: XX / YY amplitudes on planes 0-1 / 2-3 (voronoi_screen.py:177-214);
             # smoothing in the reference's own order of operations (screen.py:353-378)
             lut4 = eng.voronoi_lut_gain(cols.contiguous(), amp.contiguous())
+            if smooth and self._use_linear(smooth_pix, cols):
+                # smoothing is linear in each of the four planes.  Seen as 2 x ncol "columns" of
+                # one plane pair each -- (c, XX) -> planes 0, 1 and (c, YY) -> planes 2, 3 of
+                # column c -- a gain slab IS a plane-pair slab of the phase-only contraction, so
+                # the same tcgen05 kernel serves it at the same 16 B/voxel instead of the 64 B of
+                # filtering the slab in place
+                ncol, n_d = cols.shape
+                lut_pairs = lut4.view(ncol, n_d, 2, 2).permute(0, 2, 1, 3).contiguous().view(2 * ncol, n_d, 2)
+                if out_flags & _lib.OUT_PLANES2:
+                    raise ValueError("gain slabs have four different planes")
+                eng.voronoi_contract(self._smoothed_indicators(smooth_pix), lut_pairs, slab,
+                                     out_flags=out_flags | _lib.OUT_PLANES2)
+                return
             if smooth and out_flags:
                 raise ValueError("the direct smoothing path needs native 4-plane slabs")
             eng.voronoi_fill_gain(self._tmpl_dev, lut4, slab, fix_nan=fix_nan and not smooth, out_flags=out_flags)

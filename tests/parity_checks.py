@@ -186,6 +186,35 @@ def check_fit(eng, seed=7, n_t=3, n_f=2, n_a=5, n_d=40):
     return scr, out
 
 
+def check_fit_small_weights(eng, seed=41, n_t=3, n_f=2, n_a=4, n_d=24):
+    """Weights in (0, 1e-3]: U_k^T W U_k can have eigenvalues at or below the cutoff of
+    pinv(..., rcond=1e-3) (stationscreen.py:501-504), which then drops them.  The kernel takes
+    its general (one-sided Jacobi) path for such systems; against the port's scipy pinv."""
+    val, weight, dirs, pos = synthetic_fit_case(seed, n_t, n_f, n_a, n_d, flag_fraction=0.02)
+    rng = np.random.default_rng(seed + 1)
+    weight = weight.astype(np.float64)
+    weight[weight > 0] = rng.uniform(0.5, 2.0, int((weight > 0).sum()))
+    # station 1: a handful of tiny weights (all eigenvalues stay above the cutoff);
+    # station 2: all but 5 directions tiny, order capped at 20 > 5 -> eigenvalues below the
+    # cutoff are dropped; one system with every weight tiny -> pinv = 0 -> zero screen
+    tiny = rng.random((n_t, n_f, n_d)) < 0.2
+    weight[:, :, 1, :] = np.where(tiny & (weight[:, :, 1, :] > 0), 3e-4, weight[:, :, 1, :])
+    keep = rng.permutation(n_d)[:5]
+    w2 = np.full((n_t, n_f, n_d), 5e-4)
+    w2[:, :, keep] = 1.0
+    weight[:, :, 2, :] = np.where(weight[:, :, 2, :] > 0, w2, 0.0)
+    weight[0, 0, 2, :] = 2e-4
+    weight = weight.astype(np.float32)
+    scr = run_engine_fit(eng, val, weight, dirs, pos)
+    ref = klfit.get_reference_station(weight, 10)
+    out = klfit.run_phase(val, weight.copy(), dirs, pos, ref, min(20, n_d - 1))
+    assert np.array_equal(scr.screen_order, out["order"])
+    assert np.array_equal(scr.weights_out, out["weights"])
+    assert np.abs(scr.vals_ph - out["screen"]).max() < TOL_FIT * 10
+    assert np.abs(scr.residuals - out["resid"]).max() < TOL_FIT * 10
+    return scr, out
+
+
 def check_fit_amplitude(eng, seed=23, n_t=6, n_f=2, n_a=4, n_d=24):
     """Amplitude-type fit (log10 screens, per-station rms clip over all times, niter=3)
     against the port of stationscreen.run / _process_station / _fit_screen."""
@@ -345,6 +374,56 @@ def check_voronoi_gain(eng, n=20, n_d=7, ncol=13, seed=19):
         assert np.array_equal(slab.cpu().numpy(), want, equal_nan=True)
         expect_formats(slab.cpu().numpy(), lambda flags, planes: eng.voronoi_fill_gain(
             tmpl, lut4, eng.empty((ncol, planes, n, n), torch.float32), fix, flags).cpu().numpy(), planes2=False)
+
+
+def check_smoothed_voronoi_gain(eng, n=24, n_d=6, n_t=3, sigma=1.5, seed=23, variant=0):
+    """Smoothed gain Voronoi through linearity (a gain slab seen as 2 x ncol plane pairs of the
+    phase-only contraction, VoronoiScreen._fill_columns) against the reference's order of
+    operations -- fill, gaussian_filter per plane, NaN fix (voronoi_screen.py:177-214,
+    screen.py:353-378) -- from the float64 oracle, and against the direct device path."""
+    from ska_sdp_screen_fitting_b200.voronoi_screen import VoronoiScreen
+
+    rng = np.random.default_rng(seed)
+    want_t = screens.nearest_patch_template(rng.uniform(0, n, n_d), rng.uniform(0, n, n_d), n)
+    ncol = n_t * 2
+    phases = rng.normal(0, 1.0, (ncol, n_d))
+    amp = rng.uniform(0.5, 1.5, (ncol, n_d, 2))
+    want = screens.voronoi_make_matrix(want_t, phases, amp).astype(np.float32)
+    want = screens.nan_fix(np.stack([screens.smooth_block(want[c], sigma) for c in range(ncol)]))
+
+    def screen(mode):
+        scr = VoronoiScreen("g", None, None, 0.0, 0.0, 1.0, 1.0, amplitude_soltab_name="amplitude000")
+        scr._engine = eng
+        scr.smooth_mode = mode
+        scr._tmpl_dev = eng.tensor(want_t, torch.int32)
+        scr._tmpl_key = "fixed"
+        scr._prepare = lambda *a: None
+        scr.source_names = [f"p{i}" for i in range(n_d)]
+        scr._has_nan = False
+        scr._dev_amp = eng.tensor(amp, torch.float64)
+        return scr
+
+    cols, amps = eng.tensor(phases, torch.float64), eng.tensor(amp, torch.float64)
+    got = {}
+    for mode in ("linear", "direct"):
+        scr = screen(mode)
+        slab = eng.empty((ncol, 4, n, n), torch.float32)
+        scr._fill_columns(cols, slab, 0.1, None, sigma, True, amp=amps)
+        got[mode] = slab.cpu().numpy()
+        err = np.abs(got[mode] - want).max()
+        assert err < 2 * TOL_SMOOTH, (mode, err)
+    assert screen("auto")._use_linear(sigma, cols) == (n * n >= 128 * 128)
+    # a non-finite amplitude sends the automatic choice to the direct form
+    bad = screen("auto")
+    bad._tmpl_dev = eng.tensor(np.ones((128, 128), np.int32), torch.int32)
+    assert bad._use_linear(sigma, cols)
+    amp_bad = amp.copy()
+    amp_bad[0, 0, 0] = np.inf
+    bad = screen("auto")
+    bad._tmpl_dev = eng.tensor(np.ones((128, 128), np.int32), torch.int32)
+    bad._dev_amp = eng.tensor(amp_bad, torch.float64)
+    assert not bad._use_linear(sigma, cols)
+    return float(np.abs(got["linear"] - got["direct"]).max())
 
 
 def gain_solutions(golden_dir, repo_solutions):

@@ -22,6 +22,10 @@ def test_pattern_cache_under_pressure(emu_engine):
     pc.check_pattern_cache_pressure(emu_engine)
 
 
+def test_fit_with_weights_below_the_pinv_cutoff(emu_engine):
+    pc.check_fit_small_weights(emu_engine)
+
+
 def test_fit_with_flags_and_outliers(emu_engine):
     pc.check_fit(emu_engine)
 
@@ -119,6 +123,10 @@ def test_smoothed_voronoi_both_forms(emu_engine):
     pc.check_smoothed_voronoi(emu_engine, n=16, ncol=3)
     pc.check_smoothed_voronoi(emu_engine, n=32, n_d=7, ncol=10, seed=7)      # tiled contraction
     pc.check_smoothed_voronoi(emu_engine, n=32, n_d=55, ncol=9, seed=8)
+
+
+def test_smoothed_gain_voronoi_linear_form(emu_engine):
+    pc.check_smoothed_voronoi_gain(emu_engine)
 
 
 def test_bswap_and_nanfix(emu_engine):

@@ -56,6 +56,10 @@ def test_soltab_write_back(gpu_engine, golden_dir, tmp_path):
     pc.check_soltab_write_back(gpu_engine, golden_dir, tmp_path, full=True)
 
 
+def test_fit_with_weights_below_the_pinv_cutoff(gpu_engine):
+    pc.check_fit_small_weights(gpu_engine)
+
+
 def test_fit_with_flags_and_outliers(gpu_engine):
     pc.check_fit(gpu_engine)
     pc.check_fit(gpu_engine, seed=17, n_t=6, n_f=3, n_a=8, n_d=45)
@@ -171,6 +175,14 @@ def test_smoothed_voronoi_both_forms(gpu_engine):
     pc.check_smoothed_voronoi(gpu_engine, n=64, n_d=45, ncol=100, sigma=2.0, seed=7, variant=1)
 
 
+def test_smoothed_gain_voronoi_linear_form(gpu_engine):
+    """Gain slabs through the tcgen05 plane-pair contraction (variant auto: 128 x 128 is the
+    smallest image it takes) and through the SIMT contraction, against the float64 oracle."""
+    pc.check_smoothed_voronoi_gain(gpu_engine)
+    diff = pc.check_smoothed_voronoi_gain(gpu_engine, n=128, n_d=45, n_t=20, sigma=2.5, seed=29)
+    assert diff < 2 * pc.TOL_SMOOTH
+
+
 def test_bswap_and_nanfix(gpu_engine):
     pc.check_bswap_nanfix(gpu_engine)
 
@@ -244,10 +256,10 @@ def test_streamed_kl_slabs_match_the_whole_fit(gpu_engine):
     """KLScreen.stream_slabs (grouped fits on a side stream issued by a helper thread, ragged
     last group) gives the same cube slabs as one fit over all time slots followed by the
     evaluation -- the fit systems are independent across time (stationscreen.py:681-722)."""
-    from ska_sdp_screen_fitting_b200 import synthetic
+    import synthetic_cases
     from ska_sdp_screen_fitting_b200.kl_screen import KLScreen
 
-    case = synthetic.make_case("small", seed=11, n_times=10, flag_fraction=0.05)
+    case = synthetic_cases.make_case("small", seed=11, n_times=10, flag_fraction=0.05)
     sol = case.solutions
     eng = gpu_engine
     kl = KLScreen("t", None, None, case.rad, case.dec, case.width_deg, case.width_deg)
