@@ -534,7 +534,7 @@ def run_e2e(args, eng, res, dist, rank, world):
     ``Screen.write()`` (what ``make_aterm_image`` runs, make_aterm_images.py:146-153) on an
     in-memory ``Solutions`` record -- per block of time slots the H2D copy of its val / weight, the
     fit, the evaluation in FITS byte order, the D2H copy of the slab on a copy stream, and the
-    placement of every byte in the output FITS file on tmpfs by parallel gathered writes.  With N
+    placement of every byte in the output FITS file on tmpfs by threaded copies into a mapping of the file.  With N
     ranks the ranks share one cube and each writes the byte range of its own time slots."""
     import shutil
 
@@ -645,9 +645,14 @@ def run_e2e(args, eng, res, dist, rank, world):
             "planes_copied": tm["planes_copied"], "out_flags": tm["out_flags"],
             "pipeline": {"columns_per_slab": slab_cols, "host_buffers": tm["host_buffers"],
                          "write_threads": tm["write_threads"], "process_s": t_proc,
-                         "write_s": tm["write_s"], "pwrite_busy_s": tm["pwrite_s"],
-                         "pwrite_GBps_while_busy": tm["file_bytes"] / max(tm["pwrite_s"], 1e-9) / 1e9,
-                         "wait_for_staging_buffer_s": tm["flush_wait_s"]},
+                         "write_s": tm["write_s"], "placement_busy_s": tm["pwrite_s"],
+                         "file_GBps_while_placing": tm["file_bytes"] / max(tm["pwrite_s"], 1e-9) / 1e9,
+                         "wait_for_staging_buffer_s": tm["flush_wait_s"],
+                         "placement": "ssf_host_place: threaded copies into a shared mapping of the FITS file, each "
+                                      "plane pair placed twice",
+                         "sink_limit": "first touch of tmpfs pages: 8-10 GB/s on these boxes whatever the method "
+                                       "(profiles/r02_file_sink.txt); `without_file` is the same pipeline up to the "
+                                       "pinned host buffer"},
             "without_file": {"value": voxels / sec_null, "seconds": sec_null,
                              "d2h_GBps": s_null.timings["d2h_bytes"] / sec_null / 1e9,
                              "note": "same pipeline, sink = pinned host buffer: separates the link from the file system"},

@@ -127,6 +127,113 @@ def main():
             b = fn(fd, t)
             os.close(fd)
             say(f"{name:18s}  {t:7d}  {nbytes / a / 1e9:10.2f}  {nbytes / b / 1e9:12.2f}")
+    # ---- combinations: who allocates the pages, who maps them, who copies
+    libc = ctypes.CDLL(None, use_errno=True)
+    libc.fallocate.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int64, ctypes.c_int64]
+    libc.madvise.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]
+    MADV_POPULATE_WRITE = 23
+
+    def mapped(fd):
+        mm = mmap.mmap(fd, nbytes, mmap.MAP_SHARED, mmap.PROT_READ | mmap.PROT_WRITE)
+        return mm, np.frombuffer(mm, np.uint8)
+
+    def copy_threads(dst, t, gate=None):
+        def work(lo, hi):
+            step = 1 << 25
+            for p in range(lo, hi, step):
+                q = min(hi, p + step)
+                if gate is not None:
+                    gate(q)
+                np.copyto(dst[p:q], src[p:q])
+        with ThreadPoolExecutor(t) as pool:
+            for f in [pool.submit(work, lo, hi) for lo, hi in bounds(t)]:
+                f.result()
+
+    import threading
+    for t in (8, 16):
+        # (a) one fallocate of everything, then copies
+        fd = fresh()
+        t0 = time.perf_counter()
+        libc.fallocate(fd, 0, 0, nbytes)
+        t1 = time.perf_counter()
+        mm, dst = mapped(fd)
+        copy_threads(dst, t)
+        t2 = time.perf_counter()
+        del dst
+        mm.close()
+        os.close(fd)
+        say(f"fallocate then copy, {t:2d} threads: fallocate {nbytes / (t1 - t0) / 1e9:.2f} GB/s, copy "
+            f"{nbytes / (t2 - t1) / 1e9:.2f} GB/s, together {nbytes / (t2 - t0) / 1e9:.2f} GB/s")
+        # (b) fallocate thread running ahead in 64 MiB calls, copies in SEQUENTIAL 256 MiB slabs behind it
+        fd = fresh()
+        front = [0]
+        cv = threading.Condition()
+
+        def allocator():
+            pos = 0
+            while pos < nbytes:
+                n = min(64 << 20, nbytes - pos)
+                libc.fallocate(fd, 0, pos, n)
+                pos += n
+                with cv:
+                    front[0] = pos
+                    cv.notify_all()
+        mm, dst = mapped(fd)
+        t0 = time.perf_counter()
+        th = threading.Thread(target=allocator)
+        th.start()
+        slab = 256 << 20
+        with ThreadPoolExecutor(t) as pool:
+            for s0 in range(0, nbytes, slab):
+                s1 = min(nbytes, s0 + slab)
+                with cv:
+                    while front[0] < s1:
+                        cv.wait()
+                edges = [s0 + (s1 - s0) * i // t // 4096 * 4096 for i in range(t)] + [s1]
+                for f in [pool.submit(np.copyto, dst[a:b], src[a:b]) for a, b in zip(edges[:-1], edges[1:])]:
+                    f.result()
+        th.join()
+        t1 = time.perf_counter()
+        del dst
+        mm.close()
+        os.close(fd)
+        say(f"fallocate thread ahead + slab copies, {t:2d} threads: {nbytes / (t1 - t0) / 1e9:.2f} GB/s")
+        # (c) MADV_POPULATE_WRITE by the copy threads on their own 32 MiB pieces, then the copy
+        fd = fresh()
+        mm, dst = mapped(fd)
+        base = dst.ctypes.data
+
+        def populate(q_unused, _state={}):
+            return None
+        def work_pop(lo, hi):
+            step = 1 << 25
+            for p in range(lo, hi, step):
+                q = min(hi, p + step)
+                libc.madvise(ctypes.c_void_p(base + p), q - p, MADV_POPULATE_WRITE)
+                np.copyto(dst[p:q], src[p:q])
+        t0 = time.perf_counter()
+        with ThreadPoolExecutor(t) as pool:
+            for f in [pool.submit(work_pop, lo, hi) for lo, hi in bounds(t)]:
+                f.result()
+        t1 = time.perf_counter()
+        del dst
+        mm.close()
+        os.close(fd)
+        say(f"madvise(POPULATE_WRITE) + copy per 32 MiB piece, {t:2d} threads: {nbytes / (t1 - t0) / 1e9:.2f} GB/s")
+        # (d) fallocate of everything, then madvise populate + copy
+        fd = fresh()
+        t0 = time.perf_counter()
+        libc.fallocate(fd, 0, 0, nbytes)
+        mm, dst = mapped(fd)
+        base = dst.ctypes.data
+        with ThreadPoolExecutor(t) as pool:
+            for f in [pool.submit(work_pop, lo, hi) for lo, hi in bounds(t)]:
+                f.result()
+        t1 = time.perf_counter()
+        del dst
+        mm.close()
+        os.close(fd)
+        say(f"fallocate, then madvise(POPULATE_WRITE) + copy, {t:2d} threads: together {nbytes / (t1 - t0) / 1e9:.2f} GB/s")
     # fallocate first (one call allocates and zeroes all pages under the inode lock)
     fd = fresh()
     t0 = time.perf_counter()

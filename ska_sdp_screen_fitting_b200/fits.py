@@ -154,9 +154,10 @@ class CubeWriter:
         a page is the expensive part of placing a slab: measured on the GPU boxes
         (profiles/r02_file_sink.txt), threads faulting pages in through a mapping top out at
         ~8 GB/s however many they are, one fallocate stream allocates 15 GB/s, and copies into
-        pages that exist run at 30-40 GB/s.  Silently does nothing where the file system has no
-        fallocate (the raw system call: glibc's posix_fallocate emulation would race with the
-        writers)."""
+        pages that exist run at 30-40 GB/s -- but the two together (one after the other, or the
+        allocator running ahead) still end at 8-10 GB/s, so Screen.write leaves this off by
+        default.  Silently does nothing where the file system has no fallocate (the raw system
+        call: glibc's posix_fallocate emulation would race with the writers)."""
         col_bytes = int(np.prod(self.shape[3:])) * 4
         lo = len(self._head) + c0 * col_bytes
         hi = lo + ncol * col_bytes

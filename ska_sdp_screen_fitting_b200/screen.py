@@ -66,16 +66,34 @@ def _interp_axis(x_old, values, axis, x_new, kind):
     return si.interp1d(x_old, values, axis=axis, kind=kind, fill_value="extrapolate")(x_new)
 
 
-def time_chunks(times):
+def time_chunks(times, max_times_per_file=None):
     """Output-file boundaries (screen.py:283-294): a new file wherever the time step exceeds
-    1.2 x the smallest step.  Returns the list of stop indices.  The reference's further,
-    free-memory dependent splits (screen.py:296-317) are deliberately not reproduced: slabs
-    are streamed, so memory never forces a file boundary and the file list is deterministic."""
+    1.2 x the smallest step.  Returns the list of stop indices.
+
+    The reference then halves any chunk longer than ``available memory / get_memory_usage``
+    time slots, repeatedly (screen.py:296-317): its file list depends on the free memory of the
+    machine it ran on.  Slabs are streamed here, so memory never forces a boundary and by
+    default the file list is a function of the time axis alone; ``max_times_per_file`` (the
+    reference's ``max_ntimes``) reproduces its extra splits for a given budget, with the same
+    first-oversized-chunk-first halving order."""
     times = np.asarray(times)
     if len(times) > 2:
         delta = times[1:] - times[:-1]
         gaps = np.where(delta > np.min(delta) * 1.2)[0] + 1
-        return [int(g) for g in gaps] + [len(times)]
+        stops = [int(g) for g in gaps] + [len(times)]
+        if max_times_per_file:
+            limit = max(1, int(max_times_per_file))
+            again = True
+            while again:
+                again = False
+                start = 0
+                for k, stop in enumerate(list(stops)):
+                    if stop - start > limit:
+                        stops.insert(k, start + (stop - start) // 2)
+                        again = True
+                        break
+                    start = stop
+        return stops
     return [len(times)]
 
 
@@ -124,7 +142,10 @@ class Screen:
         self.slab_bytes = 1 << 30        # device slab budget for write() (two slabs are in flight)
         self.block_columns = 24576       # columns handed to write() at a time by _blocks
         self.host_buffers = 3            # pinned staging buffers between the copy stream and the file
-        self.write_threads = min(16, os.cpu_count() or 1)   # parallel pwrite calls per staged slab
+        self.write_threads = min(8, os.cpu_count() or 1)    # placement threads per staged slab (tmpfs page allocation
+                                                            # stops scaling at 8: profiles/r02_file_sink.txt)
+        self.max_times_per_file = None   # reference's memory-driven extra file splits (screen.py:296-317), opt-in
+        self.preallocate = False         # fallocate thread ahead of the placement (no gain on tmpfs: profiles/r02_file_sink.txt)
         self.file_mapping = True         # place slabs by threaded copies into a mapping of the file (else pwritev)
         self.sink = "file"               # "null": stop at the pinned host buffer (benchmarks: link vs file system)
         self.aterm_type = "gain"         # "tec": 5-axis dTEC cube (KLScreen on a soltab of type tec)
@@ -229,7 +250,7 @@ class Screen:
         over the concatenation of those ranges."""
         rank, world, _ = _dist_info()
         chunks, ranges, g_start, local = [], [], 0, 0
-        for g_stop in time_chunks(times):
+        for g_stop in time_chunks(times, self.max_times_per_file):
             my0, my1 = split_range(g_start, g_stop, world, rank)
             chunks.append((g_start, g_stop, my0, my1, local))
             ranges.append((my0, my1))
@@ -404,7 +425,7 @@ class Screen:
                         dist.barrier()
                     if rank != 0:
                         writer = fits.CubeWriter(outfile, shape, cards, create=False)
-                    if self.file_mapping and my1 > my0:
+                    if self.file_mapping and self.preallocate and my1 > my0:
                         writer.preallocate((my0 - g_start) * per_t, (my1 - my0) * per_t)
                 for r0, _r1, cols_all, amp_all in self._blocks(local0, local0 + (my1 - my0)):
                     col_base = (my0 - g_start + (r0 - local0)) * per_t     # first column of the block in the file

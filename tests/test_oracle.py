@@ -426,3 +426,31 @@ def test_port_fit_at_real_direction_counts_against_the_reference(tag):
     for f, a in ((0, 1), (1, 5)):
         data = screens.kl_make_matrix(x[ix], y[ix], out["pp"], out["screen"][:, f, a, :])
         assert np.abs(data.astype(np.float32) - g["cube_sample"][:, f, a]).max() < 1e-6
+
+
+def test_memory_driven_file_splits_follow_the_reference_rule():
+    """screen.py:296-317: chunks longer than max_ntimes are halved, first oversized chunk first,
+    until none is left.  Opt-in here (``Screen.max_times_per_file``); restated inline."""
+    from ska_sdp_screen_fitting_b200.screen import time_chunks
+
+    def reference_rule(times, max_ntimes):
+        delta = times[1:] - times[:-1]
+        gaps_ind = np.append(np.where(delta > np.min(delta) * 1.2)[0] + 1, np.array([len(times)]))
+        check_gaps = True
+        while check_gaps:
+            check_gaps = False
+            g_start = 0
+            for gnum, g_stop in enumerate(gaps_ind.copy()):
+                if g_stop - g_start > max_ntimes:
+                    gaps_ind = np.insert(gaps_ind, gnum, np.array([g_start + int((g_stop - g_start) / 2)]))
+                    check_gaps = True
+                    break
+                g_start = g_stop
+        return [int(g) for g in gaps_ind]
+
+    times = np.arange(100.0) * 8.0
+    times[40:] += 100.0
+    times[77:] += 50.0
+    assert time_chunks(times) == [40, 77, 100]
+    for limit in (1, 3, 7, 16, 50, 1000):
+        assert time_chunks(times, limit) == reference_rule(times, limit)
