@@ -33,6 +33,7 @@ sys.path.insert(1, os.path.join(ROOT, "tests"))        # synthetic_cases: the se
 
 FIT_AHEAD = 2
 FIT_GROUP = 4      # slabs per fit call of the streaming KL path
+KL_WARM_SKALOW = 48   # slabs over which the SKA-Low KL pass warms the flag-pattern cache before the timed steps
 METRIC = "screen voxels/s (pix*ant*time*freq), KL & Voronoi"
 UNIT = "voxel/s"
 BYTES_PER_VOXEL = 16
@@ -259,7 +260,13 @@ def measure_workload(args, eng, dist, workload, steps, warmup, rank, local, part
     import torch
 
     slots = args.slots or auto_slots(workload)
-    n_steps = warmup + steps
+    # SKA-Low shape: at 1 % flags two thirds of the 100-direction systems carry a flag pattern and
+    # a cold pattern cache decomposes ~490 matrices per slab; after some tens of slabs the one- and
+    # two-flag patterns are cached and ~90 per slab are new.  A 2048-slot x 32-freq job has 65 536
+    # slabs, so the steady state is what the timed region should see: the KL pass warms the cache
+    # over KL_WARM_SKALOW slabs first (each warm-up step is a full fit + evaluation step).
+    kl_warm = max(warmup, KL_WARM_SKALOW) if workload == "skalow" else warmup
+    n_steps = kl_warm + steps
     # (FIT_AHEAD + 2) fit groups more than are evaluated: the pipelined KL path fits FIT_GROUP
     # slabs per call and keeps FIT_AHEAD groups (+ the one in flight) in front of the evaluation
     # through a bounded queue, so in steady state the fit never runs out of slabs during the K
@@ -284,7 +291,8 @@ def measure_workload(args, eng, dist, workload, steps, warmup, rank, local, part
     peak, peak_src = measured_peaks()
     kept = {}
 
-    def timed(step_fn, timer_keys):
+    def timed(step_fn, timer_keys, warmup=warmup):
+        n_steps = warmup + steps
         for i in range(warmup):
             step_fn(i)
         eng.check_fit_status()
@@ -349,7 +357,7 @@ def measure_workload(args, eng, dist, workload, steps, warmup, rank, local, part
             k, _ = next(stream)
             assert k == i
 
-        res = timed(kl_step, ["kl_eval", "kl_patterns_update", "kl_flag_outliers", "kl_fit_pass"])
+        res = timed(kl_step, ["kl_eval", "kl_patterns_update", "kl_flag_outliers", "kl_fit_pass"], warmup=kl_warm)
         stream.close()                        # stops the fit helper thread
         torch.cuda.synchronize()
         return res
@@ -359,6 +367,7 @@ def measure_workload(args, eng, dist, workload, steps, warmup, rank, local, part
         # side-stream spans (queueing behind the evaluation's CTAs + execution)
         fit_breakdown = {k: {"calls": kern[k][0], "mean_ms": kern[k][1]} for k in kern if k != "kl_eval"}
         fit_breakdown["pattern_slots_in_use"] = kl._patterns.stats()[0]
+        fit_breakdown["warmup_steps"] = kl_warm
         fit_breakdown["host_s"] = dict(eng.host_times)
         n_launch, k_ms = kern["kl_eval"]
         # the same kernel timed alone (no fit running beside it on the side stream): explains

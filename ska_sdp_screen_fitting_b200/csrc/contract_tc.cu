@@ -672,8 +672,15 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int kc4 = Kp >> 2;
   float *raw = sm;
+#ifdef SSF_BK_SS
+  // experiment: split basis operand in SHARED memory (canonical layout, SS-mode MMAs) instead of TMEM
+  float *a_hi_s = sm + TC_M * Kp, *a_lo_s = a_hi_s + TC_M * Kp;
+  float *b_base = sm + 3 * TC_M * Kp;
+  uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (3 * TC_M + 2 * nb * NR) * Kp);
+#else
   float *b_base = sm + TC_M * Kp;                // stage s: hi at s*2*NR*Kp, lo right after
   uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (TC_M + 2 * nb * NR) * Kp);
+#endif
   uint32_t *tmem_holder = reinterpret_cast<uint32_t *>(bars + BK_NBARS);
   volatile int *sched = reinterpret_cast<volatile int *>(tmem_holder + 1);     // [BK_SR] published items
   const uint32_t b_full = smem_u32(bars), b_empty = smem_u32(bars + BK_MAXB);
@@ -806,6 +813,17 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
           const uint32_t d_tmem = tmem_base + (uint32_t)(t * TSTRIDE);
           // corrections first, K steps dealt onto the C accumulator chains (see chains_for);
           // one K step = 8 TF32 = 8 TMEM columns of A = 16 in the descriptor's start-address field
+#ifdef SSF_BK_SS
+          {
+            const uint64_t da_hi = make_desc(smem_u32(a_hi_s), lbo, sbo), da_lo = make_desc(smem_u32(a_lo_s), lbo, sbo);
+            for (int ks = 0; ks < ksteps; ++ks)
+              tc_mma_tf32(d_tmem, da_lo + (uint64_t)(ks * 16), db_hi + (uint64_t)(ks * 16), IDESC, ks > 0);
+            for (int ks = 0; ks < ksteps; ++ks)
+              tc_mma_tf32(d_tmem, da_hi + (uint64_t)(ks * 16), db_lo + (uint64_t)(ks * 16), IDESC, 1);
+            for (int ks = 0; ks < ksteps; ++ks)
+              tc_mma_tf32(d_tmem, da_hi + (uint64_t)(ks * 16), db_hi + (uint64_t)(ks * 16), IDESC, 1);
+          }
+#else
           if (SSF_TC_PRODUCTS == 4)
             for (int ks = 0; ks < ksteps; ++ks)
               tc_mma_tf32_ts(d_tmem + (uint32_t)((ks % C) * NR), ta_lo + (uint32_t)(ks * 8),
@@ -819,6 +837,7 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
           for (int ks = 0; ks < ksteps; ++ks)
             tc_mma_tf32_ts(d_tmem + (uint32_t)((ks % C) * NR), ta_hi + (uint32_t)(ks * 8), db_hi + (uint64_t)(ks * 16),
                            IDESC, 1);
+#endif
           tc_commit(b_empty + 8 * s);
           tc_commit(t_full + 8 * t);
         }
@@ -846,11 +865,22 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
           hi[u] = to_tf32(x);
           lo[u] = to_tf32(x - hi[u]);
         }
+#ifdef SSF_BK_SS
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          a_hi_s[canon(r, k0 + u, kc4)] = hi[u];
+          a_lo_s[canon(r, k0 + u, kc4)] = lo[u];
+        }
+      }
+      fence_proxy_async();
+      tc_fence_before();
+#else
         tmem_st8(ta_hi + (uint32_t)k0, hi);
         tmem_st8(ta_lo + (uint32_t)k0, lo);
       }
       asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
       tc_fence_before();
+#endif
       mbar_arrive(raw_free);
       mbar_arrive(a_ready);
     }
@@ -982,7 +1012,11 @@ int launch_bigk(const float *Bt, const float *G, int ndir, int ldg, int64_t npix
   const int Kp = (ndir + 7) / 8 * 8;
   const int64_t n_ct = (ncol + CT - 1) / CT;
   // as many coefficient stages as fit next to the raw basis tile (KL at Kp = 104: 3, gain: 4)
+#ifdef SSF_BK_SS
+  auto smem_for = [&](int stages) { return sizeof(float) * (size_t)(3 * TC_M + 2 * stages * NR) * Kp + 512; };
+#else
   auto smem_for = [&](int stages) { return sizeof(float) * (size_t)(TC_M + 2 * stages * NR) * Kp + 512; };
+#endif
   int nb = 2;
   while (nb < BK_MAXB && smem_for(nb + 1) <= 227 * 1024) ++nb;
   if (const char *e = getenv("SSF_TC_NB")) {         // experiment hook: ring depth

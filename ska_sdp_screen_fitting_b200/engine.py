@@ -416,7 +416,14 @@ class PatternCache:
     can be issued while the evaluation kernel owns the device.  Slot 0 is the full pattern.
     When the slots run out the device forgets all patterns but slot 0 and starts over."""
 
-    def __init__(self, engine, pp, r0=R_0, beta=BETA, cut=PINV_CUT, max_bytes=2 << 30):
+    def __init__(self, engine, pp, r0=R_0, beta=BETA, cut=PINV_CUT, max_bytes=None):
+        if max_bytes is None:
+            # a sixteenth of the free device memory, 2 .. 16 GiB: when the cache is full it forgets
+            # everything (and the next passes decompose every pattern again -- 8 ms per 2048
+            # matrices of 100 directions), so on a 180 GB part it should rarely be full: at the
+            # SKA-Low shape (one new pattern per ~4 systems at 1 % flags) 16 GiB last ~500 slabs
+            free = torch.cuda.mem_get_info(engine.device)[0] if engine.device.type == "cuda" else 0
+            max_bytes = int(min(max(free // 16, 2 << 30), 16 << 30)) if free else 2 << 30
         self.eng = engine
         self.pp = pp
         self.ndir = n = pp.shape[0]

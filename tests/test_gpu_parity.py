@@ -163,6 +163,38 @@ def test_template_bit_exact_at_full_size(gpu_engine):
     assert np.array_equal(tmpl.cpu().numpy(), screens.nearest_patch_template(px, py, 1024))
 
 
+@pytest.mark.parametrize("n", [512, 1024])
+def test_nearest_patch_kernel_against_the_reference_template(gpu_engine, n, capsys):
+    """SURVEY 7.4-1 iii: the two definitions of "the Voronoi template" side by side.  The
+    reference rasterises Voronoi polygons with PIL (integer vertex truncation, host pipeline
+    restated in template.py = the default template_mode="reference"); ``assign_kernel`` is the
+    exact float64 nearest-patch rule.  They may only differ along cell boundaries: the count is
+    printed (and bounded by the total boundary length)."""
+    import synthetic_cases
+    from ska_sdp_screen_fitting_b200 import template, wcs
+
+    case = synthetic_cases.make_case("lofar", seed=3, n_times=1, n_freqs=1, n_pix=n, cellsize_deg=5.12 / n)
+    ra, dec = case.patch_radec[:, 0], case.patch_radec[:, 1]
+    ref, _, _ = template.reference_template(ra, dec, case.rad, case.dec, case.width_deg, case.cellsize_deg)
+    assert ref.shape == (n, n)
+    px, py = wcs.patch_pixels(ra, dec, case.rad, case.dec, n, case.cellsize_deg)
+    got = gpu_engine.voronoi_assign(gpu_engine.tensor(px, torch.float64), gpu_engine.tensor(py, torch.float64),
+                                    n, n).cpu().numpy()
+    differ = got != ref
+    count = int(differ.sum())
+    # every differing pixel touches a cell boundary of the exact template (8-neighbourhood)
+    edge = np.zeros_like(differ)
+    for dy in (-1, 0, 1):
+        for dx in (-1, 0, 1):
+            shifted = np.roll(np.roll(got, dy, 0), dx, 1)
+            edge |= shifted != got
+    with capsys.disabled():
+        print(f"\n[template] {n} x {n}, {len(ra)} patches: assign_kernel differs from the reference-style template "
+              f"in {count} of {n * n} pixels ({100.0 * count / (n * n):.3f} %), boundary pixels {int(edge.sum())}")
+    assert not (differ & ~edge).any()
+    assert count <= edge.sum()
+
+
 def test_smoothing(gpu_engine):
     pc.check_smooth(gpu_engine)
     pc.check_smooth(gpu_engine, shape=(3, 130, 257), sigmas=(0.5, 2.0, 5.0, 10.0), seed=5)
