@@ -18,6 +18,7 @@ per-antenna weight sums picks the reference station).
 Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement".
 """
 import argparse
+import gc
 import json
 import os
 import subprocess
@@ -313,13 +314,20 @@ def measure_workload(args, eng, dist, workload, steps, warmup, rank, local, part
         # that lead to its steady-state value on both sides of the timed region (and order the
         # main stream after it), so the region holds as many slab fits as slab evaluations
         kl.settle_fit_lead()
+        # no collector pauses inside the timed steps (as timeit does): a generation-2 pass holds
+        # the GIL for tens of ms and stalls the thread that issues the fits
+        gc.collect()
+        gc.disable()
         t_begin = time.time()
         ev0.record()
-        for i in range(warmup, n_steps):
-            step_fn(i)
-        kl.settle_fit_lead()
-        ev1.record()
-        torch.cuda.synchronize()
+        try:
+            for i in range(warmup, n_steps):
+                step_fn(i)
+            kl.settle_fit_lead()
+            ev1.record()
+            torch.cuda.synchronize()
+        finally:
+            gc.enable()
         t_end = time.time()
         if dist is not None:
             dist.barrier()

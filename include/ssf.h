@@ -222,6 +222,13 @@ int ssf_voronoi_contract(const float *S, const float *lut, int ndir, int64_t npi
 int ssf_gauss_smooth(float *images, int64_t nimg, int ny, int nx, double sigma,
                      float *scratch, void *stream);
 
+/* The same filter on the 4 * ncol planes of a slab [ncol, 4, ny, nx], with the NaN fix of
+ * screen.py:364-378 (below) fused into the stores of the second pass when `fix_nan` is set: the
+ * reference's order of operations for slabs that carry NaN (screen.py:353-378) in two passes
+ * over the slab instead of three. */
+int ssf_gauss_smooth_slab(float *slab, int64_t ncol, int ny, int nx, double sigma,
+                          float *scratch, int fix_nan, void *stream);
+
 /* NaN -> 1.0 (planes 0, 2) / 0.0 (planes 1, 3), screen.py:364-378, on a slab. */
 int ssf_nan_fix(float *slab, int64_t ncol, int64_t npix, void *stream);
 

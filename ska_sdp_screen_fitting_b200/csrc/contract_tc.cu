@@ -753,24 +753,34 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
       // the item after the next is fetched while this item's tiles are issued: the atomic's
       // round trip (a microsecond under a saturated store stream) is never waited for
       int item = blockIdx.x;
+#ifdef SSF_BK_STATIC
+      int next = item + (int)gridDim.x;                // experiment: static round-robin item list
+#else
       int next = (int)gridDim.x + atomicAdd(next_item, 1);
+#endif
       if (next >= n_items) next = -1;
       publish(0, item);
       load_raw(item);
       uint32_t T = 0;
       for (int j = 0; item >= 0; ++j) {
         int next2 = -1;
+#ifdef SSF_BK_STATIC
+        if (next >= 0) next2 = next + (int)gridDim.x;
+#else
         if (next >= 0) next2 = (int)gridDim.x + atomicAdd(next_item, 1);
+#endif
         publish(j + 1, next);
         bool raw_sent = next < 0;
         BK_ITEM(item, pix0, ct0, nt);
         (void)pix0;
         for (int it = 0; it < nt; ++it, ++T) {
           // the raw tile of the next item goes out as soon as the converters have read this one's
+#ifndef SSF_BK_LATE_RAW
           if (!raw_sent && mbar_test(raw_free, j & 1)) {
             load_raw(next);
             raw_sent = true;
           }
+#endif
           const int s = T % nb;
           if (T >= (uint32_t)nb) mbar_wait(b_empty + 8 * s, (T / nb - 1) & 1);
           mbar_expect_tx(b_full + 8 * s, stage_bytes);
@@ -779,6 +789,9 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
         }
         if (!raw_sent) {
           mbar_wait(raw_free, j & 1);
+#ifdef SSF_BK_LATE_RAW
+          mbar_wait(a_free, j & 1);                    // experiment: no prefetch under the contraction
+#endif
           load_raw(next);
         }
         item = next;

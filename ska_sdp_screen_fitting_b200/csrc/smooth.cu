@@ -96,17 +96,130 @@ __global__ void xpass_shfl_kernel(const float *__restrict__ in, float *__restric
   if (lane < span && x < nx) dst[x] = acc;
 }
 
+// ---- register-blocked passes (the default while the tile fits shared memory) ----------------
+// Every thread produces BLK consecutive outputs ALONG the filter direction from a sliding window
+// of BLK registers: per tap one broadcast load of the weight, one load of the sample entering the
+// window and BLK FMAs -- the tap-per-output kernels above pay one shared-memory load per FMA
+// (0.11 of the HBM bound at sigma = 5 px).  The accumulation order (taps ascending, one FMA each)
+// is the same as theirs, so the results are identical bit for bit.  Taps beyond 2r are never
+// executed (a zero weight times a NaN sample would be a NaN).
+constexpr int BLK = 8;
+
+// window step for tap k (compile-time slot u = k mod 8): accumulate, then replace the oldest sample
+#define SSF_SMOOTH_TAPS(LOAD)                                                          \
+  float acc[BLK], win[BLK];                                                            \
+  _Pragma("unroll") for (int j = 0; j < BLK; ++j) {                                    \
+    acc[j] = 0.0f;                                                                     \
+    win[j] = LOAD(j);                                                                  \
+  }                                                                                    \
+  const int ntap = 2 * r + 1;                                                          \
+  int k0 = 0;                                                                          \
+  for (; k0 + BLK <= ntap; k0 += BLK) {                                                \
+    _Pragma("unroll") for (int u = 0; u < BLK; ++u) {                                  \
+      const float w = c_w[k0 + u];                                                     \
+      _Pragma("unroll") for (int j = 0; j < BLK; ++j) acc[j] = fmaf(w, win[(j + u) & (BLK - 1)], acc[j]); \
+      win[u] = LOAD(k0 + u + BLK);                                                     \
+    }                                                                                  \
+  }                                                                                    \
+  _Pragma("unroll") for (int u = 0; u < BLK; ++u) {                                    \
+    if (k0 + u < ntap) {                                                               \
+      const float w = c_w[k0 + u];                                                     \
+      _Pragma("unroll") for (int j = 0; j < BLK; ++j) acc[j] = fmaf(w, win[(j + u) & (BLK - 1)], acc[j]); \
+      win[u] = LOAD(k0 + u + BLK);                                                     \
+    }                                                                                  \
+  }
+
+// y pass: block 32 (x) by YT (y groups); thread (tx, ty) owns rows y0 + 8 ty .. + 7 of column x.
+// smem: taps[2r + 1], tile[(8 YT + 2r + 1)][32] (the last row is read by the final window
+// refill and never used).
+template <int YT>
+__global__ void ypass_blocked_kernel(const float *__restrict__ in, float *__restrict__ out, int ny, int nx, int r,
+                                     const float *__restrict__ taps) {
+  SSF_DYN_SMEM(float, c_w);
+  float *tile = c_w + 2 * r + 1;
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  for (int k = ty * 32 + tx; k <= 2 * r; k += 32 * YT) c_w[k] = taps[k];
+  const int64_t img = blockIdx.z;
+  const float *src = in + img * (int64_t)ny * nx;
+  float *dst = out + img * (int64_t)ny * nx;
+  const int x = blockIdx.x * 32 + tx;
+  const int y0 = blockIdx.y * (YT * BLK);
+  const int rows = YT * BLK + 2 * r + 1;
+  for (int j = ty; j < rows; j += YT) {
+    const int yy = reflect(y0 + j - r, ny);
+    tile[j * 32 + tx] = (x < nx && j < rows - 1) ? src[(int64_t)yy * nx + x] : 0.0f;
+  }
+  __syncthreads();
+  const int base = ty * BLK;
+#define SSF_LOAD_Y(i) tile[(base + (i)) * 32 + tx]
+  SSF_SMOOTH_TAPS(SSF_LOAD_Y)
+#undef SSF_LOAD_Y
+  if (x < nx) {
+#pragma unroll
+    for (int j = 0; j < BLK; ++j) {
+      const int y = y0 + base + j;
+      if (y < ny) dst[(int64_t)y * nx + x] = acc[j];
+    }
+  }
+}
+
+// x pass: block 32 (rows, lane = row so that the lanes of a warp walk different rows of an
+// odd-pitched tile: no bank conflicts) by XT (x groups); thread (lane, tg) owns columns
+// x0 + 8 tg .. + 7 of its row.  Results go back through the tile so that the global stores are
+// coalesced along x; `fix` (0 none, 1 + plane parity) fuses the NaN fix of screen.py:364-378.
+template <int XT>
+__global__ void xpass_blocked_kernel(const float *__restrict__ in, float *__restrict__ out, int ny, int nx, int r,
+                                     const float *__restrict__ taps, int fix_nan) {
+  SSF_DYN_SMEM(float, c_w);
+  float *tile = c_w + 2 * r + 1;
+  const int lane = threadIdx.x, tg = threadIdx.y, tid = tg * 32 + lane;
+  for (int k = tid; k <= 2 * r; k += 32 * XT) c_w[k] = taps[k];
+  const int64_t img = blockIdx.z;
+  const float *src = in + img * (int64_t)ny * nx;
+  float *dst = out + img * (int64_t)ny * nx;
+  const int x0 = blockIdx.x * (XT * BLK), y0 = blockIdx.y * 32;
+  const int width = XT * BLK + 2 * r + 1;            // last column: read by the final refill, never used
+  const int pitch = width | 1;
+  for (int i = tid; i < 32 * width; i += 32 * XT) {
+    const int rr = i / width, cc = i - rr * width;
+    const int y = y0 + rr;
+    tile[rr * pitch + cc] = (y < ny && cc < width - 1) ? src[(int64_t)y * nx + reflect(x0 + cc - r, nx)] : 0.0f;
+  }
+  __syncthreads();
+  const int base = tg * BLK;
+  const float *row = tile + lane * pitch;
+#define SSF_LOAD_X(i) row[base + (i)]
+  SSF_SMOOTH_TAPS(SSF_LOAD_X)
+#undef SSF_LOAD_X
+  __syncthreads();                                   // everybody has read its inputs: reuse the tile for the outputs
+#pragma unroll
+  for (int j = 0; j < BLK; ++j) tile[lane * pitch + base + j] = acc[j];
+  __syncthreads();
+  const float nan_to = (img & 1) ? 0.0f : 1.0f;      // planes 0, 2 (real) -> 1; planes 1, 3 (imaginary) -> 0
+  for (int i = tid; i < 32 * XT * BLK; i += 32 * XT) {
+    const int rr = i / (XT * BLK), cc = i - rr * (XT * BLK);
+    const int y = y0 + rr, x = x0 + cc;
+    if (y < ny && x < nx) {
+      float v = tile[rr * pitch + cc];
+      if (fix_nan && v != v) v = nan_to;
+      dst[(int64_t)y * nx + x] = v;
+    }
+  }
+}
+#undef SSF_SMOOTH_TAPS
+
 }  // namespace
 
-extern "C" int ssf_gauss_smooth(float *images, int64_t nimg, int ny, int nx, double sigma,
-                                float *scratch, void *stream_) {
-  SSF_REQUIRE(images && scratch, "ssf_gauss_smooth: null pointer");
-  SSF_REQUIRE(ny >= 1 && nx >= 1 && nimg >= 0, "ssf_gauss_smooth: bad sizes");
-  SSF_REQUIRE(sigma > 0.0, "ssf_gauss_smooth: sigma must be > 0");
+namespace {
+int gauss_smooth_impl(const char *who, float *images, int64_t nimg, int ny, int nx, double sigma, float *scratch,
+                      int fix_nan, cudaStream_t stream) {
+  SSF_REQUIRE(images && scratch, "%s: null pointer", who);
+  SSF_REQUIRE(ny >= 1 && nx >= 1 && nimg >= 0, "%s: bad sizes", who);
+  SSF_REQUIRE(sigma > 0.0, "%s: sigma must be > 0", who);
+  SSF_REQUIRE(!fix_nan || nimg % 4 == 0, "%s: the NaN fix needs whole columns of 4 planes", who);
   if (nimg == 0) return SSF_OK;
-  cudaStream_t stream = (cudaStream_t)stream_;
   const int r = (int)(4.0 * sigma + 0.5);
-  SSF_REQUIRE(r <= MAX_RADIUS, "ssf_gauss_smooth: radius %d exceeds %d", r, MAX_RADIUS);
+  SSF_REQUIRE(r <= MAX_RADIUS, "%s: radius %d exceeds %d", who, r, MAX_RADIUS);
   // weights in float64 exactly as scipy's _gaussian_kernel1d, rounded once to float32
   static thread_local float hw[2 * MAX_RADIUS + 1];
   double sum = 0.0;
@@ -125,16 +238,40 @@ extern "C" int ssf_gauss_smooth(float *images, int64_t nimg, int ny, int nx, dou
   } free_taps{taps, stream};
   // pageable source: the runtime stages it before the call returns, so hw may be reused at once
   SSF_CUDA(cudaMemcpyAsync(taps, hw, sizeof(float) * (2 * r + 1), cudaMemcpyHostToDevice, stream));
-  // gridDim.z is limited to 65535 images per launch
-  for (int64_t i0 = 0; i0 < nimg; i0 += 65535) {
-    int nz = (int)((nimg - i0) < 65535 ? (nimg - i0) : 65535);
+  // register-blocked passes while their tiles fit (radius <= ~190 pixels), else the tap-per-output ones
+  constexpr int YT = 16, XT = 16;
+  const size_t smem_y = sizeof(float) * ((size_t)(YT * BLK + 2 * r + 1) * 32 + 2 * r + 1);
+  const size_t smem_x = sizeof(float) * ((size_t)32 * ((XT * BLK + 2 * r + 1) | 1) + 2 * r + 1);
+  const bool blocked = smem_y <= 100 * 1024 && smem_x <= 100 * 1024;
+  bool fixed = false;
+  // gridDim.z is limited to 65535 images per launch (kept a multiple of 4: plane parity = image parity)
+  for (int64_t i0 = 0; i0 < nimg; i0 += 65532) {
+    int nz = (int)((nimg - i0) < 65532 ? (nimg - i0) : 65532);
     float *img = images + i0 * (int64_t)ny * nx;
     float *tmp = scratch + i0 * (int64_t)ny * nx;
+    if (blocked) {
+      {
+        dim3 grid(ssf::div_up(nx, 32), ssf::div_up(ny, YT * BLK), nz), block(32, YT);
+        if (smem_y > 48 * 1024)
+          SSF_CUDA(cudaFuncSetAttribute(ypass_blocked_kernel<YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_y));
+        SSF_LAUNCH(ypass_blocked_kernel<YT>, grid, block, smem_y, stream, img, tmp, ny, nx, r, taps);
+        SSF_LAUNCHED();
+      }
+      {
+        dim3 grid(ssf::div_up(nx, XT * BLK), ssf::div_up(ny, 32), nz), block(32, XT);
+        if (smem_x > 48 * 1024)
+          SSF_CUDA(cudaFuncSetAttribute(xpass_blocked_kernel<XT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_x));
+        SSF_LAUNCH(xpass_blocked_kernel<XT>, grid, block, smem_x, stream, tmp, img, ny, nx, r, taps, fix_nan);
+        SSF_LAUNCHED();
+        fixed = true;
+      }
+      continue;
+    }
     {
       constexpr int TY = 16;
       dim3 grid(ssf::div_up(nx, 32), ssf::div_up(ny, TY), nz), block(32, TY);
       size_t smem = sizeof(float) * (32 * (TY + 2 * r) + 2 * r + 1);
-      SSF_REQUIRE(smem <= 200 * 1024, "ssf_gauss_smooth: radius too large for the y tile");
+      SSF_REQUIRE(smem <= 200 * 1024, "%s: radius too large for the y tile", who);
       if (smem > 48 * 1024)
         SSF_CUDA(cudaFuncSetAttribute(ypass_kernel<TY>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)smem));
@@ -154,5 +291,19 @@ extern "C" int ssf_gauss_smooth(float *images, int64_t nimg, int ny, int nx, dou
       SSF_LAUNCHED();
     }
   }
+  if (fix_nan && !fixed) return ssf_nan_fix(images, nimg / 4, (int64_t)ny * nx, (void *)stream);
   return SSF_OK;
+}
+}  // namespace
+
+extern "C" int ssf_gauss_smooth(float *images, int64_t nimg, int ny, int nx, double sigma,
+                                float *scratch, void *stream) {
+  return gauss_smooth_impl("ssf_gauss_smooth", images, nimg, ny, nx, sigma, scratch, 0, (cudaStream_t)stream);
+}
+
+extern "C" int ssf_gauss_smooth_slab(float *slab, int64_t ncol, int ny, int nx, double sigma, float *scratch,
+                                     int fix_nan, void *stream) {
+  SSF_REQUIRE(ncol >= 0, "ssf_gauss_smooth_slab: bad sizes");
+  return gauss_smooth_impl("ssf_gauss_smooth_slab", slab, ncol * 4, ny, nx, sigma, scratch, fix_nan,
+                           (cudaStream_t)stream);
 }

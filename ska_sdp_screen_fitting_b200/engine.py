@@ -386,6 +386,19 @@ class Engine:
                   self.stream())
         return images
 
+    def gauss_smooth_slab(self, slab, sigma, fix_nan=True, scratch=None):
+        """In place on a slab [ncol, 4, ny, nx] float32; ``fix_nan`` fuses the NaN fix of
+        screen.py:364-378 into the second pass."""
+        self._check(slab, torch.float32, "slab")
+        ncol, planes, ny, nx = slab.shape
+        if planes != 4:
+            raise ValueError("slab must be [ncol, 4, ny, nx]")
+        if scratch is None:
+            scratch = torch.empty_like(slab)
+        self._timed_call("gauss_smooth", "ssf_gauss_smooth_slab", _ptr(slab), ncol, ny, nx, float(sigma),
+                         _ptr(scratch), 1 if fix_nan else 0, self.stream())
+        return slab
+
     def nan_fix(self, slab, ncol, npix):
         self._call("ssf_nan_fix", _ptr(slab), ncol, npix, self.stream())
         return slab

@@ -191,9 +191,7 @@ class VoronoiScreen(Screen):
                 raise ValueError("the direct smoothing path needs native 4-plane slabs")
             eng.voronoi_fill_gain(self._tmpl_dev, lut4, slab, fix_nan=fix_nan and not smooth, out_flags=out_flags)
             if smooth:
-                eng.gauss_smooth(slab, smooth_pix)
-                if fix_nan:
-                    eng.nan_fix(slab, cols.shape[0], npix)
+                eng.gauss_smooth_slab(slab, smooth_pix, fix_nan=fix_nan)
             return
         lut = eng.voronoi_lut(cols.contiguous())
         if smooth and self._use_linear(smooth_pix, cols):
@@ -202,8 +200,6 @@ class VoronoiScreen(Screen):
             if out_flags:
                 raise ValueError("the direct smoothing path needs native 4-plane slabs")
             eng.voronoi_fill(self._tmpl_dev, lut, slab, fix_nan=False)
-            eng.gauss_smooth(slab, smooth_pix)
-            if fix_nan:
-                eng.nan_fix(slab, cols.shape[0], npix)
+            eng.gauss_smooth_slab(slab, smooth_pix, fix_nan=fix_nan)
         else:
             eng.voronoi_fill(self._tmpl_dev, lut, slab, fix_nan=fix_nan, out_flags=out_flags)

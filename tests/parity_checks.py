@@ -565,6 +565,21 @@ def check_smoothed_voronoi(eng, n=24, n_d=6, ncol=5, sigma=1.5, seed=4, variant=
     eng.gauss_smooth(slab, sigma)
     eng.nan_fix(slab, ncol, n * n)
     assert np.abs(slab.cpu().numpy() - want).max() < TOL_SMOOTH
+    # a NaN phase spreads over the filter support and is then fixed (screen.py:353-378): the
+    # fused form (ssf_gauss_smooth_slab) against smooth + separate NaN fix, bit for bit, and
+    # against the oracle on the pixels the NaN does not reach
+    ph_nan = phases.reshape(ncol, n_d).copy()
+    ph_nan[0, 0] = np.nan
+    lut_nan = eng.voronoi_lut(eng.tensor(ph_nan, torch.float64))
+    a, b = eng.empty((ncol, 4, n, n), torch.float32), eng.empty((ncol, 4, n, n), torch.float32)
+    eng.voronoi_fill(tmpl, lut_nan, a, False)
+    eng.voronoi_fill(tmpl, lut_nan, b, False)
+    eng.gauss_smooth(a, sigma)
+    eng.nan_fix(a, ncol, n * n)
+    eng.gauss_smooth_slab(b, sigma, fix_nan=True)
+    assert np.array_equal(a.cpu().numpy(), b.cpu().numpy())
+    want_nan = screens.voronoi_cube(ph_nan.reshape(1, 1, ncol, n_d), want_t, sigma)[0, 0]
+    assert np.abs(b.cpu().numpy() - want_nan).max() < TOL_SMOOTH
     ind = eng.gauss_smooth(eng.voronoi_indicators(tmpl, n_d), sigma)
     slab2 = eng.empty((ncol, 4, n, n), torch.float32)
     eng.voronoi_contract(ind, lut, slab2, variant)
