@@ -969,6 +969,270 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
   }
 }
 
+// ------------------------------------------------------------------------------------ narrow-tile kernel
+// More than 56 directions with TWO CTAs per SM.  The persistent kernel above is bound by its
+// one-CTA-per-SM structure, not by its pipeline (every one-CTA variant of either kernel
+// loses 10-15 points against two CTAs at the same shape).  Two CTAs fit an SM at 100 directions
+// when the split basis operand lives in TENSOR memory and the tiles are narrow:
+//   tensor memory, 256 columns per CTA:  D[TS][16] at column 0 | A_hi[Kp] | A_lo[Kp] at the top
+//                                        (Kp = 104: 208 operand columns + 3 accumulator stages)
+//   shared memory (floats):  raw[Kp][128] (one TMA tensor copy)  B[nb stages][hi, lo][16 Kp]
+//                                        (Kp = 104: 53 KB + 4 x 13 KB per CTA)
+// A CTA = one 128-pixel tile and a run of 16-row coefficient tiles (KL: 16 slab columns, Voronoi:
+// 8 columns x Re / Im).  The eight epilogue warps first split the raw basis tile into tensor
+// memory (warp w: lane quadrant w % 4, K half w / 4), then work as in the kernel of 4.1: thread =
+// pixel, 8 accumulator columns per warp and tile (tcgen05.ld x8).  The second resident CTA's
+// store stream covers this CTA's staging.  MODE 0 = Voronoi, 1 = KL.
+constexpr int NW_N = 16;                         // rows of a coefficient tile = N of the MMA
+constexpr int NW_MAXB = 6;
+constexpr int NW_NBARS = 2 * NW_MAXB + 2 * T_STAGES + 2;
+__host__ __device__ constexpr int narrow_columns(int mode) { return mode == 1 ? NW_N : NW_N / 2; }
+
+// Coefficient tiles of the narrow kernel: Bs[tile][hi | lo][canon(row, k)], 16 rows x Kp.
+// KL: row r = slab column 16 t + r.  Voronoi: rows r < 8 = Re, r >= 8 = Im of column 8 t + (r & 7).
+template <int MODE>
+__global__ void split_b_narrow_kernel(const float *__restrict__ G, int ndir, int ldg, int64_t ncol, int Kp,
+                                      int64_t n_ct, float *__restrict__ Bs) {
+  const int kc4 = Kp >> 2;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n_ct * NW_N * kc4) return;
+  const int kc = (int)(idx % kc4);
+  const int r = (int)((idx / kc4) % NW_N);
+  const int64_t tile = idx / ((int64_t)kc4 * NW_N);
+  float x[4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const int k = 4 * kc + u;
+    float v = 0.0f;
+    if (MODE == 1) {
+      const int64_t col = tile * NW_N + r;
+      if (col < ncol && k < ndir) v = G[col * ldg + k];
+    } else {
+      const int64_t col = tile * (NW_N / 2) + (r & 7);
+      if (col < ncol && k < ndir) v = G[(col * ndir + k) * 2 + (r >> 3)];
+    }
+    x[u] = v;
+  }
+  const float4 hv = make_float4(to_tf32(x[0]), to_tf32(x[1]), to_tf32(x[2]), to_tf32(x[3]));
+  const float4 lv = make_float4(to_tf32(x[0] - hv.x), to_tf32(x[1] - hv.y), to_tf32(x[2] - hv.z),
+                                to_tf32(x[3] - hv.w));
+  float *dst = Bs + tile * (2 * NW_N * Kp) + canon(r, 4 * kc, kc4);
+  *reinterpret_cast<float4 *>(dst) = hv;
+  *reinterpret_cast<float4 *>(dst + NW_N * Kp) = lv;
+}
+
+// Epilogue stores of one thread's 8 accumulator columns (its pixel, 8 slab columns).
+template <bool CHECK>
+__device__ __forceinline__ void store_kl8(const float (&v)[8], float *out, int64_t npix, int nvalid, ssf::OutFmt fmt) {
+  const int64_t p2 = 2 * npix, p3 = 3 * npix, pc = fmt.planes * npix;
+  const bool four = fmt.planes == 4;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (CHECK && j >= nvalid) break;
+    if (fmt.planes == 1) {                                   // dTEC cube: the raw screen value
+      st_cube(out, ssf::out_word(v[j], fmt.prmt));
+      out += npix;
+      continue;
+    }
+    float sn, cs;
+    sincos_reduced(v[j], &sn, &cs);
+    cs = ssf::out_word(ssf::fix_re(cs), fmt.prmt);
+    sn = ssf::out_word(ssf::fix_im(sn), fmt.prmt);
+    st_cube(out, cs);
+    st_cube(out + npix, sn);
+    if (four) {
+      st_cube(out + p2, cs);
+      st_cube(out + p3, sn);
+    }
+    out += pc;
+  }
+}
+template <bool CHECK>
+__device__ __forceinline__ void store_vo8(const float (&v)[8], float *out, int64_t npix, int nvalid, int h,
+                                          ssf::OutFmt fmt) {
+  const int64_t p2 = 2 * npix, pc = fmt.planes * npix;
+  const bool four = fmt.planes == 4;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (CHECK && j >= nvalid) break;
+    const float x = ssf::out_word(h == 0 ? ssf::fix_re(v[j]) : ssf::fix_im(v[j]), fmt.prmt);
+    st_cube(out, x);
+    if (four) st_cube(out + p2, x);
+    out += pc;
+  }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(320, 2)
+contract_tc_narrow_kernel(const __grid_constant__ CUtensorMap bt_map, const float *__restrict__ Bs, int ndir,
+                          int64_t npix, int64_t ncol, float *__restrict__ slab, int tiles_per_chunk, int Kp, int nb,
+                          ssf::OutFmt fmt) {
+  constexpr int NEPI = 8;
+  constexpr int CT = narrow_columns(MODE);       // slab columns per coefficient tile
+  constexpr uint32_t IDESC = idesc_for(NW_N);
+  SSF_DYN_SMEM(float, sm);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int kc4 = Kp >> 2;
+  float *raw = sm;                               // [Kp][128]
+  float *b_base = sm + TC_M * Kp;                // stage s: hi at s*2*16*Kp, lo right after
+  uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (TC_M + 2 * nb * NW_N) * Kp);
+  uint32_t *tmem_holder = reinterpret_cast<uint32_t *>(bars + NW_NBARS);
+  const uint32_t b_full = smem_u32(bars), b_empty = smem_u32(bars + NW_MAXB);
+  const uint32_t t_full = smem_u32(bars + 2 * NW_MAXB), t_empty = smem_u32(bars + 2 * NW_MAXB + T_STAGES);
+  const uint32_t raw_full = smem_u32(bars + 2 * NW_MAXB + 2 * T_STAGES), a_ready = raw_full + 8;
+  const uint32_t stage_bytes = (uint32_t)(2 * NW_N * Kp * sizeof(float));
+  const int acol = 256 - 2 * Kp;                 // first TMEM column of A_hi; accumulator stages below it
+  const int TS = acol / NW_N < T_STAGES ? acol / NW_N : T_STAGES;
+
+  const int64_t pix0 = (int64_t)blockIdx.y * TC_M;
+  const int64_t n_ct = (ncol + CT - 1) / CT;
+  const int64_t ct_begin = (int64_t)blockIdx.x * tiles_per_chunk;
+  int64_t ct_end = ct_begin + tiles_per_chunk;
+  if (ct_end > n_ct) ct_end = n_ct;
+  if (ct_begin >= ct_end) return;                // whole CTA, before any barrier / allocation
+  const int n_tiles = (int)(ct_end - ct_begin);
+  const float *b_src = Bs + ct_begin * (2 * NW_N * Kp);
+
+  if (warp == NEPI) {
+    if (elect_one()) {
+      for (int i = 0; i < NW_MAXB; ++i) {
+        mbar_init(b_full + 8 * i, 1);
+        mbar_init(b_empty + 8 * i, 1);
+      }
+      for (int i = 0; i < T_STAGES; ++i) {
+        mbar_init(t_full + 8 * i, 1);
+        mbar_init(t_empty + 8 * i, NEPI);
+      }
+      mbar_init(raw_full, 1);
+      mbar_init(a_ready, NEPI);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      // raw basis tile: one tensor-map copy, box = Kp direction rows x 128 pixels (rows beyond ndir
+      // are out of bounds and arrive as zeros); then the first coefficient tiles
+      mbar_expect_tx(raw_full, (uint32_t)Kp * TC_M * (uint32_t)sizeof(float));
+      tma_load_2d(smem_u32(raw), &bt_map, (int)pix0, 0, raw_full);
+      for (int it = 0; it < nb && it < n_tiles; ++it) {
+        mbar_expect_tx(b_full + 8 * it, stage_bytes);
+        bulk_g2s(smem_u32(b_base + (size_t)it * 2 * NW_N * Kp), b_src + (size_t)it * 2 * NW_N * Kp, stage_bytes,
+                 b_full + 8 * it);
+      }
+    }
+  }
+  if (warp == NEPI + 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(tmem_holder)),
+                 "n"(256)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+
+  if (warp == NEPI) {
+    // ===== TMA lane: refill stage s once the MMAs of the tile that used it have retired =====
+    if (elect_one()) {
+      for (int it = nb; it < n_tiles; ++it) {
+        const int s = it % nb, use = it / nb;
+        mbar_wait(b_empty + 8 * s, (use - 1) & 1);
+        mbar_expect_tx(b_full + 8 * s, stage_bytes);
+        bulk_g2s(smem_u32(b_base + (size_t)s * 2 * NW_N * Kp), b_src + (size_t)it * 2 * NW_N * Kp, stage_bytes,
+                 b_full + 8 * s);
+      }
+    }
+  } else if (warp == NEPI + 1) {
+    // ===== MMA lane: A from tensor memory =====
+    mbar_wait(a_ready, 0);                       // the split basis tile is in TMEM
+    tc_fence_after();
+    if (elect_one()) {
+      const uint32_t lbo = 128, sbo = (uint32_t)kc4 * 128;
+      const uint32_t ta_hi = tmem_base + (uint32_t)acol, ta_lo = ta_hi + (uint32_t)Kp;
+      const int ksteps = Kp >> 3;
+      for (int it = 0; it < n_tiles; ++it) {
+        const int s = it % nb, t = it % TS;
+        mbar_wait(b_full + 8 * s, (it / nb) & 1);
+        if (it >= TS) mbar_wait(t_empty + 8 * t, (it / TS - 1) & 1);
+        tc_fence_after();
+        const float *bh = b_base + (size_t)s * 2 * NW_N * Kp;
+        const uint64_t db_hi = make_desc(smem_u32(bh), lbo, sbo), db_lo = make_desc(smem_u32(bh + NW_N * Kp), lbo, sbo);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(t * NW_N);
+        // corrections first (see contract_tc_kernel); one K step = 8 TMEM columns of A = 16 in the
+        // descriptor's start-address field
+        if (SSF_TC_PRODUCTS == 4)
+          for (int ks = 0; ks < ksteps; ++ks)
+            tc_mma_tf32_ts(d_tmem, ta_lo + (uint32_t)(ks * 8), db_lo + (uint64_t)(ks * 16), IDESC, ks > 0);
+        for (int ks = 0; ks < ksteps; ++ks)
+          tc_mma_tf32_ts(d_tmem, ta_lo + (uint32_t)(ks * 8), db_hi + (uint64_t)(ks * 16), IDESC,
+                         SSF_TC_PRODUCTS == 4 || ks > 0);
+        for (int ks = 0; ks < ksteps; ++ks)
+          tc_mma_tf32_ts(d_tmem, ta_hi + (uint32_t)(ks * 8), db_lo + (uint64_t)(ks * 16), IDESC, 1);
+        for (int ks = 0; ks < ksteps; ++ks)
+          tc_mma_tf32_ts(d_tmem, ta_hi + (uint32_t)(ks * 8), db_hi + (uint64_t)(ks * 16), IDESC, 1);
+        tc_commit(b_empty + 8 * s);
+        tc_commit(t_full + 8 * t);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ===== epilogue warps: first the split of the basis tile into TMEM ... =====
+    const int q = warp & 3, h = (warp >> 2) & 1;
+    {
+      const int r = 32 * q + lane;               // pixel row = TMEM lane
+      const uint32_t ta_hi = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)acol, ta_lo = ta_hi + (uint32_t)Kp;
+      const int ksteps = Kp >> 3, half = (ksteps + 1) >> 1;
+      mbar_wait(raw_full, 0);
+      for (int ks = h * half; ks < (h == 0 ? half : ksteps); ++ks) {
+        const int k0 = ks * 8;
+        float hi[8], lo[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const float x = (k0 + u < ndir) ? raw[(k0 + u) * TC_M + r] : 0.0f;
+          hi[u] = to_tf32(x);
+          lo[u] = to_tf32(x - hi[u]);
+        }
+        tmem_st8(ta_hi + (uint32_t)k0, hi);
+        tmem_st8(ta_lo + (uint32_t)k0, lo);
+      }
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(a_ready);
+    }
+    // ===== ... then the tiles: thread = pixel, 8 accumulator columns per warp =====
+    const int64_t pix = pix0 + 32 * q + lane;
+    for (int it = 0; it < n_tiles; ++it) {
+      const int t = it % TS;
+      const int64_t c0 = (ct_begin + it) * CT;
+      mbar_wait(t_full + 8 * t, (it / TS) & 1);
+      tc_fence_after();
+      float v[8];
+      tmem_ld8(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * NW_N + 8 * h), v);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(t_empty + 8 * t);
+      if (MODE == 1) {
+        float *out = slab + (c0 + 8 * h) * fmt.planes * npix + pix;
+        const int64_t left = ncol - (c0 + 8 * h);
+        if (left >= 8) store_kl8<false>(v, out, npix, 8, fmt);
+        else if (left > 0) store_kl8<true>(v, out, npix, (int)left, fmt);
+      } else {
+        // rows 0..7 = Re (h = 0) -> planes 0, 2; rows 8..15 = Im (h = 1) -> planes 1, 3
+        float *out = slab + c0 * fmt.planes * npix + (int64_t)h * npix + pix;
+        const int64_t left = ncol - c0;
+        if (left >= 8) store_vo8<false>(v, out, npix, 8, h, fmt);
+        else if (left > 0) store_vo8<true>(v, out, npix, (int)left, h, fmt);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == NEPI + 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(256) : "memory");
+  }
+}
+
 // Returns pool scratch to the stream-ordered pool on every exit path of a launcher.
 struct ScratchGuard {
   void *ptr;
@@ -1086,6 +1350,56 @@ int launch_bigk(const float *Bt, const float *G, int ndir, int ldg, int64_t npix
   return guard.release();
 }
 
+template <int MODE>
+int launch_narrow(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
+                  ssf::OutFmt fmt, cudaMemPool_t pool, cudaStream_t stream) {
+  constexpr int CT = narrow_columns(MODE);
+  const int Kp = (ndir + 7) / 8 * 8;
+  const int64_t n_ct = (ncol + CT - 1) / CT;
+  // coefficient stages: as many as two resident CTAs leave room for next to the raw basis tile
+  auto smem_for = [&](int stages) { return sizeof(float) * (size_t)(TC_M + 2 * stages * NW_N) * Kp + 8 * NW_NBARS + 64; };
+  int nb = 2;
+  while (nb < NW_MAXB && 2 * (smem_for(nb + 1) + 1024) <= 227 * 1024) ++nb;
+  if (const char *e = getenv("SSF_TC_NB")) {
+    const int want = atoi(e);
+    if (want >= 2 && want <= NW_MAXB && 2 * (smem_for(want) + 1024) <= 227 * 1024) nb = want;
+  }
+  const size_t smem = smem_for(nb);
+  const size_t bs_bytes = sizeof(float) * (size_t)n_ct * 2 * NW_N * Kp;
+  float *Bs = nullptr;
+  SSF_CUDA(cudaMallocFromPoolAsync(reinterpret_cast<void **>(&Bs), bs_bytes, pool, stream));
+  ScratchGuard guard{Bs, stream};
+  SSF_LAUNCH(split_b_narrow_kernel<MODE>, ssf::div_up(n_ct * NW_N * (Kp >> 2), 256), 256, 0, stream, G, ndir, ldg, ncol,
+             Kp, n_ct, Bs);
+  SSF_LAUNCHED();
+  // tensor map of the basis: [ndir rows][npix] float32, box = Kp rows x 128 pixels, no swizzle
+  const EncodeFn encode = tensor_map_encoder();
+  SSF_REQUIRE(encode != nullptr, "cuTensorMapEncodeTiled is not available");
+  CUtensorMap bt_map;
+  const cuuint64_t gdim[2] = {(cuuint64_t)npix, (cuuint64_t)ndir};
+  const cuuint64_t gstride[1] = {(cuuint64_t)npix * sizeof(float)};
+  const cuuint32_t box[2] = {(cuuint32_t)TC_M, (cuuint32_t)Kp};
+  const cuuint32_t estride[2] = {1, 1};
+  const CUresult cr = encode(&bt_map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(Bt), gdim, gstride, box,
+                             estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  SSF_REQUIRE(cr == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d)", (int)cr);
+  auto kfn = contract_tc_narrow_kernel<MODE>;
+  SSF_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // about 256 slab columns per CTA (0.5 MB of cube), as for the kernel of 4.1
+  int64_t per = 256 / CT;
+  if (const char *e = getenv("SSF_TC_PER")) {
+    per = atoi(e);
+    if (per < 1) per = 1;
+  }
+  if (per > n_ct) per = n_ct;
+  const int gx = (int)((n_ct + per - 1) / per);
+  dim3 grid(gx, (unsigned)(npix / TC_M));
+  SSF_LAUNCH(kfn, grid, 320, smem, stream, bt_map, Bs, ndir, npix, ncol, slab, (int)per, Kp, nb, fmt);
+  SSF_LAUNCHED();
+  return guard.release();
+}
+
 // Stream-ordered scratch for the split coefficient tiles, from a library-private memory pool
 // (kept warm: release threshold = max), one per device.
 cudaMemPool_t scratch_pool(int device) {
@@ -1169,6 +1483,15 @@ int launch_tc(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, 
     // (experiment hooks: SSF_TC_BIGK=0 never, SSF_TC_BIGK=2 always)
     const char *e = getenv("SSF_TC_BIGK");
     const bool never = e && e[0] == '0', always = e && e[0] == '2';
+    // phase-only modes above 56 directions: the narrow-tile kernel keeps two CTAs per SM
+    // (SSF_TC_NARROW=0: the persistent kernel instead; =2: always, for experiments)
+    const char *en = getenv("SSF_TC_NARROW");
+    const bool narrow_never = en && en[0] == '0', narrow_always = en && en[0] == '2';
+    // Measured (profiles/r02_kernels_t_narrow.txt): KL 0.81-0.84 against 0.74-0.77 for the persistent
+    // kernel at 1024^2 (60-112 directions), equal (0.70) at 2048^2; the 8-column Voronoi tiles are
+    // too fine (0.55 against 0.66), so that mode stays on the persistent kernel.
+    if (MODE == 1 && !always && ((per_sm == 1 && !never && !narrow_never) || narrow_always))
+      return launch_narrow<1>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, pool, stream);
     if ((per_sm == 1 && !never) || always) return launch_bigk<MODE>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, pool, stream);
   }
   float *Bs = nullptr;

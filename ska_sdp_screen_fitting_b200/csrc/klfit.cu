@@ -9,7 +9,8 @@
 
 namespace {
 
-constexpr int FT = 128;  // threads per CTA (>= SSF_MAX_DIR)
+// Threads per CTA of the fit kernel: a template parameter FT >= ndir (64 up to 64 directions,
+// 128 above): half the idle lanes, registers and barrier width at the LOFAR direction count.
 constexpr double TWO_PI = 6.283185307179586476925286766559;
 constexpr double PI = 3.141592653589793238462643383279;
 
@@ -59,6 +60,7 @@ __host__ __device__ inline size_t smem_doubles(int nall) {
 // On return s.wh/s.fall hold the results: white_out/resid_out are written to global.
 // Weights all equal: closed form; all > cut: Cholesky solve; some weight in (0, cut]: the general
 // pinv by one-sided Jacobi (below).  Always returns true (kept for the callers' status plumbing).
+template <int FT>
 __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restrict__ pp, int nall,
                          int n, int k, double r0sq, double half_beta, double cut,
                          double *__restrict__ white_out, double *__restrict__ resid_out, int kind) {
@@ -309,6 +311,7 @@ __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restr
   return true;
 }
 
+template <int FT>
 __global__ void __launch_bounds__(FT)
 fit_pass_kernel(const double *__restrict__ phase, const float *__restrict__ weights,
                 const int32_t *__restrict__ pat, const double *__restrict__ pp, int nall, int64_t nsys,
@@ -358,7 +361,7 @@ fit_pass_kernel(const double *__restrict__ phase, const float *__restrict__ weig
     const int kind = (mode & 2) ? 1 : ((mode & 4) ? 2 : 0);
     const bool amp = kind == 1;
     if ((mode & 1) == 0) {
-      bool ok = fit_once(s, pt, pp, nall, n, (int)ord, r0sq, half_beta, cut, w_out, r_out, kind);
+      bool ok = fit_once<FT>(s, pt, pp, nall, n, (int)ord, r0sq, half_beta, cut, w_out, r_out, kind);
       if (!ok && tid == 0) atomicExch(status, 1);
       if (tid == 0) order[sys] = ord;
       continue;
@@ -370,7 +373,7 @@ fit_pass_kernel(const double *__restrict__ phase, const float *__restrict__ weig
     double sign = 1.0, prev_redchi2 = 0.0;
     for (int oi = 0; oi < 4; ++oi) {
       if (oi > 0) {
-        bool ok = fit_once(s, pt, pp, nall, n, (int)ord, r0sq, half_beta, cut, w_out, r_out, kind);
+        bool ok = fit_once<FT>(s, pt, pp, nall, n, (int)ord, r0sq, half_beta, cut, w_out, r_out, kind);
         if (!ok && tid == 0) atomicExch(status, 1);
       }
       if (hit_lower2 || hit_upper2) break;
@@ -614,12 +617,20 @@ extern "C" int ssf_kl_fit_pass(const double *phase, const float *weights, const 
   SSF_REQUIRE(mode >= 0 && mode <= 5, "ssf_kl_fit_pass: mode must be in 0..5 (bit 1 amplitude and bit 2 tec exclude each other)");
   if (nsys <= 0) return SSF_OK;
   size_t smem = sizeof(double) * smem_doubles(ndir);
-  if (smem > 48 * 1024)
-    SSF_CUDA(cudaFuncSetAttribute(fit_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int64_t blocks = nsys < ssf::sm_count() * 16 ? nsys : ssf::sm_count() * 16;
-  SSF_LAUNCH(fit_pass_kernel, (int)blocks, FT, smem, (cudaStream_t)stream, phase, weights, pat, pp, ndir,
-             nsys, C, pinvC, U, r0 * r0, beta / 2.0, pinv_cut, mode, order, station_order, white, resid,
-             status);
+  if (ndir <= 64) {
+    if (smem > 48 * 1024)
+      SSF_CUDA(cudaFuncSetAttribute(fit_pass_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    SSF_LAUNCH(fit_pass_kernel<64>, (int)blocks, 64, smem, (cudaStream_t)stream, phase, weights, pat, pp, ndir,
+               nsys, C, pinvC, U, r0 * r0, beta / 2.0, pinv_cut, mode, order, station_order, white, resid,
+               status);
+  } else {
+    if (smem > 48 * 1024)
+      SSF_CUDA(cudaFuncSetAttribute(fit_pass_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    SSF_LAUNCH(fit_pass_kernel<128>, (int)blocks, 128, smem, (cudaStream_t)stream, phase, weights, pat, pp, ndir,
+               nsys, C, pinvC, U, r0 * r0, beta / 2.0, pinv_cut, mode, order, station_order, white, resid,
+               status);
+  }
   SSF_LAUNCHED();
   return SSF_OK;
 }
