@@ -1,15 +1,14 @@
 mkdir -p gpurun_out
-for v in 1 0; do
-SSF_TC_NARROW=$([ $v = 1 ] && echo 1 || echo 0) timeout 600 python bench.py --workload skalow --no-e2e --no-cpu-baseline > gpurun_out/r02u_skalow_$v.json 2> gpurun_out/r02u_skalow_$v.err; echo "narrow=$v exit $?"; tail -2 gpurun_out/r02u_skalow_$v.err
-python - <<PY
-import json
-d=json.load(open('gpurun_out/r02u_skalow_$v.json'))
-print(d['value'], d['ms_per_step'], d['roofline']['frac'], d['roofline']['alone']['frac'], d['roofline']['kernel_share_of_step'], d['fit'])
-PY
-done
-timeout 600 python bench.py --no-e2e --no-cpu-baseline --no-extras > gpurun_out/r02u_lofar.json 2> gpurun_out/r02u_lofar.err; tail -2 gpurun_out/r02u_lofar.err
-python - <<PY
-import json
-d=json.load(open('gpurun_out/r02u_lofar.json'))
-print(d['value'], d['ms_per_step'], d['roofline']['frac'], d['roofline']['alone']['frac'], d['fit'])
-PY
+(timeout 900 python -m pytest tests -m gpu -q > gpurun_out/r02z_gputest.log 2>&1; echo "pytest exit $?" >> gpurun_out/r02z_gputest.log); tail -3 gpurun_out/r02z_gputest.log
+(timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r02z_smoke.log 2>&1; echo "smoke exit $?" >> gpurun_out/r02z_smoke.log); tail -2 gpurun_out/r02z_smoke.log
+timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/r02z_bench_reference.json 2>/dev/null; echo "ref exit $?"
+timeout 900 python bench.py > gpurun_out/r02z_bench_lofar.json 2> gpurun_out/r02z_bench.err; echo "bench exit $?"; tail -2 gpurun_out/r02z_bench.err
+B="python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline"
+$B > gpurun_out/ncu_plain_b.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/r02z_launches.csv $B > gpurun_out/ncu_b.log 2>&1
+tail -2 gpurun_out/ncu_b.log
+P="python scripts/prof_kernel.py"
+$P kl --reps 1 --warmup 1 > gpurun_out/p1.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:contract_tc -c 1 -o gpurun_out/r02z_kl45 $P kl --reps 1 --warmup 1 > gpurun_out/n1.log 2>&1
+$P gain --reps 1 --warmup 1 > gpurun_out/p2.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:contract_tc -c 1 -o gpurun_out/r02z_gain45 $P gain --reps 1 --warmup 1 > gpurun_out/n2.log 2>&1
+$P kl --ndir 100 --n 2048 --ncol 512 --reps 1 --warmup 1 > gpurun_out/p3.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:contract_tc -c 1 -o gpurun_out/r02z_kl100 $P kl --ndir 100 --n 2048 --ncol 512 --reps 1 --warmup 1 > gpurun_out/n3.log 2>&1
+$P gain --ndir 100 --n 2048 --ncol 512 --reps 1 --warmup 1 > gpurun_out/p4.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:contract_tc -c 1 -o gpurun_out/r02z_gain100 $P gain --ndir 100 --n 2048 --ncol 512 --reps 1 --warmup 1 > gpurun_out/n4.log 2>&1
+ls -la gpurun_out/r02z_*
