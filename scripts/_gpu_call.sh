@@ -1,14 +1,17 @@
 mkdir -p gpurun_out
-(timeout 900 python -m pytest tests -m gpu -q > gpurun_out/r02z_gputest.log 2>&1; echo "pytest exit $?" >> gpurun_out/r02z_gputest.log); tail -3 gpurun_out/r02z_gputest.log
-(timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r02z_smoke.log 2>&1; echo "smoke exit $?" >> gpurun_out/r02z_smoke.log); tail -2 gpurun_out/r02z_smoke.log
-timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/r02z_bench_reference.json 2>/dev/null; echo "ref exit $?"
-timeout 900 python bench.py > gpurun_out/r02z_bench_lofar.json 2> gpurun_out/r02z_bench.err; echo "bench exit $?"; tail -2 gpurun_out/r02z_bench.err
-B="python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline"
-$B > gpurun_out/ncu_plain_b.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/r02z_launches.csv $B > gpurun_out/ncu_b.log 2>&1
-tail -2 gpurun_out/ncu_b.log
-P="python scripts/prof_kernel.py"
-$P kl --reps 1 --warmup 1 > gpurun_out/p1.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:contract_tc -c 1 -o gpurun_out/r02z_kl45 $P kl --reps 1 --warmup 1 > gpurun_out/n1.log 2>&1
-$P gain --reps 1 --warmup 1 > gpurun_out/p2.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:contract_tc -c 1 -o gpurun_out/r02z_gain45 $P gain --reps 1 --warmup 1 > gpurun_out/n2.log 2>&1
-$P kl --ndir 100 --n 2048 --ncol 512 --reps 1 --warmup 1 > gpurun_out/p3.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:contract_tc -c 1 -o gpurun_out/r02z_kl100 $P kl --ndir 100 --n 2048 --ncol 512 --reps 1 --warmup 1 > gpurun_out/n3.log 2>&1
-$P gain --ndir 100 --n 2048 --ncol 512 --reps 1 --warmup 1 > gpurun_out/p4.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:contract_tc -c 1 -o gpurun_out/r02z_gain100 $P gain --ndir 100 --n 2048 --ncol 512 --reps 1 --warmup 1 > gpurun_out/n4.log 2>&1
-ls -la gpurun_out/r02z_*
+P="timeout 120 python scripts/prof_kernel.py"
+run_set() {
+  echo "##### build flags: '$1'"
+  SSF_NVCC_EXTRA="$1" python -m ska_sdp_screen_fitting_b200._build > /dev/null 2>&1 || echo BUILD FAILED
+  export SSF_NVCC_EXTRA="$1"
+  shift
+  for args in "$@"; do eval "$args" 2>&1 | grep -v "^  \|^Traceback\|^torch\.\|^Search\|^CUDA\|^For debug\|^Compile\|^$" | tail -1; done
+  unset SSF_NVCC_EXTRA
+}
+{
+run_set "-DSSF_NW_WRAP=65536" "$P kl --ndir 100 --n 2048 --ncol 512" "$P kl --ndir 100 --n 1024 --ncol 2048"
+run_set "" "$P kl --ndir 100 --n 2048 --ncol 512" "$P kl --ndir 100 --n 1024 --ncol 2048" "$P kl --ndir 100 --n 2048 --ncol 256" "$P kl --ndir 100 --n 2048 --ncol 1024" "SSF_TC_NARROW=2 $P kl --ndir 45 --n 2048 --ncol 372" "$P kl --ndir 45 --n 2048 --ncol 372" "$P kl --ndir 64 --n 2048 --ncol 512" "$P kl --ndir 80 --n 2048 --ncol 512"
+} > gpurun_out/r02v_wrap.txt 2>&1
+cat gpurun_out/r02v_wrap.txt
+python -m ska_sdp_screen_fitting_b200._build > /dev/null 2>&1
+timeout 200 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2

@@ -1109,7 +1109,11 @@ contract_tc_narrow_kernel(const __grid_constant__ CUtensorMap bt_map, const floa
       // raw basis tile: one tensor-map copy, box = Kp direction rows x 128 pixels (rows beyond ndir
       // are out of bounds and arrive as zeros); then the first coefficient tiles
       mbar_expect_tx(raw_full, (uint32_t)Kp * TC_M * (uint32_t)sizeof(float));
+#ifdef SSF_NW_WRAP                                     // experiment: basis tiles from an L2-resident window (wrong values)
+      tma_load_2d(smem_u32(raw), &bt_map, (int)(pix0 % SSF_NW_WRAP), 0, raw_full);
+#else
       tma_load_2d(smem_u32(raw), &bt_map, (int)pix0, 0, raw_full);
+#endif
       for (int it = 0; it < nb && it < n_tiles; ++it) {
         mbar_expect_tx(b_full + 8 * it, stage_bytes);
         bulk_g2s(smem_u32(b_base + (size_t)it * 2 * NW_N * Kp), b_src + (size_t)it * 2 * NW_N * Kp, stage_bytes,
