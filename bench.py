@@ -34,7 +34,11 @@ sys.path.insert(1, os.path.join(ROOT, "tests"))        # synthetic_cases: the se
 
 FIT_AHEAD = 2
 FIT_GROUP = 4      # slabs per fit call of the streaming KL path
-KL_WARM_SKALOW = 48   # slabs over which the SKA-Low KL pass warms the flag-pattern cache before the timed steps
+# Slabs over which the SKA-Low KL pass warms the flag-pattern cache before the timed steps.  New
+# patterns per 512-system slab at 1 % flags (simulated): 138 cold, 76 after 48 slabs, 53 after 100,
+# 42 after 200, 35-40 from 300 on; a 65 536-slot cache fills (and starts over) every ~1500 slabs, so
+# the average over a 65 536-slab job is ~44 per slab -- what the timed steps see after 192 slabs.
+KL_WARM_SKALOW = int(os.environ.get("SSF_BENCH_KL_WARM", "192"))
 METRIC = "screen voxels/s (pix*ant*time*freq), KL & Voronoi"
 UNIT = "voxel/s"
 BYTES_PER_VOXEL = 16

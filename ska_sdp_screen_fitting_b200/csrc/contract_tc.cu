@@ -973,61 +973,75 @@ contract_tc_bigk_kernel(const __grid_constant__ CUtensorMap bt_map, const float 
 // More than 56 directions with TWO CTAs per SM.  The persistent kernel above is bound by its
 // one-CTA-per-SM structure, not by its pipeline (every one-CTA variant of either kernel
 // loses 10-15 points against two CTAs at the same shape).  Two CTAs fit an SM at 100 directions
-// when the split basis operand lives in TENSOR memory and the tiles are narrow:
-//   tensor memory, 256 columns per CTA:  D[TS][16] at column 0 | A_hi[Kp] | A_lo[Kp] at the top
-//                                        (Kp = 104: 208 operand columns + 3 accumulator stages)
-//   shared memory (floats):  raw[Kp][128] (one TMA tensor copy)  B[nb stages][hi, lo][16 Kp]
-//                                        (Kp = 104: 53 KB + 4 x 13 KB per CTA)
-// A CTA = one 128-pixel tile and a run of 16-row coefficient tiles (KL: 16 slab columns, Voronoi:
-// 8 columns x Re / Im).  The eight epilogue warps first split the raw basis tile into tensor
-// memory (warp w: lane quadrant w % 4, K half w / 4), then work as in the kernel of 4.1: thread =
-// pixel, 8 accumulator columns per warp and tile (tcgen05.ld x8).  The second resident CTA's
-// store stream covers this CTA's staging.  MODE 0 = Voronoi, 1 = KL.
-constexpr int NW_N = 16;                         // rows of a coefficient tile = N of the MMA
+// when half of the split basis operand lives in TENSOR memory and the tiles are narrow:
+//   tensor memory, 256 columns per CTA:  D[TS][NT] at column 0 | A_hi[Kp] at the top
+//                                        (Kp = 104: four stages of NT = 32 accumulator columns)
+//   shared memory (floats):  A_lo[128 Kp] in the canonical layout, written IN PLACE over the raw
+//                            basis tile raw[Kp][128] (one TMA tensor copy)  B[nb stages][hi, lo][NT Kp]
+//                                        (Kp = 104: 53 KB + 2 x 27 KB per CTA)
+// A CTA = one 128-pixel tile and a run of NT-row coefficient tiles (KL: NT slab columns, Voronoi:
+// NT / 2 columns x Re / Im); NT = 32 while two CTAs fit, else 16.  The eight epilogue warps first
+// split the raw basis tile: each thread reads its whole share (pixel row = lane quadrant w % 4, K
+// half w / 4) into registers, all meet at a named barrier, then A_hi goes to tensor memory
+// (tcgen05.st) and A_lo over the raw bytes.  The products are  A_lo B_hi (both operands from shared
+// memory),  A_hi B_lo and A_hi B_hi (A from tensor memory).  Then the warps work as in the kernel
+// of 4.1: thread = pixel, NT / 2 accumulator columns per warp and tile.  The second resident
+// CTA's store stream covers this CTA's staging.  MODE 0 = Voronoi, 1 = KL.
 constexpr int NW_MAXB = 6;
 constexpr int NW_NBARS = 2 * NW_MAXB + 2 * T_STAGES + 2;
-__host__ __device__ constexpr int narrow_columns(int mode) { return mode == 1 ? NW_N : NW_N / 2; }
-
-// Coefficient tiles of the narrow kernel: Bs[tile][hi | lo][canon(row, k)], 16 rows x Kp.
-// KL: row r = slab column 16 t + r.  Voronoi: rows r < 8 = Re, r >= 8 = Im of column 8 t + (r & 7).
-template <int MODE>
+template <int MODE, int NT>
 __global__ void split_b_narrow_kernel(const float *__restrict__ G, int ndir, int ldg, int64_t ncol, int Kp,
-                                      int64_t n_ct, float *__restrict__ Bs) {
+                                   int64_t n_ct, float *__restrict__ Bs) {
   const int kc4 = Kp >> 2;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= n_ct * NW_N * kc4) return;
+  if (idx >= n_ct * NT * kc4) return;
   const int kc = (int)(idx % kc4);
-  const int r = (int)((idx / kc4) % NW_N);
-  const int64_t tile = idx / ((int64_t)kc4 * NW_N);
+  const int r = (int)((idx / kc4) % NT);
+  const int64_t tile = idx / ((int64_t)kc4 * NT);
   float x[4];
 #pragma unroll
   for (int u = 0; u < 4; ++u) {
     const int k = 4 * kc + u;
     float v = 0.0f;
     if (MODE == 1) {
-      const int64_t col = tile * NW_N + r;
+      const int64_t col = tile * NT + r;
       if (col < ncol && k < ndir) v = G[col * ldg + k];
     } else {
-      const int64_t col = tile * (NW_N / 2) + (r & 7);
-      if (col < ncol && k < ndir) v = G[(col * ndir + k) * 2 + (r >> 3)];
+      const int64_t col = tile * (NT / 2) + (r % (NT / 2));
+      if (col < ncol && k < ndir) v = G[(col * ndir + k) * 2 + (r / (NT / 2))];
     }
     x[u] = v;
   }
   const float4 hv = make_float4(to_tf32(x[0]), to_tf32(x[1]), to_tf32(x[2]), to_tf32(x[3]));
   const float4 lv = make_float4(to_tf32(x[0] - hv.x), to_tf32(x[1] - hv.y), to_tf32(x[2] - hv.z),
                                 to_tf32(x[3] - hv.w));
-  float *dst = Bs + tile * (2 * NW_N * Kp) + canon(r, 4 * kc, kc4);
+  float *dst = Bs + tile * (2 * NT * Kp) + canon(r, 4 * kc, kc4);
   *reinterpret_cast<float4 *>(dst) = hv;
-  *reinterpret_cast<float4 *>(dst + NW_N * Kp) = lv;
+  *reinterpret_cast<float4 *>(dst + NT * Kp) = lv;
 }
 
-// Epilogue stores of one thread's 8 accumulator columns (its pixel, 8 slab columns).
-template <bool CHECK>
-__device__ __forceinline__ void store_kl8(const float (&v)[8], float *out, int64_t npix, int nvalid, ssf::OutFmt fmt) {
+// 32 lanes x 16 consecutive accumulator columns -> 16 registers per thread.
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float *v) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// Epilogue stores of one thread's NC accumulator columns (its pixel, NC slab columns).
+template <int NC, bool CHECK>
+__device__ __forceinline__ void store_kl_n(const float (&v)[NC], float *out, int64_t npix, int nvalid, ssf::OutFmt fmt) {
   const int64_t p2 = 2 * npix, p3 = 3 * npix, pc = fmt.planes * npix;
   const bool four = fmt.planes == 4;
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
+  for (int j = 0; j < NC; ++j) {
     if (CHECK && j >= nvalid) break;
     if (fmt.planes == 1) {                                   // dTEC cube: the raw screen value
       st_cube(out, ssf::out_word(v[j], fmt.prmt));
@@ -1047,13 +1061,13 @@ __device__ __forceinline__ void store_kl8(const float (&v)[8], float *out, int64
     out += pc;
   }
 }
-template <bool CHECK>
-__device__ __forceinline__ void store_vo8(const float (&v)[8], float *out, int64_t npix, int nvalid, int h,
-                                          ssf::OutFmt fmt) {
+template <int NC, bool CHECK>
+__device__ __forceinline__ void store_vo_n(const float (&v)[NC], float *out, int64_t npix, int nvalid, int h,
+                                           ssf::OutFmt fmt) {
   const int64_t p2 = 2 * npix, pc = fmt.planes * npix;
   const bool four = fmt.planes == 4;
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
+  for (int j = 0; j < NC; ++j) {
     if (CHECK && j >= nvalid) break;
     const float x = ssf::out_word(h == 0 ? ssf::fix_re(v[j]) : ssf::fix_im(v[j]), fmt.prmt);
     st_cube(out, x);
@@ -1062,27 +1076,29 @@ __device__ __forceinline__ void store_vo8(const float (&v)[8], float *out, int64
   }
 }
 
-template <int MODE>
+template <int MODE, int NT>
 __global__ void __launch_bounds__(320, 2)
 contract_tc_narrow_kernel(const __grid_constant__ CUtensorMap bt_map, const float *__restrict__ Bs, int ndir,
-                          int64_t npix, int64_t ncol, float *__restrict__ slab, int tiles_per_chunk, int Kp, int nb,
-                          ssf::OutFmt fmt) {
+                       int64_t npix, int64_t ncol, float *__restrict__ slab, int tiles_per_chunk, int Kp, int nb,
+                       ssf::OutFmt fmt) {
   constexpr int NEPI = 8;
-  constexpr int CT = narrow_columns(MODE);       // slab columns per coefficient tile
-  constexpr uint32_t IDESC = idesc_for(NW_N);
+  constexpr int NC = NT / 2;                     // accumulator columns per epilogue warp
+  constexpr int CT = MODE == 1 ? NT : NT / 2;    // slab columns per coefficient tile
+  constexpr uint32_t IDESC = idesc_for(NT);
+  constexpr int MAXKS = (SSF_MAX_DIR + 7) / 8 / 2;   // K steps per converter thread (half of <= 14)
   SSF_DYN_SMEM(float, sm);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int kc4 = Kp >> 2;
-  float *raw = sm;                               // [Kp][128]
-  float *b_base = sm + TC_M * Kp;                // stage s: hi at s*2*16*Kp, lo right after
-  uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (TC_M + 2 * nb * NW_N) * Kp);
+  float *raw = sm;                               // [Kp][128] until the split, then A_lo in the canonical layout
+  float *b_base = sm + TC_M * Kp;                // stage s: hi at s*2*NT*Kp, lo right after
+  uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (TC_M + 2 * nb * NT) * Kp);
   uint32_t *tmem_holder = reinterpret_cast<uint32_t *>(bars + NW_NBARS);
   const uint32_t b_full = smem_u32(bars), b_empty = smem_u32(bars + NW_MAXB);
   const uint32_t t_full = smem_u32(bars + 2 * NW_MAXB), t_empty = smem_u32(bars + 2 * NW_MAXB + T_STAGES);
   const uint32_t raw_full = smem_u32(bars + 2 * NW_MAXB + 2 * T_STAGES), a_ready = raw_full + 8;
-  const uint32_t stage_bytes = (uint32_t)(2 * NW_N * Kp * sizeof(float));
-  const int acol = 256 - 2 * Kp;                 // first TMEM column of A_hi; accumulator stages below it
-  const int TS = acol / NW_N < T_STAGES ? acol / NW_N : T_STAGES;
+  const uint32_t stage_bytes = (uint32_t)(2 * NT * Kp * sizeof(float));
+  const int acol = 256 - Kp;                     // first TMEM column of A_hi; accumulator stages below it
+  const int TS = acol / NT < T_STAGES ? acol / NT : T_STAGES;
 
   const int64_t pix0 = (int64_t)blockIdx.y * TC_M;
   const int64_t n_ct = (ncol + CT - 1) / CT;
@@ -1091,7 +1107,7 @@ contract_tc_narrow_kernel(const __grid_constant__ CUtensorMap bt_map, const floa
   if (ct_end > n_ct) ct_end = n_ct;
   if (ct_begin >= ct_end) return;                // whole CTA, before any barrier / allocation
   const int n_tiles = (int)(ct_end - ct_begin);
-  const float *b_src = Bs + ct_begin * (2 * NW_N * Kp);
+  const float *b_src = Bs + ct_begin * (2 * NT * Kp);
 
   if (warp == NEPI) {
     if (elect_one()) {
@@ -1106,17 +1122,11 @@ contract_tc_narrow_kernel(const __grid_constant__ CUtensorMap bt_map, const floa
       mbar_init(raw_full, 1);
       mbar_init(a_ready, NEPI);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-      // raw basis tile: one tensor-map copy, box = Kp direction rows x 128 pixels (rows beyond ndir
-      // are out of bounds and arrive as zeros); then the first coefficient tiles
       mbar_expect_tx(raw_full, (uint32_t)Kp * TC_M * (uint32_t)sizeof(float));
-#ifdef SSF_NW_WRAP                                     // experiment: basis tiles from an L2-resident window (wrong values)
-      tma_load_2d(smem_u32(raw), &bt_map, (int)(pix0 % SSF_NW_WRAP), 0, raw_full);
-#else
       tma_load_2d(smem_u32(raw), &bt_map, (int)pix0, 0, raw_full);
-#endif
       for (int it = 0; it < nb && it < n_tiles; ++it) {
         mbar_expect_tx(b_full + 8 * it, stage_bytes);
-        bulk_g2s(smem_u32(b_base + (size_t)it * 2 * NW_N * Kp), b_src + (size_t)it * 2 * NW_N * Kp, stage_bytes,
+        bulk_g2s(smem_u32(b_base + (size_t)it * 2 * NT * Kp), b_src + (size_t)it * 2 * NT * Kp, stage_bytes,
                  b_full + 8 * it);
       }
     }
@@ -1134,40 +1144,40 @@ contract_tc_narrow_kernel(const __grid_constant__ CUtensorMap bt_map, const floa
   const uint32_t tmem_base = *tmem_holder;
 
   if (warp == NEPI) {
-    // ===== TMA lane: refill stage s once the MMAs of the tile that used it have retired =====
+    // ===== TMA lane =====
     if (elect_one()) {
       for (int it = nb; it < n_tiles; ++it) {
         const int s = it % nb, use = it / nb;
         mbar_wait(b_empty + 8 * s, (use - 1) & 1);
         mbar_expect_tx(b_full + 8 * s, stage_bytes);
-        bulk_g2s(smem_u32(b_base + (size_t)s * 2 * NW_N * Kp), b_src + (size_t)it * 2 * NW_N * Kp, stage_bytes,
+        bulk_g2s(smem_u32(b_base + (size_t)s * 2 * NT * Kp), b_src + (size_t)it * 2 * NT * Kp, stage_bytes,
                  b_full + 8 * s);
       }
     }
   } else if (warp == NEPI + 1) {
-    // ===== MMA lane: A from tensor memory =====
-    mbar_wait(a_ready, 0);                       // the split basis tile is in TMEM
+    // ===== MMA lane: A_lo from shared memory, A_hi from tensor memory =====
+    mbar_wait(a_ready, 0);
     tc_fence_after();
     if (elect_one()) {
       const uint32_t lbo = 128, sbo = (uint32_t)kc4 * 128;
-      const uint32_t ta_hi = tmem_base + (uint32_t)acol, ta_lo = ta_hi + (uint32_t)Kp;
+      const uint64_t da_lo = make_desc(smem_u32(raw), lbo, sbo);
+      const uint32_t ta_hi = tmem_base + (uint32_t)acol;
       const int ksteps = Kp >> 3;
       for (int it = 0; it < n_tiles; ++it) {
         const int s = it % nb, t = it % TS;
         mbar_wait(b_full + 8 * s, (it / nb) & 1);
         if (it >= TS) mbar_wait(t_empty + 8 * t, (it / TS - 1) & 1);
         tc_fence_after();
-        const float *bh = b_base + (size_t)s * 2 * NW_N * Kp;
-        const uint64_t db_hi = make_desc(smem_u32(bh), lbo, sbo), db_lo = make_desc(smem_u32(bh + NW_N * Kp), lbo, sbo);
-        const uint32_t d_tmem = tmem_base + (uint32_t)(t * NW_N);
-        // corrections first (see contract_tc_kernel); one K step = 8 TMEM columns of A = 16 in the
-        // descriptor's start-address field
+        const float *bh = b_base + (size_t)s * 2 * NT * Kp;
+        const uint64_t db_hi = make_desc(smem_u32(bh), lbo, sbo), db_lo = make_desc(smem_u32(bh + NT * Kp), lbo, sbo);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(t * NT);
+        // corrections first; one K step = 8 TMEM columns of A_hi = 16 in a descriptor's start field
         if (SSF_TC_PRODUCTS == 4)
           for (int ks = 0; ks < ksteps; ++ks)
-            tc_mma_tf32_ts(d_tmem, ta_lo + (uint32_t)(ks * 8), db_lo + (uint64_t)(ks * 16), IDESC, ks > 0);
+            tc_mma_tf32(d_tmem, da_lo + (uint64_t)(ks * 16), db_lo + (uint64_t)(ks * 16), IDESC, ks > 0);
         for (int ks = 0; ks < ksteps; ++ks)
-          tc_mma_tf32_ts(d_tmem, ta_lo + (uint32_t)(ks * 8), db_hi + (uint64_t)(ks * 16), IDESC,
-                         SSF_TC_PRODUCTS == 4 || ks > 0);
+          tc_mma_tf32(d_tmem, da_lo + (uint64_t)(ks * 16), db_hi + (uint64_t)(ks * 16), IDESC,
+                      SSF_TC_PRODUCTS == 4 || ks > 0);
         for (int ks = 0; ks < ksteps; ++ks)
           tc_mma_tf32_ts(d_tmem, ta_hi + (uint32_t)(ks * 8), db_lo + (uint64_t)(ks * 16), IDESC, 1);
         for (int ks = 0; ks < ksteps; ++ks)
@@ -1178,53 +1188,72 @@ contract_tc_narrow_kernel(const __grid_constant__ CUtensorMap bt_map, const floa
     }
     __syncwarp();
   } else {
-    // ===== epilogue warps: first the split of the basis tile into TMEM ... =====
+    // ===== epilogue warps: first the split of the basis tile (A_hi -> TMEM, A_lo in place) ... =====
     const int q = warp & 3, h = (warp >> 2) & 1;
     {
       const int r = 32 * q + lane;               // pixel row = TMEM lane
-      const uint32_t ta_hi = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)acol, ta_lo = ta_hi + (uint32_t)Kp;
+      const uint32_t ta_hi = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)acol;
       const int ksteps = Kp >> 3, half = (ksteps + 1) >> 1;
+      const int ks0 = h * half, ks1 = h == 0 ? half : ksteps;
+      float x[MAXKS][8];
       mbar_wait(raw_full, 0);
-      for (int ks = h * half; ks < (h == 0 ? half : ksteps); ++ks) {
-        const int k0 = ks * 8;
-        float hi[8], lo[8];
+#pragma unroll
+      for (int i = 0; i < MAXKS; ++i)
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
-          const float x = (k0 + u < ndir) ? raw[(k0 + u) * TC_M + r] : 0.0f;
-          hi[u] = to_tf32(x);
-          lo[u] = to_tf32(x - hi[u]);
+          const int k = (ks0 + i) * 8 + u;
+          x[i][u] = (ks0 + i < ks1 && k < ndir) ? raw[k * TC_M + r] : 0.0f;
         }
-        tmem_st8(ta_hi + (uint32_t)k0, hi);
-        tmem_st8(ta_lo + (uint32_t)k0, lo);
+      // every epilogue thread holds its share of the raw tile: the bytes may be overwritten
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+#pragma unroll
+      for (int i = 0; i < MAXKS; ++i) {
+        if (ks0 + i < ks1) {
+          const int k0 = (ks0 + i) * 8;
+          float hi[8];
+          float4 l0, l1;
+#pragma unroll
+          for (int u = 0; u < 8; ++u) hi[u] = to_tf32(x[i][u]);
+          l0 = make_float4(to_tf32(x[i][0] - hi[0]), to_tf32(x[i][1] - hi[1]), to_tf32(x[i][2] - hi[2]),
+                           to_tf32(x[i][3] - hi[3]));
+          l1 = make_float4(to_tf32(x[i][4] - hi[4]), to_tf32(x[i][5] - hi[5]), to_tf32(x[i][6] - hi[6]),
+                           to_tf32(x[i][7] - hi[7]));
+          tmem_st8(ta_hi + (uint32_t)k0, hi);
+          *reinterpret_cast<float4 *>(raw + canon(r, k0, kc4)) = l0;
+          *reinterpret_cast<float4 *>(raw + canon(r, k0 + 4, kc4)) = l1;
+        }
       }
       asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      fence_proxy_async();                       // A_lo is read by the tensor core (async proxy)
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(a_ready);
     }
-    // ===== ... then the tiles: thread = pixel, 8 accumulator columns per warp =====
+    // ===== ... then the tiles: thread = pixel, NC accumulator columns per warp =====
     const int64_t pix = pix0 + 32 * q + lane;
     for (int it = 0; it < n_tiles; ++it) {
       const int t = it % TS;
       const int64_t c0 = (ct_begin + it) * CT;
       mbar_wait(t_full + 8 * t, (it / TS) & 1);
       tc_fence_after();
-      float v[8];
-      tmem_ld8(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * NW_N + 8 * h), v);
+      float v[NC];
+      const uint32_t ta = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * NT + NC * h);
+      if (NC == 16) tmem_ld16(ta, v);
+      else tmem_ld8(ta, v);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(t_empty + 8 * t);
       if (MODE == 1) {
-        float *out = slab + (c0 + 8 * h) * fmt.planes * npix + pix;
-        const int64_t left = ncol - (c0 + 8 * h);
-        if (left >= 8) store_kl8<false>(v, out, npix, 8, fmt);
-        else if (left > 0) store_kl8<true>(v, out, npix, (int)left, fmt);
+        float *out = slab + (c0 + NC * h) * fmt.planes * npix + pix;
+        const int64_t left = ncol - (c0 + NC * h);
+        if (left >= NC) store_kl_n<NC, false>(v, out, npix, NC, fmt);
+        else if (left > 0) store_kl_n<NC, true>(v, out, npix, (int)left, fmt);
       } else {
-        // rows 0..7 = Re (h = 0) -> planes 0, 2; rows 8..15 = Im (h = 1) -> planes 1, 3
+        // rows 0..NC-1 = Re (h = 0) -> planes 0, 2; rows NC.. = Im (h = 1) -> planes 1, 3
         float *out = slab + c0 * fmt.planes * npix + (int64_t)h * npix + pix;
         const int64_t left = ncol - c0;
-        if (left >= 8) store_vo8<false>(v, out, npix, 8, h, fmt);
-        else if (left > 0) store_vo8<true>(v, out, npix, (int)left, h, fmt);
+        if (left >= NC) store_vo_n<NC, false>(v, out, npix, NC, h, fmt);
+        else if (left > 0) store_vo_n<NC, true>(v, out, npix, (int)left, h, fmt);
       }
     }
   }
@@ -1354,29 +1383,19 @@ int launch_bigk(const float *Bt, const float *G, int ndir, int ldg, int64_t npix
   return guard.release();
 }
 
-template <int MODE>
-int launch_narrow(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
-                  ssf::OutFmt fmt, cudaMemPool_t pool, cudaStream_t stream) {
-  constexpr int CT = narrow_columns(MODE);
+template <int MODE, int NT>
+int launch_narrow_nt(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
+                  ssf::OutFmt fmt, cudaMemPool_t pool, cudaStream_t stream, int nb, size_t smem) {
+  constexpr int CT = MODE == 1 ? NT : NT / 2;
   const int Kp = (ndir + 7) / 8 * 8;
   const int64_t n_ct = (ncol + CT - 1) / CT;
-  // coefficient stages: as many as two resident CTAs leave room for next to the raw basis tile
-  auto smem_for = [&](int stages) { return sizeof(float) * (size_t)(TC_M + 2 * stages * NW_N) * Kp + 8 * NW_NBARS + 64; };
-  int nb = 2;
-  while (nb < NW_MAXB && 2 * (smem_for(nb + 1) + 1024) <= 227 * 1024) ++nb;
-  if (const char *e = getenv("SSF_TC_NB")) {
-    const int want = atoi(e);
-    if (want >= 2 && want <= NW_MAXB && 2 * (smem_for(want) + 1024) <= 227 * 1024) nb = want;
-  }
-  const size_t smem = smem_for(nb);
-  const size_t bs_bytes = sizeof(float) * (size_t)n_ct * 2 * NW_N * Kp;
+  const size_t bs_bytes = sizeof(float) * (size_t)n_ct * 2 * NT * Kp;
   float *Bs = nullptr;
   SSF_CUDA(cudaMallocFromPoolAsync(reinterpret_cast<void **>(&Bs), bs_bytes, pool, stream));
   ScratchGuard guard{Bs, stream};
-  SSF_LAUNCH(split_b_narrow_kernel<MODE>, ssf::div_up(n_ct * NW_N * (Kp >> 2), 256), 256, 0, stream, G, ndir, ldg, ncol,
-             Kp, n_ct, Bs);
+  SSF_LAUNCH((split_b_narrow_kernel<MODE, NT>), ssf::div_up(n_ct * NT * (Kp >> 2), 256), 256, 0, stream, G, ndir, ldg,
+             ncol, Kp, n_ct, Bs);
   SSF_LAUNCHED();
-  // tensor map of the basis: [ndir rows][npix] float32, box = Kp rows x 128 pixels, no swizzle
   const EncodeFn encode = tensor_map_encoder();
   SSF_REQUIRE(encode != nullptr, "cuTensorMapEncodeTiled is not available");
   CUtensorMap bt_map;
@@ -1388,10 +1407,9 @@ int launch_narrow(const float *Bt, const float *G, int ndir, int ldg, int64_t np
                              estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   SSF_REQUIRE(cr == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d)", (int)cr);
-  auto kfn = contract_tc_narrow_kernel<MODE>;
+  auto kfn = contract_tc_narrow_kernel<MODE, NT>;
   SSF_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  // about 256 slab columns per CTA (0.5 MB of cube), as for the kernel of 4.1
-  int64_t per = 256 / CT;
+  int64_t per = 256 / CT;                        // about 256 slab columns per CTA, as for the kernel of 4.1
   if (const char *e = getenv("SSF_TC_PER")) {
     per = atoi(e);
     if (per < 1) per = 1;
@@ -1402,6 +1420,31 @@ int launch_narrow(const float *Bt, const float *G, int ndir, int ldg, int64_t np
   SSF_LAUNCH(kfn, grid, 320, smem, stream, bt_map, Bs, ndir, npix, ncol, slab, (int)per, Kp, nb, fmt);
   SSF_LAUNCHED();
   return guard.release();
+}
+
+// 32-row tiles while two CTAs (basis tile + two coefficient stages each) fit an SM, else 16-row ones.
+template <int MODE>
+int launch_narrow(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, int64_t ncol, float *slab,
+               ssf::OutFmt fmt, cudaMemPool_t pool, cudaStream_t stream) {
+  const int Kp = (ndir + 7) / 8 * 8;
+  auto smem_for = [&](int nt, int stages) {
+    return sizeof(float) * (size_t)(TC_M + 2 * stages * nt) * Kp + 8 * NW_NBARS + 64;
+  };
+  auto fits2 = [&](int nt, int stages) { return 2 * (smem_for(nt, stages) + 1024) <= 227 * 1024; };
+  int nt = fits2(32, 2) ? 32 : 16;
+  if (const char *e = getenv("SSF_TC_NT")) {        // experiment hook: tile rows
+    const int want = atoi(e);
+    if ((want == 16 || want == 32) && fits2(want, 2)) nt = want;
+  }
+  int nb = 2;
+  while (nb < NW_MAXB && fits2(nt, nb + 1)) ++nb;
+  if (const char *e = getenv("SSF_TC_NB")) {
+    const int want = atoi(e);
+    if (want >= 2 && want <= NW_MAXB && fits2(nt, want)) nb = want;
+  }
+  const size_t smem = smem_for(nt, nb);
+  if (nt == 32) return launch_narrow_nt<MODE, 32>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, pool, stream, nb, smem);
+  return launch_narrow_nt<MODE, 16>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, pool, stream, nb, smem);
 }
 
 // Stream-ordered scratch for the split coefficient tiles, from a library-private memory pool
@@ -1487,15 +1530,15 @@ int launch_tc(const float *Bt, const float *G, int ndir, int ldg, int64_t npix, 
     // (experiment hooks: SSF_TC_BIGK=0 never, SSF_TC_BIGK=2 always)
     const char *e = getenv("SSF_TC_BIGK");
     const bool never = e && e[0] == '0', always = e && e[0] == '2';
-    // phase-only modes above 56 directions: the narrow-tile kernel keeps two CTAs per SM
-    // (SSF_TC_NARROW=0: the persistent kernel instead; =2: always, for experiments)
+    // KL screens above 56 directions: the narrow-tile kernel keeps two CTAs per SM
+    // (SSF_TC_NARROW=0: the persistent kernel instead; =2: always, any mode but gain, for experiments).
+    // Measured (profiles/r02_kernels_w_narrow.txt): KL 0.90 at 60 directions / 1024^2 and 0.80 at 64 / 2048^2
+    // against 0.76-0.77 for the persistent kernel, 0.72-0.76 against 0.69-0.72 at 100 / 2048^2; the
+    // Voronoi tiles of this layout (16 columns) stay behind the persistent kernel (0.66 against 0.70).
     const char *en = getenv("SSF_TC_NARROW");
     const bool narrow_never = en && en[0] == '0', narrow_always = en && en[0] == '2';
-    // Measured (profiles/r02_kernels_t_narrow.txt): KL 0.81-0.84 against 0.74-0.77 for the persistent
-    // kernel at 1024^2 (60-112 directions), equal (0.70) at 2048^2; the 8-column Voronoi tiles are
-    // too fine (0.55 against 0.66), so that mode stays on the persistent kernel.
-    if (MODE == 1 && !always && ((per_sm == 1 && !never && !narrow_never) || narrow_always))
-      return launch_narrow<1>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, pool, stream);
+    if (MODE != 2 && !always && ((MODE == 1 && per_sm == 1 && !never && !narrow_never) || narrow_always))
+      return launch_narrow<(MODE == 2 ? 1 : MODE)>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, pool, stream);
     if ((per_sm == 1 && !never) || always) return launch_bigk<MODE>(Bt, G, ndir, ldg, npix, ncol, slab, fmt, pool, stream);
   }
   float *Bs = nullptr;
