@@ -32,7 +32,12 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(1, os.path.join(ROOT, "tests"))        # synthetic_cases: the seeded input generator
 
-FIT_AHEAD = 2
+# Fit groups the streamed fit keeps in front of the evaluation.  6 groups = 24 LOFAR steps = ~100 ms of
+# slack: the thread that issues the fits is descheduled for 20-80 ms now and then on these (virtual)
+# hosts -- wall time of one stage 70 ms with 0.5 ms of CPU time, with or without the NVML poller,
+# the collector, allocations -- and with a lead of 2 groups (35 ms) that stalled the GPU: one
+# bench run in ~10 read 6-7 ms per step instead of 4.3.
+FIT_AHEAD = int(os.environ.get("SSF_BENCH_FIT_AHEAD", "6"))
 FIT_GROUP = 4      # slabs per fit call of the streaming KL path
 # Slabs over which the SKA-Low KL pass warms the flag-pattern cache before the timed steps.  New
 # patterns per 512-system slab at 1 % flags (simulated): 138 cold, 76 after 48 slabs, 53 after 100,
@@ -128,6 +133,7 @@ class ClockSampler:
 
     def _poll_nvml(self):
         pynvml, handle, smax = self._nvml
+        period = float(os.environ.get("SSF_BENCH_NVML_PERIOD", "0.05"))
         while not self._stop.is_set():
             try:
                 sm = float(pynvml.nvmlDeviceGetClockInfo(handle, pynvml.NVML_CLOCK_SM))
@@ -138,7 +144,7 @@ class ClockSampler:
                 self.rows.append((time.time(), sm, smax, [n for n, m in self.REASONS.items() if bits & m]))
             except Exception:  # noqa: BLE001
                 pass
-            self._stop.wait(0.05)
+            self._stop.wait(period)
 
     def _pump(self):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]

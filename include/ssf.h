@@ -96,6 +96,11 @@ int ssf_kl_patterns_update(const uint64_t *masks, int64_t nsys, int ndir, const 
                            double *C, double *pinvC, double *U, double *sv,
                            int32_t *counters, int32_t *status, int32_t *pat, void *stream);
 
+/* Grid width of ssf_kl_fit_pass in CTAs per SM, process-wide (0 = the default, 16).  The streamed
+ * path (fits on a side stream beside the cube kernels) sets 2 so that fit CTAs fit next to the
+ * resident evaluation CTAs instead of replacing them; an eager fit of a whole table wants 16. */
+int ssf_kl_fit_ctas_per_sm(int ctas);
+
 /* ------------------------------------------------------------------------------------
  * KL fit, one pass over all systems.  Replaces _fit_screen (stationscreen.py:433-594) and
  * the per-time body of _process_station (:681-779) for phase screens.

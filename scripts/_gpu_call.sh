@@ -1,9 +1,11 @@
 mkdir -p gpurun_out
-for w in 192 48; do
-SSF_BENCH_KL_WARM=$w timeout 600 python bench.py --workload skalow --no-e2e --no-cpu-baseline > gpurun_out/r02y_skalow_$w.json 2> gpurun_out/r02y_skalow_$w.err; tail -2 gpurun_out/r02y_skalow_$w.err
+for a in 6 2; do
+for i in 1 2 3 4 5 6 7 8 9 10 11 12; do
+SSF_BENCH_FIT_AHEAD=$a timeout 600 python bench.py --no-e2e --no-cpu-baseline --no-extras > gpurun_out/st.json 2> gpurun_out/st.err
 python - <<PY
 import json
-d=json.load(open('gpurun_out/r02y_skalow_$w.json'))
-print($w, d['value'], d['ms_per_step'], d['roofline']['frac'], d['roofline']['alone']['frac'], d['roofline']['kernel_share_of_step'], d['fit_breakdown']['pattern_slots_in_use'])
+d=json.load(open('gpurun_out/st.json'))
+print('ahead $a', round(d['ms_per_step'],3), round(d['fit_host_ms_per_slab'],2), round(d['roofline']['frac'],3))
 PY
+done
 done

@@ -35,6 +35,7 @@ SIGNATURES = {
                                  _P, _P, _P, _P, _P]),
     "ssf_kl_patterns_update": (c_int, [_P, c_int64, c_int, _P, c_double, c_double, c_double, _P, _P, c_int,
                                        _P, c_int, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "ssf_kl_fit_ctas_per_sm": (c_int, [c_int]),
     "ssf_kl_fit_pass": (c_int, [_P, _P, _P, _P, c_int, c_int64, _P, _P, _P, c_double, c_double,
                                 c_double, c_int, _P, _P, _P, _P, _P, _P]),
     "ssf_kl_flag_outliers": (c_int, [_P, _P, c_int, c_int64, c_double, _P, _P]),

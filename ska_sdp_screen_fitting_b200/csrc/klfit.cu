@@ -5,9 +5,15 @@
 //
 // Replaces _fit_screen (stationscreen.py:433-594), the per-time body of _process_station
 // (:681-779), _circ_chi2 (:353-387) and _flag_outliers (:303-350).
+#include <stdlib.h>
+
+#include <atomic>
+
 #include "common.cuh"
 
 namespace {
+
+std::atomic<int> g_fit_ctas_per_sm{16};
 
 // Threads per CTA of the fit kernel: a template parameter FT >= ndir (64 up to 64 directions,
 // 128 above): half the idle lanes, registers and barrier width at the LOFAR direction count.
@@ -605,6 +611,18 @@ amp_flag_kernel(const double *__restrict__ val, const double *__restrict__ resid
 
 }  // namespace
 
+// Grid width of ssf_kl_fit_pass in CTAs per SM (process-wide; 0 restores the default of 16).  A
+// fit that runs beside the cube kernels on a side stream is better off narrow: with 1-2 CTAs per
+// SM (64 threads, 21 KB of shared memory at 45 directions) it fits NEXT to the two resident
+// evaluation CTAs, with 16 it takes their place as they retire (measured on the LOFAR step:
+// evaluation kernel 0.871 -> 0.885-0.893 of the HBM peak inside the step; the fit call itself
+// 1.2 -> 2.8 ms per 23 808 systems, still far inside the 17.6 ms it has).
+extern "C" int ssf_kl_fit_ctas_per_sm(int ctas) {
+  SSF_REQUIRE(ctas >= 0 && ctas <= 32, "ssf_kl_fit_ctas_per_sm: 0 (default) .. 32");
+  g_fit_ctas_per_sm.store(ctas == 0 ? 16 : ctas, std::memory_order_relaxed);
+  return SSF_OK;
+}
+
 extern "C" int ssf_kl_fit_pass(const double *phase, const float *weights, const int32_t *pat,
                                const double *pp, int ndir, int64_t nsys, const double *C,
                                const double *pinvC, const double *U, double r0, double beta,
@@ -617,7 +635,9 @@ extern "C" int ssf_kl_fit_pass(const double *phase, const float *weights, const 
   SSF_REQUIRE(mode >= 0 && mode <= 5, "ssf_kl_fit_pass: mode must be in 0..5 (bit 1 amplitude and bit 2 tec exclude each other)");
   if (nsys <= 0) return SSF_OK;
   size_t smem = sizeof(double) * smem_doubles(ndir);
-  int64_t blocks = nsys < ssf::sm_count() * 16 ? nsys : ssf::sm_count() * 16;
+  // CTAs per SM of the grid-stride fit: 16 unless ssf_kl_fit_ctas_per_sm() set another value
+  const int per_sm = g_fit_ctas_per_sm.load(std::memory_order_relaxed);
+  int64_t blocks = nsys < (int64_t)ssf::sm_count() * per_sm ? nsys : (int64_t)ssf::sm_count() * per_sm;
   if (ndir <= 64) {
     if (smem > 48 * 1024)
       SSF_CUDA(cudaFuncSetAttribute(fit_pass_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

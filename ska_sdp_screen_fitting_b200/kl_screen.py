@@ -79,7 +79,8 @@ class KLScreen(Screen):
         self._pinv_full = None
         self._fit_stream = None
         self._patterns = None
-        self.fit_ahead = 2                # fit blocks the streaming fit runs ahead of the evaluation
+        self.fit_ahead = 4                # fit blocks the streaming fit runs ahead of the evaluation (slack for host hiccups)
+        self.fit_ctas_per_sm = 2          # grid width of the streamed fit (CTAs per SM; the eager fit uses 16)
         self.fit_group = 4                # stream_slabs: slabs fitted per fit call (amortises the per-call host work)
         self.keep_fit_results = True      # streamed write(): bring white / resid / order / weights back to the host
         self.write_soltabs = False        # append the screen soltabs to the input h5parm after the fit (write_back)
@@ -231,6 +232,20 @@ class KLScreen(Screen):
             self._fit_stream = torch.cuda.Stream(eng.device, priority=-1)   # the fit fills freed SM slots first
         side = self._fit_stream
         side.wait_stream(main)                           # inputs / setup are ready
+        # Give the side stream's allocator pool one large cached segment up front: every tensor
+        # of a fit call (a few dozen MB per block) is then carved from it, and the steady state
+        # never reaches cudaMalloc -- which waits for the work queued on the device (the main
+        # thread runs many evaluation launches ahead) and so stalled the fit thread for tens of
+        # ms at random (seen as fit_host_ms_per_slab 6-7 ms instead of 0.5 in two bench runs).
+        if not getattr(self, "_fit_pool_primed", False):
+            rows = max((r1 - r0) for r0, r1 in bounds) if bounds else 0
+            n_f, n_a = len(self.freqs_ph), len(self.station_names)
+            per_block = rows * n_f * n_a * self._pp_dev.shape[0] * 8
+            with torch.cuda.stream(side):
+                reserve = torch.empty(int(min(max(24 * per_block, 256 << 20), 4 << 30)), dtype=torch.uint8,
+                                      device=eng.device)
+                del reserve
+            self._fit_pool_primed = True
         state = {"last_done": None, "blocked": False}
 
         def launch_fit(r0, r1):
@@ -284,6 +299,9 @@ class KLScreen(Screen):
                 main.wait_event(state["last_done"])
 
         self._settle = settle
+        # a fit that runs beside the cube kernels is launched narrow (ssf_kl_fit_ctas_per_sm): its
+        # CTAs then fit next to the resident evaluation CTAs instead of replacing them
+        eng._call("ssf_kl_fit_ctas_per_sm", int(self.fit_ctas_per_sm))
         helper = threading.Thread(target=issue_fits, name="ssf-fit", daemon=True)
         helper.start()
         try:
@@ -298,6 +316,7 @@ class KLScreen(Screen):
             stop.set()
             helper.join(timeout=30)
             self._settle = None
+            eng._call("ssf_kl_fit_ctas_per_sm", 0)
 
     def stream_slabs(self, val_dev, wt_dev, slots, ring, cellsize_deg, first=0, count=None, out_flags=0):
         """Fit + evaluation of device-resident solutions slab by slab: yields ``(k, slab)`` for
