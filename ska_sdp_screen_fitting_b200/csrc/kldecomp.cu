@@ -29,14 +29,12 @@ inline double rsqrt(double x) { return 1.0 / sqrt(x); }
 inline double __drcp_rn(double x) { return 1.0 / x; }
 #endif
 
+// One flag pattern (slot `pat`) by the whole CTA; `sm` = the CTA's dynamic shared memory.
 template <int THREADS>
-__global__ void __launch_bounds__(THREADS)
-decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__restrict__ masks,
-                 double r0sq, double half_beta, double cut, double *__restrict__ Cout,
-                 double *__restrict__ Pout, double *__restrict__ Uout, double *__restrict__ svout,
-                 const int32_t *__restrict__ range, int32_t *__restrict__ status,
-                 const double *U0) {
-  SSF_DYN_SMEM(double, sm);
+__device__ void decompose_one(double *sm, const int pat, const double *__restrict__ pp, int ndir,
+                              const uint64_t *__restrict__ masks, double r0sq, double half_beta, double cut,
+                              double *__restrict__ Cout, double *__restrict__ Pout, double *__restrict__ Uout,
+                              double *__restrict__ svout, int32_t *__restrict__ status, const double *U0) {
   __shared__ int s_idx[SSF_MAX_DIR];
   __shared__ double s_c[2][SSF_MAX_DIR / 2 + 1], s_s[2][SSF_MAX_DIR / 2 + 1];   // double-buffered rotations
   __shared__ int s_p[2][SSF_MAX_DIR / 2 + 1], s_q[2][SSF_MAX_DIR / 2 + 1];
@@ -47,10 +45,6 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
   __shared__ double s_off, s_tot;
   __shared__ double s_inv[SSF_MAX_DIR + 16], s_gsu[SSF_MAX_DIR + 16], s_gsa[SSF_MAX_DIR + 16];
 
-  // range != null: device-resident pattern cache -- this launch covers the slots
-  // [range[1], range[0]) that ssf_kl_patterns_update has just handed out (grid = upper bound)
-  const int pat = range ? range[1] + (int)blockIdx.x : (int)blockIdx.x;
-  if (range && pat >= range[0]) return;
   const int tid = threadIdx.x;
   const uint64_t m0 = masks[2 * pat], m1 = masks[2 * pat + 1];
   if (tid == 0) {
@@ -473,6 +467,27 @@ decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__rest
   }
 }
 
+// range == null: patterns 0 .. npat-1 (ssf_kl_decompose).  range != null: device-resident pattern
+// cache -- the slots [range[1], range[0]) that ssf_kl_patterns_update has just handed out.  The
+// grid strides over the patterns, so the launch needs no grid as large as the (host-unknown) upper
+// bound of new patterns: a few CTAs per SM instead of one -- mostly empty -- CTA per SYSTEM of the
+// pass (23 808 at the LOFAR shape), each of which had to be given a 35 KB shared-memory slot that
+// an evaluation CTA could have had.
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+decompose_kernel(const double *__restrict__ pp, int ndir, const uint64_t *__restrict__ masks, int npat,
+                 double r0sq, double half_beta, double cut, double *__restrict__ Cout,
+                 double *__restrict__ Pout, double *__restrict__ Uout, double *__restrict__ svout,
+                 const int32_t *__restrict__ range, int32_t *__restrict__ status,
+                 const double *U0) {
+  SSF_DYN_SMEM(double, sm);
+  const int first = range ? range[1] : 0, end = range ? range[0] : npat;
+  for (int pat = first + (int)blockIdx.x; pat < end; pat += (int)gridDim.x) {
+    decompose_one<THREADS>(sm, pat, pp, ndir, masks, r0sq, half_beta, cut, Cout, Pout, Uout, svout, status, U0);
+    __syncthreads();
+  }
+}
+
 
 // ------------------------------------------------------------------------------------ pattern cache
 // Device-resident map  flag pattern (128-bit mask) -> slot of its decomposition, so that a fit
@@ -610,10 +625,10 @@ extern "C" int ssf_kl_decompose(const double *pp, int ndir, const uint64_t *mask
   SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
   SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
   if (ndir > 64) {
-    SSF_LAUNCH(decompose_kernel<BIG>, npat, BIG, smem, (cudaStream_t)stream, pp, ndir, masks, r0 * r0,
+    SSF_LAUNCH(decompose_kernel<BIG>, npat, BIG, smem, (cudaStream_t)stream, pp, ndir, masks, npat, r0 * r0,
                beta / 2.0, pinv_cut, C, pinvC, U, sv, (const int32_t *)nullptr, (int32_t *)nullptr, (const double *)nullptr);
   } else {
-    SSF_LAUNCH(decompose_kernel<256>, npat, 256, smem, (cudaStream_t)stream, pp, ndir, masks, r0 * r0,
+    SSF_LAUNCH(decompose_kernel<256>, npat, 256, smem, (cudaStream_t)stream, pp, ndir, masks, npat, r0 * r0,
                beta / 2.0, pinv_cut, C, pinvC, U, sv, (const int32_t *)nullptr, (int32_t *)nullptr, (const double *)nullptr);
   }
   SSF_LAUNCHED();
@@ -653,14 +668,16 @@ extern "C" int ssf_kl_patterns_update(const uint64_t *masks, int64_t nsys, int n
     const char *e = getenv("SSF_DECOMP_WARM");
     return !(e && e[0] == '0');
   }();
-  const int64_t bound = nsys < max_slots ? nsys : max_slots;
+  int64_t bound = nsys < max_slots ? nsys : max_slots;
+  const int64_t cap = (int64_t)ssf::sm_count() * 4;         // the kernel strides over the new slots
+  if (bound > cap) bound = cap;
   if (ndir > 64) {
     SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
-    SSF_LAUNCH(decompose_kernel<BIG>, (int)bound, BIG, smem, st, pp, ndir, slot_masks, r0 * r0, beta / 2.0, pinv_cut,
+    SSF_LAUNCH(decompose_kernel<BIG>, (int)bound, BIG, smem, st, pp, ndir, slot_masks, 0, r0 * r0, beta / 2.0, pinv_cut,
                C, pinvC, U, sv, (const int32_t *)counters, status, warm ? (const double *)U : (const double *)nullptr);
   } else {
     SSF_CUDA(cudaFuncSetAttribute(decompose_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
-    SSF_LAUNCH(decompose_kernel<256>, (int)bound, 256, smem, st, pp, ndir, slot_masks, r0 * r0, beta / 2.0, pinv_cut,
+    SSF_LAUNCH(decompose_kernel<256>, (int)bound, 256, smem, st, pp, ndir, slot_masks, 0, r0 * r0, beta / 2.0, pinv_cut,
                C, pinvC, U, sv, (const int32_t *)counters, status, warm ? (const double *)U : (const double *)nullptr);
   }
   SSF_LAUNCHED();
