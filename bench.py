@@ -415,8 +415,8 @@ def measure_workload(args, eng, dist, workload, steps, warmup, rank, local, part
             fit_alone.append(a.elapsed_time(b))
         eng.check_fit_status()
         fit_ms = sorted(fit_alone)[1]
-        kname = (("contract_tc_narrow_kernel (ssf_kl_eval, tcgen05 split-TF32, two CTAs per SM, basis operand in "
-                  "TMEM, 16-column tiles)"
+        kname = (("contract_tc_narrow_kernel (ssf_kl_eval, tcgen05 split-TF32, two CTAs per SM, A_hi in TMEM / A_lo in "
+                  "shared memory, 32-column tiles)"
                   if big else "contract_tc_kernel<KL> (ssf_kl_eval, tcgen05 split-TF32)") if tc
                  else "contract_tile_kernel<KL> (ssf_kl_eval, FP32 SIMT)")
         r = roof(kname, k_ms, n_launch, ms, traffic_key="kl_eval")
