@@ -234,6 +234,23 @@ int ssf_gauss_smooth(float *images, int64_t nimg, int ny, int nx, double sigma,
 int ssf_gauss_smooth_slab(float *slab, int64_t ncol, int ny, int nx, double sigma,
                           float *scratch, int fix_nan, void *stream);
 
+/* ssf_gauss_smooth without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Same filter, same kernels and the
+ * same results as ssf_gauss_smooth, but the intermediate image and the taps live in a file-scope
+ * device array inside the library (SSF_SMOOTH_STATIC_MAX_FLOATS floats = 16 MiB, plus the taps;
+ * every GPU that loads the library holds it until the process exits), so the call makes no
+ * cudaMalloc / cudaFree / stream-ordered allocation of any kind.
+ *   limit   nimg * ny * nx <= SSF_SMOOTH_STATIC_MAX_FLOATS, else SSF_EINVAL with a message that
+ *           names the size (ssf_gauss_smooth_static_max_floats() returns the built-in limit);
+ *   sharing every call on a device uses the same array, which keeps the last call's contents
+ *           (nothing in it needs to start at zero: each call rewrites all it reads).  Calls that
+ *           overlap on the GPU -- two streams, or two host threads -- race on it: serialise them. */
+#define SSF_SMOOTH_STATIC_MAX_FLOATS (4 * 1024 * 1024)
+int ssf_gauss_smooth_static(float *images, int64_t nimg, int ny, int nx, double sigma,
+                            void *stream);
+int64_t ssf_gauss_smooth_static_max_floats(void);
+
 /* NaN -> 1.0 (planes 0, 2) / 0.0 (planes 1, 3), screen.py:364-378, on a slab. */
 int ssf_nan_fix(float *slab, int64_t ncol, int64_t npix, void *stream);
 

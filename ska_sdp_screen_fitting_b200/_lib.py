@@ -54,6 +54,8 @@ SIGNATURES = {
     "ssf_voronoi_contract": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, c_int, c_int, _P]),
     "ssf_gauss_smooth": (c_int, [_P, c_int64, c_int, c_int, c_double, _P, _P]),
     "ssf_gauss_smooth_slab": (c_int, [_P, c_int64, c_int, c_int, c_double, _P, c_int, _P]),
+    "ssf_gauss_smooth_static": (c_int, [_P, c_int64, c_int, c_int, c_double, _P]),
+    "ssf_gauss_smooth_static_max_floats": (c_int64, []),
     "ssf_nan_fix": (c_int, [_P, c_int64, c_int64, _P]),
     "ssf_bswap32": (c_int, [_P, c_int64, _P]),
     "ssf_copy_rows_d2h": (c_int, [_P, c_int64, _P, c_int64, c_int64, c_int64, _P]),

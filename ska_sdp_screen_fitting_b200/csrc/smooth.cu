@@ -5,6 +5,8 @@
 // shared-memory row tiles otherwise.
 #include "common.cuh"
 
+#include <mutex>
+
 namespace {
 
 constexpr int MAX_RADIUS = 1024;
@@ -306,4 +308,111 @@ extern "C" int ssf_gauss_smooth_slab(float *slab, int64_t ncol, int ny, int nx, 
   SSF_REQUIRE(ncol >= 0, "ssf_gauss_smooth_slab: bad sizes");
   return gauss_smooth_impl("ssf_gauss_smooth_slab", slab, ncol * 4, ny, nx, sigma, scratch, fix_nan,
                            (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// ssf_gauss_smooth_static: the same filter for callers that may not allocate (CUDA graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The intermediate image of the two passes and the taps
+// live in ONE file-scope device array of fixed size, held by every GPU that loads the library
+// until the process exits: SSF_SMOOTH_STATIC_MAX_FLOATS floats (16 MiB) of intermediate, then the
+// taps.  All calls share it: it keeps the last call's contents, and two calls that overlap on the
+// GPU (different streams, or different host threads) race on it -- callers serialise them.
+// Nothing in it has to start at zero: the first pass writes every intermediate value the second
+// pass reads, and the taps [0, 2r] are rewritten by every call before the first pass runs.
+// The existing entry points above are untouched; this one only launches the same kernels.
+namespace {
+constexpr int64_t STATIC_MAX_FLOATS = SSF_SMOOTH_STATIC_MAX_FLOATS;
+constexpr int STATIC_MAX_DEVICES = 64;
+static __device__ __align__(256) float g_static_scratch[STATIC_MAX_FLOATS + 2 * MAX_RADIUS + 64];
+
+// In host code `g_static_scratch` is a stand-in for the symbol, not a device address: the address
+// comes from cudaGetSymbolAddress, once per device, with that device current.
+int static_scratch_address(float **out) {
+  static std::mutex lock;
+  static float *address[STATIC_MAX_DEVICES] = {};
+  int device = -1;
+  SSF_CUDA(cudaGetDevice(&device));
+  SSF_REQUIRE(device >= 0 && device < STATIC_MAX_DEVICES, "ssf_gauss_smooth_static: device %d out of range", device);
+  std::lock_guard<std::mutex> hold(lock);
+  if (!address[device]) {
+    float *ptr = nullptr;
+    SSF_CUDA(cudaGetSymbolAddress(reinterpret_cast<void **>(&ptr), g_static_scratch));
+    SSF_REQUIRE(ptr != nullptr, "ssf_gauss_smooth_static: no address for the scratch symbol on device %d", device);
+    address[device] = ptr;
+  }
+  *out = address[device];
+  return SSF_OK;
+}
+}  // namespace
+
+extern "C" int64_t ssf_gauss_smooth_static_max_floats(void) { return STATIC_MAX_FLOATS; }
+
+extern "C" int ssf_gauss_smooth_static(float *images, int64_t nimg, int ny, int nx, double sigma, void *stream_) {
+  const char *who = "ssf_gauss_smooth_static";
+  cudaStream_t stream = (cudaStream_t)stream_;
+  SSF_REQUIRE(images, "%s: null pointer", who);
+  SSF_REQUIRE(ny >= 1 && nx >= 1 && nimg >= 0, "%s: bad sizes", who);
+  SSF_REQUIRE(sigma > 0.0, "%s: sigma must be > 0", who);
+  SSF_REQUIRE(nimg <= STATIC_MAX_FLOATS / ((int64_t)ny * nx),
+              "%s: %lld images of %d x %d need %lld floats of scratch, the static array holds %lld "
+              "(use ssf_gauss_smooth with caller-owned scratch)",
+              who, (long long)nimg, ny, nx, (long long)nimg * ny * nx, (long long)STATIC_MAX_FLOATS);
+  if (nimg == 0) return SSF_OK;
+  const int r = (int)(4.0 * sigma + 0.5);
+  SSF_REQUIRE(r <= MAX_RADIUS, "%s: radius %d exceeds %d", who, r, MAX_RADIUS);
+  float *scratch = nullptr;
+  if (int rc = static_scratch_address(&scratch)) return rc;
+  float *taps = scratch + STATIC_MAX_FLOATS;          // 256-byte aligned: STATIC_MAX_FLOATS is a multiple of 64
+  // weights as in gauss_smooth_impl: float64 like scipy's _gaussian_kernel1d, rounded once to float32
+  static thread_local float hw[2 * MAX_RADIUS + 1];
+  static thread_local double dw[2 * MAX_RADIUS + 1];
+  double sum = 0.0;
+  for (int k = -r; k <= r; ++k) {
+    dw[k + r] = exp(-0.5 / (sigma * sigma) * (double)(k * k));
+    sum += dw[k + r];
+  }
+  for (int k = 0; k <= 2 * r; ++k) hw[k] = (float)(dw[k] / sum);
+  // pageable source: staged by the runtime before the call returns (no allocation of ours)
+  SSF_CUDA(cudaMemcpyAsync(taps, hw, sizeof(float) * (2 * r + 1), cudaMemcpyHostToDevice, stream));
+  constexpr int YT = 16, XT = 16;
+  const size_t smem_y = sizeof(float) * ((size_t)(YT * BLK + 2 * r + 1) * 32 + 2 * r + 1);
+  const size_t smem_x = sizeof(float) * ((size_t)32 * ((XT * BLK + 2 * r + 1) | 1) + 2 * r + 1);
+  const bool blocked = smem_y <= 100 * 1024 && smem_x <= 100 * 1024;
+  for (int64_t i0 = 0; i0 < nimg; i0 += 65532) {
+    const int nz = (int)((nimg - i0) < 65532 ? (nimg - i0) : 65532);
+    float *img = images + i0 * (int64_t)ny * nx;
+    float *tmp = scratch + i0 * (int64_t)ny * nx;
+    if (blocked) {
+      dim3 gy(ssf::div_up(nx, 32), ssf::div_up(ny, YT * BLK), nz), by(32, YT);
+      if (smem_y > 48 * 1024)
+        SSF_CUDA(cudaFuncSetAttribute(ypass_blocked_kernel<YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_y));
+      SSF_LAUNCH(ypass_blocked_kernel<YT>, gy, by, smem_y, stream, img, tmp, ny, nx, r, taps);
+      SSF_LAUNCHED();
+      dim3 gx(ssf::div_up(nx, XT * BLK), ssf::div_up(ny, 32), nz), bx(32, XT);
+      if (smem_x > 48 * 1024)
+        SSF_CUDA(cudaFuncSetAttribute(xpass_blocked_kernel<XT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_x));
+      SSF_LAUNCH(xpass_blocked_kernel<XT>, gx, bx, smem_x, stream, tmp, img, ny, nx, r, taps, 0);
+      SSF_LAUNCHED();
+      continue;
+    }
+    {
+      constexpr int TY = 16;
+      dim3 grid(ssf::div_up(nx, 32), ssf::div_up(ny, TY), nz), block(32, TY);
+      const size_t smem = sizeof(float) * (32 * (TY + 2 * r) + 2 * r + 1);
+      SSF_REQUIRE(smem <= 200 * 1024, "%s: radius too large for the y tile", who);
+      if (smem > 48 * 1024)
+        SSF_CUDA(cudaFuncSetAttribute(ypass_kernel<TY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      SSF_LAUNCH(ypass_kernel<TY>, grid, block, smem, stream, img, tmp, ny, nx, r, taps);
+      SSF_LAUNCHED();
+    }
+    {
+      constexpr int TX = 256;
+      dim3 grid(ssf::div_up(nx, TX), ny, nz);
+      const size_t smem = sizeof(float) * (TX + 2 * r + 2 * r + 1);
+      SSF_LAUNCH(xpass_smem_kernel<TX>, grid, TX, smem, stream, tmp, img, ny, nx, r, taps);
+      SSF_LAUNCHED();
+    }
+  }
+  return SSF_OK;
 }

@@ -386,6 +386,16 @@ class Engine:
                   self.stream())
         return images
 
+    def gauss_smooth_static(self, images, sigma):
+        """gauss_smooth with the library's own fixed scratch (``ssf_gauss_smooth_static``): no
+        allocation anywhere in the call, at most ``ssf_gauss_smooth_static_max_floats()`` pixels,
+        one call at a time per GPU (the scratch is shared).  Not used by the screens."""
+        self._check(images, torch.float32, "images")
+        ny, nx = images.shape[-2:]
+        nimg = images.numel() // (ny * nx)
+        self._call("ssf_gauss_smooth_static", _ptr(images), nimg, ny, nx, float(sigma), self.stream())
+        return images
+
     def gauss_smooth_slab(self, slab, sigma, fix_nan=True, scratch=None):
         """In place on a slab [ncol, 4, ny, nx] float32; ``fix_nan`` fuses the NaN fix of
         screen.py:364-378 into the second pass."""
