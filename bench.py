@@ -357,10 +357,16 @@ def measure_workload(args, eng, dist, workload, steps, warmup, rank, local, part
 
     def roof(kernel, k_ms, n_launch, ms, bytes_per_voxel=BYTES_PER_VOXEL, traffic_key=None):
         achieved = voxels_per_step * bytes_per_voxel / (k_ms * 1e-3) / 1e9
-        return {"bound": "hbm", "kernel": kernel, "achieved": achieved, "peak": peak, "unit": "GB/s",
+        line = {"bound": "hbm", "kernel": kernel, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": recorded_traffic(traffic_key, workload) if traffic_key else None,
                 "algorithmic_bytes_per_voxel": bytes_per_voxel, "kernel_ms": k_ms, "kernel_launches": n_launch,
                 "peak_source": peak_src, "kernel_share_of_step": k_ms * n_launch / ms}
+        if achieved > peak:
+            # the peak is a COPY bandwidth (half reads, half writes); these kernels only write, and a
+            # write-only stream is not held to it: scripts/stream_write_probe.cu measures 7.0-7.5 TB/s
+            # for stores alone on this part (profiles/r02_stream_write_probe.txt)
+            line["note"] = "write-only kernel: above the measured COPY bandwidth, below the 7.5 TB/s of a bare store stream"
+        return line
 
     tc = args.variant != 0 and (n * n) % 128 == 0
     big = n_d > 56

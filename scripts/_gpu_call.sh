@@ -1,4 +1,18 @@
 mkdir -p gpurun_out
-(timeout 600 python -m pytest tests/test_zz_no_alloc.py -m gpu -q > gpurun_out/r02y_noalloc_alone.log 2>&1; echo "pytest exit $?" >> gpurun_out/r02y_noalloc_alone.log); tail -4 gpurun_out/r02y_noalloc_alone.log
-(timeout 1200 python -m pytest tests -x -m gpu -q > gpurun_out/r02y_gputest.log 2>&1; echo "pytest exit $?" >> gpurun_out/r02y_gputest.log); tail -4 gpurun_out/r02y_gputest.log
-(timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r02y_smoke.log 2>&1; echo "smoke exit $?" >> gpurun_out/r02y_smoke.log); tail -2 gpurun_out/r02y_smoke.log
+P="python scripts/prof_kernel.py"
+L=ska_sdp_screen_fitting_b200/libssf_b200.so
+{
+echo "# two-CTA KL kernel, 45 directions: product library, then the SSF_TC_WRAP=64 build (every CTA reads its basis tile from the first 64 pixel tiles: an L2-resident window, wrong results)"
+$P kl --ndir 45 --n 2048 --ncol 372
+$P kl --ndir 45 --n 1024 --ncol 1488
+$P kl --ndir 45 --n 512 --ncol 5952
+$P kl --ndir 56 --n 2048 --ncol 372
+cp $L /tmp/lib.bak; cp scripts/_libssf_wrap64.so $L
+echo "# SSF_TC_WRAP=64"
+$P kl --ndir 45 --n 2048 --ncol 372
+$P kl --ndir 45 --n 1024 --ncol 1488
+$P kl --ndir 45 --n 512 --ncol 5952
+$P kl --ndir 56 --n 2048 --ncol 372
+cp /tmp/lib.bak $L
+} > gpurun_out/r02y_tc_wrap.txt 2>&1
+cat gpurun_out/r02y_tc_wrap.txt

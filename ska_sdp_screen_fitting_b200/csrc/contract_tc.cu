@@ -456,7 +456,13 @@ contract_tc_kernel(const float *__restrict__ Bt, const float *__restrict__ Bs, i
     for (int u = 0; u < 8; ++u) {
       const int i = i0 + u * THREADS;
       const int r = i & (TC_M - 1), k = i >> 7;
+#ifdef SSF_TC_WRAP
+      // experiment (wrong results): every CTA takes its basis tile from the first SSF_TC_WRAP pixel
+      // tiles, an L2-resident window -- what the DRAM reads of the basis cost a large image
+      x[u] = k < ndir ? __ldg(Bt + (int64_t)k * npix + (int64_t)(blockIdx.y % SSF_TC_WRAP) * TC_M + r) : 0.0f;
+#else
       x[u] = k < ndir ? __ldg(Bt + (int64_t)k * npix + pix0 + r) : 0.0f;   // k >= ndir also covers i >= 128 Kp
+#endif
     }
 #pragma unroll
     for (int u = 0; u < 8; ++u) {

@@ -1,5 +1,7 @@
 // Voronoi (tessellated) screen kernels: nearest-patch template, cos/sin LUT, cube fill,
 // indicator images, NaN fix.  All are HBM-bound streaming kernels: 16 B written per voxel.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -200,6 +202,24 @@ int grid_for(int64_t work, int threads, int ctas_per_sm) {
   return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
 }
 
+// Grid of the fill kernels: 512 CTAs per SM (8 are resident), each thread a few grid-strided
+// passes.  A grid of exactly the resident CTAs looping to the end (round 1: 8 per SM) is a static
+// partition, and a write-only stream then ends with its slowest SM: 0.90 of the copy bandwidth
+// at 512^2, 0.80 at 2048^2; with 512 CTAs per SM the hardware hands out the work and the same
+// kernel reaches 1.09 / 1.00 (a write-only stream is not bound by the copy figure; the probe
+// scripts/stream_write_probe.cu measures 7.5 TB/s for one-pass CTAs).  One pass per thread is
+// best for the plain fill (1.15) but re-reads the LUT row too often for gain / plane-pair fills.
+// Experiment hook SSF_FILL_CTAS: CTAs per SM, 0 = one pass per thread (profiles/r02_fill_grid.txt).
+int fill_grid(int64_t work) {
+  static const int ctas = [] {
+    const char *e = getenv("SSF_FILL_CTAS");
+    return e ? atoi(e) : 512;
+  }();
+  const int64_t blocks = (work + 255) / 256;
+  if (ctas <= 0) return (int)(blocks < 0x7fffffff ? (blocks > 0 ? blocks : 1) : 0x7fffffff);
+  return grid_for(work, 256, ctas);
+}
+
 }  // namespace
 
 extern "C" int ssf_voronoi_assign(const double *px, const double *py, int ndir, int nx, int ny,
@@ -233,10 +253,10 @@ extern "C" int ssf_voronoi_fill(const int32_t *tmpl, const float *lut, int ndir,
   if (ncol == 0) return SSF_OK;
   bool vec = (npix % 4 == 0) && ((uintptr_t)slab % 16 == 0) && ((uintptr_t)tmpl % 16 == 0);
   if (vec) {
-    SSF_LAUNCH(fill_kernel<true>, grid_for(npix / 4 * ncol, 256, 8), 256, 0, (cudaStream_t)stream,
+    SSF_LAUNCH(fill_kernel<true>, fill_grid(npix / 4 * ncol), 256, 0, (cudaStream_t)stream,
                tmpl, (const float2 *)lut, ndir, npix, ncol, slab, fix_nan, fmt);
   } else {
-    SSF_LAUNCH(fill_kernel<false>, grid_for(npix * ncol, 256, 8), 256, 0, (cudaStream_t)stream,
+    SSF_LAUNCH(fill_kernel<false>, fill_grid(npix * ncol), 256, 0, (cudaStream_t)stream,
                tmpl, (const float2 *)lut, ndir, npix, ncol, slab, fix_nan, fmt);
   }
   SSF_LAUNCHED();
@@ -266,10 +286,10 @@ extern "C" int ssf_voronoi_fill_gain(const int32_t *tmpl, const float *lut4, int
   if (ncol == 0) return SSF_OK;
   bool vec = (npix % 4 == 0) && ((uintptr_t)slab % 16 == 0) && ((uintptr_t)tmpl % 16 == 0);
   if (vec) {
-    SSF_LAUNCH(fill_gain_kernel<true>, grid_for(npix / 4 * ncol, 256, 8), 256, 0, (cudaStream_t)stream,
+    SSF_LAUNCH(fill_gain_kernel<true>, fill_grid(npix / 4 * ncol), 256, 0, (cudaStream_t)stream,
                tmpl, (const float4 *)lut4, ndir, npix, ncol, slab, fix_nan, fmt.prmt);
   } else {
-    SSF_LAUNCH(fill_gain_kernel<false>, grid_for(npix * ncol, 256, 8), 256, 0, (cudaStream_t)stream,
+    SSF_LAUNCH(fill_gain_kernel<false>, fill_grid(npix * ncol), 256, 0, (cudaStream_t)stream,
                tmpl, (const float4 *)lut4, ndir, npix, ncol, slab, fix_nan, fmt.prmt);
   }
   SSF_LAUNCHED();
@@ -279,7 +299,7 @@ extern "C" int ssf_voronoi_fill_gain(const int32_t *tmpl, const float *lut4, int
 extern "C" int ssf_voronoi_indicators(const int32_t *tmpl, int ndir, int64_t npix, float *ind,
                                       void *stream) {
   SSF_REQUIRE(tmpl && ind, "ssf_voronoi_indicators: null pointer");
-  SSF_LAUNCH(indicator_kernel, grid_for(npix * ndir, 256, 8), 256, 0, (cudaStream_t)stream, tmpl, ndir, npix, ind);
+  SSF_LAUNCH(indicator_kernel, grid_for(npix * ndir, 256, 512), 256, 0, (cudaStream_t)stream, tmpl, ndir, npix, ind);
   SSF_LAUNCHED();
   return SSF_OK;
 }
@@ -287,7 +307,7 @@ extern "C" int ssf_voronoi_indicators(const int32_t *tmpl, int ndir, int64_t npi
 extern "C" int ssf_nan_fix(float *slab, int64_t ncol, int64_t npix, void *stream) {
   SSF_REQUIRE(slab, "ssf_nan_fix: null pointer");
   if (ncol == 0) return SSF_OK;
-  SSF_LAUNCH(nan_fix_kernel, grid_for(ncol * 4 * npix, 256, 8), 256, 0, (cudaStream_t)stream, slab, ncol, npix);
+  SSF_LAUNCH(nan_fix_kernel, grid_for(ncol * 4 * npix, 256, 512), 256, 0, (cudaStream_t)stream, slab, ncol, npix);
   SSF_LAUNCHED();
   return SSF_OK;
 }
@@ -296,7 +316,7 @@ extern "C" int ssf_bswap32(void *data, int64_t count, void *stream) {
   SSF_REQUIRE(data, "ssf_bswap32: null pointer");
   SSF_REQUIRE(((uintptr_t)data % 16) == 0, "ssf_bswap32: buffer must be 16-byte aligned");
   if (count <= 0) return SSF_OK;
-  SSF_LAUNCH(bswap32_kernel, grid_for(count / 4 + 1, 256, 8), 256, 0, (cudaStream_t)stream,
+  SSF_LAUNCH(bswap32_kernel, grid_for(count / 4 + 1, 256, 512), 256, 0, (cudaStream_t)stream,
              (uint32_t *)data, count);
   SSF_LAUNCHED();
   return SSF_OK;

@@ -2,8 +2,8 @@
 TEST INFRASTRUCTURE: build ``tests/emu/_build/libssf_emu.so`` -- the kernel sources of
 ``ska_sdp_screen_fitting_b200/csrc`` compiled by g++ against the CUDA emulator of
 ``cuda_emu.h`` -- so kernel LOGIC can be checked against the oracle in the GPU-less build
-container.  Never shipped, never loaded by the product unless a test sets
-``SSF_B200_LIBRARY``.
+container.  Never shipped and never loaded by the product: tests hand its path to
+``tests/emu/emu_engine.EmuEngine``.
 """
 import hashlib
 import os
