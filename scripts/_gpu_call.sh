@@ -1,18 +1,13 @@
 mkdir -p gpurun_out
-P="python scripts/prof_kernel.py"
-L=ska_sdp_screen_fitting_b200/libssf_b200.so
-{
-echo "# two-CTA KL kernel, 45 directions: product library, then the SSF_TC_WRAP=64 build (every CTA reads its basis tile from the first 64 pixel tiles: an L2-resident window, wrong results)"
-$P kl --ndir 45 --n 2048 --ncol 372
-$P kl --ndir 45 --n 1024 --ncol 1488
-$P kl --ndir 45 --n 512 --ncol 5952
-$P kl --ndir 56 --n 2048 --ncol 372
-cp $L /tmp/lib.bak; cp scripts/_libssf_wrap64.so $L
-echo "# SSF_TC_WRAP=64"
-$P kl --ndir 45 --n 2048 --ncol 372
-$P kl --ndir 45 --n 1024 --ncol 1488
-$P kl --ndir 45 --n 512 --ncol 5952
-$P kl --ndir 56 --n 2048 --ncol 372
-cp /tmp/lib.bak $L
-} > gpurun_out/r02y_tc_wrap.txt 2>&1
-cat gpurun_out/r02y_tc_wrap.txt
+(timeout 1200 python -m pytest tests -x -m gpu -q > gpurun_out/r02zc_gputest.log 2>&1; echo "pytest exit $?" >> gpurun_out/r02zc_gputest.log); tail -3 gpurun_out/r02zc_gputest.log
+timeout 900 python bench.py > gpurun_out/r02zc_bench_lofar.json 2> gpurun_out/r02zc_bench.err; echo "bench exit $?"; tail -2 gpurun_out/r02zc_bench.err
+python - <<PY
+import json
+d=json.loads(open('gpurun_out/r02zc_bench_lofar.json').read().strip().splitlines()[-1])
+print('value',d['value'],'ms',d['ms_per_step'],'frac',d['roofline']['frac'])
+print({k:v for k,v in d.items() if 'fit' in k})
+for k,v in d.items():
+    if isinstance(v,dict) and 'roofline' in v: print(k, v.get('value'), v.get('ms_per_step'), v['roofline'].get('frac'))
+for k,v in d.get('extra',{}).items(): print(k, v['value'], v['ms_per_step'], v['roofline']['frac'], {a:b for a,b in v.items() if 'fit' in a})
+e=d['e2e']; print('e2e',e['value'],'without_file',e['without_file']['value'])
+PY

@@ -23,6 +23,7 @@ constexpr double PI = 3.141592653589793238462643383279;
 struct Pattern {
   const double *C, *P, *U;  // [n][n] blocks with row stride ld
   const double *Pfull;      // pinv of the full pattern (pattern 0)
+  const double *Cfull;      // structure matrix of the full pattern: C(e, d) for ALL direction pairs
   int ld;
 };
 
@@ -71,7 +72,6 @@ __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restr
                          int n, int k, double r0sq, double half_beta, double cut,
                          double *__restrict__ white_out, double *__restrict__ resid_out, int kind) {
   const bool amp = kind == 1;           // kind: 0 phase, 1 amplitude (log10), 2 tec (linear, :549-562)
-  __shared__ int sh_uniform, sh_ok;
   const int tid = threadIdx.x;
   const int ld = pt.ld;
   if (tid < n) {
@@ -85,16 +85,8 @@ __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restr
     s.wc[tid] = s.w[s.idx[tid]];
   }
   __syncthreads();
-  if (tid == 0) {
-    int uni = 1;
-    double wmin = s.wc[0];
-    for (int i = 1; i < n; ++i) {
-      uni &= (s.wc[i] == s.wc[0]);
-      wmin = fmin(wmin, s.wc[i]);
-    }
-    sh_uniform = uni;
-    sh_ok = uni ? 1 : (wmin > cut);
-  }
+  // bit 0: some weight differs from the first one; bit 1: some weight is not above the cutoff
+  const int my_bad = tid < n ? ((s.wc[tid] == s.wc[0] ? 0 : 1) | (s.wc[tid] > cut ? 0 : 2)) : 0;
   // rr1 = U_k^T W r   (:513-516, :522-525)
   if (tid < k) {
     double ac = 0.0, as = 0.0;
@@ -106,8 +98,9 @@ __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restr
     s.zc[tid] = ac;
     s.zs[tid] = as;
   }
-  __syncthreads();
-  const bool general = !sh_ok;          // uniform over the CTA
+  // the barrier the stage needs anyway, with the two votes (the reduction is a boolean OR)
+  const bool uniform = !__syncthreads_or(my_bad & 1);               // both uniform over the CTA
+  const bool general = __syncthreads_or(my_bad & 2) && !uniform;
   if (general) {
     // Some weight lies in (0, cut]: A = U_k^T W U_k may have eigenvalues <= cut, which
     // pinv(A, rcond=1e-3) drops (:501-504; absolute cutoff).  One-sided (Hestenes) Jacobi on
@@ -190,7 +183,7 @@ __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restr
       s.yc[tid] = ac * isw;
       s.ys[tid] = as * isw;
     }
-  } else if (sh_uniform) {
+  } else if (uniform) {
     // A = w0 U_k^T U_k = w0 I  ->  pinv(A) = I / w0 when w0 > cut, else 0   (:501-504)
     if (tid < k) {
       double w0 = s.wc[0];
@@ -294,15 +287,12 @@ __device__ bool fit_once(const Smem &s, const Pattern &pt, const double *__restr
     if (tid < n) s.fall[s.idx[tid]] = s.fit[tid];
     __syncthreads();
     if (tid < nall && !(s.w[tid] > 0.0)) {
+      // c_val = -((|pp_e - pp_tid|^2 / r0^2)^(beta/2)) / 2 is entry (e, tid) of the FULL pattern's
+      // structure matrix, which decompose_one built from the same expression (kldecomp.cu): read
+      // it (coalesced over tid) instead of n pow() calls in the few threads of flagged directions
+      // while the rest of the CTA waits -- 19 % of the kernel's stall samples in round 2
       double a = 0.0;
-      for (int i = 0; i < n; ++i) {
-        int e = s.idx[i];
-        double dx = pp[2 * e] - pp[2 * tid], dy = pp[2 * e + 1] - pp[2 * tid + 1];
-        double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
-        double q = d2 / r0sq;
-        double c = q > 0.0 ? -0.5 * pow(q, half_beta) : 0.0;
-        a = fma(c, s.wh[i], a);
-      }
+      for (int i = 0; i < n; ++i) a = fma(pt.Cfull[s.idx[i] * ld + tid], s.wh[i], a);
       s.fall[tid] = a;
     }
     __syncthreads();
@@ -327,6 +317,7 @@ fit_pass_kernel(const double *__restrict__ phase, const float *__restrict__ weig
                 double *__restrict__ resid, int32_t *__restrict__ status) {
   SSF_DYN_SMEM(double, sm);
   __shared__ int sh_n, sh_k, sh_go;
+  __shared__ unsigned sh_vote[FT / 32];
   __shared__ double sh_t1[FT], sh_t2[FT];
   const int tid = threadIdx.x;
   Smem s = carve(sm, nall);
@@ -337,12 +328,20 @@ fit_pass_kernel(const double *__restrict__ phase, const float *__restrict__ weig
       s.ph[tid] = phase[sys * nall + tid];
       s.w[tid] = (double)weights[sys * nall + tid];
     }
+    // compact list of the unflagged directions, in direction order: warp votes + popcounts
+    const bool keep = tid < nall && s.w[tid] > 0.0;
+    const unsigned vote = __ballot_sync(0xffffffffu, keep);
+    if ((tid & 31) == 0) sh_vote[tid >> 5] = vote;
     __syncthreads();
-    if (tid == 0) {
-      int n = 0;
-      for (int d = 0; d < nall; ++d)
-        if (s.w[d] > 0.0) s.idx[n++] = d;
-      sh_n = n;
+    {
+      int before = 0, all = 0;
+      for (int w = 0; w < FT / 32; ++w) {
+        const int c = __popc(sh_vote[w]);
+        if (w < (tid >> 5)) before += c;
+        all += c;
+      }
+      if (keep) s.idx[before + __popc(vote & ((1u << (tid & 31)) - 1u))] = tid;
+      if (tid == 0) sh_n = all;
     }
     __syncthreads();
     const int n = sh_n;
@@ -356,6 +355,7 @@ fit_pass_kernel(const double *__restrict__ phase, const float *__restrict__ weig
     pt.P = P + off;
     pt.U = U + off;
     pt.Pfull = P;
+    pt.Cfull = C;
     pt.ld = nall;
     double *w_out = white + sys * nall;
     double *r_out = resid + sys * nall;

@@ -89,6 +89,27 @@ static inline T __shfl_up_sync(unsigned m, T v, int delta) {
   return __shfl_sync(m, v, lane >= delta ? lane - delta : lane);
 }
 
+// warp vote: OR-butterfly over the lanes' bits (every lane of the warp calls, as on the device)
+static inline unsigned __ballot_sync(unsigned m, int pred) {
+  int lane = (threadIdx.x + threadIdx.y * blockDim.x + threadIdx.z * blockDim.x * blockDim.y) & 31;
+  uint32_t v = pred ? (1u << lane) : 0u;
+  for (int o = 16; o; o >>= 1) v |= __shfl_xor_sync(m, v, o);
+  return v;
+}
+static inline int __popc(unsigned v) { return __builtin_popcount(v); }
+// barrier with an OR reduction over the block (one block runs at a time: a static is the block's)
+static inline int __syncthreads_or(int pred) {
+  static int acc;
+  emu::sync_block();
+  if (threadIdx.x == 0 && threadIdx.y == 0 && threadIdx.z == 0) acc = 0;
+  emu::sync_block();
+  if (pred) acc = 1;                       // a boolean OR, as on the device (not a bitwise one)
+  emu::sync_block();
+  const int r = acc;
+  emu::sync_block();
+  return r;
+}
+
 template <typename T> static inline T __ldg(const T *p) { return *p; }
 template <typename T> static inline void __stcs(T *p, T v) { *p = v; }
 static inline double __dadd_rn(double a, double b) { volatile double r = a + b; return r; }
