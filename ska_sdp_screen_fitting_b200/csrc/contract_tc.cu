@@ -1129,7 +1129,11 @@ contract_tc_narrow_kernel(const __grid_constant__ CUtensorMap bt_map, const floa
       mbar_init(a_ready, NEPI);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       mbar_expect_tx(raw_full, (uint32_t)Kp * TC_M * (uint32_t)sizeof(float));
+#ifdef SSF_TC_WRAP
+      tma_load_2d(smem_u32(raw), &bt_map, (int)(blockIdx.y % SSF_TC_WRAP) * TC_M, 0, raw_full);   // experiment, see contract_tc_kernel
+#else
       tma_load_2d(smem_u32(raw), &bt_map, (int)pix0, 0, raw_full);
+#endif
       for (int it = 0; it < nb && it < n_tiles; ++it) {
         mbar_expect_tx(b_full + 8 * it, stage_bytes);
         bulk_g2s(smem_u32(b_base + (size_t)it * 2 * NT * Kp), b_src + (size_t)it * 2 * NT * Kp, stage_bytes,
