@@ -208,13 +208,17 @@ int grid_for(int64_t work, int threads, int ctas_per_sm) {
 // at 512^2, 0.80 at 2048^2; with 512 CTAs per SM the hardware hands out the work and the same
 // kernel reaches 1.09 / 1.00 (a write-only stream is not bound by the copy figure; the probe
 // scripts/stream_write_probe.cu measures 7.5 TB/s for one-pass CTAs).  One pass per thread is
-// best for the plain fill (1.15) but re-reads the LUT row too often for gain / plane-pair fills.
-// Experiment hook SSF_FILL_CTAS: CTAs per SM, 0 = one pass per thread (profiles/r02_fill_grid.txt).
-int fill_grid(int64_t work) {
-  static const int ctas = [] {
+// best for the four-plane phase fill (1.15 / 1.06: 64 B of stores per thread and one LUT row per
+// CTA) but starts too many CTAs per byte for the plane-pair fill (0.73) and re-reads the wider
+// LUT row too often for the gain fill (0.99): `one_pass` is set for the former only.
+// Experiment hook SSF_FILL_CTAS: CTAs per SM for every fill, 0 = one pass per thread
+// (profiles/r02_fill_grid.txt).
+int fill_grid(int64_t work, bool one_pass) {
+  static const int forced = [] {
     const char *e = getenv("SSF_FILL_CTAS");
-    return e ? atoi(e) : 512;
+    return e ? atoi(e) : -1;
   }();
+  const int ctas = forced >= 0 ? forced : (one_pass ? 0 : 512);
   const int64_t blocks = (work + 255) / 256;
   if (ctas <= 0) return (int)(blocks < 0x7fffffff ? (blocks > 0 ? blocks : 1) : 0x7fffffff);
   return grid_for(work, 256, ctas);
@@ -253,10 +257,10 @@ extern "C" int ssf_voronoi_fill(const int32_t *tmpl, const float *lut, int ndir,
   if (ncol == 0) return SSF_OK;
   bool vec = (npix % 4 == 0) && ((uintptr_t)slab % 16 == 0) && ((uintptr_t)tmpl % 16 == 0);
   if (vec) {
-    SSF_LAUNCH(fill_kernel<true>, fill_grid(npix / 4 * ncol), 256, 0, (cudaStream_t)stream,
+    SSF_LAUNCH(fill_kernel<true>, fill_grid(npix / 4 * ncol, fmt.planes == 4), 256, 0, (cudaStream_t)stream,
                tmpl, (const float2 *)lut, ndir, npix, ncol, slab, fix_nan, fmt);
   } else {
-    SSF_LAUNCH(fill_kernel<false>, fill_grid(npix * ncol), 256, 0, (cudaStream_t)stream,
+    SSF_LAUNCH(fill_kernel<false>, fill_grid(npix * ncol, false), 256, 0, (cudaStream_t)stream,
                tmpl, (const float2 *)lut, ndir, npix, ncol, slab, fix_nan, fmt);
   }
   SSF_LAUNCHED();
@@ -286,10 +290,10 @@ extern "C" int ssf_voronoi_fill_gain(const int32_t *tmpl, const float *lut4, int
   if (ncol == 0) return SSF_OK;
   bool vec = (npix % 4 == 0) && ((uintptr_t)slab % 16 == 0) && ((uintptr_t)tmpl % 16 == 0);
   if (vec) {
-    SSF_LAUNCH(fill_gain_kernel<true>, fill_grid(npix / 4 * ncol), 256, 0, (cudaStream_t)stream,
+    SSF_LAUNCH(fill_gain_kernel<true>, fill_grid(npix / 4 * ncol, false), 256, 0, (cudaStream_t)stream,
                tmpl, (const float4 *)lut4, ndir, npix, ncol, slab, fix_nan, fmt.prmt);
   } else {
-    SSF_LAUNCH(fill_gain_kernel<false>, fill_grid(npix * ncol), 256, 0, (cudaStream_t)stream,
+    SSF_LAUNCH(fill_gain_kernel<false>, fill_grid(npix * ncol, false), 256, 0, (cudaStream_t)stream,
                tmpl, (const float4 *)lut4, ndir, npix, ncol, slab, fix_nan, fmt.prmt);
   }
   SSF_LAUNCHED();

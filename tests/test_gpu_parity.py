@@ -258,6 +258,36 @@ def test_full_size_properties(gpu_engine):
     assert np.abs(got_s - np.sin(want)).max() < pc.TOL_KL
 
 
+def test_fill_kernels_beyond_one_grid_pass(gpu_engine):
+    """The plane-pair and gain fills stride over a grid capped at 512 CTAs per SM: at 512^2 x 320
+    columns their threads take more than one pass (the small parity cases never do), and the
+    four-plane fill launches its largest one-pass grid.  Bit-exact against a torch gather of the
+    same LUT, for the phase fill (4 planes, plane pairs big-endian) and the gain fill."""
+    from ska_sdp_screen_fitting_b200 import _lib
+
+    eng = gpu_engine
+    gen = torch.Generator(device=eng.device)
+    gen.manual_seed(17)
+    n, n_d, ncol = 512, 45, 320
+    npix = n * n
+    tmpl = torch.randint(1, n_d + 1, (n, n), generator=gen, device=eng.device, dtype=torch.int32)
+    idx = (tmpl.view(-1) - 1).long()
+    lut = torch.randn((ncol, n_d, 2), generator=gen, device=eng.device, dtype=torch.float32)
+    slab = eng.empty((ncol, 4, npix), torch.float32)
+    eng.voronoi_fill(tmpl, lut, slab)
+    want = lut[:, idx, :].permute(0, 2, 1)                      # [ncol, 2, npix]
+    assert torch.equal(slab[:, 0], want[:, 0]) and torch.equal(slab[:, 1], want[:, 1])
+    assert torch.equal(slab[:, 2], want[:, 0]) and torch.equal(slab[:, 3], want[:, 1])
+    pair = eng.empty((ncol, 2, npix), torch.float32)
+    eng.voronoi_fill(tmpl, lut, pair, out_flags=_lib.OUT_PLANES2 | _lib.OUT_BIG_ENDIAN)
+    swapped = pair.view(torch.uint8).view(ncol, 2, npix, 4).flip(-1).contiguous().view(torch.float32).view(ncol, 2, npix)
+    assert torch.equal(swapped, want)
+    del pair, swapped
+    lut4 = torch.randn((ncol, n_d, 4), generator=gen, device=eng.device, dtype=torch.float32)
+    eng.voronoi_fill_gain(tmpl, lut4, slab)
+    assert torch.equal(slab, lut4[:, idx, :].permute(0, 2, 1))
+
+
 def test_host_entry_points(gpu_engine):
     import ctypes
 
