@@ -107,7 +107,10 @@ int ssf_kl_fit_ctas_per_sm(int ctas);
  *
  *   phase   [nsys, ndir] f64   referenced phases (rad)
  *   weights [nsys, ndir] f32   >0 = used
- *   pat     [nsys] i32         index of each system's flag pattern in the decompose output
+ *   pat     [nsys] i32         index of each system's flag pattern in the decompose output;
+ *                              pattern 0 must be the FULL pattern (no direction flagged): its
+ *                              pinv and its structure matrix serve the prediction at flagged
+ *                              directions (:565-574) of every other pattern
  *   order   [nsys] f64 in/out  current screen order (the reference stores it as float)
  *   station_order [nsys] f64   per-system lower bound (= order of the station, :656)
  *   mode 0: iteration 0       -> one fit at min(order, n_unfl-1)         (:681-722)
@@ -119,9 +122,9 @@ int ssf_kl_fit_ctas_per_sm(int ctas);
  *                                residual val - fit, chi^2 = sum w resid^2 (:742-746)
  *   white, resid [nsys, ndir] f64 in/out (mode 1 reads the residual of the previous pass)
  * Systems with no unflagged direction are left untouched (:683-684).
- *   status  [1] i32 in/out     set to 1 if any system had a weight in (0, pinv_cut] (the
- *                              Cholesky normal-equation path does not cover it); the
- *                              caller zero-initialises it and checks it after the pass.
+ *   status  [1] i32 in/out     error flag of the pass (the caller zero-initialises it and
+ *                              checks it afterwards); weights in (0, pinv_cut] are NOT an
+ *                              error: such systems take the general pinv path (round 2).
  */
 int ssf_kl_fit_pass(const double *phase, const float *weights, const int32_t *pat,
                     const double *pp, int ndir, int64_t nsys,
