@@ -87,7 +87,7 @@ def recorded_traffic(kernel, workload="lofar"):
 
 class ClockSampler:
     """SM clocks / throttle reasons sampled DURING the timed region: in-process NVML
-    (nvidia_ml_py) every 50 ms from a helper thread; `nvidia-smi -lms` as the fallback.  One
+    (nvidia_ml_py) every 20 ms from a helper thread; `nvidia-smi -lms` as the fallback.  One
     nvidia-smi process per rank on an 8-GPU box takes seconds to start and contends for the
     driver with the ranks' launches, NVML in-process does neither."""
 
@@ -133,7 +133,7 @@ class ClockSampler:
 
     def _poll_nvml(self):
         pynvml, handle, smax = self._nvml
-        period = float(os.environ.get("SSF_BENCH_NVML_PERIOD", "0.05"))
+        period = float(os.environ.get("SSF_BENCH_NVML_PERIOD", "0.02"))
         while not self._stop.is_set():
             try:
                 sm = float(pynvml.nvmlDeviceGetClockInfo(handle, pynvml.NVML_CLOCK_SM))
