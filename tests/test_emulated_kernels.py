@@ -56,6 +56,13 @@ def test_fit_at_45_directions_against_the_reference_golden(emu_engine, golden_di
     pc.check_phase_golden(emu_engine, golden_dir, "phase45", cube=False)
 
 
+def test_fit_at_100_directions_against_the_reference_golden(emu_engine, golden_dir):
+    """The 128-thread fit (above 64 directions: four warps in the vote that compacts the unflagged
+    directions, 100-long matrix-vector loops, decompose_kernel<512>) against the reference's own
+    outputs at the SKA-Low direction count."""
+    pc.check_phase_golden(emu_engine, golden_dir, "phase100", cube=False)
+
+
 def test_fit_amplitude_type(emu_engine):
     pc.check_fit_amplitude(emu_engine)
 
