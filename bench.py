@@ -824,12 +824,17 @@ def run_reference(args):
             total_s += secs
             total_v += value * secs
     value = total_v / total_s
-    st, nd, _, _, npx, _ = synthetic.SHAPES[args.workload]
+    # the same `config` as the GPU arm prints for this workload (its step is the full slab; this
+    # arm's step is the bounded sample named in cpu_baseline.sample)
+    st, nd, _, nf, npx, _ = synthetic.SHAPES[args.workload]
+    if args.workload == "skalow":
+        nf = 1
+    slots = args.slots or auto_slots(args.workload)
     return {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_s / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "impl": "reference",
-            "config": workload_config(args.workload, npx, nd, None, None),
+            "config": workload_config(args.workload, npx, nd, slots * nf * st, slots),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample + ", per step"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
