@@ -166,3 +166,26 @@ def test_host_entry_points(emu_engine, emu_library):
     _lib.call("ssf_kl_cube_host", x.ctypes.data, y.ctypes.data, n, n, pp2.ctypes.data, n_d,
               white.ctypes.data, ncol, 100.0, 5.0 / 3.0, 1e-3, out.ctypes.data, lib=lib)
     assert np.abs(out - screens.kl_make_matrix(x, y, pp, white)).max() < pc.TOL_KL
+
+
+def test_fill_kernels_take_several_grid_passes(emu_library):
+    """The fill kernels are grid-strided; the parity cases above never fill one grid pass.  With the
+    grid capped at one CTA per SM (experiment hook SSF_FILL_CTAS, read once per process, hence the
+    subprocess) a 64 x 64 x 41-column slab takes several passes per thread, ragged at the end."""
+    import os
+    import subprocess
+    import sys
+
+    here = os.path.dirname(os.path.abspath(__file__))
+    code = (
+        "import sys; sys.path.insert(0, %r); sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "from emu_engine import EmuEngine\n"
+        "import parity_checks as pc\n"
+        "eng = EmuEngine(%r)\n"
+        "pc.check_voronoi(eng, n=64, n_d=7, ncol=41, seed=5)\n"
+        "pc.check_voronoi_gain(eng, n=64, n_d=7, ncol=41, seed=6)\n"
+        "print('ok')\n" % (os.path.dirname(here), here, os.path.join(here, "emu"), emu_library))
+    env = dict(os.environ, SSF_FILL_CTAS="1")
+    res = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0 and res.stdout.strip().endswith("ok"), res.stdout + res.stderr
+
